@@ -1,0 +1,189 @@
+/*
+ * tcif.h -- C ABI of the B200-native interface hot path of thermocapillaryInterFoam.
+ *
+ * The reference has no FFI for this path: the boundary is two C++ member functions of
+ * libincompressibleMultiphaseSystems.so (phasesSystem/Make/files:28)
+ *     tmp<volVectorField> phaseSystem::divCapillaryStress() const   phaseSystem.H:493-494,
+ *                                                                    phaseSystem.C:1038-1105
+ *     void multiphaseSystem::solveAlphas()                           multiphaseSystem.H:93-94,
+ *                                                                    multiphaseSystem.C:170-429
+ * plus the OpenFOAM-v2106 MULES entry points solveAlphas() calls (multiphaseSystem.C:305-317,
+ * 321, 365-375).  Every entry point below names the reference interface it replaces; the
+ * OpenFOAM-typed binding a maintainer adds is shown in INTEGRATION.md / foam_shim/.
+ *
+ * Conventions = OpenFOAM's: scalar = double (WM_DP), label = int32 (WM_LABEL_SIZE=32),
+ * vectors AoS (x,y,z) exactly as Field<vector>::cdata() lays them out.  A vol field is
+ * internal[nCells] + boundary[nBoundaryFaces] (patch arrays concatenated in patch order,
+ * `empty` patches have size 0); a surface field is internal[nInternalFaces] + boundary[..].
+ * On processor patches the boundary value of a vol field is the neighbour-rank cell value
+ * (processorFvPatchField, = patchNeighbourField()).  Host pointers are borrowed for the
+ * duration of a call only.  All functions return 0 on success, non-zero on error with a
+ * message in tcif_last_error(); there is NO CPU fallback: without a CUDA device
+ * tcif_create() fails.  One context per rank/GPU; calls on one context are not re-entrant.
+ */
+#ifndef TCIF_H
+#define TCIF_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TCIF_API __attribute__((visibility("default")))
+
+#define TCIF_MAX_PHASES 4
+#define TCIF_MAX_PAIRS 6
+#define TCIF_SIGMA_MAX_COEFFS 64
+
+/* fvPatch kinds the path distinguishes (coupled = processor). */
+enum { TCIF_PATCH_GENERIC = 0, TCIF_PATCH_EMPTY = 1, TCIF_PATCH_WEDGE = 2, TCIF_PATCH_PROCESSOR = 3 };
+/* alpha boundary conditions on non-coupled patches: zeroGradient | fixedValue (fixesValue()). */
+enum { TCIF_BC_ZERO_GRADIENT = 0, TCIF_BC_FIXED_VALUE = 1 };
+/* surfaceTensionModel: constant | temperatureDependent with Function1 polynomial / table. */
+enum { TCIF_SIGMA_NONE = -1, TCIF_SIGMA_CONSTANT = 0, TCIF_SIGMA_POLYNOMIAL = 1, TCIF_SIGMA_TABLE = 2 };
+/* MULES limiter: extrema contributed by non-coupled, non-fixed-value patches. */
+enum { TCIF_BEXT_GLOBAL = 0, TCIF_BEXT_PATCHVALUE = 1 };
+
+typedef struct tcif_ctx tcif_ctx;
+typedef struct tcif_group tcif_group;
+
+/* What the shim reads off an fvMesh (lduAddr().lowerAddr()/upperAddr(), Sf(), weights(),
+ * V(), boundary()[p].faceCells()/Sf()/magSf()/deltaCoeffs()/weights()). */
+typedef struct tcif_mesh_desc {
+    int32_t nCells, nInternalFaces, nPatches, nBoundaryFaces;
+    const int32_t *owner, *neighbour;      /* [nInternalFaces], upper-triangular order */
+    const double *Sf;                      /* [nInternalFaces*3]                       */
+    const double *weights;                 /* [nInternalFaces]                         */
+    const double *V;                       /* [nCells]                                 */
+    const int32_t *patchType;              /* [nPatches] TCIF_PATCH_*                  */
+    const int32_t *patchStart;             /* [nPatches] offset into boundary arrays   */
+    const int32_t *patchSize;              /* [nPatches] (0 for empty)                 */
+    const int32_t *patchNeighbProcNo;      /* [nPatches] (-1 unless processor)         */
+    const int32_t *faceCells;              /* [nBoundaryFaces]                         */
+    const double *SfBoundary;              /* [nBoundaryFaces*3]                       */
+    const double *magSfBoundary;           /* [nBoundaryFaces]                         */
+    const double *deltaCoeffsBoundary;     /* [nBoundaryFaces]                         */
+    const double *weightsBoundary;         /* [nBoundaryFaces] (1 on non-coupled)      */
+} tcif_mesh_desc;
+
+/* fvSolution solver-dict keys MULES reads (nLimiterIter, smoothLimiter, extremaCoeff) +
+ * build-independent knobs. */
+typedef struct tcif_config {
+    int32_t nPhases;            /* phases in HashTable iteration order     */
+    int32_t nLimiterIter;       /* default 3                                           */
+    double smoothLimiter;       /* default 0                                           */
+    double extremaCoeff;        /* default 0                                           */
+    int32_t boundaryExtrema;    /* TCIF_BEXT_GLOBAL                                    */
+    int32_t device;             /* CUDA ordinal, -1 = current device                   */
+    int32_t flags;              /* reserved, 0                                         */
+} tcif_config;
+
+/* ---- life cycle -------------------------------------------------------------------- */
+/* Replaces the mesh/field references phaseSystem holds (phaseSystem.C:207-290): uploads
+ * addressing + geometry once, builds the cell-ordered face lists on the device. */
+TCIF_API int tcif_create(const tcif_mesh_desc *mesh, const tcif_config *cfg, tcif_ctx **out);
+TCIF_API void tcif_destroy(tcif_ctx *ctx);
+/* Message of the last failed call (ctx may be NULL for tcif_create failures). */
+TCIF_API const char *tcif_last_error(const tcif_ctx *ctx);
+TCIF_API const char *tcif_version(void);
+/* Number of visible CUDA devices (0 => every tcif_create fails). */
+TCIF_API int tcif_device_count(void);
+/* Run the context's kernels on a caller-owned cudaStream_t (NULL = context's own stream). */
+TCIF_API int tcif_set_stream(tcif_ctx *ctx, void *cudaStream);
+TCIF_API int tcif_synchronize(tcif_ctx *ctx);
+/* Pinned host allocation for shim-side staging buffers (cudaHostAlloc / cudaFreeHost). */
+TCIF_API void *tcif_host_alloc(uint64_t bytes);
+TCIF_API void tcif_host_free(void *p);
+
+/* lduAddressing::ownerStartAddr / losortAddr / losortStartAddr as built for the device
+ * (bit-exact check of the cell-ordered face lists against OpenFOAM's own). */
+TCIF_API int tcif_get_ldu_csr(tcif_ctx *ctx, int32_t *ownerStart, int32_t *losort, int32_t *losortStart);
+
+/* ---- processor-patch communication (Pstream stand-in) ------------------------------ */
+/* NCCL over NVLink: rank 0 makes the id, the host plumbing (torch.distributed / MPI)
+ * broadcasts its 128 bytes, every rank joins.  patchNeighbProcNo are NCCL ranks. */
+TCIF_API int tcif_comm_unique_id(void *id128);
+TCIF_API int tcif_comm_init_nccl(tcif_ctx *ctx, int rank, int nRanks, const void *id128);
+/* In-process group (several contexts on one GPU, one host thread each; used by tests). */
+TCIF_API int tcif_group_create(int nRanks, tcif_group **out);
+TCIF_API void tcif_group_destroy(tcif_group *g);
+TCIF_API int tcif_comm_init_local(tcif_ctx *ctx, int rank, tcif_group *g);
+
+/* ---- fields (device-resident cache of the host fields) ------------------------------ */
+/* alpha.<phase> (phaseModel.C:41-62): boundary-condition kinds per patch, values. */
+TCIF_API int tcif_set_alpha_bc(tcif_ctx *ctx, int phase, const int32_t *bcKindPerPatch);
+TCIF_API int tcif_set_alpha(tcif_ctx *ctx, int phase, const double *internal, const double *boundary);
+TCIF_API int tcif_get_alpha(tcif_ctx *ctx, int phase, double *internal, double *boundary);
+/* psi.oldTime(): copy alpha -> alpha0 for every phase (start of a time step / sub-cycle). */
+TCIF_API int tcif_store_old_alphas(tcif_ctx *ctx);
+TCIF_API int tcif_set_alpha_old(tcif_ctx *ctx, int phase, const double *internal);
+/* T looked up by temperatureDependent (name from dict entry "T"). */
+TCIF_API int tcif_set_temperature(tcif_ctx *ctx, const double *internal, const double *boundary);
+/* surfaceTension ((a and b) {type constant|temperatureDependent; sigma ...}) entry
+ * (phaseSystem.C:266-273): constant: coeffs[0]; polynomial: n (a,e) pairs; table: n (T,s). */
+TCIF_API int tcif_set_sigma(tcif_ctx *ctx, int phase1, int phase2, int kind, int n, const double *coeffs);
+/* phi (phaseSystem.C:227-239). */
+TCIF_API int tcif_set_phi(tcif_ctx *ctx, const double *internal, const double *boundary);
+/* phiAlphaCorrs[phase] / phiAlpha / phase.alphaPhi() (multiphaseSystem.C:203-216, 363, 377). */
+TCIF_API int tcif_set_phi_alpha(tcif_ctx *ctx, int phase, const double *internal, const double *boundary);
+TCIF_API int tcif_get_phi_alpha(tcif_ctx *ctx, int phase, double *internal, double *boundary);
+/* Su_/Sp_ (multiphaseSystem.C:279-292); NULL = zero field. */
+TCIF_API int tcif_set_su_sp(tcif_ctx *ctx, int phase, const double *Su, const double *Sp);
+
+/* ---- the hot path ------------------------------------------------------------------- */
+/* phaseSystem::divCapillaryStress() (phaseSystem.C:1038-1105) on the resident alpha, T. */
+TCIF_API int tcif_div_capillary_stress(tcif_ctx *ctx);
+/* Result as volVectorField: internal [nCells*3] + patch values [nBoundaryFaces*3]. */
+TCIF_API int tcif_get_force(tcif_ctx *ctx, double *internal, double *boundary);
+/* One-call drop-in with host buffers (upload alpha[P], T; compute; download). */
+TCIF_API int tcif_div_capillary_stress_host(tcif_ctx *ctx, const double *const *alphaInternal,
+                                            const double *const *alphaBoundary, const double *Tinternal,
+                                            const double *Tboundary, double *Finternal, double *Fboundary);
+/* fvc::grad(alpha.<phase>) with Gauss linear (phaseSystem.C:1076-1077): [nCells*3], [nBF*3]. */
+TCIF_API int tcif_grad_alpha(tcif_ctx *ctx, int phase, double *internal, double *boundary);
+
+/* MULES::limit(rDeltaT, 1, alpha, phi, phiAlpha, Sp, Su, 1, 0, returnCorr)  (multiphaseSystem.C:305-317). */
+TCIF_API int tcif_mules_limit(tcif_ctx *ctx, int phase, double rDeltaT, int returnCorr);
+/* MULES::limitSum(phiAlphaCorrs)  (multiphaseSystem.C:321). */
+TCIF_API int tcif_mules_limit_sum(tcif_ctx *ctx);
+/* phiAlpha += upwind<scalar>(mesh, phi).flux(alpha)  (multiphaseSystem.C:346, the bounded
+ * upwind flux; with the implicit predictor it is alpha1Eqn.flux(), :363). */
+TCIF_API int tcif_add_upwind_flux(tcif_ctx *ctx, int phase);
+/* MULES::explicitSolve(1, alpha, phi, phiAlpha, Sp, Su, 1, 0)  (multiphaseSystem.C:365-375). */
+TCIF_API int tcif_mules_explicit_solve(tcif_ctx *ctx, int phase, double deltaT);
+
+/* One metric stage on resident fields: divCapillaryStress over all pairs +
+ * one solveAlphas corrector over all phases (limit(returnCorr) x P, limitSum, per phase
+ * phiAlpha += upwind flux; explicitSolve).  alpha0 := alpha at entry. */
+TCIF_API int tcif_stage(tcif_ctx *ctx, double deltaT);
+/* Same through host buffers (uploads alpha[P], T, phi, phiAlpha[P]; downloads F, alpha[P],
+ * alphaPhi[P]); boundary arrays may be NULL when nBoundaryFaces == 0. */
+TCIF_API int tcif_stage_host(tcif_ctx *ctx, double deltaT,
+                             double *const *alphaInternal, double *const *alphaBoundary,
+                             const double *Tinternal, const double *Tboundary,
+                             const double *phiInternal, const double *phiBoundary,
+                             double *const *phiAlphaInternal, double *const *phiAlphaBoundary,
+                             double *Finternal, double *Fboundary);
+
+/* Logging scalars of multiphaseSystem.C:408-425: sum(V*alpha), min, max (global over ranks). */
+TCIF_API int tcif_alpha_stats(tcif_ctx *ctx, int phase, double out3[3]);
+
+/* ---- measurement -------------------------------------------------------------------- */
+/* Per-kernel CUDA-event timers on the launching stream.  ids are stable (tcif_timer_name). */
+TCIF_API int tcif_timers_enable(tcif_ctx *ctx, int on);
+TCIF_API int tcif_timers_reset(tcif_ctx *ctx);
+TCIF_API int tcif_timer_count(void);
+TCIF_API const char *tcif_timer_name(int id);
+/* ms[id] = accumulated device ms, launches[id] = launch count, bytes[id] = algorithmic bytes
+ * accumulated over those launches (DESIGN.md states the per-cell/face figures). */
+TCIF_API int tcif_timers_read(tcif_ctx *ctx, double *ms, int64_t *launches, double *bytes);
+/* Kernel launches issued by this context since creation (gpu_launches evidence). */
+TCIF_API int64_t tcif_launch_count(const tcif_ctx *ctx);
+/* Bytes of HBM the context holds. */
+TCIF_API int64_t tcif_device_bytes(const tcif_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,296 @@
+"""ctypes binding of the CPU ORACLE (oracle/tcif_oracle.c).  TEST INFRASTRUCTURE ONLY:
+imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs; never by the product package.  PARITY UNPINNED (see tcif_oracle.h)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int32)
+
+BC_ZERO_GRADIENT, BC_FIXED_VALUE = 0, 1
+SIGMA_CONSTANT, SIGMA_POLYNOMIAL, SIGMA_TABLE = 0, 1, 2
+BEXT_GLOBAL, BEXT_PATCHVALUE = 0, 1
+
+
+class OrcMesh(C.Structure):
+    _fields_ = [("nCells", C.c_int32), ("nIF", C.c_int32), ("nPatches", C.c_int32), ("nBF", C.c_int32),
+                ("owner", c_ip), ("neighbour", c_ip), ("Sf", c_dp), ("w", c_dp), ("V", c_dp),
+                ("patchType", c_ip), ("patchStart", c_ip), ("patchSize", c_ip), ("patchNbrProc", c_ip),
+                ("faceCells", c_ip), ("Sfb", c_dp), ("magSfb", c_dp), ("deltaCoeffsb", c_dp), ("wb", c_dp)]
+
+
+class OrcSigma(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("n", C.c_int32), ("c", C.c_double * 64)]
+
+
+class OrcMulesCfg(C.Structure):
+    _fields_ = [("nLimiterIter", C.c_int32), ("smoothLimiter", C.c_double), ("extremaCoeff", C.c_double),
+                ("boundaryExtrema", C.c_int32)]
+
+
+HALO_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int, c_dp, c_dp)
+REDUCE_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int, c_dp)
+
+
+class OrcComm(C.Structure):
+    _fields_ = [("user", C.c_void_p), ("halo", HALO_FN), ("reduce", REDUCE_FN)]
+
+
+def build(force: bool = False) -> str:
+    so = os.path.join(_HERE, "libtcif_oracle.so")
+    src = [os.path.join(_HERE, f) for f in ("tcif_oracle.c", "tcif_oracle.h")]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src if os.path.exists(s)):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(build())
+        _LIB.orc_deltaN.restype = C.c_double
+        _LIB.orc_sigma_eval.restype = C.c_double
+        _LIB.orc_stage_threads.restype = C.c_double
+    return _LIB
+
+
+def _d(a):
+    return a.ctypes.data_as(c_dp) if a is not None else None
+
+
+def _i(a):
+    return a.ctypes.data_as(c_ip) if a is not None else None
+
+
+def f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+class MeshHandle:
+    """Keeps contiguous copies alive and exposes the orc_mesh struct."""
+
+    def __init__(self, m):
+        self.m = m
+        self.keep = dict(
+            owner=i32(m.owner), neighbour=i32(m.neighbour), Sf=f64(m.Sf), w=f64(m.w), V=f64(m.V),
+            patchType=i32(m.patchType), patchStart=i32(m.patchStart), patchSize=i32(m.patchSize),
+            patchNbrProc=i32(m.patchNbrProc), faceCells=i32(m.faceCells), Sfb=f64(m.Sfb), magSfb=f64(m.magSfb),
+            deltaCoeffsb=f64(m.deltaCoeffsb), wb=f64(m.wb))
+        k = self.keep
+        self.s = OrcMesh(m.nCells, len(k["owner"]), len(k["patchType"]), len(k["faceCells"]),
+                         _i(k["owner"]), _i(k["neighbour"]), _d(k["Sf"]), _d(k["w"]), _d(k["V"]),
+                         _i(k["patchType"]), _i(k["patchStart"]), _i(k["patchSize"]), _i(k["patchNbrProc"]),
+                         _i(k["faceCells"]), _d(k["Sfb"]), _d(k["magSfb"]), _d(k["deltaCoeffsb"]), _d(k["wb"]))
+
+    @property
+    def ref(self):
+        return C.byref(self.s)
+
+
+def make_sigma(spec) -> OrcSigma:
+    """spec: ("constant", s0) | ("polynomial", [(a,e),...]) | ("table", [(T,s),...])."""
+    s = OrcSigma()
+    kind, val = spec
+    if kind == "constant":
+        s.kind, s.n = SIGMA_CONSTANT, 1
+        s.c[0] = float(val)
+    else:
+        s.kind = SIGMA_POLYNOMIAL if kind == "polynomial" else SIGMA_TABLE
+        s.n = len(val)
+        for i, (a, b) in enumerate(val):
+            s.c[2 * i], s.c[2 * i + 1] = float(a), float(b)
+    return s
+
+
+def sigma_array(specs):
+    arr = (OrcSigma * max(1, len(specs)))()
+    for i, sp in enumerate(specs):
+        arr[i] = make_sigma(sp)
+    return arr
+
+
+def mules_cfg(nLimiterIter=3, smoothLimiter=0.0, extremaCoeff=0.0, boundaryExtrema=BEXT_GLOBAL):
+    return OrcMulesCfg(nLimiterIter, smoothLimiter, extremaCoeff, boundaryExtrema)
+
+
+def _pp(arrs):
+    """list of float64 arrays -> double** """
+    p = (c_dp * len(arrs))()
+    for k, a in enumerate(arrs):
+        p[k] = _d(a)
+    return p
+
+
+def make_comm(halo=None, reduce=None):
+    """halo(ncomp, send[nc,ncomp]) -> recv array; reduce(op, vals) -> vals. Returns (OrcComm, keepalive)."""
+    def _h(user, ncomp, nc, send, recv):
+        s = np.ctypeslib.as_array(send, shape=(nc, ncomp))
+        r = np.ctypeslib.as_array(recv, shape=(nc, ncomp))
+        r[...] = halo(ncomp, s.copy())
+
+    def _r(user, op, n, vals):
+        v = np.ctypeslib.as_array(vals, shape=(n,))
+        v[...] = reduce(op, v.copy())
+    hf, rf = HALO_FN(_h), REDUCE_FN(_r)
+    return OrcComm(None, hf, rf), (hf, rf)
+
+
+def grad(m, ai, ab, bc, comm=None):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    gi, gb = np.zeros((h.s.nCells, 3)), np.zeros((h.s.nBF, 3))
+    ai, ab, bc = f64(ai), f64(ab), i32(bc)
+    lib().orc_grad(h.ref, C.byref(comm) if comm else None, _d(ai), _d(ab), _i(bc), _d(gi), _d(gb))
+    return gi, gb
+
+
+def interpolate(m, vi, vb):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    vi, vb = f64(vi), f64(vb)
+    ncomp = 1 if vi.ndim == 1 else vi.shape[1]
+    si = np.zeros((h.s.nIF,) + vi.shape[1:]); sb = np.zeros((h.s.nBF,) + vi.shape[1:])
+    lib().orc_interpolate(h.ref, ncomp, _d(vi), _d(vb), _d(si), _d(sb))
+    return si, sb
+
+
+def div_tensor(m, Ti, Tb, comm=None):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    Ti, Tb = f64(Ti), f64(Tb)
+    di, db = np.zeros((h.s.nCells, 3)), np.zeros((h.s.nBF, 3))
+    lib().orc_div_tensor(h.ref, C.byref(comm) if comm else None, _d(Ti), _d(Tb), _d(di), _d(db))
+    return di, db
+
+
+def sigma_eval(spec, T):
+    s = make_sigma(spec)
+    return lib().orc_sigma_eval(C.byref(s), C.c_double(T))
+
+
+def deltaN(m, comm=None):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    return lib().orc_deltaN(h.ref, C.byref(comm) if comm else None)
+
+
+def div_capillary_stress(m, alphas_i, alphas_b, alphaBc, sigma_specs, Ti, Tb, comm=None):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    P = len(alphas_i)
+    ai = [f64(a) for a in alphas_i]; ab = [f64(a) for a in alphas_b]
+    bc = i32(alphaBc).reshape(P, -1)
+    Ti, Tb = f64(Ti), f64(Tb)
+    Fi, Fb = np.zeros((h.s.nCells, 3)), np.zeros((h.s.nBF, 3))
+    sg = sigma_array(sigma_specs)
+    lib().orc_div_capillary_stress(h.ref, C.byref(comm) if comm else None, P, _pp(ai), _pp(ab), _i(bc), sg,
+                                   _d(Ti), _d(Tb), _d(Fi), _d(Fb))
+    return Fi, Fb
+
+
+def mules_limiter(m, cfg, rDeltaT, psii, psib, psi0, psiBc, phiBDi, phiBDb, phiCorri, phiCorrb, Sp, Su,
+                  psiMax=1.0, psiMin=0.0, comm=None):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    a = [f64(x) for x in (psii, psib, psi0, phiBDi, phiBDb, phiCorri, phiCorrb, Sp, Su)]
+    bc = i32(psiBc)
+    li, lb = np.zeros(h.s.nIF), np.zeros(h.s.nBF)
+    lib().orc_mules_limiter(h.ref, C.byref(comm) if comm else None, C.byref(cfg), C.c_double(rDeltaT),
+                            _d(a[0]), _d(a[1]), _d(a[2]), _i(bc), _d(a[3]), _d(a[4]), _d(a[5]), _d(a[6]),
+                            _d(a[7]), _d(a[8]), C.c_double(psiMax), C.c_double(psiMin), _d(li), _d(lb))
+    return li, lb
+
+
+def mules_limit(m, cfg, rDeltaT, psii, psib, psi0, psiBc, phii, phib, phiPsii, phiPsib, Sp, Su,
+                returnCorr, psiMax=1.0, psiMin=0.0, comm=None):
+    """Returns new (phiPsii, phiPsib)."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    a = [f64(x) for x in (psii, psib, psi0, phii, phib, Sp, Su)]
+    pi, pb = f64(phiPsii).copy(), f64(phiPsib).copy()
+    bc = i32(psiBc)
+    lib().orc_mules_limit(h.ref, C.byref(comm) if comm else None, C.byref(cfg), C.c_double(rDeltaT),
+                          _d(a[0]), _d(a[1]), _d(a[2]), _i(bc), _d(a[3]), _d(a[4]), _d(pi), _d(pb),
+                          _d(a[5]), _d(a[6]), C.c_double(psiMax), C.c_double(psiMin), int(bool(returnCorr)))
+    return pi, pb
+
+
+def mules_limit_sum(m, phiCorri, phiCorrb):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    ci = [f64(x).copy() for x in phiCorri]; cb = [f64(x).copy() for x in phiCorrb]
+    lib().orc_mules_limit_sum(h.ref, len(ci), _pp(ci), _pp(cb))
+    return ci, cb
+
+
+def mules_explicit_solve(m, cfg, deltaT, psii, psib, psi0, psiBc, phii, phib, phiPsii, phiPsib, Sp, Su,
+                         psiMax=1.0, psiMin=0.0, comm=None):
+    """Returns (psii, psib, phiPsii, phiPsib) new."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    a = [f64(x) for x in (psi0, phii, phib, Sp, Su)]
+    qi, qb = f64(psii).copy(), f64(psib).copy()
+    pi, pb = f64(phiPsii).copy(), f64(phiPsib).copy()
+    bc = i32(psiBc)
+    lib().orc_mules_explicit_solve(h.ref, C.byref(comm) if comm else None, C.byref(cfg), C.c_double(deltaT),
+                                   _d(qi), _d(qb), _d(a[0]), _i(bc), _d(a[1]), _d(a[2]), _d(pi), _d(pb),
+                                   _d(a[3]), _d(a[4]), C.c_double(psiMax), C.c_double(psiMin))
+    return qi, qb, pi, pb
+
+
+def upwind_flux(m, phii, phib, psii, psib):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    a = [f64(x) for x in (phii, phib, psii, psib)]
+    oi, ob = np.zeros(h.s.nIF), np.zeros(h.s.nBF)
+    lib().orc_upwind_flux(h.ref, _d(a[0]), _d(a[1]), _d(a[2]), _d(a[3]), _d(oi), _d(ob), 0)
+    return oi, ob
+
+
+def stage(m, cfg, alphas_i, alphas_b, alphaBc, sigma_specs, Ti, Tb, phii, phib, phiAlpha_i, phiAlpha_b,
+          deltaT, comm=None):
+    """One metric stage.  Returns dict(F_i,F_b, alpha_i[], alpha_b[], alphaPhi_i[], alphaPhi_b[])."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    P = len(alphas_i)
+    ai = [f64(a).copy() for a in alphas_i]; ab = [f64(a).copy() for a in alphas_b]
+    pi = [f64(a).copy() for a in phiAlpha_i]; pb = [f64(a).copy() for a in phiAlpha_b]
+    bc = i32(alphaBc).reshape(P, -1)
+    Ti, Tb, phii, phib = f64(Ti), f64(Tb), f64(phii), f64(phib)
+    Fi, Fb = np.zeros((h.s.nCells, 3)), np.zeros((h.s.nBF, 3))
+    sg = sigma_array(sigma_specs)
+    lib().orc_stage(h.ref, C.byref(comm) if comm else None, C.byref(cfg), P, _pp(ai), _pp(ab), _i(bc), sg,
+                    _d(Ti), _d(Tb), _d(phii), _d(phib), _pp(pi), _pp(pb), None, None, C.c_double(deltaT),
+                    _d(Fi), _d(Fb))
+    return dict(F_i=Fi, F_b=Fb, alpha_i=ai, alpha_b=ab, alphaPhi_i=pi, alphaPhi_b=pb)
+
+
+def stage_threads(meshes, cfg, alphas_i, alphas_b, alphaBc, sigma_specs, Ti, Tb, phii, phib, phiAlpha_i,
+                  phiAlpha_b, deltaT, nStages=1):
+    """Domain-decomposed stage, one thread per sub-domain.  Per-domain lists.  Returns (seconds, results[])."""
+    nD = len(meshes)
+    hs = [MeshHandle(m) for m in meshes]
+    marr = (OrcMesh * nD)(*[h.s for h in hs])
+    P = len(alphas_i[0])
+    ai = [[f64(a).copy() for a in alphas_i[d]] for d in range(nD)]
+    ab = [[f64(a).copy() for a in alphas_b[d]] for d in range(nD)]
+    pi = [[f64(a).copy() for a in phiAlpha_i[d]] for d in range(nD)]
+    pb = [[f64(a).copy() for a in phiAlpha_b[d]] for d in range(nD)]
+    bcs = [i32(alphaBc[d]).reshape(P, -1) for d in range(nD)]
+    Tis = [f64(x) for x in Ti]; Tbs = [f64(x) for x in Tb]
+    phis = [f64(x) for x in phii]; phibs = [f64(x) for x in phib]
+    Fis = [np.zeros((h.s.nCells, 3)) for h in hs]; Fbs = [np.zeros((h.s.nBF, 3)) for h in hs]
+    ppp = C.POINTER(c_dp)
+
+    def ppl(lists):
+        keep = [_pp(l) for l in lists]
+        arr = (ppp * nD)(*[C.cast(k, ppp) for k in keep])
+        return arr, keep
+    aiA, k1 = ppl(ai); abA, k2 = ppl(ab); piA, k3 = ppl(pi); pbA, k4 = ppl(pb)
+    bcA = (c_ip * nD)(*[_i(b) for b in bcs])
+    sg = sigma_array(sigma_specs)
+    secs = lib().orc_stage_threads(nD, marr, C.byref(cfg), P, aiA, abA, bcA, sg, _pp(Tis), _pp(Tbs), _pp(phis),
+                                   _pp(phibs), piA, pbA, C.c_double(deltaT), _pp(Fis), _pp(Fbs), int(nStages))
+    res = [dict(F_i=Fis[d], F_b=Fbs[d], alpha_i=ai[d], alpha_b=ab[d], alphaPhi_i=pi[d], alphaPhi_b=pb[d])
+           for d in range(nD)]
+    return secs, res

@@ -1,0 +1,187 @@
+/*
+ * tcif_oracle.h -- CPU ORACLE for the thermocapillaryInterFoam interface hot path.
+ *
+ * THIS IS TEST INFRASTRUCTURE, NOT PRODUCT CODE.  Only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline / --impl reference legs may load it.  The product path
+ * (thermocapillaryinterfoam_b200/, include/tcif.h) never includes, links or calls it.
+ *
+ * PARITY UNPINNED: the arithmetic of this path lives in OpenFOAM v2106 (OpenCFD/ESI),
+ * a third-party dependency that is neither vendored under /root/reference nor
+ * installed in this image (README.md:5,11,47-49 and .github/workflows/build.yml:23 of
+ * the reference pin it by prose / CI image only), and the reference ships no test,
+ * tutorial or golden vector for this path.  The oracle therefore
+ * restates (i) the reference's own composition of operators
+ *     phasesSystem/phaseSystem/phaseSystem.C:1038-1105   divCapillaryStress()
+ *     phasesSystem/phaseSystem/phaseSystem.C:1274-1295   nHat()
+ *     phasesSystem/phaseSystem/phaseSystem.C:1132-1136   surfaceTensionCoeff()
+ *     phasesSystem/multiphaseSystem/multiphaseSystem.C:296-375  limit/limitSum/explicitSolve calls
+ * and (ii) the published OpenFOAM-v2106 algorithms those calls resolve to
+ * (gaussGrad, gaussDivScheme, linear interpolation, MULES limiter / limit / limitSum /
+ * explicitSolve, surfaceTensionModels constant + temperatureDependent), loop for loop,
+ * one memory sweep per OpenFOAM operator with full-field temporaries, in the
+ * reference's accumulation order.  It is pinned by known-answer tests only
+ * (tests/test_oracle_known_answers.py).
+ *
+ * Layout conventions = OpenFOAM's: scalar = double, label = int32, vectors AoS (x,y,z),
+ * tensors AoS row-major (xx,xy,xz,yx,yy,yz,zx,zy,zz); a vol field is internal[nCells]
+ * plus boundary[nBF] (patch arrays concatenated in patch order; empty patches have
+ * size 0); a surface field is internal[nIF] plus boundary[nBF].  On coupled
+ * (processor) patches the boundary value of a vol field is the neighbour-rank cell
+ * value (= patchNeighbourField()).
+ */
+#ifndef TCIF_ORACLE_H
+#define TCIF_ORACLE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { ORC_PATCH_GENERIC = 0, ORC_PATCH_EMPTY = 1, ORC_PATCH_WEDGE = 2, ORC_PATCH_PROCESSOR = 3 };
+enum { ORC_BC_ZERO_GRADIENT = 0, ORC_BC_FIXED_VALUE = 1 };
+enum { ORC_SIGMA_CONSTANT = 0, ORC_SIGMA_POLYNOMIAL = 1, ORC_SIGMA_TABLE = 2 };
+enum { ORC_RED_SUM = 0, ORC_RED_MIN = 1, ORC_RED_MAX = 2 };
+enum { ORC_BEXT_GLOBAL = 0, ORC_BEXT_PATCHVALUE = 1 };
+
+typedef struct orc_mesh {
+    int32_t nCells, nIF, nPatches, nBF;
+    const int32_t *owner, *neighbour;          /* [nIF]  lduAddr lower/upper            */
+    const double *Sf;                          /* [nIF*3]                               */
+    const double *w;                           /* [nIF]  mesh.weights() (linear)        */
+    const double *V;                           /* [nCells]                              */
+    const int32_t *patchType, *patchStart, *patchSize, *patchNbrProc;  /* [nPatches]    */
+    const int32_t *faceCells;                  /* [nBF]                                 */
+    const double *Sfb;                         /* [nBF*3]                               */
+    const double *magSfb;                      /* [nBF]                                 */
+    const double *deltaCoeffsb;                /* [nBF]                                 */
+    const double *wb;                          /* [nBF]  1 on non-coupled patches       */
+} orc_mesh;
+
+/* Function1<scalar> "sigma": constant | polynomial ((a e)...) | table ((T s)...) clamp */
+typedef struct orc_sigma {
+    int32_t kind, n;
+    double c[64];      /* constant: c[0]; polynomial: (a_i,e_i) pairs; table: (T_i,s_i) pairs */
+} orc_sigma;
+
+/* Per-rank communication hooks (Pstream stand-in).  halo(): `send` holds, for every
+ * coupled boundary face in ascending boundary index, ncomp interleaved doubles of the
+ * local patchInternalField; `recv` returns the neighbour rank's values in the same
+ * layout.  reduce(): in-place all-reduce of n doubles.  NULL hooks = serial run. */
+typedef void (*orc_halo_fn)(void *user, int ncomp, int nCoupledFaces, const double *send, double *recv);
+typedef void (*orc_reduce_fn)(void *user, int op, int n, double *vals);
+typedef struct orc_comm { void *user; orc_halo_fn halo; orc_reduce_fn reduce; } orc_comm;
+
+typedef struct orc_mules_cfg {
+    int32_t nLimiterIter;        /* 3   */
+    double smoothLimiter;        /* 0   */
+    double extremaCoeff;         /* 0   */
+    int32_t boundaryExtrema;     /* ORC_BEXT_GLOBAL */
+} orc_mules_cfg;
+
+/* ---- operators ---- */
+
+/* A.2 fvc::interpolate(vf) with `linear`, ncomp components interleaved. */
+void orc_interpolate(const orc_mesh *m, int ncomp, const double *vi, const double *vb,
+                     double *sfi, double *sfb);
+
+/* A.3 fvc::grad(alpha) with Gauss linear + gaussGrad::correctBoundaryConditions.
+ * alphaBc[nPatches] gives the BC kind of alpha on non-coupled patches. */
+void orc_grad(const orc_mesh *m, const orc_comm *c, const double *ai, const double *ab,
+              const int32_t *alphaBc, double *gi, double *gb);
+
+/* A.4 fvc::div(T), T a volTensorField (9 comps). */
+void orc_div_tensor(const orc_mesh *m, const orc_comm *c, const double *Ti, const double *Tb,
+                    double *di, double *db);
+
+/* A.5 sigma field from temperature. */
+void orc_sigma_field(const orc_mesh *m, const orc_sigma *s, const double *Ti, const double *Tb,
+                     double *si, double *sb);
+double orc_sigma_eval(const orc_sigma *s, double T);
+
+/* deltaN = 1e-8/cbrt(average(V))  (phaseSystem.C:1287-1291). */
+double orc_deltaN(const orc_mesh *m, const orc_comm *c);
+
+/* phaseSystem::nHat (phaseSystem.C:1274-1295). */
+void orc_nHat(const orc_mesh *m, const orc_comm *c,
+              const double *a1i, const double *a1b, const int32_t *bc1,
+              const double *a2i, const double *a2b, const int32_t *bc2,
+              double *ni, double *nb);
+
+/* phaseSystem::divCapillaryStress (phaseSystem.C:1038-1105).  alphas in table order;
+ * sigma[q] for pairs q enumerated (0,1),(0,2),..,(1,2),..; alphaBc[p*nPatches+patch]. */
+void orc_div_capillary_stress(const orc_mesh *m, const orc_comm *c, int nPhases,
+                              const double *const *alphai, const double *const *alphab,
+                              const int32_t *alphaBc, const orc_sigma *sigma,
+                              const double *Ti, const double *Tb,
+                              double *Fi, double *Fb);
+
+/* A.6 MULES::limiter: lambda (internal [nIF] + boundary [nBF]) out. */
+void orc_mules_limiter(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg,
+                       double rDeltaT, const double *psii, const double *psib,
+                       const double *psi0, const int32_t *psiBc,
+                       const double *phiBDi, const double *phiBDb,
+                       const double *phiCorri, const double *phiCorrb,
+                       const double *Sp, const double *Su, double psiMax, double psiMin,
+                       double *lami, double *lamb);
+
+/* A.6 MULES::limit: phiPsi in/out. */
+void orc_mules_limit(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg,
+                     double rDeltaT, const double *psii, const double *psib,
+                     const double *psi0, const int32_t *psiBc,
+                     const double *phii, const double *phib,
+                     double *phiPsii, double *phiPsib,
+                     const double *Sp, const double *Su, double psiMax, double psiMin,
+                     int returnCorr);
+
+/* A.6 MULES::limitSum over nPhases correction fluxes (internal + coupled patches). */
+void orc_mules_limit_sum(const orc_mesh *m, int nPhases, double *const *phiCorri,
+                         double *const *phiCorrb);
+
+/* A.6 MULES::explicitSolve: psi (internal+boundary) and phiPsi in/out. */
+void orc_mules_explicit_solve(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg,
+                              double deltaT, double *psii, double *psib,
+                              const double *psi0, const int32_t *psiBc,
+                              const double *phii, const double *phib,
+                              double *phiPsii, double *phiPsib,
+                              const double *Sp, const double *Su, double psiMax, double psiMin);
+
+/* upwind flux phi*psi_upwind (A.7), added into out (out += flux) when add != 0. */
+void orc_upwind_flux(const orc_mesh *m, const double *phii, const double *phib,
+                     const double *psii, const double *psib,
+                     double *outi, double *outb, int add);
+
+/* vol-field boundary evaluation: zeroGradient -> adjacent cell, fixedValue -> kept,
+ * processor -> halo. */
+void orc_correct_bcs(const orc_mesh *m, const orc_comm *c, int ncomp, const double *vi,
+                     double *vb, const int32_t *bc);
+
+/* One metric "stage" (SURVEY.md 8(d)): divCapillaryStress over all pairs + one MULES
+ * corrector over all phases (limit(returnCorr) x P, limitSum, then per phase
+ * phiAlpha = corr + upwind flux; explicitSolve).  alpha (i,b) are updated in place;
+ * phiAlpha[p] holds the HO flux on entry and alphaPhi on exit. */
+void orc_stage(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg, int nPhases,
+               double *const *alphai, double *const *alphab, const int32_t *alphaBc,
+               const orc_sigma *sigma, const double *Ti, const double *Tb,
+               const double *phii, const double *phib,
+               double *const *phiAlphai, double *const *phiAlphab,
+               const double *const *Su, const double *const *Sp, double deltaT,
+               double *Fi, double *Fb);
+
+/* Run `orc_stage` on nDom sub-domains at once, one worker thread per sub-domain with
+ * processor-patch halo exchange through shared memory (the CPU baseline of SURVEY.md
+ * 8(d): "domain-decomposed on all host cores").  All per-domain pointers are arrays of
+ * length nDom.  nStages repeats the stage (alpha carried over, phiAlpha re-read from
+ * phiAlpha0).  Returns wall seconds of the stage loop. */
+double orc_stage_threads(int nDom, const orc_mesh *meshes, const orc_mules_cfg *cfg, int nPhases,
+                         double *const *const *alphai, double *const *const *alphab,
+                         const int32_t *const *alphaBc, const orc_sigma *sigma,
+                         const double *const *Ti, const double *const *Tb,
+                         const double *const *phii, const double *const *phib,
+                         double *const *const *phiAlphai, double *const *const *phiAlphab,
+                         double deltaT, double *const *Fi, double *const *Fb, int nStages);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

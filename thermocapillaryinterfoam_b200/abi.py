@@ -1,0 +1,346 @@
+"""ctypes binding of the C ABI in include/tcif.h (libtcif.so, hand-written CUDA for sm_100a).
+
+This is the *only* compute path of the package: there is no CPU fallback.  Loading fails
+loudly when the CUDA library has not been built (``python -c 'import __graft_entry__ as g;
+g.build()'``) and ``Context`` creation fails when no B200 is visible.
+
+The binding is deliberately thin: one Python method per exported entry point, numpy arrays in
+OpenFOAM layout (vectors AoS [n,3], vol field = internal[nCells] + boundary[nBoundaryFaces]).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtcif.so")
+
+PATCH_GENERIC, PATCH_EMPTY, PATCH_WEDGE, PATCH_PROCESSOR = 0, 1, 2, 3
+BC_ZERO_GRADIENT, BC_FIXED_VALUE = 0, 1
+SIGMA_CONSTANT, SIGMA_POLYNOMIAL, SIGMA_TABLE = 0, 1, 2
+BEXT_GLOBAL, BEXT_PATCHVALUE = 0, 1
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int32)
+
+
+class TcifError(RuntimeError):
+    """Non-zero return of a tcif_* entry point (the shim turns these into FatalError)."""
+
+
+class MeshDesc(C.Structure):
+    _fields_ = [("nCells", C.c_int32), ("nInternalFaces", C.c_int32), ("nPatches", C.c_int32),
+                ("nBoundaryFaces", C.c_int32),
+                ("owner", c_ip), ("neighbour", c_ip), ("Sf", c_dp), ("weights", c_dp), ("V", c_dp),
+                ("patchType", c_ip), ("patchStart", c_ip), ("patchSize", c_ip), ("patchNeighbProcNo", c_ip),
+                ("faceCells", c_ip), ("SfBoundary", c_dp), ("magSfBoundary", c_dp),
+                ("deltaCoeffsBoundary", c_dp), ("weightsBoundary", c_dp)]
+
+
+class Config(C.Structure):
+    _fields_ = [("nPhases", C.c_int32), ("nLimiterIter", C.c_int32), ("smoothLimiter", C.c_double),
+                ("extremaCoeff", C.c_double), ("boundaryExtrema", C.c_int32), ("device", C.c_int32),
+                ("flags", C.c_int32)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libtcif.so.  Raises if it has not been built -- never falls back to anything."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise TcifError(f"{LIB_PATH} is missing: build it with __graft_entry__.build() "
+                        "(nvcc -gencode arch=compute_100a,code=sm_100a); there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    L.tcif_last_error.restype = C.c_char_p
+    L.tcif_last_error.argtypes = [C.c_void_p]
+    L.tcif_version.restype = C.c_char_p
+    L.tcif_timer_name.restype = C.c_char_p
+    L.tcif_host_alloc.restype = C.c_void_p
+    L.tcif_host_alloc.argtypes = [C.c_uint64]
+    L.tcif_host_free.argtypes = [C.c_void_p]
+    L.tcif_launch_count.restype = C.c_int64
+    L.tcif_launch_count.argtypes = [C.c_void_p]
+    L.tcif_device_bytes.restype = C.c_int64
+    L.tcif_device_bytes.argtypes = [C.c_void_p]
+    L.tcif_destroy.argtypes = [C.c_void_p]
+    L.tcif_destroy.restype = None
+    L.tcif_group_destroy.argtypes = [C.c_void_p]
+    L.tcif_group_destroy.restype = None
+    _lib = L
+    return L
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _d(a):
+    return a.ctypes.data_as(c_dp) if a is not None else None
+
+
+def _i(a):
+    return a.ctypes.data_as(c_ip) if a is not None else None
+
+
+def _pp(arrs):
+    p = (c_dp * max(1, len(arrs)))()
+    for k, a in enumerate(arrs):
+        p[k] = _d(a)
+    return p
+
+
+def device_count() -> int:
+    return int(lib().tcif_device_count())
+
+
+def version() -> str:
+    return lib().tcif_version().decode()
+
+
+def pinned_empty(shape, dtype=np.float64):
+    """numpy array on cudaHostAlloc'd memory (tcif_host_alloc); freed when the array dies."""
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = lib().tcif_host_alloc(C.c_uint64(max(n, 1)))
+    if not p:
+        raise TcifError("tcif_host_alloc failed")
+    buf = (C.c_char * max(n, 1)).from_address(p)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    _PINNED[id(buf)] = (buf, p)
+    import weakref
+    weakref.finalize(arr, _free_pinned, id(buf))
+    return arr
+
+
+_PINNED: dict = {}
+
+
+def _free_pinned(key):
+    buf, p = _PINNED.pop(key, (None, None))
+    if p:
+        lib().tcif_host_free(C.c_void_p(p))
+
+
+class Group:
+    """In-process rank group: several contexts on one GPU, one host thread per rank (tests)."""
+
+    def __init__(self, nRanks: int):
+        self.h = C.c_void_p()
+        if lib().tcif_group_create(int(nRanks), C.byref(self.h)):
+            raise TcifError("tcif_group_create failed")
+        self.n = nRanks
+
+    def close(self):
+        if self.h:
+            lib().tcif_group_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+def nccl_unique_id() -> bytes:
+    buf = C.create_string_buffer(128)
+    if lib().tcif_comm_unique_id(buf):
+        raise TcifError(lib().tcif_last_error(None).decode())
+    return buf.raw
+
+
+class Context:
+    """One rank's device-resident mesh + fields (tcif_ctx)."""
+
+    def __init__(self, mesh, nPhases, nLimiterIter=3, smoothLimiter=0.0, extremaCoeff=0.0,
+                 boundaryExtrema=BEXT_GLOBAL, device=-1):
+        """`mesh` is any object with the attributes of tcif_mesh_desc's arrays (owner, neighbour, Sf,
+        w, V, patchType, patchStart, patchSize, patchNbrProc, faceCells, Sfb, magSfb, deltaCoeffsb, wb)."""
+        L = lib()
+        self.nCells = int(mesh.nCells)
+        k = dict(owner=_i32(mesh.owner), neighbour=_i32(mesh.neighbour), Sf=_f64(mesh.Sf), w=_f64(mesh.w),
+                 V=_f64(mesh.V), patchType=_i32(mesh.patchType), patchStart=_i32(mesh.patchStart),
+                 patchSize=_i32(mesh.patchSize), patchNbrProc=_i32(mesh.patchNbrProc),
+                 faceCells=_i32(mesh.faceCells), Sfb=_f64(mesh.Sfb), magSfb=_f64(mesh.magSfb),
+                 dcb=_f64(mesh.deltaCoeffsb), wb=_f64(mesh.wb))
+        self.nIF = int(k["owner"].shape[0])
+        self.nBF = int(k["faceCells"].shape[0])
+        self.nPatches = int(k["patchType"].shape[0])
+        self.P = int(nPhases)
+        desc = MeshDesc(self.nCells, self.nIF, self.nPatches, self.nBF, _i(k["owner"]), _i(k["neighbour"]),
+                        _d(k["Sf"]), _d(k["w"]), _d(k["V"]), _i(k["patchType"]), _i(k["patchStart"]),
+                        _i(k["patchSize"]), _i(k["patchNbrProc"]), _i(k["faceCells"]), _d(k["Sfb"]),
+                        _d(k["magSfb"]), _d(k["dcb"]), _d(k["wb"]))
+        cfg = Config(self.P, int(nLimiterIter), float(smoothLimiter), float(extremaCoeff), int(boundaryExtrema),
+                     int(device), 0)
+        self.h = C.c_void_p()
+        if L.tcif_create(C.byref(desc), C.byref(cfg), C.byref(self.h)):
+            raise TcifError(L.tcif_last_error(None).decode())
+        self._group = None
+
+    # -- plumbing
+    def _ck(self, rc):
+        if rc:
+            raise TcifError(lib().tcif_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().tcif_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def synchronize(self):
+        self._ck(lib().tcif_synchronize(self.h))
+
+    def set_stream(self, cuda_stream_ptr):
+        self._ck(lib().tcif_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    def comm_init_local(self, rank, group: Group):
+        self._group = group
+        self._ck(lib().tcif_comm_init_local(self.h, int(rank), group.h))
+
+    def comm_init_nccl(self, rank, nRanks, id128: bytes):
+        self._ck(lib().tcif_comm_init_nccl(self.h, int(rank), int(nRanks), C.c_char_p(id128)))
+
+    def ldu_csr(self):
+        os_, lo, ls = (np.zeros(self.nCells + 1, np.int32), np.zeros(self.nIF, np.int32),
+                       np.zeros(self.nCells + 1, np.int32))
+        self._ck(lib().tcif_get_ldu_csr(self.h, _i(os_), _i(lo), _i(ls)))
+        return os_, lo, ls
+
+    # -- fields
+    def set_alpha_bc(self, phase, kinds):
+        k = _i32(kinds)
+        assert k.shape[0] == self.nPatches
+        self._ck(lib().tcif_set_alpha_bc(self.h, int(phase), _i(k)))
+
+    def set_alpha(self, phase, internal, boundary):
+        a, b = _f64(internal), _f64(boundary)
+        assert a.shape[0] == self.nCells and b.shape[0] == self.nBF
+        self._ck(lib().tcif_set_alpha(self.h, int(phase), _d(a), _d(b)))
+
+    def get_alpha(self, phase):
+        a, b = np.empty(self.nCells), np.empty(self.nBF)
+        self._ck(lib().tcif_get_alpha(self.h, int(phase), _d(a), _d(b)))
+        return a, b
+
+    def store_old_alphas(self):
+        self._ck(lib().tcif_store_old_alphas(self.h))
+
+    def set_alpha_old(self, phase, internal):
+        a = _f64(internal)
+        self._ck(lib().tcif_set_alpha_old(self.h, int(phase), _d(a)))
+
+    def set_temperature(self, internal, boundary):
+        a, b = _f64(internal), _f64(boundary)
+        self._ck(lib().tcif_set_temperature(self.h, _d(a), _d(b)))
+
+    def set_sigma(self, phase1, phase2, spec):
+        """spec: ("constant", s0) | ("polynomial", [(a,e),..]) | ("table", [(T,s),..])."""
+        kind, val = spec
+        if kind == "constant":
+            co, n, k = _f64([val]), 1, SIGMA_CONSTANT
+        else:
+            co = _f64(np.asarray(val, dtype=np.float64).reshape(-1))
+            n = len(val)
+            k = SIGMA_POLYNOMIAL if kind == "polynomial" else SIGMA_TABLE if kind == "table" else 99
+        self._ck(lib().tcif_set_sigma(self.h, int(phase1), int(phase2), k, n, _d(co)))
+
+    def set_phi(self, internal, boundary):
+        a, b = _f64(internal), _f64(boundary)
+        assert a.shape[0] == self.nIF and b.shape[0] == self.nBF
+        self._ck(lib().tcif_set_phi(self.h, _d(a), _d(b)))
+
+    def set_phi_alpha(self, phase, internal, boundary):
+        a, b = _f64(internal), _f64(boundary)
+        assert a.shape[0] == self.nIF and b.shape[0] == self.nBF
+        self._ck(lib().tcif_set_phi_alpha(self.h, int(phase), _d(a), _d(b)))
+
+    def get_phi_alpha(self, phase):
+        a, b = np.empty(self.nIF), np.empty(self.nBF)
+        self._ck(lib().tcif_get_phi_alpha(self.h, int(phase), _d(a), _d(b)))
+        return a, b
+
+    def set_su_sp(self, phase, Su=None, Sp=None):
+        su = _f64(Su) if Su is not None else None
+        sp = _f64(Sp) if Sp is not None else None
+        self._ck(lib().tcif_set_su_sp(self.h, int(phase), _d(su), _d(sp)))
+
+    # -- hot path
+    def div_capillary_stress(self):
+        self._ck(lib().tcif_div_capillary_stress(self.h))
+
+    def get_force(self):
+        Fi, Fb = np.empty((self.nCells, 3)), np.empty((self.nBF, 3))
+        self._ck(lib().tcif_get_force(self.h, _d(Fi), _d(Fb)))
+        return Fi, Fb
+
+    def div_capillary_stress_host(self, alphas_i, alphas_b, Ti=None, Tb=None, Fi=None, Fb=None):
+        ai = [_f64(a) for a in alphas_i]
+        ab = [_f64(a) for a in alphas_b]
+        Ti = _f64(Ti) if Ti is not None else None
+        Tb = _f64(Tb) if Tb is not None else None
+        Fi = np.empty((self.nCells, 3)) if Fi is None else Fi
+        Fb = np.empty((self.nBF, 3)) if Fb is None else Fb
+        self._ck(lib().tcif_div_capillary_stress_host(self.h, _pp(ai), _pp(ab), _d(Ti), _d(Tb), _d(Fi), _d(Fb)))
+        return Fi, Fb
+
+    def grad_alpha(self, phase):
+        gi, gb = np.empty((self.nCells, 3)), np.empty((self.nBF, 3))
+        self._ck(lib().tcif_grad_alpha(self.h, int(phase), _d(gi), _d(gb)))
+        return gi, gb
+
+    def mules_limit(self, phase, rDeltaT, returnCorr):
+        self._ck(lib().tcif_mules_limit(self.h, int(phase), C.c_double(rDeltaT), int(bool(returnCorr))))
+
+    def mules_limit_sum(self):
+        self._ck(lib().tcif_mules_limit_sum(self.h))
+
+    def add_upwind_flux(self, phase):
+        self._ck(lib().tcif_add_upwind_flux(self.h, int(phase)))
+
+    def mules_explicit_solve(self, phase, deltaT):
+        self._ck(lib().tcif_mules_explicit_solve(self.h, int(phase), C.c_double(deltaT)))
+
+    def stage(self, deltaT):
+        self._ck(lib().tcif_stage(self.h, C.c_double(deltaT)))
+
+    def stage_host(self, deltaT, alphas_i, alphas_b, Ti, Tb, phii, phib, phiAlpha_i, phiAlpha_b, Fi, Fb):
+        """In-place on the given float64 C-contiguous arrays (alphas and phiAlpha are in/out)."""
+        for a in list(alphas_i) + list(alphas_b) + list(phiAlpha_i) + list(phiAlpha_b) + [Fi, Fb]:
+            assert a.dtype == np.float64 and a.flags.c_contiguous
+        self._ck(lib().tcif_stage_host(self.h, C.c_double(deltaT), _pp(alphas_i), _pp(alphas_b), _d(Ti), _d(Tb),
+                                       _d(phii), _d(phib), _pp(phiAlpha_i), _pp(phiAlpha_b), _d(Fi), _d(Fb)))
+
+    def alpha_stats(self, phase):
+        out = (C.c_double * 3)()
+        self._ck(lib().tcif_alpha_stats(self.h, int(phase), out))
+        return float(out[0]), float(out[1]), float(out[2])
+
+    # -- measurement
+    def timers_enable(self, on=True):
+        self._ck(lib().tcif_timers_enable(self.h, int(bool(on))))
+
+    def timers_reset(self):
+        self._ck(lib().tcif_timers_reset(self.h))
+
+    def timers_read(self):
+        n = lib().tcif_timer_count()
+        ms, ln, by = (C.c_double * n)(), (C.c_int64 * n)(), (C.c_double * n)()
+        self._ck(lib().tcif_timers_read(self.h, ms, ln, by))
+        return {lib().tcif_timer_name(i).decode(): dict(ms=ms[i], launches=int(ln[i]), bytes=by[i]) for i in range(n)}
+
+    @property
+    def launch_count(self):
+        return int(lib().tcif_launch_count(self.h))
+
+    @property
+    def device_bytes(self):
+        return int(lib().tcif_device_bytes(self.h))

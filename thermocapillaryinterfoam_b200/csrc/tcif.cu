@@ -1,0 +1,1181 @@
+// tcif.cu -- C ABI (include/tcif.h) of the B200-native interface hot path: device-resident
+// mesh + fields, kernel orchestration, processor-patch exchange, timers.
+//
+// Mirrors (does not copy) the reference call surface:
+//   phaseSystem::divCapillaryStress()      /root/reference/phasesSystem/phaseSystem/phaseSystem.C:1038-1105
+//   multiphaseSystem::solveAlphas() MULES  /root/reference/phasesSystem/multiphaseSystem/multiphaseSystem.C:296-375
+// There is no CPU fallback: every entry point needs a CUDA device.
+#include "tcif_device.cuh"
+#include "../../include/tcif.h"
+
+#include <dlfcn.h>
+#include <algorithm>
+#include <condition_variable>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+using namespace tcif;
+
+namespace {
+
+thread_local std::string g_createError;
+
+[[noreturn]] void failf(const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    throw std::runtime_error(buf);
+}
+
+#define CUDA_OK(call)                                                                              \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) failf("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
+
+// ---- timers ---------------------------------------------------------------------------
+enum TimerId {
+    T_GRAD_TENSOR = 0, T_DIV_TENSOR, T_MULES_SETUP, T_MULES_ITER, T_MULES_FINAL, T_LIMIT_SUM,
+    T_BOUNDARY, T_HALO, T_CONVERT, T_STATS, T_COUNT
+};
+const char *kTimerNames[T_COUNT] = {
+    "grad_tensor", "div_tensor", "mules_setup", "mules_iter", "mules_final", "limit_sum",
+    "boundary", "halo", "convert", "stats"};
+
+struct EvPair { cudaEvent_t a, b; int id; double bytes; };
+
+// ---- NCCL, bound at run time (torch ships libnccl.so.2; the system has one too) --------
+typedef struct ncclComm *ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+struct NcclApi {
+    void *h = nullptr;
+    int (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    int (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*Send)(const void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+const int kNcclDouble = 8;   // ncclFloat64
+NcclApi g_nccl;
+std::mutex g_ncclMutex;
+
+void nccl_load() {
+    std::lock_guard<std::mutex> lk(g_ncclMutex);
+    if (g_nccl.h) return;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    void *h = nullptr;
+    for (const char *n : names) { h = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+    if (!h) failf("cannot load libnccl.so.2: %s", dlerror());
+#define NSYM(field, sym)                                                   \
+    *(void **)(&g_nccl.field) = dlsym(h, sym);                             \
+    if (!g_nccl.field) failf("libnccl: missing symbol %s", sym);
+    NSYM(GetUniqueId, "ncclGetUniqueId") NSYM(CommInitRank, "ncclCommInitRank") NSYM(CommDestroy, "ncclCommDestroy")
+    NSYM(Send, "ncclSend") NSYM(Recv, "ncclRecv") NSYM(AllGather, "ncclAllGather")
+    NSYM(GroupStart, "ncclGroupStart") NSYM(GroupEnd, "ncclGroupEnd") NSYM(GetErrorString, "ncclGetErrorString")
+#undef NSYM
+    g_nccl.h = h;
+}
+#define NCCL_OK(call)                                                                        \
+    do {                                                                                     \
+        int r_ = (call);                                                                     \
+        if (r_ != 0) failf("%s failed: %s", #call, g_nccl.GetErrorString(r_));               \
+    } while (0)
+
+}  // namespace
+
+// ---- in-process group: several contexts on one GPU, one host thread each ----------------
+struct tcif_group {
+    int n = 0;
+    std::mutex mu;
+    std::condition_variable cv;
+    int waiting = 0;
+    long generation = 0;
+    std::vector<tcif_ctx *> members;
+    std::vector<double> red;     // n * 16 doubles
+    void barrier() {
+        std::unique_lock<std::mutex> lk(mu);
+        long gen = generation;
+        if (++waiting == n) { waiting = 0; ++generation; cv.notify_all(); }
+        else cv.wait(lk, [&] { return generation != gen; });
+    }
+};
+
+struct tcif_ctx {
+    std::string err;
+    int device = 0;
+    cudaStream_t ownStream = nullptr, stream = nullptr;
+    // host copy of the small mesh tables
+    int nC = 0, nIF = 0, nBF = 0, nPatches = 0, stride = 0, Ko = 0, Kn = 0, nBndCells = 0, nCoupled = 0;
+    size_t nFd = 0;
+    std::vector<int> patchType, patchStart, patchSize, patchNbr;
+    std::vector<int> cpPatch, cpOff;    // coupled patches: patch id, offset in coupled-face units
+    double sumV = 0.0;
+    DMesh dm{};
+    int *d_faceMap = nullptr;           // host face f -> device slot
+    std::vector<void *> allocs;
+    int64_t devBytes = 0;
+    // config
+    tcif_config cfg{};
+    int P = 0, Q = 0;
+    // fields
+    double *alpha[4]{}, *alpha0[4]{}, *alphaNew[4]{}, *alphab[4]{};
+    int *bc[4]{};
+    double *Tc = nullptr, *Tb = nullptr;
+    bool haveT = false;
+    SigmaModel hSig[6];
+    bool sigSet[6]{};
+    SigmaModel *dSig = nullptr;
+    double *phi = nullptr, *phib = nullptr;
+    double *phiHO[4]{}, *phiHOb[4]{}, *phiPsi[4]{}, *phiPsib[4]{}, *phiCorr[4]{}, *phiCorrb[4]{}, *phiBDb[4]{};
+    double *Qp[4]{}, *Qm[4]{}, *sP[4]{}, *sM[4]{}, *lpA[4]{}, *lmA[4]{}, *lpB[4]{}, *lmB[4]{};
+    double *lamA[4]{}, *lamB[4]{}, *lamb[4]{}, *lpHalo[4]{}, *lmHalo[4]{};
+    double *Su[4]{}, *Sp[4]{};
+    bool haveSu[4]{}, haveSp[4]{};
+    double *Tq = nullptr, *gBnd = nullptr, *TqHalo = nullptr, *G = nullptr, *Gb = nullptr, *F = nullptr, *Fb = nullptr;
+    double deltaN = 0.0;
+    bool deltaNValid = false;
+    double *staging = nullptr;
+    size_t stagingDoubles = 0;
+    double *sendBuf = nullptr, *recvBuf = nullptr;
+    size_t haloDoubles = 0;
+    double *statsPart = nullptr, *statsOut = nullptr;
+    double *h_small = nullptr;          // pinned, 64 doubles
+    // comm
+    int rank = 0, nRanks = 1;
+    tcif_group *group = nullptr;
+    ncclComm_t nccl = nullptr;
+    double *d_gather = nullptr;         // nRanks*16 doubles (nccl scalar reductions)
+    // timers
+    bool timersOn = false;
+    std::vector<EvPair> evs;
+    std::vector<EvPair> evPool;
+    double tMs[T_COUNT]{}, tBytes[T_COUNT]{};
+    int64_t tLaunch[T_COUNT]{};
+    int64_t launches = 0;
+
+    template <class T> T *dalloc(size_t n, bool zero = true) {
+        void *p = nullptr;
+        size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+        CUDA_OK(cudaMalloc(&p, bytes));
+        allocs.push_back(p);
+        devBytes += (int64_t)bytes;
+        if (zero) CUDA_OK(cudaMemsetAsync(p, 0, bytes, stream));
+        return (T *)p;
+    }
+    template <class T> T *upload(const std::vector<T> &v) {
+        T *p = dalloc<T>(v.size(), false);
+        if (!v.empty()) CUDA_OK(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+        return p;
+    }
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+template <class F> void timed(tcif_ctx *c, int id, double bytes, F &&launch) {
+    if (c->timersOn) {
+        EvPair e;
+        if (!c->evPool.empty()) { e = c->evPool.back(); c->evPool.pop_back(); }
+        else { CUDA_OK(cudaEventCreate(&e.a)); CUDA_OK(cudaEventCreate(&e.b)); }
+        e.id = id; e.bytes = bytes;
+        CUDA_OK(cudaEventRecord(e.a, c->stream));
+        launch();
+        CUDA_OK(cudaEventRecord(e.b, c->stream));
+        c->evs.push_back(e);
+    } else launch();
+    CUDA_OK(cudaGetLastError());
+}
+
+void timers_collect(tcif_ctx *c) {
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    for (auto &e : c->evs) {
+        float ms = 0.f;
+        CUDA_OK(cudaEventElapsedTime(&ms, e.a, e.b));
+        c->tMs[e.id] += ms; c->tBytes[e.id] += e.bytes; c->tLaunch[e.id] += 1;
+        c->evPool.push_back(e);
+    }
+    c->evs.clear();
+}
+
+// ---- mesh upload: OpenFOAM ldu addressing -> owner-slot-major padded ELL ----------------
+void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
+    const int nC = m->nCells, nIF = m->nInternalFaces, nBF = m->nBoundaryFaces, nP = m->nPatches;
+    if (nC <= 0 || nIF < 0 || nBF < 0 || nP < 0) failf("tcif_create: bad mesh sizes");
+    if (nIF && (!m->owner || !m->neighbour || !m->Sf || !m->weights)) failf("tcif_create: null internal-face arrays");
+    if (!m->V) failf("tcif_create: null V");
+    c->nC = nC; c->nIF = nIF; c->nBF = nBF; c->nPatches = nP;
+    c->stride = (nC + 31) / 32 * 32;
+    const int stride = c->stride;
+    // rank of each face among its owner's / neighbour's faces in ascending face index
+    std::vector<int> cntO(nC, 0), cntN(nC, 0), kOwn(nIF), kNei(nIF);
+    for (int f = 0; f < nIF; ++f) {
+        int o = m->owner[f], n = m->neighbour[f];
+        if (o < 0 || o >= nC || n < 0 || n >= nC || o == n) failf("tcif_create: face %d has bad owner/neighbour (%d,%d)", f, o, n);
+        kOwn[f] = cntO[o]++; kNei[f] = cntN[n]++;
+    }
+    int Ko = 0, Kn = 0;
+    for (int i = 0; i < nC; ++i) { Ko = std::max(Ko, cntO[i]); Kn = std::max(Kn, cntN[i]); }
+    Ko = std::max(Ko, 1); Kn = std::max(Kn, 1);
+    c->Ko = Ko; c->Kn = Kn;
+    c->nFd = (size_t)Ko * stride;
+    if ((size_t)std::max(Ko, Kn) * stride > 0x7fffffffULL) failf("tcif_create: mesh too large for int32 face slots");
+    std::vector<int> faceMap(nIF), nbrOwn((size_t)Ko * stride, -1), neiFace((size_t)Kn * stride, -1);
+    std::vector<double> sx(c->nFd, 0.0), sy(c->nFd, 0.0), sz(c->nFd, 0.0), w(c->nFd, 0.0);
+    for (int f = 0; f < nIF; ++f) {
+        int o = m->owner[f], n = m->neighbour[f];
+        size_t fd = (size_t)kOwn[f] * stride + o;
+        faceMap[f] = (int)fd;
+        nbrOwn[fd] = n;
+        neiFace[(size_t)kNei[f] * stride + n] = (int)fd;
+        sx[fd] = m->Sf[3 * (size_t)f]; sy[fd] = m->Sf[3 * (size_t)f + 1]; sz[fd] = m->Sf[3 * (size_t)f + 2];
+        w[fd] = m->weights[f];
+    }
+    DMesh &d = c->dm;
+    d.nC = nC; d.stride = stride; d.Ko = Ko; d.Kn = Kn; d.nFd = (int)c->nFd; d.nBF = nBF; d.nPatches = nP;
+    d.nbrOwn = c->upload(nbrOwn); d.neiFace = c->upload(neiFace);
+    d.Sfx = c->upload(sx); d.Sfy = c->upload(sy); d.Sfz = c->upload(sz); d.w = c->upload(w);
+    c->d_faceMap = c->upload(faceMap);
+    std::vector<double> V(m->V, m->V + nC);
+    double sumV = 0.0;
+    for (int i = 0; i < nC; ++i) { if (!(V[i] > 0)) failf("tcif_create: cell %d has non-positive volume", i); sumV += V[i]; }
+    c->sumV = sumV;
+    d.V = c->upload(V);
+    // patches
+    c->patchType.assign(m->patchType, m->patchType + nP);
+    c->patchStart.assign(m->patchStart, m->patchStart + nP);
+    c->patchSize.assign(m->patchSize, m->patchSize + nP);
+    c->patchNbr.assign(nP, -1);
+    if (m->patchNeighbProcNo) c->patchNbr.assign(m->patchNeighbProcNo, m->patchNeighbProcNo + nP);
+    std::vector<int> bfPatch(nBF, 0), bfType(nBF, 0), coupled, cOff, cSize;
+    int covered = 0;
+    for (int p = 0; p < nP; ++p) {
+        int s = c->patchStart[p], n = c->patchSize[p], t = c->patchType[p];
+        if (t < 0 || t > 3) failf("tcif_create: patch %d has unknown type %d", p, t);
+        if (t == TCIF_PATCH_EMPTY && n != 0) failf("tcif_create: empty patch %d must have size 0 (fields carry no values on it)", p);
+        if (n < 0 || s < 0 || s + n > nBF || s != covered) failf("tcif_create: patch %d range [%d,%d) is not contiguous in patch order", p, s, s + n);
+        covered += n;
+        if (t == TCIF_PATCH_PROCESSOR) {
+            if (c->patchNbr[p] < 0) failf("tcif_create: processor patch %d without neighbour rank", p);
+            c->cpPatch.push_back(p); c->cpOff.push_back((int)coupled.size());
+            int off = (int)coupled.size();
+            for (int i = 0; i < n; ++i) { coupled.push_back(s + i); cOff.push_back(off); cSize.push_back(n); }
+        }
+        for (int i = 0; i < n; ++i) { bfPatch[s + i] = p; bfType[s + i] = t; }
+    }
+    if (covered != nBF) failf("tcif_create: patches cover %d of %d boundary faces", covered, nBF);
+    c->nCoupled = (int)coupled.size();
+    // boundary faces grouped by cell (ascending cell, ascending boundary-face index = patch order)
+    std::vector<int> fc(nBF);
+    for (int b = 0; b < nBF; ++b) { fc[b] = m->faceCells[b]; if (fc[b] < 0 || fc[b] >= nC) failf("tcif_create: faceCells[%d] out of range", b); }
+    std::vector<int> order(nBF);
+    for (int b = 0; b < nBF; ++b) order[b] = b;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return fc[a] < fc[b]; });
+    std::vector<int> bndCells, bndStart;
+    for (int k = 0; k < nBF; ++k) {
+        if (k == 0 || fc[order[k]] != fc[order[k - 1]]) { bndCells.push_back(fc[order[k]]); bndStart.push_back(k); }
+    }
+    bndStart.push_back(nBF);
+    c->nBndCells = (int)bndCells.size();
+    d.nBndCells = c->nBndCells; d.nCoupled = c->nCoupled;
+    d.bndCells = c->upload(bndCells); d.bndCellStart = c->upload(bndStart); d.bndFaces = c->upload(order);
+    d.faceCells = c->upload(fc); d.bfPatch = c->upload(bfPatch); d.bfType = c->upload(bfType);
+    std::vector<double> bx(nBF), by(nBF), bz(nBF), mag(nBF), dc(nBF), wb(nBF);
+    for (int b = 0; b < nBF; ++b) {
+        bx[b] = m->SfBoundary[3 * (size_t)b]; by[b] = m->SfBoundary[3 * (size_t)b + 1]; bz[b] = m->SfBoundary[3 * (size_t)b + 2];
+        mag[b] = m->magSfBoundary ? m->magSfBoundary[b] : std::sqrt(bx[b] * bx[b] + by[b] * by[b] + bz[b] * bz[b]);
+        dc[b] = m->deltaCoeffsBoundary ? m->deltaCoeffsBoundary[b] : 0.0;
+        wb[b] = m->weightsBoundary ? m->weightsBoundary[b] : 1.0;
+    }
+    d.Sfbx = c->upload(bx); d.Sfby = c->upload(by); d.Sfbz = c->upload(bz);
+    d.magSfb = c->upload(mag); d.dcb = c->upload(dc); d.wb = c->upload(wb);
+    d.coupledFaces = c->upload(coupled); d.coupledOff = c->upload(cOff); d.coupledSize = c->upload(cSize);
+}
+
+void alloc_fields(tcif_ctx *c) {
+    const int P = c->P, Q = c->Q, nBF = c->nBF;
+    const size_t cs = c->stride, fs = c->nFd, bs = std::max(nBF, 1);
+    for (int p = 0; p < P; ++p) {
+        c->alpha[p] = c->dalloc<double>(cs); c->alpha0[p] = c->dalloc<double>(cs); c->alphaNew[p] = c->dalloc<double>(cs);
+        c->alphab[p] = c->dalloc<double>(bs);
+        c->bc[p] = c->dalloc<int>(std::max(c->nPatches, 1));
+        c->phiHO[p] = c->dalloc<double>(fs); c->phiHOb[p] = c->dalloc<double>(bs);
+        c->phiPsi[p] = c->dalloc<double>(fs); c->phiPsib[p] = c->dalloc<double>(bs);
+        c->phiCorr[p] = c->dalloc<double>(fs); c->phiCorrb[p] = c->dalloc<double>(bs); c->phiBDb[p] = c->dalloc<double>(bs);
+        c->Qp[p] = c->dalloc<double>(cs); c->Qm[p] = c->dalloc<double>(cs); c->sP[p] = c->dalloc<double>(cs); c->sM[p] = c->dalloc<double>(cs);
+        c->lpA[p] = c->dalloc<double>(cs); c->lmA[p] = c->dalloc<double>(cs); c->lpB[p] = c->dalloc<double>(cs); c->lmB[p] = c->dalloc<double>(cs);
+        c->lamA[p] = c->dalloc<double>(fs); c->lamB[p] = c->dalloc<double>(fs); c->lamb[p] = c->dalloc<double>(bs);
+        c->lpHalo[p] = c->dalloc<double>(bs); c->lmHalo[p] = c->dalloc<double>(bs);
+    }
+    c->Tc = c->dalloc<double>(cs); c->Tb = c->dalloc<double>(bs);
+    c->phi = c->dalloc<double>(fs); c->phib = c->dalloc<double>(bs);
+    c->dSig = c->dalloc<SigmaModel>(std::max(Q, 1));
+    c->Tq = c->dalloc<double>((size_t)std::max(Q, 1) * 6 * cs);
+    c->gBnd = c->dalloc<double>((size_t)P * 3 * std::max(c->nBndCells, 1));
+    c->TqHalo = c->dalloc<double>((size_t)std::max(Q, 1) * 6 * bs);
+    c->F = c->dalloc<double>(3 * cs); c->Fb = c->dalloc<double>(3 * bs);
+    c->stagingDoubles = std::max<size_t>(3 * cs, std::max<size_t>((size_t)std::max(c->nIF, 1), 3 * bs));
+    c->staging = c->dalloc<double>(c->stagingDoubles);
+    int maxComp = std::max(std::max(Q * 6, 3 * P), 3);
+    c->haloDoubles = (size_t)std::max(c->nCoupled, 1) * maxComp;
+    c->sendBuf = c->dalloc<double>(c->haloDoubles); c->recvBuf = c->dalloc<double>(c->haloDoubles);
+    c->statsPart = c->dalloc<double>(1024 * 3); c->statsOut = c->dalloc<double>(16);
+    CUDA_OK(cudaHostAlloc((void **)&c->h_small, 64 * sizeof(double), cudaHostAllocDefault));
+    for (int q = 0; q < 6; ++q) { c->hSig[q].kind = SIGMA_CONSTANT; c->hSig[q].n = 1; memset(c->hSig[q].c, 0, sizeof c->hSig[q].c); }
+}
+
+// ---- scalar all-reduce over ranks (deterministic: gathered, combined in rank order) -----
+enum { RED_SUM = 0, RED_MIN = 1, RED_MAX = 2 };
+void allreduce_host(tcif_ctx *c, double *v, const int *ops, int n) {
+    if (n > 16) failf("allreduce_host: n > 16");
+    if (c->group) {
+        tcif_group *g = c->group;
+        memcpy(&g->red[(size_t)c->rank * 16], v, sizeof(double) * n);
+        g->barrier();
+        for (int i = 0; i < n; ++i) {
+            double r = g->red[i];
+            for (int k = 1; k < g->n; ++k) {
+                double x = g->red[(size_t)k * 16 + i];
+                r = ops[i] == RED_SUM ? r + x : ops[i] == RED_MIN ? std::min(r, x) : std::max(r, x);
+            }
+            v[i] = r;
+        }
+        g->barrier();
+    } else if (c->nccl) {
+        memcpy(c->h_small, v, sizeof(double) * n);
+        CUDA_OK(cudaMemcpyAsync(c->statsOut, c->h_small, sizeof(double) * 16, cudaMemcpyHostToDevice, c->stream));
+        NCCL_OK(g_nccl.AllGather(c->statsOut, c->d_gather, 16, kNcclDouble, c->nccl, c->stream));
+        std::vector<double> all((size_t)c->nRanks * 16);
+        CUDA_OK(cudaMemcpyAsync(all.data(), c->d_gather, all.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        for (int i = 0; i < n; ++i) {
+            double r = all[i];
+            for (int k = 1; k < c->nRanks; ++k) {
+                double x = all[(size_t)k * 16 + i];
+                r = ops[i] == RED_SUM ? r + x : ops[i] == RED_MIN ? std::min(r, x) : std::max(r, x);
+            }
+            v[i] = r;
+        }
+    }
+}
+
+void require_comm(tcif_ctx *c) {
+    if (c->nCoupled > 0 && !c->group && !c->nccl)
+        failf("mesh has processor patches but no communicator is attached (tcif_comm_init_nccl / tcif_comm_init_local)");
+}
+
+// deltaN = 1e-8/cbrt(average(mesh.V()))   phaseSystem.C:1287-1291 (global average)
+void ensure_deltaN(tcif_ctx *c) {
+    if (c->deltaNValid) return;
+    double v[2] = {c->sumV, (double)c->nC};
+    int ops[2] = {RED_SUM, RED_SUM};
+    allreduce_host(c, v, ops, 2);
+    c->deltaN = 1e-8 / cbrt(v[0] / v[1]);
+    c->deltaNValid = true;
+}
+
+// ---- processor-patch exchange -----------------------------------------------------------
+// send buffer (patch-major) -> neighbour ranks -> recv buffer.
+void exchange(tcif_ctx *c, int ncomp) {
+    if (c->group) {
+        tcif_group *g = c->group;
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        g->barrier();
+        for (size_t i = 0; i < c->cpPatch.size(); ++i) {
+            int p = c->cpPatch[i], e = c->patchNbr[p], n = c->patchSize[p];
+            if (e < 0 || e >= g->n || !g->members[e]) failf("processor patch %d: neighbour rank %d not in group", p, e);
+            tcif_ctx *o = g->members[e];
+            int peerOff = -1;
+            for (size_t j = 0; j < o->cpPatch.size(); ++j)
+                if (o->patchNbr[o->cpPatch[j]] == c->rank) { peerOff = o->cpOff[j]; if (o->patchSize[o->cpPatch[j]] != n) failf("processor patch size mismatch"); break; }
+            if (peerOff < 0) failf("rank %d has no patch facing rank %d", e, c->rank);
+            CUDA_OK(cudaMemcpyAsync(c->recvBuf + (size_t)c->cpOff[i] * ncomp, o->sendBuf + (size_t)peerOff * ncomp,
+                                    sizeof(double) * (size_t)n * ncomp, cudaMemcpyDeviceToDevice, c->stream));
+        }
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        g->barrier();
+    } else if (c->nccl) {
+        NCCL_OK(g_nccl.GroupStart());
+        for (size_t i = 0; i < c->cpPatch.size(); ++i) {
+            int p = c->cpPatch[i], e = c->patchNbr[p], n = c->patchSize[p];
+            NCCL_OK(g_nccl.Send(c->sendBuf + (size_t)c->cpOff[i] * ncomp, (size_t)n * ncomp, kNcclDouble, e, c->nccl, c->stream));
+            NCCL_OK(g_nccl.Recv(c->recvBuf + (size_t)c->cpOff[i] * ncomp, (size_t)n * ncomp, kNcclDouble, e, c->nccl, c->stream));
+        }
+        NCCL_OK(g_nccl.GroupEnd());
+    } else failf("exchange without communicator");
+}
+
+// processorFvPatchField::evaluate for ncomp cell arrays at once: dst[d][bf] := neighbour-rank src[d][faceCell]
+void halo_cells(tcif_ctx *c, int ncomp, const double *const *src, double *const *dst) {
+    if (c->nCoupled == 0) return;
+    require_comm(c);
+    if ((size_t)ncomp * c->nCoupled > c->haloDoubles || ncomp > 36) failf("halo_cells: too many components");
+    HaloArgs h;
+    h.ncomp = ncomp;
+    for (int d = 0; d < ncomp; ++d) { h.src[d] = src[d]; h.dst[d] = dst[d]; }
+    double bytes = 16.0 * ncomp * c->nCoupled;
+    timed(c, T_HALO, bytes, [&] {
+        k_halo_pack<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, h, c->sendBuf);
+        c->launches++;
+        exchange(c, ncomp);
+        k_halo_unpack<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, h, c->recvBuf);
+        c->launches++;
+    });
+}
+
+// ---- kernel dispatch ----------------------------------------------------------------------
+int kshape(const tcif_ctx *c) { return (c->Ko == 3 && c->Kn == 3) ? 3 : (c->Ko == 2 && c->Kn == 2) ? 2 : 0; }
+
+#define DISPATCH_K(...)                                      \
+    switch (kshape(c)) {                                     \
+        case 3: { constexpr int KO = 3, KN = 3; (void)KO; (void)KN; __VA_ARGS__; } break; \
+        case 2: { constexpr int KO = 2, KN = 2; (void)KO; (void)KN; __VA_ARGS__; } break; \
+        default: { constexpr int KO = 0, KN = 0; (void)KO; (void)KN; __VA_ARGS__; } break; \
+    }
+#define DISPATCH_P(...)                                      \
+    switch (c->P) {                                          \
+        case 2: { constexpr int PP = 2; __VA_ARGS__; } break; \
+        case 3: { constexpr int PP = 3; __VA_ARGS__; } break; \
+        case 4: { constexpr int PP = 4; __VA_ARGS__; } break; \
+        default: failf("nPhases must be 2..4");              \
+    }
+
+ForceArgs force_args(tcif_ctx *c, bool withTensor, bool withG) {
+    ForceArgs a{};
+    for (int p = 0; p < c->P; ++p) { a.alpha[p] = c->alpha[p]; a.alphab[p] = c->alphab[p]; a.bc[p] = c->bc[p]; }
+    a.T = c->Tc; a.Tb = c->Tb; a.sig = c->dSig; a.deltaN = c->deltaN;
+    a.Tq = withTensor ? c->Tq : nullptr; a.gBnd = c->gBnd; a.TqHalo = c->TqHalo;
+    a.G = withG ? c->G : nullptr; a.F = c->F;
+    return a;
+}
+
+template <bool BND, bool WG> void launch_grad_tensor(tcif_ctx *c, const ForceArgs &a) {
+    int n = BND ? c->nBndCells : c->nC;
+    if (n == 0) return;
+    int grid = cdiv(n, TCIF_TPB);
+    DISPATCH_P(DISPATCH_K(k_grad_tensor<PP, KO, KN, BND, WG><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, a)));
+    c->launches++;
+}
+template <bool BND> void launch_div_tensor(tcif_ctx *c, const ForceArgs &a) {
+    int n = BND ? c->nBndCells : c->nC;
+    if (n == 0) return;
+    int grid = cdiv(n, TCIF_TPB);
+    DISPATCH_P(DISPATCH_K(k_div_tensor<PP, KO, KN, BND><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, a)));
+    c->launches++;
+}
+
+// compulsory HBM bytes of the volume sweeps (every array touched once; DESIGN.md "Kernels")
+double bytes_grad_tensor(const tcif_ctx *c, bool tensor, bool g) {
+    double perCell = 8.0 * c->P + 8 /*V*/ + 4.0 * (c->Ko + c->Kn) + 32.0 * c->Ko;
+    if (tensor) perCell += 48.0 * c->Q + (c->haveT ? 8 : 0);
+    if (g) perCell += 24.0 * c->P;
+    return perCell * c->nC;
+}
+double bytes_div_tensor(const tcif_ctx *c) {
+    return (48.0 * c->Q + 8 + 4.0 * (c->Ko + c->Kn) + 32.0 * c->Ko + 24) * c->nC;
+}
+double bytes_mules_setup(const tcif_ctx *c, int nPh) {
+    return nPh * (double)c->nC * (8 + 8 + 8 /*psi psi0 V*/ + 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko * 3 /*phi phiIn phiCorr*/ + 48 /*Q+-,s+-,l+-*/);
+}
+double bytes_mules_iter(const tcif_ctx *c, int nPh, bool first) {
+    return nPh * (double)c->nC * (4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko * (first ? 2 : 3) + 16 + 16 + 32);
+}
+double bytes_mules_final(const tcif_ctx *c, int nPh, int mode, bool first) {
+    double perCell = 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko * (first ? 2 : 3) + 16;
+    if (mode >= 1) perCell += 8.0 * c->Ko + 8;          // phi, psi
+    if (mode == 2) perCell += 24;                       // psi0, V, psiNew
+    return nPh * (double)c->nC * perCell;
+}
+
+void do_force(tcif_ctx *c) {
+    if (c->Q < 1) failf("divCapillaryStress needs at least two phases");
+    for (int q = 0; q < c->Q; ++q) {
+        if (!c->sigSet[q]) failf("surfaceTension entry missing for pair %d (all pairs need one; phaseSystem.C:1135)", q);
+        if (c->hSig[q].kind != SIGMA_CONSTANT && !c->haveT) failf("temperatureDependent sigma without a temperature field");
+    }
+    require_comm(c);
+    ensure_deltaN(c);
+    ForceArgs a = force_args(c, true, false);
+    timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, true, false), [&] { launch_grad_tensor<false, false>(c, a); });
+    timed(c, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, false>(c, a); });
+    if (c->nCoupled) {
+        const double *src[36]; double *dst[36];
+        for (int k = 0; k < c->Q * 6; ++k) { src[k] = c->Tq + (size_t)k * c->stride; dst[k] = c->TqHalo + (size_t)k * std::max(c->nBF, 1); }
+        halo_cells(c, c->Q * 6, src, dst);
+    }
+    timed(c, T_DIV_TENSOR, bytes_div_tensor(c), [&] { launch_div_tensor<false>(c, a); });
+    timed(c, T_BOUNDARY, 0, [&] { launch_div_tensor<true>(c, a); });
+    if (c->nBF) {
+        timed(c, T_BOUNDARY, 0, [&] {
+            k_extrapolate_bnd<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, 3, (size_t)c->stride, c->F, c->Fb);
+            c->launches++;
+        });
+        if (c->nCoupled) {
+            const double *src[3]; double *dst[3];
+            for (int d = 0; d < 3; ++d) { src[d] = c->F + (size_t)d * c->stride; dst[d] = c->Fb + (size_t)d * c->nBF; }
+            halo_cells(c, 3, src, dst);
+        }
+    }
+}
+
+// fvc::grad(alpha_p) for every phase into G / Gb (Gauss linear + gaussGrad boundary correction)
+void do_grad(tcif_ctx *c) {
+    require_comm(c);
+    if (!c->G) { c->G = c->dalloc<double>((size_t)c->P * 3 * c->stride); c->Gb = c->dalloc<double>((size_t)c->P * 3 * std::max(c->nBF, 1)); }
+    ForceArgs a = force_args(c, false, true);
+    timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, false, true), [&] { launch_grad_tensor<false, true>(c, a); });
+    timed(c, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, a); });
+    if (!c->nBF) return;
+    for (int p = 0; p < c->P; ++p) {
+        double *gi = c->G + (size_t)p * 3 * c->stride, *gb = c->Gb + (size_t)p * 3 * c->nBF;
+        timed(c, T_BOUNDARY, 0, [&] {
+            k_extrapolate_bnd<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, 3, (size_t)c->stride, gi, gb);
+            c->launches++;
+        });
+        if (c->nCoupled) {
+            const double *src[3]; double *dst[3];
+            for (int d = 0; d < 3; ++d) { src[d] = gi + (size_t)d * c->stride; dst[d] = gb + (size_t)d * c->nBF; }
+            halo_cells(c, 3, src, dst);
+        }
+        timed(c, T_BOUNDARY, 0, [&] {
+            k_grad_bnd_correct<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->alpha[p], c->alphab[p], c->bc[p], gb);
+            c->launches++;
+        });
+    }
+}
+
+// psi.correctBoundaryConditions() for a set of phases: zeroGradient patches + processor halo
+void correct_alpha_bcs(tcif_ctx *c, const int *phases, int nPh) {
+    if (!c->nBF) return;
+    for (int k = 0; k < nPh; ++k) {
+        int p = phases[k];
+        timed(c, T_BOUNDARY, 0, [&] {
+            k_correct_bc_scalar<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->alpha[p], c->alphab[p], c->bc[p]);
+            c->launches++;
+        });
+    }
+    if (c->nCoupled) {
+        const double *src[4]; double *dst[4];
+        for (int k = 0; k < nPh; ++k) { src[k] = c->alpha[phases[k]]; dst[k] = c->alphab[phases[k]]; }
+        halo_cells(c, nPh, src, dst);
+    }
+}
+
+MulesBatch mules_batch(tcif_ctx *c, const int *phases, int nPh, bool fromHO) {
+    MulesBatch b{};
+    b.nPh = nPh;
+    for (int k = 0; k < nPh; ++k) {
+        int p = phases[k];
+        MulesPh &ph = b.ph[k];
+        ph.psi = c->alpha[p]; ph.psi0 = c->alpha0[p]; ph.psib = c->alphab[p];
+        ph.Su = c->haveSu[p] ? c->Su[p] : nullptr; ph.Sp = c->haveSp[p] ? c->Sp[p] : nullptr;
+        ph.bc = c->bc[p];
+        ph.phiIn = fromHO ? c->phiHO[p] : c->phiPsi[p]; ph.phiInb = fromHO ? c->phiHOb[p] : c->phiPsib[p];
+        ph.phiPsi = c->phiPsi[p]; ph.phiPsib = c->phiPsib[p];
+        ph.phiCorr = c->phiCorr[p]; ph.phiCorrb = c->phiCorrb[p]; ph.phiBDb = c->phiBDb[p];
+        ph.Qp = c->Qp[p]; ph.Qm = c->Qm[p]; ph.sP = c->sP[p]; ph.sM = c->sM[p];
+        ph.lpA = c->lpA[p]; ph.lmA = c->lmA[p]; ph.lpB = c->lpB[p]; ph.lmB = c->lmB[p];
+        ph.lamA = c->lamA[p]; ph.lamB = c->lamB[p]; ph.lamb = c->lamb[p];
+        ph.lpHalo = c->lpHalo[p]; ph.lmHalo = c->lmHalo[p];
+        ph.psiNew = c->alphaNew[p];
+    }
+    return b;
+}
+
+template <bool BND> void launch_setup(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm) {
+    int n = BND ? c->nBndCells : c->nC;
+    if (n == 0) return;
+    int grid = cdiv(n, TCIF_TPB) * b.nPh;
+    DISPATCH_K(k_mules_setup<KO, KN, BND><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm));
+    c->launches++;
+}
+template <bool BND> void launch_iter(tcif_ctx *c, const MulesBatch &b, int first, int flip) {
+    int n = BND ? c->nBndCells : c->nC;
+    if (n == 0) return;
+    int grid = cdiv(n, TCIF_TPB) * b.nPh;
+    DISPATCH_K(k_mules_iter<KO, KN, BND><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, first, flip));
+    c->launches++;
+}
+template <bool BND, int MODE> void launch_final(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm, int first, int flip, int nIter) {
+    int n = BND ? c->nBndCells : c->nC;
+    if (n == 0) return;
+    int grid = cdiv(n, TCIF_TPB) * b.nPh;
+    DISPATCH_K(k_mules_final<KO, KN, BND, MODE><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, first, flip, nIter));
+    c->launches++;
+}
+
+void halo_lambda(tcif_ctx *c, const MulesBatch &b, int flip) {
+    if (!c->nCoupled) return;
+    const double *src[8]; double *dst[8];
+    for (int k = 0; k < b.nPh; ++k) {
+        src[2 * k] = flip ? b.ph[k].lpB : b.ph[k].lpA; dst[2 * k] = b.ph[k].lpHalo;
+        src[2 * k + 1] = flip ? b.ph[k].lmB : b.ph[k].lmA; dst[2 * k + 1] = b.ph[k].lmHalo;
+    }
+    halo_cells(c, 2 * b.nPh, src, dst);
+}
+
+// MULES::limit for a batch of phases.  mode 0: returnCorr=true; 1: returnCorr=false;
+// 2: explicitSolve's limit fused with surfaceIntegrate + Euler update (psi -> alphaNew).
+void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode, bool addUpwind, bool fromHO) {
+    require_comm(c);
+    MulesBatch b = mules_batch(c, phases, nPh, fromHO);
+    MulesParams prm{};
+    prm.rDeltaT = rDeltaT; prm.psiMax = 1.0; prm.psiMin = 0.0;
+    prm.extremaCoeff = c->cfg.extremaCoeff; prm.smoothLimiter = c->cfg.smoothLimiter;
+    prm.boundaryExtrema = c->cfg.boundaryExtrema; prm.addUpwind = addUpwind ? 1 : 0;
+    prm.phi = c->phi; prm.phib = c->phib;
+    const int L = c->cfg.nLimiterIter;
+    timed(c, T_MULES_SETUP, bytes_mules_setup(c, nPh), [&] { launch_setup<false>(c, b, prm); });
+    timed(c, T_BOUNDARY, 0, [&] { launch_setup<true>(c, b, prm); });
+    int first = 1, flip = 0;
+    for (int j = 1; j < L; ++j) {
+        halo_lambda(c, b, flip);
+        timed(c, T_MULES_ITER, bytes_mules_iter(c, nPh, first), [&] { launch_iter<false>(c, b, first, flip); });
+        timed(c, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b, first, flip); });
+        flip ^= 1; first = 0;
+    }
+    if (L > 0) halo_lambda(c, b, flip);
+    double fb = bytes_mules_final(c, nPh, mode, first);
+    if (mode == 0) {
+        timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, 0>(c, b, prm, first, flip, L); });
+        timed(c, T_BOUNDARY, 0, [&] { launch_final<true, 0>(c, b, prm, first, flip, L); });
+    } else if (mode == 1) {
+        timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, 1>(c, b, prm, first, flip, L); });
+        timed(c, T_BOUNDARY, 0, [&] { launch_final<true, 1>(c, b, prm, first, flip, L); });
+    } else {
+        timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, 2>(c, b, prm, first, flip, L); });
+        timed(c, T_BOUNDARY, 0, [&] { launch_final<true, 2>(c, b, prm, first, flip, L); });
+        for (int k = 0; k < nPh; ++k) std::swap(c->alpha[phases[k]], c->alphaNew[phases[k]]);
+    }
+}
+
+void do_limit_sum(tcif_ctx *c) {
+    LimitSumArgs a{};
+    a.nPh = c->P;
+    for (int p = 0; p < c->P; ++p) a.f[p] = c->phiPsi[p];
+    timed(c, T_LIMIT_SUM, 16.0 * c->P * c->nFd, [&] {
+        k_limit_sum<<<cdiv((long long)c->nFd, TCIF_TPB), TCIF_TPB, 0, c->stream>>>((int)c->nFd, a);
+        c->launches++;
+    });
+    if (c->nCoupled) {
+        LimitSumArgs ab{};
+        ab.nPh = c->P;
+        for (int p = 0; p < c->P; ++p) ab.f[p] = c->phiPsib[p];
+        timed(c, T_BOUNDARY, 0, [&] {
+            k_limit_sum_coupled<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nCoupled, c->dm.coupledFaces, ab);
+            c->launches++;
+        });
+    }
+}
+
+// MULES::explicitSolve for a batch of phases (optionally preceded by phiAlpha += upwind flux)
+void do_explicit(tcif_ctx *c, const int *phases, int nPh, double deltaT, bool addUpwind) {
+    if (!(deltaT > 0)) failf("explicitSolve: deltaT must be positive");
+    correct_alpha_bcs(c, phases, nPh);
+    do_limit(c, phases, nPh, 1.0 / deltaT, 2, addUpwind, false);
+    correct_alpha_bcs(c, phases, nPh);
+}
+
+void store_old(tcif_ctx *c) {
+    for (int p = 0; p < c->P; ++p)
+        CUDA_OK(cudaMemcpyAsync(c->alpha0[p], c->alpha[p], sizeof(double) * c->nC, cudaMemcpyDeviceToDevice, c->stream));
+}
+
+void do_stage(tcif_ctx *c, double deltaT) {
+    if (!(deltaT > 0)) failf("tcif_stage: deltaT must be positive");
+    int all[4] = {0, 1, 2, 3};
+    do_force(c);
+    store_old(c);
+    do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true);      // multiphaseSystem.C:296-319
+    do_limit_sum(c);                                            // :321
+    do_explicit(c, all, c->P, deltaT, true);                    // :346 (bounded flux) + :365-375
+}
+
+// ---- host <-> device field transfers ----------------------------------------------------
+void up_cells(tcif_ctx *c, double *dst, const double *src) {
+    CUDA_OK(cudaMemcpyAsync(dst, src, sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
+}
+void up_bnd(tcif_ctx *c, double *dst, const double *src) {
+    if (c->nBF && src) CUDA_OK(cudaMemcpyAsync(dst, src, sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
+}
+void up_faces(tcif_ctx *c, double *dst, const double *src) {
+    if (!c->nIF) return;
+    CUDA_OK(cudaMemcpyAsync(c->staging, src, sizeof(double) * c->nIF, cudaMemcpyDefault, c->stream));
+    timed(c, T_CONVERT, 20.0 * c->nIF, [&] {
+        k_face_scatter<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nIF, c->d_faceMap, c->staging, dst);
+        c->launches++;
+    });
+}
+void down_faces(tcif_ctx *c, double *dst, const double *src) {
+    if (!c->nIF) return;
+    timed(c, T_CONVERT, 20.0 * c->nIF, [&] {
+        k_face_gather<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nIF, c->d_faceMap, src, c->staging);
+        c->launches++;
+    });
+    CUDA_OK(cudaMemcpyAsync(dst, c->staging, sizeof(double) * c->nIF, cudaMemcpyDefault, c->stream));
+}
+// SoA (3 comps, given strides) -> host AoS
+void down_vec(tcif_ctx *c, double *dst, const double *src, int n, size_t strideSrc) {
+    if (!n || !dst) return;
+    timed(c, T_CONVERT, 48.0 * n, [&] {
+        k_soa_to_aos3<<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(n, strideSrc, src, c->staging);
+        c->launches++;
+    });
+    CUDA_OK(cudaMemcpyAsync(dst, c->staging, sizeof(double) * 3 * (size_t)n, cudaMemcpyDefault, c->stream));
+}
+
+void check_phase(tcif_ctx *c, int p) { if (p < 0 || p >= c->P) failf("phase index %d out of range [0,%d)", p, c->P); }
+int pair_index(int P, int p1, int p2) {
+    int q = 0;
+    for (int a = 0; a < P; ++a) for (int b = a + 1; b < P; ++b, ++q) if (a == p1 && b == p2) return q;
+    return -1;
+}
+
+}  // namespace
+
+// ========================================================================================
+// C ABI
+// ========================================================================================
+#define API_BEGIN(ctx)                                        \
+    if (!(ctx)) return 1;                                     \
+    try {                                                     \
+        DeviceGuard guard_((ctx)->device);
+#define API_END(ctx)                                          \
+        return 0;                                             \
+    } catch (const std::exception &e) {                       \
+        (ctx)->err = e.what();                                \
+        return 1;                                             \
+    }
+
+extern "C" {
+
+const char *tcif_version(void) { return "tcif 0.1 (sm_100a, fp64, fmad=off)"; }
+
+int tcif_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char *tcif_last_error(const tcif_ctx *ctx) { return ctx ? ctx->err.c_str() : g_createError.c_str(); }
+
+int tcif_create(const tcif_mesh_desc *mesh, const tcif_config *cfg, tcif_ctx **out) {
+    if (out) *out = nullptr;
+    tcif_ctx *c = nullptr;
+    int prevDev = -1;
+    try {
+        if (!mesh || !cfg || !out) failf("tcif_create: null argument");
+        int nDev = tcif_device_count();
+        if (nDev <= 0) failf("tcif_create: no CUDA device available (this library has no CPU fallback)");
+        if (cfg->nPhases < 2 || cfg->nPhases > TCIF_MAX_PHASES) failf("tcif_create: nPhases must be 2..%d", TCIF_MAX_PHASES);
+        if (cfg->nLimiterIter < 0 || cfg->nLimiterIter > 64) failf("tcif_create: nLimiterIter out of range");
+        if (cfg->boundaryExtrema != TCIF_BEXT_GLOBAL && cfg->boundaryExtrema != TCIF_BEXT_PATCHVALUE) failf("tcif_create: bad boundaryExtrema");
+        c = new tcif_ctx();
+        c->cfg = *cfg;
+        cudaGetDevice(&prevDev);
+        c->device = cfg->device >= 0 ? cfg->device : prevDev;
+        if (c->device >= nDev) failf("tcif_create: device %d not present (%d visible)", c->device, nDev);
+        CUDA_OK(cudaSetDevice(c->device));
+        cudaDeviceProp prop;
+        CUDA_OK(cudaGetDeviceProperties(&prop, c->device));
+        if (prop.major < 10) failf("tcif_create: device %d is sm_%d%d; this build targets sm_100a only", c->device, prop.major, prop.minor);
+        CUDA_OK(cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking));
+        c->stream = c->ownStream;
+        c->P = cfg->nPhases; c->Q = c->P * (c->P - 1) / 2;
+        build_mesh(c, mesh);
+        alloc_fields(c);
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        if (prevDev >= 0) cudaSetDevice(prevDev);
+        *out = c;
+        return 0;
+    } catch (const std::exception &e) {
+        g_createError = e.what();
+        if (c) { tcif_destroy(c); }
+        if (prevDev >= 0) cudaSetDevice(prevDev);
+        return 1;
+    }
+}
+
+void tcif_destroy(tcif_ctx *c) {
+    if (!c) return;
+    DeviceGuard guard(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->nccl && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl);
+    if (c->group) { std::lock_guard<std::mutex> lk(c->group->mu); if (c->rank < (int)c->group->members.size()) c->group->members[c->rank] = nullptr; }
+    for (auto &e : c->evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    for (auto &e : c->evPool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    for (void *p : c->allocs) cudaFree(p);
+    if (c->h_small) cudaFreeHost(c->h_small);
+    if (c->ownStream) cudaStreamDestroy(c->ownStream);
+    delete c;
+}
+
+int tcif_set_stream(tcif_ctx *c, void *s) {
+    API_BEGIN(c)
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    c->stream = s ? (cudaStream_t)s : c->ownStream;
+    API_END(c)
+}
+
+int tcif_synchronize(tcif_ctx *c) {
+    API_BEGIN(c)
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+void *tcif_host_alloc(uint64_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void tcif_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+int tcif_get_ldu_csr(tcif_ctx *c, int32_t *ownerStart, int32_t *losort, int32_t *losortStart) {
+    API_BEGIN(c)
+    const int nC = c->nC, nIF = c->nIF;
+    std::vector<int> faceMap(nIF), nbrOwn(c->nFd);
+    CUDA_OK(cudaMemcpy(faceMap.data(), c->d_faceMap, sizeof(int) * nIF, cudaMemcpyDeviceToHost));
+    CUDA_OK(cudaMemcpy(nbrOwn.data(), c->dm.nbrOwn, sizeof(int) * c->nFd, cudaMemcpyDeviceToHost));
+    std::vector<int> os(nC + 1, 0), ls(nC + 1, 0);
+    for (int f = 0; f < nIF; ++f) { os[faceMap[f] % c->stride + 1]++; ls[nbrOwn[faceMap[f]] + 1]++; }
+    for (int i = 0; i < nC; ++i) { os[i + 1] += os[i]; ls[i + 1] += ls[i]; }
+    if (ownerStart) memcpy(ownerStart, os.data(), sizeof(int) * (nC + 1));
+    if (losortStart) memcpy(losortStart, ls.data(), sizeof(int) * (nC + 1));
+    if (losort) {
+        std::vector<int> pos(ls.begin(), ls.end() - 1);
+        for (int f = 0; f < nIF; ++f) losort[pos[nbrOwn[faceMap[f]]]++] = f;
+    }
+    API_END(c)
+}
+
+// ---- communication -----------------------------------------------------------------------
+int tcif_comm_unique_id(void *id128) {
+    try {
+        if (!id128) failf("null id buffer");
+        nccl_load();
+        ncclUniqueId id;
+        NCCL_OK(g_nccl.GetUniqueId(&id));
+        memcpy(id128, &id, 128);
+        return 0;
+    } catch (const std::exception &e) { g_createError = e.what(); return 1; }
+}
+
+int tcif_comm_init_nccl(tcif_ctx *c, int rank, int nRanks, const void *id128) {
+    API_BEGIN(c)
+    if (c->group || c->nccl) failf("communicator already attached");
+    if (rank < 0 || rank >= nRanks || !id128) failf("tcif_comm_init_nccl: bad arguments");
+    nccl_load();
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    NCCL_OK(g_nccl.CommInitRank(&c->nccl, nRanks, id, rank));
+    c->rank = rank; c->nRanks = nRanks;
+    for (int p : c->cpPatch) if (c->patchNbr[p] >= nRanks || c->patchNbr[p] == rank) failf("processor patch %d: neighbour rank %d invalid", p, c->patchNbr[p]);
+    c->d_gather = c->dalloc<double>((size_t)nRanks * 16);
+    c->deltaNValid = false;
+    API_END(c)
+}
+
+int tcif_group_create(int nRanks, tcif_group **out) {
+    if (!out || nRanks < 1) return 1;
+    tcif_group *g = new tcif_group();
+    g->n = nRanks; g->members.assign(nRanks, nullptr); g->red.assign((size_t)nRanks * 16, 0.0);
+    *out = g;
+    return 0;
+}
+void tcif_group_destroy(tcif_group *g) { delete g; }
+
+int tcif_comm_init_local(tcif_ctx *c, int rank, tcif_group *g) {
+    API_BEGIN(c)
+    if (c->group || c->nccl) failf("communicator already attached");
+    if (!g || rank < 0 || rank >= g->n) failf("tcif_comm_init_local: bad arguments");
+    {
+        std::lock_guard<std::mutex> lk(g->mu);
+        if (g->members[rank]) failf("rank %d already joined", rank);
+        g->members[rank] = c;
+    }
+    c->group = g; c->rank = rank; c->nRanks = g->n;
+    c->deltaNValid = false;
+    API_END(c)
+}
+
+// ---- fields ---------------------------------------------------------------------------------
+int tcif_set_alpha_bc(tcif_ctx *c, int phase, const int32_t *bcKind) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (c->nPatches) {
+        for (int p = 0; p < c->nPatches; ++p) if (bcKind[p] != TCIF_BC_ZERO_GRADIENT && bcKind[p] != TCIF_BC_FIXED_VALUE) failf("unsupported alpha boundary condition %d on patch %d", bcKind[p], p);
+        CUDA_OK(cudaMemcpyAsync(c->bc[phase], bcKind, sizeof(int) * c->nPatches, cudaMemcpyDefault, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+    }
+    API_END(c)
+}
+
+int tcif_set_alpha(tcif_ctx *c, int phase, const double *internal, const double *boundary) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (!internal || (c->nBF && !boundary)) failf("tcif_set_alpha: null field");
+    up_cells(c, c->alpha[phase], internal);
+    up_bnd(c, c->alphab[phase], boundary);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_get_alpha(tcif_ctx *c, int phase, double *internal, double *boundary) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (internal) CUDA_OK(cudaMemcpyAsync(internal, c->alpha[phase], sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
+    if (boundary && c->nBF) CUDA_OK(cudaMemcpyAsync(boundary, c->alphab[phase], sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_store_old_alphas(tcif_ctx *c) {
+    API_BEGIN(c)
+    store_old(c);
+    API_END(c)
+}
+
+int tcif_set_alpha_old(tcif_ctx *c, int phase, const double *internal) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (!internal) failf("tcif_set_alpha_old: null field");
+    up_cells(c, c->alpha0[phase], internal);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_set_temperature(tcif_ctx *c, const double *internal, const double *boundary) {
+    API_BEGIN(c)
+    if (!internal || (c->nBF && !boundary)) failf("tcif_set_temperature: null field");
+    up_cells(c, c->Tc, internal);
+    up_bnd(c, c->Tb, boundary);
+    c->haveT = true;
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_set_sigma(tcif_ctx *c, int phase1, int phase2, int kind, int n, const double *coeffs) {
+    API_BEGIN(c)
+    check_phase(c, phase1); check_phase(c, phase2);
+    if (phase1 == phase2) failf("tcif_set_sigma: a pair needs two different phases");
+    int q = pair_index(c->P, std::min(phase1, phase2), std::max(phase1, phase2));
+    SigmaModel s;
+    memset(&s, 0, sizeof s);
+    if (kind == TCIF_SIGMA_CONSTANT) { if (n < 1 || !coeffs) failf("constant sigma needs one coefficient"); s.kind = SIGMA_CONSTANT; s.n = 1; s.c[0] = coeffs[0]; }
+    else if (kind == TCIF_SIGMA_POLYNOMIAL || kind == TCIF_SIGMA_TABLE) {
+        if (n < 1 || 2 * n > TCIF_SIGMA_MAX_COEFFS || !coeffs) failf("sigma Function1 needs 1..%d (x,y) pairs", TCIF_SIGMA_MAX_COEFFS / 2);
+        s.kind = kind == TCIF_SIGMA_POLYNOMIAL ? SIGMA_POLYNOMIAL : SIGMA_TABLE; s.n = n;
+        for (int i = 0; i < 2 * n; ++i) s.c[i] = coeffs[i];
+        if (kind == TCIF_SIGMA_TABLE) for (int i = 1; i < n; ++i) if (!(s.c[2 * i] > s.c[2 * (i - 1)])) failf("sigma table abscissae must increase");
+    } else failf("unsupported surfaceTensionModel kind %d (constant | temperatureDependent polynomial/table)", kind);
+    c->hSig[q] = s; c->sigSet[q] = true;
+    CUDA_OK(cudaMemcpyAsync(c->dSig + q, &c->hSig[q], sizeof(SigmaModel), cudaMemcpyHostToDevice, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_set_phi(tcif_ctx *c, const double *internal, const double *boundary) {
+    API_BEGIN(c)
+    if ((c->nIF && !internal) || (c->nBF && !boundary)) failf("tcif_set_phi: null field");
+    up_faces(c, c->phi, internal);
+    up_bnd(c, c->phib, boundary);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_set_phi_alpha(tcif_ctx *c, int phase, const double *internal, const double *boundary) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if ((c->nIF && !internal) || (c->nBF && !boundary)) failf("tcif_set_phi_alpha: null field");
+    up_faces(c, c->phiHO[phase], internal);
+    up_bnd(c, c->phiHOb[phase], boundary);
+    CUDA_OK(cudaMemcpyAsync(c->phiPsi[phase], c->phiHO[phase], sizeof(double) * c->nFd, cudaMemcpyDeviceToDevice, c->stream));
+    if (c->nBF) CUDA_OK(cudaMemcpyAsync(c->phiPsib[phase], c->phiHOb[phase], sizeof(double) * c->nBF, cudaMemcpyDeviceToDevice, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_get_phi_alpha(tcif_ctx *c, int phase, double *internal, double *boundary) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (internal) down_faces(c, internal, c->phiPsi[phase]);
+    if (boundary && c->nBF) CUDA_OK(cudaMemcpyAsync(boundary, c->phiPsib[phase], sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_set_su_sp(tcif_ctx *c, int phase, const double *Su, const double *Sp) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (Su) { if (!c->Su[phase]) c->Su[phase] = c->dalloc<double>(c->stride); up_cells(c, c->Su[phase], Su); }
+    if (Sp) { if (!c->Sp[phase]) c->Sp[phase] = c->dalloc<double>(c->stride); up_cells(c, c->Sp[phase], Sp); }
+    c->haveSu[phase] = Su != nullptr; c->haveSp[phase] = Sp != nullptr;
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+// ---- hot path ---------------------------------------------------------------------------------
+int tcif_div_capillary_stress(tcif_ctx *c) {
+    API_BEGIN(c)
+    do_force(c);
+    API_END(c)
+}
+
+int tcif_get_force(tcif_ctx *c, double *internal, double *boundary) {
+    API_BEGIN(c)
+    down_vec(c, internal, c->F, c->nC, c->stride);
+    if (boundary && c->nBF) down_vec(c, boundary, c->Fb, c->nBF, c->nBF);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_div_capillary_stress_host(tcif_ctx *c, const double *const *ai, const double *const *ab, const double *Ti,
+                                   const double *Tb, double *Fi, double *Fb) {
+    API_BEGIN(c)
+    if (!ai || (c->nBF && !ab)) failf("tcif_div_capillary_stress_host: null alpha lists");
+    for (int p = 0; p < c->P; ++p) { up_cells(c, c->alpha[p], ai[p]); if (c->nBF) up_bnd(c, c->alphab[p], ab[p]); }
+    if (Ti) { up_cells(c, c->Tc, Ti); up_bnd(c, c->Tb, Tb); c->haveT = true; }
+    do_force(c);
+    down_vec(c, Fi, c->F, c->nC, c->stride);
+    if (Fb && c->nBF) down_vec(c, Fb, c->Fb, c->nBF, c->nBF);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_grad_alpha(tcif_ctx *c, int phase, double *internal, double *boundary) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    do_grad(c);
+    down_vec(c, internal, c->G + (size_t)phase * 3 * c->stride, c->nC, c->stride);
+    if (boundary && c->nBF) down_vec(c, boundary, c->Gb + (size_t)phase * 3 * c->nBF, c->nBF, c->nBF);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_mules_limit(tcif_ctx *c, int phase, double rDeltaT, int returnCorr) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    do_limit(c, &phase, 1, rDeltaT, returnCorr ? 0 : 1, false, false);
+    API_END(c)
+}
+
+int tcif_mules_limit_sum(tcif_ctx *c) {
+    API_BEGIN(c)
+    do_limit_sum(c);
+    API_END(c)
+}
+
+int tcif_add_upwind_flux(tcif_ctx *c, int phase) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    timed(c, T_MULES_SETUP, 0, [&] {
+        int grid = cdiv(c->nC, TCIF_TPB);
+        DISPATCH_K(k_add_upwind<KO><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, c->phi, c->alpha[phase], c->phiPsi[phase]));
+        c->launches++;
+        if (c->nBF) {
+            k_add_upwind_bnd<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->phib, c->alpha[phase], c->alphab[phase], c->phiPsib[phase]);
+            c->launches++;
+        }
+    });
+    API_END(c)
+}
+
+int tcif_mules_explicit_solve(tcif_ctx *c, int phase, double deltaT) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    do_explicit(c, &phase, 1, deltaT, false);
+    API_END(c)
+}
+
+int tcif_stage(tcif_ctx *c, double deltaT) {
+    API_BEGIN(c)
+    do_stage(c, deltaT);
+    API_END(c)
+}
+
+int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const *ab, const double *Ti, const double *Tb,
+                    const double *phii, const double *phib, double *const *pai, double *const *pab, double *Fi, double *Fb) {
+    API_BEGIN(c)
+    if (!ai || !pai || (c->nBF && (!ab || !pab))) failf("tcif_stage_host: null field lists");
+    for (int p = 0; p < c->P; ++p) { up_cells(c, c->alpha[p], ai[p]); if (c->nBF) up_bnd(c, c->alphab[p], ab[p]); }
+    if (Ti) { up_cells(c, c->Tc, Ti); up_bnd(c, c->Tb, Tb); c->haveT = true; }
+    if (phii || !c->nIF) { up_faces(c, c->phi, phii); up_bnd(c, c->phib, phib); }
+    for (int p = 0; p < c->P; ++p) { up_faces(c, c->phiHO[p], pai[p]); if (c->nBF) up_bnd(c, c->phiHOb[p], pab[p]); }
+    do_stage(c, deltaT);
+    down_vec(c, Fi, c->F, c->nC, c->stride);
+    if (Fb && c->nBF) down_vec(c, Fb, c->Fb, c->nBF, c->nBF);
+    for (int p = 0; p < c->P; ++p) {
+        CUDA_OK(cudaMemcpyAsync(ai[p], c->alpha[p], sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
+        if (c->nBF) CUDA_OK(cudaMemcpyAsync(ab[p], c->alphab[p], sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
+        down_faces(c, pai[p], c->phiPsi[p]);
+        if (c->nBF) CUDA_OK(cudaMemcpyAsync(pab[p], c->phiPsib[p], sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
+    }
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_alpha_stats(tcif_ctx *c, int phase, double out3[3]) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    int nPart = std::min(1024, cdiv(c->nC, TCIF_TPB));
+    timed(c, T_STATS, 16.0 * c->nC, [&] {
+        k_stats_partial<<<nPart, TCIF_TPB, 0, c->stream>>>(c->nC, c->dm.V, c->alpha[phase], c->statsPart);
+        k_stats_final<<<1, 32, 0, c->stream>>>(nPart, c->statsPart, c->statsOut);
+        c->launches += 2;
+    });
+    CUDA_OK(cudaMemcpyAsync(c->h_small, c->statsOut, sizeof(double) * 3, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    double v[3] = {c->h_small[0], c->h_small[1], c->h_small[2]};
+    int ops[3] = {RED_SUM, RED_MIN, RED_MAX};
+    allreduce_host(c, v, ops, 3);
+    out3[0] = v[0]; out3[1] = v[1]; out3[2] = v[2];
+    API_END(c)
+}
+
+// ---- measurement ------------------------------------------------------------------------------
+int tcif_timers_enable(tcif_ctx *c, int on) {
+    API_BEGIN(c)
+    if (!on && c->timersOn) timers_collect(c);
+    c->timersOn = on != 0;
+    API_END(c)
+}
+int tcif_timers_reset(tcif_ctx *c) {
+    API_BEGIN(c)
+    timers_collect(c);
+    for (int i = 0; i < T_COUNT; ++i) { c->tMs[i] = 0; c->tBytes[i] = 0; c->tLaunch[i] = 0; }
+    API_END(c)
+}
+int tcif_timer_count(void) { return T_COUNT; }
+const char *tcif_timer_name(int id) { return (id >= 0 && id < T_COUNT) ? kTimerNames[id] : ""; }
+int tcif_timers_read(tcif_ctx *c, double *ms, int64_t *launches, double *bytes) {
+    API_BEGIN(c)
+    timers_collect(c);
+    for (int i = 0; i < T_COUNT; ++i) {
+        if (ms) ms[i] = c->tMs[i];
+        if (launches) launches[i] = c->tLaunch[i];
+        if (bytes) bytes[i] = c->tBytes[i];
+    }
+    API_END(c)
+}
+int64_t tcif_launch_count(const tcif_ctx *c) { return c ? c->launches : 0; }
+int64_t tcif_device_bytes(const tcif_ctx *c) { return c ? c->devBytes : 0; }
+
+}  // extern "C"
