@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py -- surface-force + MULES Mcell-updates/s (BASELINE.json metric) on N B200s of one node.
+
+One "step" = one stage: divCapillaryStress over all phase pairs + one solveAlphas
+corrector (limit x P, limitSum, explicitSolve x P) on frozen synthetic fields of BASELINE.json
+configs[4] (synthetic 3-D 3-phase box, 64 M cells; strong scaling: the SAME box split over N ranks
+by the `simple` block decomposition, processor-patch halo exchange over NCCL).
+
+  value : stages timed with CUDA events on the launching stream, inputs resident in HBM
+  e2e   : the same stage through tcif_stage_host (host buffers in pinned memory; H2D of every
+          input field and D2H of every output field inside the timed region)
+  roofline / cpu_baseline : see DESIGN.md "Measurement"
+  --impl reference : the CPU oracle (restatement of the reference path, oracle/) domain-decomposed
+          on all host cores -- the reference's own OpenFOAM binary cannot be built here.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "surface-force+MULES Mcell-updates/s"
+UNIT = "Mcell-updates/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=5)
+    ap.add_argument("--n", type=int, default=0, help="cells per box edge (0 = BASELINE size)")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-n", type=int, default=0, help="edge of the CPU-baseline sample box (0 = auto)")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---- contract algorithmic bytes (SURVEY.md 8(d) / BASELINE.md section 3) ---------------------
+def contract_bytes(nC, nIF, nBF, P, QT, L):
+    BS = nC * (64 * P + 8 * QT + 40) + 80 * nIF + nBF * (56 + 40 * P + 8 * QT)
+    BM = P * (nIF * (136 + 96 * L) + nC * (184 + 128 * L))
+    return BS + BM
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[5 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "power_w_max": float(max(pw)), "samples": len(sm)}
+
+
+# ---- CPU arm: the oracle, domain-decomposed on the host cores ----------------------------------
+def cpu_layout(cores):
+    nd = 1
+    while nd * 2 <= min(cores, 64):
+        nd *= 2
+    procs = [1, 1, 1]
+    d, k = 0, nd
+    while k > 1:
+        procs[d % 3] *= 2
+        k //= 2
+        d += 1
+    return nd, tuple(procs)
+
+
+def cpu_stage_rate(config, n_edge, nStages, cores):
+    """Mcell-updates/s of the CPU oracle on an n_edge^3 sample of the workload, one thread per sub-domain."""
+    from oracle import oracle as orc
+    from thermocapillaryinterfoam_b200 import cases, mesh as hm
+    spec = cases.case(config, n_edge)
+    nd, procs = cpu_layout(cores)
+    meshes = [hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, r) for r in range(nd)]
+    fs = [cases.synthetic_fields(spec, m) for m in meshes]
+    secs, _ = orc.stage_threads(meshes, orc.mules_cfg(3), [f["alpha_i"] for f in fs], [f["alpha_b"] for f in fs],
+                                [f["alphaBc"] for f in fs], spec.sigma, [f["T_i"] for f in fs], [f["T_b"] for f in fs],
+                                [f["phi_i"] for f in fs], [f["phi_b"] for f in fs], [f["phiAlpha_i"] for f in fs],
+                                [f["phiAlpha_b"] for f in fs], spec.deltaT, nStages=nStages)
+    return spec.nCells * nStages / secs / 1e6, secs, nd, procs, spec
+
+
+def cpu_sample_edge(args, cores):
+    if args.cpu_n:
+        return args.cpu_n
+    full = args.n or {1: 64, 2: 512, 3: 128, 4: 200, 5: 400}[args.config]
+    return min(full, 128 if cores >= 8 else 96)
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    edge = cpu_sample_edge(args, cores)
+    nd, procs = cpu_layout(cores)
+    for _ in range(min(args.warmup, 1)):
+        cpu_stage_rate(args.config, edge, 1, cores)
+    rate, secs, nd, procs, spec = cpu_stage_rate(args.config, edge, args.steps, cores)
+    sample = (f"{spec.name} {edge}^3 = {spec.nCells} cells, {spec.nPhases} phases, {args.steps} stages, "
+              f"{nd} sub-domains {procs[0]}x{procs[1]}x{procs[2]} (one thread each)")
+    line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args), "sample": sample},
+            "cpu_baseline": {"value": rate, "unit": UNIT, "cores": nd, "kind": "port", "sample": sample,
+                             "host_cores": cores},
+            "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "CPU oracle (restatement of the reference path; the OpenFOAM v2106 binary is unbuildable here)"}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(args):
+    from thermocapillaryinterfoam_b200 import cases
+    spec = cases.case(args.config, args.n or None)
+    return f"configs[{args.config - 1}] {spec.name} {spec.n[0]}x{spec.n[1]}x{spec.n[2]} = {spec.nCells} cells, {spec.nPhases} phases"
+
+
+# ---- GPU arm -----------------------------------------------------------------------------------
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from thermocapillaryinterfoam_b200 import abi, cases, mesh as hm
+
+    if not torch.cuda.is_available() or abi.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device -- the hot path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    spec = cases.case(args.config, args.n or None)
+    procs = hm.procs_for(world)
+    t0 = time.time()
+    m = hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, rank)
+    f = cases.synthetic_fields(spec, m)
+    nC, nIF, nBF = m.nCells, m.nIF, m.nBF
+    ctx = abi.Context(m, spec.nPhases, device=local_rank)
+    m.close()
+    del m
+    if world > 1:
+        ids = [abi.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init_nccl(rank, world, ids[0])
+    stream = torch.cuda.Stream(device=dev)
+    ctx.set_stream(stream.cuda_stream)
+    cases.load_case(ctx, spec, f)
+    dt = f["deltaT"]
+    setup_s = time.time() - t0
+    P = spec.nPhases
+    QT = sum(1 for s in spec.sigma if s[0] != "constant")
+
+    # ---- value: device-resident stages --------------------------------------------------------
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            ctx.stage(dt)
+        ctx.timers_enable(True)
+        ctx.timers_reset()
+        launches0 = ctx.launch_count
+        sampler = ClockSampler(local_rank)
+        barrier()
+        if rank == 0:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            ctx.stage(dt)
+        e1.record(stream)
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        launches = ctx.launch_count - launches0
+        timers = ctx.timers_read()
+        ctx.timers_enable(False)
+    total_cells = spec.nCells
+    value = total_cells * args.steps / (ms * 1e-3) / 1e6
+
+    # ---- roofline: dominant kernel, CUDA-event time on the launching stream -------------------
+    hbm, how = peaks()
+    vol = {k: v for k, v in timers.items() if v["launches"] and v["bytes"] > 0 and k not in ("halo", "convert", "stats")}
+    top = max(vol, key=lambda k: vol[k]["ms"])
+    tk = vol[top]
+    achieved = tk["bytes"] / (tk["ms"] * 1e-3) / 1e9
+    step_ms_sum = sum(v["ms"] for v in timers.values())
+    stage_bytes_compulsory = sum(v["bytes"] for k, v in timers.items() if k not in ("convert", "stats")) / args.steps
+    contract = contract_bytes(nC, nIF, nBF, P, QT, 3)
+    roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                "traffic": None, "peak_source": how, "launches": tk["launches"],
+                "avg_launch_ms": tk["ms"] / tk["launches"], "kernel_share_of_step": tk["ms"] / step_ms_sum,
+                "bytes_per_launch": tk["bytes"] / tk["launches"],
+                "stage": {"compulsory_bytes_per_cell": stage_bytes_compulsory / nC,
+                          "achieved_GBs_compulsory": stage_bytes_compulsory * args.steps / (ms * 1e-3) / 1e9,
+                          "contract_bytes_per_cell": contract / nC,
+                          "achieved_GBs_contract": contract * args.steps / (ms * 1e-3) / 1e9,
+                          "frac_contract": contract * args.steps / (ms * 1e-3) / 1e9 / hbm},
+                "per_kernel_ms_per_step": {k: v["ms"] / args.steps for k, v in timers.items() if v["launches"]}}
+
+    # ---- e2e: host buffers through tcif_stage_host ------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        def pin(a):
+            b = abi.pinned_empty(a.shape)
+            b[...] = a
+            return b
+        ai = [pin(a) for a in f["alpha_i"]]; ab = [pin(a) for a in f["alpha_b"]]
+        pi0 = [pin(a) for a in f["phiAlpha_i"]]; pb0 = [pin(a) for a in f["phiAlpha_b"]]
+        pi = [abi.pinned_empty(a.shape) for a in pi0]; pb = [abi.pinned_empty(a.shape) for a in pb0]
+        Ti, Tb, phii, phib = pin(f["T_i"]), pin(f["T_b"]), pin(f["phi_i"]), pin(f["phi_b"])
+        Fi, Fb = abi.pinned_empty((nC, 3)), abi.pinned_empty((nBF, 3))
+        h2d = 8 * (P * (nC + nBF) + (nC + nBF) + (nIF + nBF) + P * (nIF + nBF))
+        d2h = 8 * (3 * (nC + nBF) + P * (nC + nBF) + P * (nIF + nBF))
+
+        def one():
+            for p in range(P):          # the HO flux is an input every step (alphaPhi overwrites the buffer)
+                pi[p][...] = pi0[p]; pb[p][...] = pb0[p]
+            ctx.stage_host(dt, ai, ab, Ti, Tb, phii, phib, pi, pb, Fi, Fb)
+        with torch.cuda.stream(stream):
+            one()
+            barrier()
+            tw = time.perf_counter()
+            for _ in range(args.e2e_steps):
+                one()
+            barrier()
+            e2e_s = max_over_ranks(time.perf_counter() - tw)
+        e2e = {"value": total_cells * args.e2e_steps / e2e_s / 1e6, "unit": UNIT,
+               "h2d_bytes_per_step": int(sum_over_ranks(h2d)), "d2h_bytes_per_step": int(sum_over_ranks(d2h)),
+               "steps": args.e2e_steps, "ms_per_step": 1e3 * e2e_s / args.e2e_steps,
+               "api": "tcif_stage_host (pinned host buffers; includes the host-side refresh of the HO-flux input)"}
+        del ai, ab, pi, pb, pi0, pb0, Ti, Tb, phii, phib, Fi, Fb
+
+    stats = [ctx.alpha_stats(p) for p in range(P)]
+    dev_bytes = ctx.device_bytes
+    ctx.close()
+
+    # ---- CPU baseline beside it (rank 0, N=1 only) --------------------------------------------
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        edge = cpu_sample_edge(args, cores)
+        nst = 4
+        rate, secs, nd, cprocs, cspec = cpu_stage_rate(args.config, edge, nst, cores)
+        cpu = {"value": rate, "unit": UNIT, "cores": nd, "kind": "port", "host_cores": cores,
+               "sample": f"{cspec.name} {edge}^3 = {cspec.nCells} cells, {cspec.nPhases} phases, {nst} stages, "
+                         f"{nd} sub-domains {cprocs[0]}x{cprocs[1]}x{cprocs[2]}, {secs:.1f} s"}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": workload_name(args), "phases": P, "pairs": len(spec.sigma), "nLimiterIter": 3,
+                           "decomposition": f"simple {procs[0]}x{procs[1]}x{procs[2]}", "cells_per_gpu": nC,
+                           "l2": "inputs larger than L2 (no flush needed)" if dev_bytes > 4 * 126e6 else
+                                 "L2-resident case: latency-bound, no roofline claim",
+                           "device_bytes_per_gpu": dev_bytes, "setup_s": round(setup_s, 1)},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+                "alpha_stats": [{"sumValpha": s[0], "min": s[1], "max": s[2]} for s in stats]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("bench.py: N>1 must be launched with torch.distributed.run (one rank per GPU)")
+    if args.impl == "reference":
+        run_reference(args, rank)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
