@@ -10,14 +10,15 @@ from thermocapillaryinterfoam_b200 import cases
 RTOL = 1e-12
 
 
-def assert_field_close(a, b, what="", rtol=RTOL):
+def assert_field_close(a, b, what="", rtol=RTOL, floor=0.0):
+    """`floor`: extra absolute tolerance for cancellation-dominated fields (stated by the caller)."""
     a, b = np.asarray(a), np.asarray(b)
     assert a.shape == b.shape, (what, a.shape, b.shape)
     if a.size == 0:
         return
     scale = max(np.max(np.abs(a)), np.max(np.abs(b)))
     err = np.abs(a - b)
-    tol = rtol * np.maximum(np.abs(a), np.abs(b)) + rtol * scale
+    tol = rtol * np.maximum(np.abs(a), np.abs(b)) + rtol * scale + floor
     bad = err > tol
     assert not bad.any(), f"{what}: {bad.sum()} of {a.size} entries differ, max err {err.max():.3e} (scale {scale:.3e})"
 

@@ -45,11 +45,15 @@ def test_grad_matches_oracle(config, n):
     f["alphaBc"] = bc
     f["alpha_b"][0][: m.patchSize[0]] = 0.25
     ctx = _ctx(m, spec, f)
+    # A Gauss gradient is a cancelling sum of terms Sf*alpha_f/V: where alpha is nearly uniform the result
+    # is tiny while each term is O(|alpha| |Sf|/V), so rounding (the GPU path uses x*(1/V) and fma) is
+    # bounded by a few ulp of the TERMS, not of the result: 64 eps * max|alpha| * max(sum|Sf|/V).
+    floor = 64 * np.finfo(float).eps * 6 * np.abs(m.Sf).max() / m.V.min()
     for p in range(spec.nPhases):
         gi, gb = ctx.grad_alpha(p)
         ri, rb = orc.grad(m, f["alpha_i"][p], f["alpha_b"][p], bc[p])
-        assert_field_close(gi, ri, f"grad alpha{p}")
-        assert_field_close(gb, rb, f"grad alpha{p} boundary")
+        assert_field_close(gi, ri, f"grad alpha{p}", floor=floor)
+        assert_field_close(gb, rb, f"grad alpha{p} boundary", floor=floor)
     ctx.close()
 
 
@@ -77,7 +81,7 @@ def test_stage_matches_oracle(config, n, L):
 
 
 def test_serial_bitwise():
-    """-fmad=false + reference accumulation order => bit-identical to the serial oracle."""
+    """-fmad=false + reference accumulation order => MULES results bit-identical to the serial oracle."""
     spec = cases.case(5, 16)
     m = global_mesh(spec)
     f = cases.synthetic_fields(spec, m)
@@ -85,12 +89,18 @@ def test_serial_bitwise():
     ctx.stage(f["deltaT"])
     ref = orc.stage(m, orc.mules_cfg(3), f["alpha_i"], f["alpha_b"], f["alphaBc"], f["sigma"], f["T_i"], f["T_b"],
                     f["phi_i"], f["phi_b"], f["phiAlpha_i"], f["phiAlpha_b"], f["deltaT"])
-    Fi, _ = ctx.get_force()
-    ndiff = int((Fi != ref["F_i"]).sum())
+    ndiff = 0
     for p in range(spec.nPhases):
         ai, _ = ctx.get_alpha(p)
-        ndiff += int((ai != ref["alpha_i"][p]).sum())
-    assert ndiff == 0, f"{ndiff} values differ in the last bit(s)"
+        pi, _ = ctx.get_phi_alpha(p)
+        ndiff += int((ai != ref["alpha_i"][p]).sum()) + int((pi != ref["alphaPhi_i"][p]).sum())
+    assert ndiff == 0, f"{ndiff} MULES values differ in the last bit(s)"
+    # the force kernels trade the reference's per-component divisions for one reciprocal per cell and
+    # contract multiply-adds (TCIF_FORCE_EXACT=0, tcif_device.cuh): a few ulp, not bit-identical
+    Fi, _ = ctx.get_force()
+    assert_field_close(Fi, ref["F_i"], "force", rtol=1e-14)
+    if "exact" in abi.version():
+        assert int((Fi != ref["F_i"]).sum()) == 0
     ctx.close()
 
 

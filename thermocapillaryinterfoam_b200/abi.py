@@ -14,7 +14,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtcif.so")
+# TCIF_LIB: alternative build of the same library (kernel-tuning experiments only)
+LIB_PATH = os.environ.get("TCIF_LIB") or os.path.join(_HERE, "libtcif.so")
 
 PATCH_GENERIC, PATCH_EMPTY, PATCH_WEDGE, PATCH_PROCESSOR = 0, 1, 2, 3
 BC_ZERO_GRADIENT, BC_FIXED_VALUE = 0, 1

@@ -6,6 +6,7 @@
 //   multiphaseSystem::solveAlphas() MULES  /root/reference/phasesSystem/multiphaseSystem/multiphaseSystem.C:296-375
 // There is no CPU fallback: every entry point needs a CUDA device.
 #include "tcif_device.cuh"
+#include "tcif_volume.cuh"
 #include "../../include/tcif.h"
 
 #include <dlfcn.h>
@@ -18,6 +19,7 @@
 #include <mutex>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 using namespace tcif;
@@ -118,6 +120,11 @@ struct tcif_ctx {
     std::string err;
     int device = 0;
     cudaStream_t ownStream = nullptr, stream = nullptr;
+    // O(surface) work (halo exchange + boundary-cell kernels) runs on `side`, concurrently with the
+    // O(volume) sweep on `stream`; evV/evB order the two (see sweep()).
+    cudaStream_t side = nullptr;
+    cudaEvent_t evV = nullptr, evB = nullptr;
+    bool noOverlap = false;
     // host copy of the small mesh tables
     int nC = 0, nIF = 0, nBF = 0, nPatches = 0, stride = 0, Ko = 0, Kn = 0, nBndCells = 0, nCoupled = 0;
     size_t nFd = 0;
@@ -191,21 +198,37 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
-template <class F> void timed(tcif_ctx *c, int id, double bytes, F &&launch) {
+template <class F> void timed_on(tcif_ctx *c, cudaStream_t st, int id, double bytes, F &&launch) {
     if (c->timersOn) {
         EvPair e;
         if (!c->evPool.empty()) { e = c->evPool.back(); c->evPool.pop_back(); }
         else { CUDA_OK(cudaEventCreate(&e.a)); CUDA_OK(cudaEventCreate(&e.b)); }
         e.id = id; e.bytes = bytes;
-        CUDA_OK(cudaEventRecord(e.a, c->stream));
+        CUDA_OK(cudaEventRecord(e.a, st));
         launch();
-        CUDA_OK(cudaEventRecord(e.b, c->stream));
+        CUDA_OK(cudaEventRecord(e.b, st));
         c->evs.push_back(e);
     } else launch();
     CUDA_OK(cudaGetLastError());
 }
+template <class F> void timed(tcif_ctx *c, int id, double bytes, F &&launch) { timed_on(c, c->stream, id, bytes, launch); }
+
+// One sweep of the path = an O(volume) kernel over the interior cells on the main stream and, on the
+// side stream, the halo exchange it does NOT need plus the O(surface) kernel over the boundary-adjacent
+// cells (which consumes the halo).  Sweep k's volume kernel reads sweep k-1's boundary results and
+// vice versa, hence the two events; the exchange and the boundary kernel hide behind the volume kernel.
+template <class FV, class FB> void sweep(tcif_ctx *c, FV &&volume, FB &&boundary) {
+    CUDA_OK(cudaEventRecord(c->evV, c->stream));
+    CUDA_OK(cudaStreamWaitEvent(c->side, c->evV, 0));
+    CUDA_OK(cudaStreamWaitEvent(c->stream, c->evB, 0));
+    volume();
+    boundary();
+    CUDA_OK(cudaEventRecord(c->evB, c->side));
+}
+void join(tcif_ctx *c) { CUDA_OK(cudaStreamWaitEvent(c->stream, c->evB, 0)); }
 
 void timers_collect(tcif_ctx *c) {
+    join(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     for (auto &e : c->evs) {
         float ms = 0.f;
@@ -235,6 +258,8 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
     int Ko = 0, Kn = 0;
     for (int i = 0; i < nC; ++i) { Ko = std::max(Ko, cntO[i]); Kn = std::max(Kn, cntN[i]); }
     Ko = std::max(Ko, 1); Kn = std::max(Kn, 1);
+    // fixed-K kernels (tcif_volume.cuh) want Ko == Kn == K in {2,3,4}: pad the smaller side
+    { int K = std::max(Ko, Kn); if (K <= 4) { K = std::max(K, 2); Ko = Kn = K; } }
     c->Ko = Ko; c->Kn = Kn;
     c->nFd = (size_t)Ko * stride;
     if ((size_t)std::max(Ko, Kn) * stride > 0x7fffffffULL) failf("tcif_create: mesh too large for int32 face slots");
@@ -296,6 +321,9 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
     bndStart.push_back(nBF);
     c->nBndCells = (int)bndCells.size();
     d.nBndCells = c->nBndCells; d.nCoupled = c->nCoupled;
+    std::vector<unsigned> mask((size_t)stride / 32, 0u);
+    for (int bc : bndCells) mask[bc >> 5] |= 1u << (bc & 31);
+    d.bndMask = c->upload(mask);
     d.bndCells = c->upload(bndCells); d.bndCellStart = c->upload(bndStart); d.bndFaces = c->upload(order);
     d.faceCells = c->upload(fc); d.bfPatch = c->upload(bfPatch); d.bfType = c->upload(bfType);
     std::vector<double> bx(nBF), by(nBF), bz(nBF), mag(nBF), dc(nBF), wb(nBF);
@@ -394,10 +422,10 @@ void ensure_deltaN(tcif_ctx *c) {
 
 // ---- processor-patch exchange -----------------------------------------------------------
 // send buffer (patch-major) -> neighbour ranks -> recv buffer.
-void exchange(tcif_ctx *c, int ncomp) {
+void exchange(tcif_ctx *c, int ncomp, cudaStream_t st) {
     if (c->group) {
         tcif_group *g = c->group;
-        CUDA_OK(cudaStreamSynchronize(c->stream));
+        CUDA_OK(cudaStreamSynchronize(st));
         g->barrier();
         for (size_t i = 0; i < c->cpPatch.size(); ++i) {
             int p = c->cpPatch[i], e = c->patchNbr[p], n = c->patchSize[p];
@@ -408,23 +436,24 @@ void exchange(tcif_ctx *c, int ncomp) {
                 if (o->patchNbr[o->cpPatch[j]] == c->rank) { peerOff = o->cpOff[j]; if (o->patchSize[o->cpPatch[j]] != n) failf("processor patch size mismatch"); break; }
             if (peerOff < 0) failf("rank %d has no patch facing rank %d", e, c->rank);
             CUDA_OK(cudaMemcpyAsync(c->recvBuf + (size_t)c->cpOff[i] * ncomp, o->sendBuf + (size_t)peerOff * ncomp,
-                                    sizeof(double) * (size_t)n * ncomp, cudaMemcpyDeviceToDevice, c->stream));
+                                    sizeof(double) * (size_t)n * ncomp, cudaMemcpyDeviceToDevice, st));
         }
-        CUDA_OK(cudaStreamSynchronize(c->stream));
+        CUDA_OK(cudaStreamSynchronize(st));
         g->barrier();
     } else if (c->nccl) {
         NCCL_OK(g_nccl.GroupStart());
         for (size_t i = 0; i < c->cpPatch.size(); ++i) {
             int p = c->cpPatch[i], e = c->patchNbr[p], n = c->patchSize[p];
-            NCCL_OK(g_nccl.Send(c->sendBuf + (size_t)c->cpOff[i] * ncomp, (size_t)n * ncomp, kNcclDouble, e, c->nccl, c->stream));
-            NCCL_OK(g_nccl.Recv(c->recvBuf + (size_t)c->cpOff[i] * ncomp, (size_t)n * ncomp, kNcclDouble, e, c->nccl, c->stream));
+            NCCL_OK(g_nccl.Send(c->sendBuf + (size_t)c->cpOff[i] * ncomp, (size_t)n * ncomp, kNcclDouble, e, c->nccl, st));
+            NCCL_OK(g_nccl.Recv(c->recvBuf + (size_t)c->cpOff[i] * ncomp, (size_t)n * ncomp, kNcclDouble, e, c->nccl, st));
         }
         NCCL_OK(g_nccl.GroupEnd());
     } else failf("exchange without communicator");
 }
 
 // processorFvPatchField::evaluate for ncomp cell arrays at once: dst[d][bf] := neighbour-rank src[d][faceCell]
-void halo_cells(tcif_ctx *c, int ncomp, const double *const *src, double *const *dst) {
+void halo_cells(tcif_ctx *c, int ncomp, const double *const *src, double *const *dst, cudaStream_t st = nullptr) {
+    if (!st) st = c->stream;
     if (c->nCoupled == 0) return;
     require_comm(c);
     if ((size_t)ncomp * c->nCoupled > c->haloDoubles || ncomp > 36) failf("halo_cells: too many components");
@@ -432,22 +461,23 @@ void halo_cells(tcif_ctx *c, int ncomp, const double *const *src, double *const 
     h.ncomp = ncomp;
     for (int d = 0; d < ncomp; ++d) { h.src[d] = src[d]; h.dst[d] = dst[d]; }
     double bytes = 16.0 * ncomp * c->nCoupled;
-    timed(c, T_HALO, bytes, [&] {
-        k_halo_pack<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, h, c->sendBuf);
+    timed_on(c, st, T_HALO, bytes, [&] {
+        k_halo_pack<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, st>>>(c->dm, h, c->sendBuf);
         c->launches++;
-        exchange(c, ncomp);
-        k_halo_unpack<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, h, c->recvBuf);
+        exchange(c, ncomp, st);
+        k_halo_unpack<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, st>>>(c->dm, h, c->recvBuf);
         c->launches++;
     });
 }
 
 // ---- kernel dispatch ----------------------------------------------------------------------
-int kshape(const tcif_ctx *c) { return (c->Ko == 3 && c->Kn == 3) ? 3 : (c->Ko == 2 && c->Kn == 2) ? 2 : 0; }
+int kshape(const tcif_ctx *c) { return (c->Ko == c->Kn && c->Ko >= 2 && c->Ko <= 4) ? c->Ko : 0; }
 
 #define DISPATCH_K(...)                                      \
     switch (kshape(c)) {                                     \
         case 3: { constexpr int KO = 3, KN = 3; (void)KO; (void)KN; __VA_ARGS__; } break; \
         case 2: { constexpr int KO = 2, KN = 2; (void)KO; (void)KN; __VA_ARGS__; } break; \
+        case 4: { constexpr int KO = 4, KN = 4; (void)KO; (void)KN; __VA_ARGS__; } break; \
         default: { constexpr int KO = 0, KN = 0; (void)KO; (void)KN; __VA_ARGS__; } break; \
     }
 #define DISPATCH_P(...)                                      \
@@ -467,18 +497,39 @@ ForceArgs force_args(tcif_ctx *c, bool withTensor, bool withG) {
     return a;
 }
 
+// volume sweeps (BND == false): fixed-K kernels of tcif_volume.cuh, generic-K fallback otherwise
+#define DISPATCH_KV(NEW, OLD)                                  \
+    switch (kshape(c)) {                                       \
+        case 2: { constexpr int K = 2; NEW; } break;           \
+        case 3: { constexpr int K = 3; NEW; } break;           \
+        case 4: { constexpr int K = 4; NEW; } break;           \
+        default: { OLD; } break;                               \
+    }
+
 template <bool BND, bool WG> void launch_grad_tensor(tcif_ctx *c, const ForceArgs &a) {
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    int grid = cdiv(n, TCIF_TPB);
-    DISPATCH_P(DISPATCH_K(k_grad_tensor<PP, KO, KN, BND, WG><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, a)));
+    if constexpr (!BND) {
+        int gv = cdiv(n, TCIF_TPB_FORCE), go = cdiv(n, TCIF_TPB);
+        DISPATCH_P(DISPATCH_KV((kv_grad_tensor<PP, K><<<gv, TCIF_TPB_FORCE, 0, c->stream>>>(c->dm, a)),
+                               (k_grad_tensor<PP, 0, 0, false, WG><<<go, TCIF_TPB, 0, c->stream>>>(c->dm, a))));
+    } else {
+        int grid = cdiv(n, TCIF_TPB);
+        DISPATCH_P(DISPATCH_K(k_grad_tensor<PP, KO, KN, true, WG><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, a)));
+    }
     c->launches++;
 }
 template <bool BND> void launch_div_tensor(tcif_ctx *c, const ForceArgs &a) {
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    int grid = cdiv(n, TCIF_TPB);
-    DISPATCH_P(DISPATCH_K(k_div_tensor<PP, KO, KN, BND><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, a)));
+    if constexpr (!BND) {
+        int gv = cdiv(n, TCIF_TPB_FORCE), go = cdiv(n, TCIF_TPB);
+        DISPATCH_P(DISPATCH_KV((kv_div_tensor<PP, K><<<gv, TCIF_TPB_FORCE, 0, c->stream>>>(c->dm, a)),
+                               (k_div_tensor<PP, 0, 0, false><<<go, TCIF_TPB, 0, c->stream>>>(c->dm, a))));
+    } else {
+        int grid = cdiv(n, TCIF_TPB);
+        DISPATCH_P(DISPATCH_K(k_div_tensor<PP, KO, KN, true><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, a)));
+    }
     c->launches++;
 }
 
@@ -514,15 +565,18 @@ void do_force(tcif_ctx *c) {
     require_comm(c);
     ensure_deltaN(c);
     ForceArgs a = force_args(c, true, false);
-    timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, true, false), [&] { launch_grad_tensor<false, false>(c, a); });
-    timed(c, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, false>(c, a); });
-    if (c->nCoupled) {
-        const double *src[36]; double *dst[36];
-        for (int k = 0; k < c->Q * 6; ++k) { src[k] = c->Tq + (size_t)k * c->stride; dst[k] = c->TqHalo + (size_t)k * std::max(c->nBF, 1); }
-        halo_cells(c, c->Q * 6, src, dst);
-    }
-    timed(c, T_DIV_TENSOR, bytes_div_tensor(c), [&] { launch_div_tensor<false>(c, a); });
-    timed(c, T_BOUNDARY, 0, [&] { launch_div_tensor<true>(c, a); });
+    sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, true, false), [&] { launch_grad_tensor<false, false>(c, a); }); },
+             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, false>(c, a); }); });
+    sweep(c, [&] { timed(c, T_DIV_TENSOR, bytes_div_tensor(c), [&] { launch_div_tensor<false>(c, a); }); },
+             [&] {
+                 if (c->nCoupled) {      // neighbour-rank tensors of the processor faces: hidden behind the volume sweep
+                     const double *src[36]; double *dst[36];
+                     for (int k = 0; k < c->Q * 6; ++k) { src[k] = c->Tq + (size_t)k * c->stride; dst[k] = c->TqHalo + (size_t)k * std::max(c->nBF, 1); }
+                     halo_cells(c, c->Q * 6, src, dst, c->side);
+                 }
+                 timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_div_tensor<true>(c, a); });
+             });
+    join(c);
     if (c->nBF) {
         timed(c, T_BOUNDARY, 0, [&] {
             k_extrapolate_bnd<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, 3, (size_t)c->stride, c->F, c->Fb);
@@ -541,8 +595,9 @@ void do_grad(tcif_ctx *c) {
     require_comm(c);
     if (!c->G) { c->G = c->dalloc<double>((size_t)c->P * 3 * c->stride); c->Gb = c->dalloc<double>((size_t)c->P * 3 * std::max(c->nBF, 1)); }
     ForceArgs a = force_args(c, false, true);
-    timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, false, true), [&] { launch_grad_tensor<false, true>(c, a); });
-    timed(c, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, a); });
+    sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, false, true), [&] { launch_grad_tensor<false, true>(c, a); }); },
+             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, a); }); });
+    join(c);
     if (!c->nBF) return;
     for (int p = 0; p < c->P; ++p) {
         double *gi = c->G + (size_t)p * 3 * c->stride, *gb = c->Gb + (size_t)p * 3 * c->nBF;
@@ -604,21 +659,46 @@ template <bool BND> void launch_setup(tcif_ctx *c, const MulesBatch &b, const Mu
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
     int grid = cdiv(n, TCIF_TPB) * b.nPh;
-    DISPATCH_K(k_mules_setup<KO, KN, BND><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm));
+    if constexpr (!BND) {
+        DISPATCH_KV((kv_mules_setup<K><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)),
+                    (k_mules_setup<0, 0, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)));
+    } else {
+        DISPATCH_K(k_mules_setup<KO, KN, true><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, b, prm));
+    }
     c->launches++;
 }
 template <bool BND> void launch_iter(tcif_ctx *c, const MulesBatch &b, int first, int flip) {
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
     int grid = cdiv(n, TCIF_TPB) * b.nPh;
-    DISPATCH_K(k_mules_iter<KO, KN, BND><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, first, flip));
+    if constexpr (!BND) {
+        if (first) {
+            DISPATCH_KV((kv_mules_iter<K, true><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, flip)),
+                        (k_mules_iter<0, 0, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, first, flip)));
+        } else {
+            DISPATCH_KV((kv_mules_iter<K, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, flip)),
+                        (k_mules_iter<0, 0, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, first, flip)));
+        }
+    } else {
+        DISPATCH_K(k_mules_iter<KO, KN, true><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, b, first, flip));
+    }
     c->launches++;
 }
 template <bool BND, int MODE> void launch_final(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm, int first, int flip, int nIter) {
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
     int grid = cdiv(n, TCIF_TPB) * b.nPh;
-    DISPATCH_K(k_mules_final<KO, KN, BND, MODE><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, first, flip, nIter));
+    if constexpr (!BND) {
+        if (first) {
+            DISPATCH_KV((kv_mules_final<K, MODE, true><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter)),
+                        (k_mules_final<0, 0, false, MODE><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, first, flip, nIter)));
+        } else {
+            DISPATCH_KV((kv_mules_final<K, MODE, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter)),
+                        (k_mules_final<0, 0, false, MODE><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, first, flip, nIter)));
+        }
+    } else {
+        DISPATCH_K(k_mules_final<KO, KN, true, MODE><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, b, prm, first, flip, nIter));
+    }
     c->launches++;
 }
 
@@ -629,7 +709,7 @@ void halo_lambda(tcif_ctx *c, const MulesBatch &b, int flip) {
         src[2 * k] = flip ? b.ph[k].lpB : b.ph[k].lpA; dst[2 * k] = b.ph[k].lpHalo;
         src[2 * k + 1] = flip ? b.ph[k].lmB : b.ph[k].lmA; dst[2 * k + 1] = b.ph[k].lmHalo;
     }
-    halo_cells(c, 2 * b.nPh, src, dst);
+    halo_cells(c, 2 * b.nPh, src, dst, c->side);
 }
 
 // MULES::limit for a batch of phases.  mode 0: returnCorr=true; 1: returnCorr=false;
@@ -643,28 +723,29 @@ void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode,
     prm.boundaryExtrema = c->cfg.boundaryExtrema; prm.addUpwind = addUpwind ? 1 : 0;
     prm.phi = c->phi; prm.phib = c->phib;
     const int L = c->cfg.nLimiterIter;
-    timed(c, T_MULES_SETUP, bytes_mules_setup(c, nPh), [&] { launch_setup<false>(c, b, prm); });
-    timed(c, T_BOUNDARY, 0, [&] { launch_setup<true>(c, b, prm); });
+    sweep(c, [&] { timed(c, T_MULES_SETUP, bytes_mules_setup(c, nPh), [&] { launch_setup<false>(c, b, prm); }); },
+             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_setup<true>(c, b, prm); }); });
     int first = 1, flip = 0;
     for (int j = 1; j < L; ++j) {
-        halo_lambda(c, b, flip);
-        timed(c, T_MULES_ITER, bytes_mules_iter(c, nPh, first), [&] { launch_iter<false>(c, b, first, flip); });
-        timed(c, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b, first, flip); });
+        sweep(c, [&] { timed(c, T_MULES_ITER, bytes_mules_iter(c, nPh, first), [&] { launch_iter<false>(c, b, first, flip); }); },
+                 [&] { halo_lambda(c, b, flip);      // syncTools::syncFaceList(min) of the previous iteration
+                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b, first, flip); }); });
         flip ^= 1; first = 0;
     }
-    if (L > 0) halo_lambda(c, b, flip);
     double fb = bytes_mules_final(c, nPh, mode, first);
-    if (mode == 0) {
-        timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, 0>(c, b, prm, first, flip, L); });
-        timed(c, T_BOUNDARY, 0, [&] { launch_final<true, 0>(c, b, prm, first, flip, L); });
-    } else if (mode == 1) {
-        timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, 1>(c, b, prm, first, flip, L); });
-        timed(c, T_BOUNDARY, 0, [&] { launch_final<true, 1>(c, b, prm, first, flip, L); });
-    } else {
-        timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, 2>(c, b, prm, first, flip, L); });
-        timed(c, T_BOUNDARY, 0, [&] { launch_final<true, 2>(c, b, prm, first, flip, L); });
+    auto fin = [&](auto modeTag) {
+        constexpr int MODE = decltype(modeTag)::value;
+        sweep(c, [&] { timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, MODE>(c, b, prm, first, flip, L); }); },
+                 [&] { if (L > 0) halo_lambda(c, b, flip);
+                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_final<true, MODE>(c, b, prm, first, flip, L); }); });
+    };
+    if (mode == 0) fin(std::integral_constant<int, 0>{});
+    else if (mode == 1) fin(std::integral_constant<int, 1>{});
+    else {
+        fin(std::integral_constant<int, 2>{});
         for (int k = 0; k < nPh; ++k) std::swap(c->alpha[phases[k]], c->alphaNew[phases[k]]);
     }
+    join(c);
 }
 
 void do_limit_sum(tcif_ctx *c) {
@@ -767,7 +848,13 @@ int pair_index(int P, int p1, int p2) {
 
 extern "C" {
 
-const char *tcif_version(void) { return "tcif 0.1 (sm_100a, fp64, fmad=off)"; }
+const char *tcif_version(void) {
+#if TCIF_FORCE_EXACT
+    return "tcif 0.2 (sm_100a, fp64, fmad=off, force kernels exact)";
+#else
+    return "tcif 0.2 (sm_100a, fp64, MULES fmad=off, force kernels reciprocal+fma)";
+#endif
+}
 
 int tcif_device_count(void) {
     int n = 0;
@@ -799,6 +886,16 @@ int tcif_create(const tcif_mesh_desc *mesh, const tcif_config *cfg, tcif_ctx **o
         if (prop.major < 10) failf("tcif_create: device %d is sm_%d%d; this build targets sm_100a only", c->device, prop.major, prop.minor);
         CUDA_OK(cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking));
         c->stream = c->ownStream;
+        {
+            int lo = 0, hi = 0;
+            CUDA_OK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            // TCIF_NO_OVERLAP=1 (profiling aid): surface work runs on the main stream, in sequence
+            const char *no = getenv("TCIF_NO_OVERLAP");
+            if (no && no[0] == '1') { c->side = c->ownStream; c->noOverlap = true; }
+            else CUDA_OK(cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, hi));   // surface work first
+            CUDA_OK(cudaEventCreateWithFlags(&c->evV, cudaEventDisableTiming));
+            CUDA_OK(cudaEventCreateWithFlags(&c->evB, cudaEventDisableTiming));
+        }
         c->P = cfg->nPhases; c->Q = c->P * (c->P - 1) / 2;
         build_mesh(c, mesh);
         alloc_fields(c);
@@ -817,6 +914,7 @@ int tcif_create(const tcif_mesh_desc *mesh, const tcif_config *cfg, tcif_ctx **o
 void tcif_destroy(tcif_ctx *c) {
     if (!c) return;
     DeviceGuard guard(c->device);
+    if (c->side) cudaStreamSynchronize(c->side);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->nccl && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl);
     if (c->group) { std::lock_guard<std::mutex> lk(c->group->mu); if (c->rank < (int)c->group->members.size()) c->group->members[c->rank] = nullptr; }
@@ -824,19 +922,25 @@ void tcif_destroy(tcif_ctx *c) {
     for (auto &e : c->evPool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (void *p : c->allocs) cudaFree(p);
     if (c->h_small) cudaFreeHost(c->h_small);
+    if (c->evV) cudaEventDestroy(c->evV);
+    if (c->evB) cudaEventDestroy(c->evB);
+    if (c->side && !c->noOverlap) cudaStreamDestroy(c->side);
     if (c->ownStream) cudaStreamDestroy(c->ownStream);
     delete c;
 }
 
 int tcif_set_stream(tcif_ctx *c, void *s) {
     API_BEGIN(c)
+    join(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     c->stream = s ? (cudaStream_t)s : c->ownStream;
+    if (c->noOverlap) c->side = c->stream;
     API_END(c)
 }
 
 int tcif_synchronize(tcif_ctx *c) {
     API_BEGIN(c)
+    join(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END(c)
 }

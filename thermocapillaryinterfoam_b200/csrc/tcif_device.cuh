@@ -24,7 +24,27 @@
 #define TCIF_VSMALL 1e-300
 #define TCIF_ROOTVSMALL 1e-150
 
+// Force kernels (grad/tensor/div): TCIF_FORCE_EXACT=1 keeps the reference's operation sequence (true
+// divisions, separate multiply/add) and is bit-identical to the serial oracle; the default (0) divides
+// once per cell / pair (x * (1/V) instead of x / V) and contracts multiply-add chains with explicit
+// fma(): the first ncu capture showed these two kernels instruction-issue bound (FP64 divisions are
+// ~35 instructions each), and the change is <= a few ulp per operation, far inside the 1e-12 contract.
+// The MULES kernels always keep the exact sequence (-fmad=false).
+#ifndef TCIF_FORCE_EXACT
+#define TCIF_FORCE_EXACT 0
+#endif
+
 namespace tcif {
+
+#if TCIF_FORCE_EXACT
+__device__ __forceinline__ double f_rcp(double x) { return x; }                 // "reciprocal" kept as divisor
+__device__ __forceinline__ double f_div(double a, double r) { return a / r; }
+__device__ __forceinline__ double f_mad(double a, double b, double c) { return a * b + c; }
+#else
+__device__ __forceinline__ double f_rcp(double x) { return 1.0 / x; }
+__device__ __forceinline__ double f_div(double a, double r) { return a * r; }
+__device__ __forceinline__ double f_mad(double a, double b, double c) { return fma(a, b, c); }
+#endif
 
 enum { PATCH_GENERIC = 0, PATCH_EMPTY = 1, PATCH_WEDGE = 2, PATCH_PROCESSOR = 3 };
 enum { BC_ZERO_GRADIENT = 0, BC_FIXED_VALUE = 1 };
@@ -39,6 +59,7 @@ struct DMesh {
     const int *neiFace;     // [Kn*stride] device face index of the k-th neighbour-side face (-1: none)
     const double *Sfx, *Sfy, *Sfz, *w;   // [Ko*stride]
     const double *V;        // [nC]
+    const unsigned *bndMask;// [stride/32] bit c: cell c owns >=1 boundary face (volume sweeps skip it)
     const int *bndCells;    // [nBndCells] ascending cell ids owning >=1 boundary face
     const int *bndCellStart;// [nBndCells+1]
     const int *bndFaces;    // boundary face ids grouped by cell, ascending
@@ -50,6 +71,8 @@ struct DMesh {
     const int *coupledOff;  // [nCoupled] offset (in coupled-face units) of the face's processor patch
     const int *coupledSize; // [nCoupled] size of the face's processor patch
 };
+
+__device__ __forceinline__ bool is_bnd_cell(const DMesh &m, int c) { return (m.bndMask[c >> 5] >> (c & 31)) & 1u; }
 
 __device__ __forceinline__ int owner_of(const DMesh &m, int fd) {
     int o = fd;
@@ -108,8 +131,8 @@ __device__ __forceinline__ void pair_tensor(double a1, double a2, const double *
     double gy = a2 * g1[1] - a1 * g2[1];
     double gz = a2 * g1[2] - a1 * g2[2];
     double mg = sqrt(gx * gx + gy * gy + gz * gz);
-    double den = mg + deltaN;
-    double nx = gx / den, ny = gy / den, nz = gz / den;
+    double rden = f_rcp(mg + deltaN);
+    double nx = f_div(gx, rden), ny = f_div(gy, rden), nz = f_div(gz, rden);
     double tm = 2.0 * mg;
     T6[0] = tm * (sigma * (1.0 - nx * nx));
     T6[1] = tm * (sigma * (0.0 - nx * ny));
@@ -125,7 +148,7 @@ k_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     int c;
     if (BND) { if (i >= m.nBndCells) return; c = m.bndCells[i]; }
-    else     { if (i >= m.nC) return; c = i; }
+    else     { if (i >= m.nC) return; c = i; if (is_bnd_cell(m, c)) return; }
     double aS[P], g[P][3];
 #pragma unroll
     for (int p = 0; p < P; ++p) { aS[p] = a.alpha[p][c]; g[p][0] = g[p][1] = g[p][2] = 0.0; }
@@ -139,8 +162,8 @@ k_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
 #pragma unroll
             for (int p = 0; p < P; ++p) {
                 double aP = a.alpha[p][o], aN = aS[p];
-                double af = w * (aP - aN) + aN;
-                g[p][0] -= sx * af; g[p][1] -= sy * af; g[p][2] -= sz * af;
+                double af = f_mad(w, aP - aN, aN);
+                g[p][0] = f_mad(-sx, af, g[p][0]); g[p][1] = f_mad(-sy, af, g[p][1]); g[p][2] = f_mad(-sz, af, g[p][2]);
             }
         }
     }
@@ -153,8 +176,8 @@ k_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
 #pragma unroll
             for (int p = 0; p < P; ++p) {
                 double aP = aS[p], aN = a.alpha[p][n];
-                double af = w * (aP - aN) + aN;
-                g[p][0] += sx * af; g[p][1] += sy * af; g[p][2] += sz * af;
+                double af = f_mad(w, aP - aN, aN);
+                g[p][0] = f_mad(sx, af, g[p][0]); g[p][1] = f_mad(sy, af, g[p][1]); g[p][2] = f_mad(sz, af, g[p][2]);
             }
         }
     }
@@ -171,9 +194,9 @@ k_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
             }
         }
     }
-    double V = m.V[c];
+    double rV = f_rcp(m.V[c]);
 #pragma unroll
-    for (int p = 0; p < P; ++p) { g[p][0] /= V; g[p][1] /= V; g[p][2] /= V; }
+    for (int p = 0; p < P; ++p) { g[p][0] = f_div(g[p][0], rV); g[p][1] = f_div(g[p][1], rV); g[p][2] = f_div(g[p][2], rV); }
     if (BND) {
 #pragma unroll
         for (int p = 0; p < P; ++p)
@@ -207,10 +230,10 @@ __device__ __forceinline__ void face_div_acc(double w, double sx, double sy, dou
                                              const double *TP, const double *TN, double sgn, double *acc) {
     double t[6];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) t[k] = w * (TP[k] - TN[k]) + TN[k];
-    double fx = sx * t[0] + sy * t[1] + sz * t[2];
-    double fy = sx * t[1] + sy * t[3] + sz * t[4];
-    double fz = sx * t[2] + sy * t[4] + sz * t[5];
+    for (int k = 0; k < 6; ++k) t[k] = f_mad(w, TP[k] - TN[k], TN[k]);
+    double fx = f_mad(sz, t[2], f_mad(sy, t[1], sx * t[0]));
+    double fy = f_mad(sz, t[4], f_mad(sy, t[3], sx * t[1]));
+    double fz = f_mad(sz, t[5], f_mad(sy, t[4], sx * t[2]));
     if (sgn > 0) { acc[0] += fx; acc[1] += fy; acc[2] += fz; }
     else         { acc[0] -= fx; acc[1] -= fy; acc[2] -= fz; }
 }
@@ -222,9 +245,9 @@ k_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs 
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     int c;
     if (BND) { if (i >= m.nBndCells) return; c = m.bndCells[i]; }
-    else     { if (i >= m.nC) return; c = i; }
+    else     { if (i >= m.nC) return; c = i; if (is_bnd_cell(m, c)) return; }
     const int kn = KN ? KN : m.Kn, ko = KO ? KO : m.Ko;
-    double V = m.V[c];
+    double rV = f_rcp(m.V[c]);
     double F[3] = {0.0, 0.0, 0.0};
 #pragma unroll 1
     for (int q = 0; q < Q; ++q) {
@@ -294,7 +317,7 @@ k_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs 
                 acc[2] += sx * t[2] + sy * t[4] + sz * t[5];
             }
         }
-        F[0] += acc[0] / V; F[1] += acc[1] / V; F[2] += acc[2] / V;
+        F[0] += f_div(acc[0], rV); F[1] += f_div(acc[1], rV); F[2] += f_div(acc[2], rV);
     }
     a.F[c] = F[0]; a.F[(size_t)m.stride + c] = F[1]; a.F[(size_t)2 * m.stride + c] = F[2];
 }
@@ -342,7 +365,7 @@ k_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatc
     const MulesPh &ph = b.ph[p];
     int c;
     if (BND) { if (i >= m.nBndCells) return; c = m.bndCells[i]; }
-    else     { if (i >= m.nC) return; c = i; }
+    else     { if (i >= m.nC) return; c = i; if (is_bnd_cell(m, c)) return; }
     const int kn = KN ? KN : m.Kn, ko = KO ? KO : m.Ko;
     const double psiC = ph.psi[c];
     double psiMaxn = prm.psiMin, psiMinn = prm.psiMax, sBD = 0.0, sP = 0.0, sM = 0.0;
@@ -448,7 +471,7 @@ k_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch
     const MulesPh &ph = b.ph[p];
     int c;
     if (BND) { if (i >= m.nBndCells) return; c = m.bndCells[i]; }
-    else     { if (i >= m.nC) return; c = i; }
+    else     { if (i >= m.nC) return; c = i; if (is_bnd_cell(m, c)) return; }
     const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
     double *lpOut = flip ? ph.lpA : ph.lpB, *lmOut = flip ? ph.lmA : ph.lmB;
     const double *lamIn = flip ? ph.lamB : ph.lamA;
@@ -508,7 +531,7 @@ k_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatc
     const MulesPh &ph = b.ph[p];
     int c;
     if (BND) { if (i >= m.nBndCells) return; c = m.bndCells[i]; }
-    else     { if (i >= m.nC) return; c = i; }
+    else     { if (i >= m.nC) return; c = i; if (is_bnd_cell(m, c)) return; }
     const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
     const double *lamIn = flip ? ph.lamB : ph.lamA;
     const int kn = KN ? KN : m.Kn, ko = KO ? KO : m.Ko;

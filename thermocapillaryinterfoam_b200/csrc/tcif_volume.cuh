@@ -1,0 +1,345 @@
+// tcif_volume.cuh -- the O(volume) sweeps for meshes with a compile-time slot count K (2: one-cell-
+// thick hex, 3: hex, 4: tet/prism), restructured for memory-level parallelism.
+//
+// round-1 ncu (profiles/r01_ncu_full_n400_*.csv) showed the first versions of these kernels latency-
+// bound: ~80 % of warp stalls on long-scoreboard with 0.8 eligible warps per scheduler, because
+// every gather sat behind a branch on its index (`if (fd >= 0)`), which forbids hoisting the load.
+// Here every thread (1) loads all 2K slot indices, (2) turns padding (-1) into a safe in-range
+// address (its own slot), (3) issues ALL gathers unconditionally, and only then (4) runs the
+// reference's arithmetic under the original `valid` predicates -- same operations, same order, so
+// results stay bit-identical to the serial oracle.  Never-reused streams (Sf, w, Q+-, sums, outputs)
+// use evict-first loads/stores (__ldcs/__stcs) so that L2 keeps the arrays neighbours gather from.
+#pragma once
+#include "tcif_device.cuh"
+
+namespace tcif {
+
+template <int K>
+__device__ __forceinline__ int owner_of_k(int stride, int fd) {   // fd mod stride, fd < K*stride
+    int o = fd;
+#pragma unroll
+    for (int j = 1; j < K; ++j) o -= (fd >= j * stride) ? stride : 0;
+    return o;
+}
+
+#ifndef TCIF_TPB_FORCE
+#define TCIF_TPB_FORCE 128
+#endif
+#ifndef TCIF_MINB_FORCE
+#define TCIF_MINB_FORCE 3
+#endif
+// register caps chosen from the A/B runs in profiles/r01_variants.md
+#ifndef TCIF_MINB_SETUP
+#define TCIF_MINB_SETUP 4
+#endif
+#ifndef TCIF_MINB_ITER
+#define TCIF_MINB_ITER 4
+#endif
+#ifndef TCIF_MINB_FINAL
+#define TCIF_MINB_FINAL 3
+#endif
+
+// slot indices of cell c: neighbour-side faces (fdN, owner oN) and owner-side faces (neighbour nO)
+template <int K>
+struct Slots {
+    int fdN[K], oN[K], nO[K];
+    bool vN[K], vO[K];
+    __device__ __forceinline__ void load(const DMesh &m, int c) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) { fdN[k] = m.neiFace[k * m.stride + c]; nO[k] = m.nbrOwn[k * m.stride + c]; }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            vN[k] = fdN[k] >= 0; vO[k] = nO[k] >= 0;
+            fdN[k] = vN[k] ? fdN[k] : c;          // padding -> own slot 0 (in range, already cached)
+            oN[k] = owner_of_k<K>(m.stride, fdN[k]);
+            nO[k] = vO[k] ? nO[k] : c;
+        }
+    }
+};
+
+// ---- K1: grad(alpha_p) for all phases + capillary stress tensors of all pairs ---------------------
+template <int P, int K>
+__global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
+kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    Slots<K> s;
+    s.load(m, c);
+    double aS[P], aO[K][P], aN[K][P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) aS[p] = a.alpha[p][c];
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+#pragma unroll
+        for (int p = 0; p < P; ++p) { aO[k][p] = a.alpha[p][s.oN[k]]; aN[k][p] = a.alpha[p][s.nO[k]]; }
+    double wN[K], sxN[K], syN[K], szN[K], wO[K], sxO[K], syO[K], szO[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        const int fd = s.fdN[k], fo = k * m.stride + c;
+        wN[k] = m.w[fd]; sxN[k] = m.Sfx[fd]; syN[k] = m.Sfy[fd]; szN[k] = m.Sfz[fd];
+        wO[k] = __ldcs(m.w + fo); sxO[k] = __ldcs(m.Sfx + fo); syO[k] = __ldcs(m.Sfy + fo); szO[k] = __ldcs(m.Sfz + fo);
+    }
+    const double rV = f_rcp(m.V[c]);
+    const double Tc = a.T ? a.T[c] : 0.0;
+    double g[P][3];
+#pragma unroll
+    for (int p = 0; p < P; ++p) g[p][0] = g[p][1] = g[p][2] = 0.0;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (s.vN[k]) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                double af = f_mad(wN[k], aO[k][p] - aS[p], aS[p]);
+                g[p][0] = f_mad(-sxN[k], af, g[p][0]); g[p][1] = f_mad(-syN[k], af, g[p][1]); g[p][2] = f_mad(-szN[k], af, g[p][2]);
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (s.vO[k]) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                double af = f_mad(wO[k], aS[p] - aN[k][p], aN[k][p]);
+                g[p][0] = f_mad(sxO[k], af, g[p][0]); g[p][1] = f_mad(syO[k], af, g[p][1]); g[p][2] = f_mad(szO[k], af, g[p][2]);
+            }
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p) { g[p][0] = f_div(g[p][0], rV); g[p][1] = f_div(g[p][1], rV); g[p][2] = f_div(g[p][2], rV); }
+    if (a.G) {
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+#pragma unroll
+            for (int d = 0; d < 3; ++d) a.G[(size_t)(p * 3 + d) * m.stride + c] = g[p][d];
+    }
+    if (a.Tq) {
+        int q = 0;
+#pragma unroll
+        for (int p1 = 0; p1 < P; ++p1)
+#pragma unroll
+            for (int p2 = p1 + 1; p2 < P; ++p2, ++q) {
+                double T6[6];
+                double sg = sigma_eval(a.sig[q], Tc);
+                pair_tensor(aS[p1], aS[p2], g[p1], g[p2], sg, a.deltaN, T6);
+#pragma unroll
+                for (int k = 0; k < 6; ++k) a.Tq[(size_t)(q * 6 + k) * m.stride + c] = T6[k];
+            }
+    }
+}
+
+// ---- K2: F = sum_q div(T_q) ---------------------------------------------------------------------------
+template <int P, int K>
+__global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
+kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
+    constexpr int Q = P * (P - 1) / 2;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    Slots<K> s;
+    s.load(m, c);
+    double wN[K], sxN[K], syN[K], szN[K], wO[K], sxO[K], syO[K], szO[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        const int fd = s.fdN[k], fo = k * m.stride + c;
+        wN[k] = m.w[fd]; sxN[k] = m.Sfx[fd]; syN[k] = m.Sfy[fd]; szN[k] = m.Sfz[fd];
+        wO[k] = __ldcs(m.w + fo); sxO[k] = __ldcs(m.Sfx + fo); syO[k] = __ldcs(m.Sfy + fo); szO[k] = __ldcs(m.Sfz + fo);
+    }
+    const double rV = f_rcp(m.V[c]);
+    double F[3] = {0.0, 0.0, 0.0};
+#pragma unroll 1
+    for (int q = 0; q < Q; ++q) {
+        const double *Tq = a.Tq + (size_t)q * 6 * m.stride;
+        double Ts[6], To[K][6], Tn[K][6];
+#pragma unroll
+        for (int kk = 0; kk < 6; ++kk) Ts[kk] = Tq[(size_t)kk * m.stride + c];
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+#pragma unroll
+            for (int kk = 0; kk < 6; ++kk) {
+                To[k][kk] = Tq[(size_t)kk * m.stride + s.oN[k]];
+                Tn[k][kk] = Tq[(size_t)kk * m.stride + s.nO[k]];
+            }
+        double acc[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+            if (s.vN[k]) face_div_acc(wN[k], sxN[k], syN[k], szN[k], To[k], Ts, -1.0, acc);
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+            if (s.vO[k]) face_div_acc(wO[k], sxO[k], syO[k], szO[k], Ts, Tn[k], 1.0, acc);
+        F[0] += f_div(acc[0], rV); F[1] += f_div(acc[1], rV); F[2] += f_div(acc[2], rV);
+    }
+    __stcs(a.F + c, F[0]); __stcs(a.F + (size_t)m.stride + c, F[1]); __stcs(a.F + (size_t)2 * m.stride + c, F[2]);
+}
+
+// ---- MULES set-up sweep (see k_mules_setup) ------------------------------------------------------------
+template <int K>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_SETUP)
+kv_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
+               const __grid_constant__ MulesParams prm) {
+    const int p = blockIdx.x % b.nPh;
+    const int c = (blockIdx.x / b.nPh) * blockDim.x + threadIdx.x;
+    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    const MulesPh &ph = b.ph[p];
+    Slots<K> s;
+    s.load(m, c);
+    const double psiC = ph.psi[c];
+    double psiO[K], phiN[K], ppN[K], psiN[K], phiO[K], ppO[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        const int fo = k * m.stride + c;
+        psiO[k] = ph.psi[s.oN[k]]; phiN[k] = prm.phi[s.fdN[k]]; ppN[k] = ph.phiIn[s.fdN[k]];
+        psiN[k] = ph.psi[s.nO[k]]; phiO[k] = prm.phi[fo]; ppO[k] = ph.phiIn[fo];
+    }
+    const double V = m.V[c], psi0 = __ldcs(ph.psi0 + c);
+    const double Su = ph.Su ? __ldcs(ph.Su + c) : 0.0, Sp = ph.Sp ? __ldcs(ph.Sp + c) : 0.0;
+    double psiMaxn = prm.psiMin, psiMinn = prm.psiMax, sBD = 0.0, sP = 0.0, sM = 0.0;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (s.vN[k]) {
+            double bd = upwind_flux(phiN[k], psiO[k], psiC);
+            double pp = ppN[k];
+            if (prm.addUpwind) pp = pp + bd;
+            double pc = pp - bd;
+            psiMaxn = dmax(psiMaxn, psiO[k]); psiMinn = dmin(psiMinn, psiO[k]);
+            sBD -= bd;
+            if (pc > 0) sM += pc; else sP -= pc;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (s.vO[k]) {
+            double bd = upwind_flux(phiO[k], psiC, psiN[k]);
+            double pp = ppO[k];
+            if (prm.addUpwind) pp = pp + bd;
+            double pc = pp - bd;
+            ph.phiCorr[k * m.stride + c] = pc;
+            psiMaxn = dmax(psiMaxn, psiN[k]); psiMinn = dmin(psiMinn, psiN[k]);
+            sBD += bd;
+            if (pc > 0) sP += pc; else sM -= pc;
+        }
+    }
+    psiMaxn = dmin(psiMaxn + prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMax);
+    psiMinn = dmax(psiMinn - prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMin);
+    if (prm.smoothLimiter > TCIF_SMALL) {
+        double sl = prm.smoothLimiter;
+        psiMaxn = dmin(sl * psiC + (1.0 - sl) * psiMaxn, prm.psiMax);
+        psiMinn = dmax(sl * psiC + (1.0 - sl) * psiMinn, prm.psiMin);
+    }
+    double Qp = V * ((prm.rDeltaT - Sp) * psiMaxn - Su) - (V * prm.rDeltaT) * psi0 + sBD;
+    double Qm = V * (Su - (prm.rDeltaT - Sp) * psiMinn) + (V * prm.rDeltaT) * psi0 - sBD;
+    __stcs(ph.Qp + c, Qp); __stcs(ph.Qm + c, Qm); __stcs(ph.sP + c, sP); __stcs(ph.sM + c, sM);
+    ph.lmA[c] = dmax(dmin((sP + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
+    ph.lpA[c] = dmax(dmin((sM + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
+}
+
+// ---- face pass of limiter iteration j + cell pass of iteration j+1 (see k_mules_iter) -------------------
+template <int K, bool FIRST>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_ITER)
+kv_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, int flip) {
+    const int p = blockIdx.x % b.nPh;
+    const int c = (blockIdx.x / b.nPh) * blockDim.x + threadIdx.x;
+    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    const MulesPh &ph = b.ph[p];
+    const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
+    double *lpOut = flip ? ph.lpA : ph.lpB, *lmOut = flip ? ph.lmA : ph.lmB;
+    const double *lamIn = flip ? ph.lamB : ph.lamA;
+    double *lamOut = flip ? ph.lamA : ph.lamB;
+    Slots<K> s;
+    s.load(m, c);
+    const double lpC = lpIn[c], lmC = lmIn[c];
+    double pcN[K], laN[K], lpO[K], lmO[K], pcO[K], laO[K], lpN[K], lmN[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        const int fo = k * m.stride + c;
+        pcN[k] = ph.phiCorr[s.fdN[k]]; laN[k] = FIRST ? 1.0 : lamIn[s.fdN[k]];
+        lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
+        pcO[k] = ph.phiCorr[fo]; laO[k] = FIRST ? 1.0 : lamIn[fo];
+        lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
+    }
+    const double Qp = __ldcs(ph.Qp + c), Qm = __ldcs(ph.Qm + c), sP = __ldcs(ph.sP + c), sM = __ldcs(ph.sM + c);
+    double slp = 0.0, slm = 0.0;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (s.vN[k]) {
+            double lam = lambda_face(laN[k], pcN[k], lpO[k], lmO[k], lpC, lmC);
+            double l = lam * pcN[k];
+            if (l > 0) slm += l; else slp -= l;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (s.vO[k]) {
+            double lam = lambda_face(laO[k], pcO[k], lpC, lmC, lpN[k], lmN[k]);
+            lamOut[k * m.stride + c] = lam;
+            double l = lam * pcO[k];
+            if (l > 0) slp += l; else slm -= l;
+        }
+    }
+    lmOut[c] = dmax(dmin((slp + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
+    lpOut[c] = dmax(dmin((slm + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
+}
+
+// ---- last face pass + apply / explicit update (see k_mules_final) ----------------------------------------
+template <int K, int MODE, bool FIRST>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
+kv_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
+               const __grid_constant__ MulesParams prm, int flip, int nIter) {
+    const int p = blockIdx.x % b.nPh;
+    const int c = (blockIdx.x / b.nPh) * blockDim.x + threadIdx.x;
+    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    const MulesPh &ph = b.ph[p];
+    const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
+    const double *lamIn = flip ? ph.lamB : ph.lamA;
+    Slots<K> s;
+    s.load(m, c);
+    const double lpC = lpIn[c], lmC = lmIn[c];
+    const double psiC = (MODE >= 1) ? ph.psi[c] : 0.0;
+    double pcN[K], laN[K], lpO[K], lmO[K], phN[K], psO[K];
+    double pcO[K], laO[K], lpN[K], lmN[K], phO[K], psN[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        const int fo = k * m.stride + c;
+        if (MODE == 2) {
+            pcN[k] = ph.phiCorr[s.fdN[k]]; laN[k] = FIRST ? 1.0 : lamIn[s.fdN[k]];
+            lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
+            phN[k] = prm.phi[s.fdN[k]]; psO[k] = ph.psi[s.oN[k]];
+        }
+        pcO[k] = ph.phiCorr[fo]; laO[k] = FIRST ? 1.0 : lamIn[fo];
+        lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
+        if (MODE >= 1) { phO[k] = prm.phi[fo]; psN[k] = ph.psi[s.nO[k]]; }
+    }
+    double V = 1.0, psi0 = 0.0, Su = 0.0, Sp = 0.0;
+    if (MODE == 2) {
+        V = m.V[c]; psi0 = __ldcs(ph.psi0 + c);
+        Su = ph.Su ? __ldcs(ph.Su + c) : 0.0; Sp = ph.Sp ? __ldcs(ph.Sp + c) : 0.0;
+    }
+    double sum = 0.0;
+    if (MODE == 2) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (s.vN[k]) {
+                double lam = laN[k];
+                if (nIter > 0) lam = lambda_face(lam, pcN[k], lpO[k], lmO[k], lpC, lmC);
+                double bd = upwind_flux(phN[k], psO[k], psiC);
+                sum -= bd + lam * pcN[k];
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (s.vO[k]) {
+            double lam = laO[k];
+            if (nIter > 0) lam = lambda_face(lam, pcO[k], lpC, lmC, lpN[k], lmN[k]);
+            double fl;
+            if (MODE == 0) fl = pcO[k] * lam;
+            else           fl = upwind_flux(phO[k], psiC, psN[k]) + lam * pcO[k];
+            ph.phiPsi[k * m.stride + c] = fl;
+            sum += fl;
+        }
+    }
+    if (MODE == 2) {
+        double d = sum / V;
+        ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
+    }
+}
+
+}  // namespace tcif
