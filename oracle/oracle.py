@@ -23,11 +23,27 @@ class OrcMesh(C.Structure):
     _fields_ = [("nCells", C.c_int32), ("nIF", C.c_int32), ("nPatches", C.c_int32), ("nBF", C.c_int32),
                 ("owner", c_ip), ("neighbour", c_ip), ("Sf", c_dp), ("w", c_dp), ("V", c_dp),
                 ("patchType", c_ip), ("patchStart", c_ip), ("patchSize", c_ip), ("patchNbrProc", c_ip),
-                ("faceCells", c_ip), ("Sfb", c_dp), ("magSfb", c_dp), ("deltaCoeffsb", c_dp), ("wb", c_dp)]
+                ("faceCells", c_ip), ("Sfb", c_dp), ("magSfb", c_dp), ("deltaCoeffsb", c_dp), ("wb", c_dp),
+                ("C", c_dp), ("deltab", c_dp)]
 
 
 class OrcSigma(C.Structure):
     _fields_ = [("kind", C.c_int32), ("n", C.c_int32), ("c", C.c_double * 64)]
+
+
+class OrcAlphaCtl(C.Structure):
+    _fields_ = [("nAlphaCorr", C.c_int32), ("nAlphaSubCycles", C.c_int32), ("schemePhi", C.c_int32),
+                ("schemePhir", C.c_int32), ("implicitPredictor", C.c_int32), ("predictorTol", C.c_double),
+                ("predictorMaxIter", C.c_int32)]
+
+
+SCHEMES = {"upwind": 0, "linear": 1, "vanLeer": 2}
+
+
+def alpha_ctl(nAlphaCorr=1, nAlphaSubCycles=1, schemePhi="vanLeer", schemePhir="linear", implicitPredictor=True,
+              predictorTol=1e-12, predictorMaxIter=200):
+    return OrcAlphaCtl(nAlphaCorr, nAlphaSubCycles, SCHEMES[schemePhi], SCHEMES[schemePhir], int(implicitPredictor),
+                       predictorTol, predictorMaxIter)
 
 
 class OrcMulesCfg(C.Structure):
@@ -58,6 +74,7 @@ def lib():
         _LIB.orc_deltaN.restype = C.c_double
         _LIB.orc_sigma_eval.restype = C.c_double
         _LIB.orc_stage_threads.restype = C.c_double
+        _LIB.orc_upwind_predictor.restype = C.c_int
     return _LIB
 
 
@@ -87,11 +104,24 @@ class MeshHandle:
             patchType=i32(m.patchType), patchStart=i32(m.patchStart), patchSize=i32(m.patchSize),
             patchNbrProc=i32(m.patchNbrProc), faceCells=i32(m.faceCells), Sfb=f64(m.Sfb), magSfb=f64(m.magSfb),
             deltaCoeffsb=f64(m.deltaCoeffsb), wb=f64(m.wb))
+        Cc = getattr(m, "C", None)
+        if Cc is not None:
+            # fvPatch::delta(): own centre -> neighbour centre on processor faces (nbrC), -> face centre elsewhere
+            fc = np.asarray(m.faceCells, dtype=np.int64)
+            db = f64(m.Cfb) - f64(Cc)[fc] if len(fc) else np.zeros((0, 3))
+            nbrC = getattr(m, "nbrC", None)
+            if nbrC is not None and len(fc):
+                for p in range(len(m.patchType)):
+                    if m.patchType[p] == 3:
+                        sl = slice(int(m.patchStart[p]), int(m.patchStart[p] + m.patchSize[p]))
+                        db[sl] = f64(nbrC)[sl] - f64(Cc)[fc[sl]]
+            self.keep["C"] = f64(Cc); self.keep["deltab"] = f64(db)
         k = self.keep
         self.s = OrcMesh(m.nCells, len(k["owner"]), len(k["patchType"]), len(k["faceCells"]),
                          _i(k["owner"]), _i(k["neighbour"]), _d(k["Sf"]), _d(k["w"]), _d(k["V"]),
                          _i(k["patchType"]), _i(k["patchStart"]), _i(k["patchSize"]), _i(k["patchNbrProc"]),
-                         _i(k["faceCells"]), _d(k["Sfb"]), _d(k["magSfb"]), _d(k["deltaCoeffsb"]), _d(k["wb"]))
+                         _i(k["faceCells"]), _d(k["Sfb"]), _d(k["magSfb"]), _d(k["deltaCoeffsb"]), _d(k["wb"]),
+                         _d(k.get("C")), _d(k.get("deltab")))
 
     @property
     def ref(self):
@@ -294,3 +324,74 @@ def stage_threads(meshes, cfg, alphas_i, alphas_b, alphaBc, sigma_specs, Ti, Tb,
     res = [dict(F_i=Fis[d], F_b=Fbs[d], alpha_i=ai[d], alpha_b=ab[d], alphaPhi_i=pi[d], alphaPhi_b=pb[d])
            for d in range(nD)]
     return secs, res
+
+
+# ---- rest of solveAlphas ---------------------------------------------------------
+def conv_flux(m, scheme, fluxi, fluxb, ai, ab, bc, comm=None):
+    """fvc::flux(flux, alpha, scheme)."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    a = [f64(x) for x in (fluxi, fluxb, ai, ab)]
+    bc = i32(bc)
+    oi, ob = np.zeros(h.s.nIF), np.zeros(h.s.nBF)
+    lib().orc_conv_flux(h.ref, C.byref(comm) if comm else None, SCHEMES[scheme], _d(a[0]), _d(a[1]), _d(a[2]), _d(a[3]),
+                        _i(bc), _d(oi), _d(ob))
+    return oi, ob
+
+
+def nHatf(m, a1i, a1b, bc1, a2i, a2b, bc2, comm=None):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    a = [f64(x) for x in (a1i, a1b, a2i, a2b)]
+    b1, b2 = i32(bc1), i32(bc2)
+    oi, ob = np.zeros(h.s.nIF), np.zeros(h.s.nBF)
+    lib().orc_nHatf(h.ref, C.byref(comm) if comm else None, _d(a[0]), _d(a[1]), _i(b1), _d(a[2]), _d(a[3]), _i(b2),
+                    _d(oi), _d(ob))
+    return oi, ob
+
+
+def flux_assembly(m, alphas_i, alphas_b, alphaBc, phii, phib, schemePhi="vanLeer", schemePhir="linear", cAlpha=None,
+                  comm=None):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    P = len(alphas_i)
+    ai = [f64(a) for a in alphas_i]; ab = [f64(a) for a in alphas_b]
+    bc = i32(alphaBc).reshape(P, -1)
+    phii, phib = f64(phii), f64(phib)
+    cA = f64(np.ones((P, P)) if cAlpha is None else cAlpha)
+    oi = [np.zeros(h.s.nIF) for _ in range(P)]; ob = [np.zeros(h.s.nBF) for _ in range(P)]
+    lib().orc_flux_assembly(h.ref, C.byref(comm) if comm else None, P, _pp(ai), _pp(ab), _i(bc), _d(phii), _d(phib),
+                            SCHEMES[schemePhi], SCHEMES[schemePhir], _d(cA), _pp(oi), _pp(ob))
+    return oi, ob
+
+
+def upwind_predictor(m, deltaT, psii, psib, psi0, psiBc, phii, phib, phiAlpha_i, phiAlpha_b, Su=None, Sp=None,
+                     tol=1e-12, maxIter=200, comm=None):
+    """Returns (psii, psib, phiAlpha_i, phiAlpha_b, sweeps)."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    qi, qb = f64(psii).copy(), f64(psib).copy()
+    pi, pb = f64(phiAlpha_i).copy(), f64(phiAlpha_b).copy()
+    a = [f64(x) for x in (psi0, phii, phib)]
+    su = f64(Su) if Su is not None else None
+    sp = f64(Sp) if Sp is not None else None
+    bc = i32(psiBc)
+    n = lib().orc_upwind_predictor(h.ref, C.byref(comm) if comm else None, C.c_double(deltaT), _d(qi), _d(qb), _d(a[0]),
+                                   _i(bc), _d(a[1]), _d(a[2]), _d(su), _d(sp), C.c_double(tol), int(maxIter), _d(pi), _d(pb))
+    return qi, qb, pi, pb, int(n)
+
+
+def solve(m, cfg, ctl, alphas_i, alphas_b, alphaBc, phii, phib, deltaT, rho, cAlpha=None, Su=None, Sp=None, comm=None):
+    """multiphaseSystem::solve().  rho: per-phase uniform densities.  Returns dict(alpha_i, alpha_b, alphaPhi_i,
+    alphaPhi_b, rhoPhi_i, rhoPhi_b)."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    P = len(alphas_i)
+    ai = [f64(a).copy() for a in alphas_i]; ab = [f64(a).copy() for a in alphas_b]
+    bc = i32(alphaBc).reshape(P, -1)
+    phii, phib = f64(phii), f64(phib)
+    cA = f64(np.ones((P, P)) if cAlpha is None else cAlpha)
+    rho = f64(rho)
+    su = [f64(x) for x in Su] if Su is not None else None
+    sp = [f64(x) for x in Sp] if Sp is not None else None
+    pi = [np.zeros(h.s.nIF) for _ in range(P)]; pb = [np.zeros(h.s.nBF) for _ in range(P)]
+    ri, rb = np.zeros(h.s.nIF), np.zeros(h.s.nBF)
+    lib().orc_solve(h.ref, C.byref(comm) if comm else None, C.byref(cfg), C.byref(ctl), P, _pp(ai), _pp(ab), _i(bc),
+                    _d(phii), _d(phib), _d(cA), _d(rho), None, None, _pp(su) if su else None, _pp(sp) if sp else None,
+                    C.c_double(deltaT), _pp(pi), _pp(pb), _d(ri), _d(rb))
+    return dict(alpha_i=ai, alpha_b=ab, alphaPhi_i=pi, alphaPhi_b=pb, rhoPhi_i=ri, rhoPhi_b=rb)

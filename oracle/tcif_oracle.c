@@ -703,3 +703,4 @@ double orc_stage_threads(int nDom, const orc_mesh *meshes, const orc_mules_cfg *
     free(sh.sendPtr); free(sh.redbuf); free(args); free(th);
     return tmax;
 }
+#include "tcif_oracle_alpha.inc"

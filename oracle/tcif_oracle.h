@@ -56,6 +56,10 @@ typedef struct orc_mesh {
     const double *magSfb;                      /* [nBF]                                 */
     const double *deltaCoeffsb;                /* [nBF]                                 */
     const double *wb;                          /* [nBF]  1 on non-coupled patches       */
+    /* only needed by the NVD/TVD convection schemes (vanLeer), may be NULL otherwise */
+    const double *C;                           /* [nCells*3] cell centres mesh.C()      */
+    const double *deltab;                      /* [nBF*3] fvPatch::delta(): on processor
+                                                  faces own centre -> neighbour centre   */
 } orc_mesh;
 
 /* Function1<scalar> "sigma": constant | polynomial ((a e)...) | table ((T s)...) clamp */
@@ -180,6 +184,58 @@ double orc_stage_threads(int nDom, const orc_mesh *meshes, const orc_mules_cfg *
                          const double *const *phii, const double *const *phib,
                          double *const *const *phiAlphai, double *const *const *phiAlphab,
                          double deltaT, double *const *Fi, double *const *Fb, int nStages);
+
+/* ---- rest of multiphaseSystem::solveAlphas() ---------------- */
+enum { ORC_SCHEME_UPWIND = 0, ORC_SCHEME_LINEAR = 1, ORC_SCHEME_VANLEER = 2 };
+
+/* fvc::flux(flux, alpha, "div(..)") = flux_f * alpha_f(scheme; upwind direction from flux)
+ * (multiphaseSystem.C:209-214, 246-251).  gradient for vanLeer: fvc::grad, Gauss linear. */
+void orc_conv_flux(const orc_mesh *m, const orc_comm *c, int scheme,
+                   const double *fluxi, const double *fluxb,
+                   const double *ai, const double *ab, const int32_t *alphaBc,
+                   double *outi, double *outb);
+
+/* phaseSystem::nHatf (phaseSystem.C:1251-1272, 1297-1305): nHatfv & Sf on all faces. */
+void orc_nHatf(const orc_mesh *m, const orc_comm *c,
+               const double *a1i, const double *a1b, const int32_t *bc1,
+               const double *a2i, const double *a2b, const int32_t *bc2,
+               double *outi, double *outb);
+
+/* Flux assembly for every phase (multiphaseSystem.C:181-274).  cAlpha[p1*nPhases+p2].
+ * out: phiAlphaCorr[p] (internal, boundary). */
+void orc_flux_assembly(const orc_mesh *m, const orc_comm *c, int nPhases,
+                       const double *const *alphai, const double *const *alphab, const int32_t *alphaBc,
+                       const double *phii, const double *phib, int schemePhi, int schemePhir,
+                       const double *cAlpha, double *const *outi, double *const *outb);
+
+/* Implicit upwind predictor (multiphaseSystem.C:348-363): solves
+ *   (V/dt - V Sp + sum_out phi) psi_c + sum_in phi psi_nb = V psi0/dt + V Su
+ * by Jacobi sweeps until max|dpsi| <= tol (globally) or maxIter, re-evaluates the boundary values and
+ * ADDS alpha1Eqn.flux() = phi*psi_upwind(new) into phiAlpha.  Returns the sweep count. */
+int orc_upwind_predictor(const orc_mesh *m, const orc_comm *c, double deltaT,
+                         double *psii, double *psib, const double *psi0, const int32_t *psiBc,
+                         const double *phii, const double *phib,
+                         const double *Su, const double *Sp, double tol, int maxIter,
+                         double *phiAlphai, double *phiAlphab);
+
+typedef struct orc_alpha_ctl {
+    int32_t nAlphaCorr, nAlphaSubCycles;
+    int32_t schemePhi, schemePhir;       /* div(phi,alpha), div(phir,alpha,alpha) */
+    int32_t implicitPredictor;           /* 1: :348-363 as coded; 0: the commented-out bounded upwind flux of :346 */
+    double predictorTol;
+    int32_t predictorMaxIter;
+} orc_alpha_ctl;
+
+/* multiphaseSystem::solve() (multiphaseSystem.C:128-168) = nAlphaSubCycles x solveAlphas() (:170-429)
+ * incl. renormalisation and rhoPhi.  alpha (i,b) in/out; alpha0 is taken at the start of every
+ * sub-cycle; rho[p]: uniform phase density when rhoi[p] == NULL.  Su/Sp NULL = no mass transfer.
+ * out: alphaPhi[p], rhoPhi (the Delta-t weighted sum over sub-cycles). */
+void orc_solve(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg, const orc_alpha_ctl *ctl,
+               int nPhases, double *const *alphai, double *const *alphab, const int32_t *alphaBc,
+               const double *phii, const double *phib, const double *cAlpha,
+               const double *rhoUniform, const double *const *rhoi, const double *const *rhob,
+               const double *const *Su, const double *const *Sp, double deltaT,
+               double *const *alphaPhii, double *const *alphaPhib, double *rhoPhii, double *rhoPhib);
 
 #ifdef __cplusplus
 }
