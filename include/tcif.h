@@ -166,6 +166,40 @@ TCIF_API int tcif_stage_host(tcif_ctx *ctx, double deltaT,
                              double *const *phiAlphaInternal, double *const *phiAlphaBoundary,
                              double *Finternal, double *Fboundary);
 
+/* ---- rest of multiphaseSystem::solveAlphas() on the device --------- */
+/* convection schemes of fvSchemes' div(phi,alpha) / div(phir,alpha,alpha) the device path supports */
+enum { TCIF_SCHEME_UPWIND = 0, TCIF_SCHEME_LINEAR = 1, TCIF_SCHEME_VANLEER = 2 };
+/* fvSolution "alpha" controls read by solve()/solveAlphas() (multiphaseSystem.C:130-131, 173-175) */
+typedef struct tcif_alpha_controls {
+    int32_t nAlphaCorr;          /* >= 1                                                  */
+    int32_t nAlphaSubCycles;     /* <= 1: no sub-cycling                                  */
+    int32_t schemePhi;           /* TCIF_SCHEME_* for div(phi,alpha.x)                    */
+    int32_t schemePhir;          /* TCIF_SCHEME_* for div(phir,alpha.y,alpha.x)           */
+    int32_t implicitPredictor;   /* 1: alpha1Eqn.solve() + .flux() as coded (:348-363);
+                                    0: the bounded explicit upwind flux of :346          */
+    double predictorTol;         /* max|dalpha| between Jacobi sweeps at convergence      */
+    int32_t predictorMaxIter;
+} tcif_alpha_controls;
+/* mesh.C() [nCells*3] and fvPatch::delta() [nBoundaryFaces*3] (own -> neighbour centre on processor
+ * faces): geometry the NVD/TVD limiter of vanLeer needs; not required for upwind/linear. */
+TCIF_API int tcif_set_cell_centres(tcif_ctx *ctx, const double *C, const double *deltaBoundary);
+/* cAlphas ((a and b) c ...) as a dense [nPhases*nPhases] table, entry [p1*nPhases+p2] (multiphaseSystem.C:226-237). */
+TCIF_API int tcif_set_calpha(tcif_ctx *ctx, const double *cAlpha);
+/* phase.rho() for rhoPhi_ (multiphaseSystem.C:397-406): a uniform value, or a vol field when internal != NULL. */
+TCIF_API int tcif_set_rho(tcif_ctx *ctx, int phase, double uniform, const double *internal, const double *boundary);
+/* phiAlphaCorrs[p] = fvc::flux(phi, alpha_p, schemePhi) + compression fluxes with nHatf, inflow fix, for all phases
+ * (multiphaseSystem.C:199-277) from the resident alpha, phi; result readable with tcif_get_phi_alpha after
+ * tcif_mules_limit or through tcif_get_flux_assembly. */
+TCIF_API int tcif_flux_assembly(tcif_ctx *ctx, int schemePhi, int schemePhir);
+TCIF_API int tcif_get_flux_assembly(tcif_ctx *ctx, int phase, double *internal, double *boundary);
+/* alpha1Eqn.solve(); phiAlpha += alpha1Eqn.flux()   (multiphaseSystem.C:348-363). */
+TCIF_API int tcif_upwind_predictor(tcif_ctx *ctx, int phase, double deltaT, double tol, int maxIter);
+TCIF_API int tcif_predictor_sweeps(const tcif_ctx *ctx, int phase);
+/* multiphaseSystem::solve() (multiphaseSystem.C:128-168): sub-cycles x correctors of flux assembly, limit,
+ * limitSum, predictor, explicitSolve, rhoPhi, renormalisation, on the resident alpha, phi, Su/Sp. */
+TCIF_API int tcif_solve_alphas(tcif_ctx *ctx, const tcif_alpha_controls *ctl, double deltaT);
+TCIF_API int tcif_get_rho_phi(tcif_ctx *ctx, double *internal, double *boundary);
+
 /* Logging scalars of multiphaseSystem.C:408-425: sum(V*alpha), min, max (global over ranks). */
 TCIF_API int tcif_alpha_stats(tcif_ctx *ctx, int phase, double out3[3]);
 

@@ -39,6 +39,22 @@ class MeshDesc(C.Structure):
                 ("deltaCoeffsBoundary", c_dp), ("weightsBoundary", c_dp)]
 
 
+class AlphaControls(C.Structure):
+    """tcif_alpha_controls: fvSolution "alpha" controls of solve()/solveAlphas()."""
+    _fields_ = [("nAlphaCorr", C.c_int32), ("nAlphaSubCycles", C.c_int32), ("schemePhi", C.c_int32),
+                ("schemePhir", C.c_int32), ("implicitPredictor", C.c_int32), ("predictorTol", C.c_double),
+                ("predictorMaxIter", C.c_int32)]
+
+
+SCHEMES = {"upwind": 0, "linear": 1, "vanLeer": 2}
+
+
+def alpha_controls(nAlphaCorr=1, nAlphaSubCycles=1, schemePhi="vanLeer", schemePhir="linear", implicitPredictor=True,
+                   predictorTol=1e-12, predictorMaxIter=200):
+    return AlphaControls(nAlphaCorr, nAlphaSubCycles, SCHEMES[schemePhi], SCHEMES[schemePhir], int(implicitPredictor),
+                         predictorTol, predictorMaxIter)
+
+
 class Config(C.Structure):
     _fields_ = [("nPhases", C.c_int32), ("nLimiterIter", C.c_int32), ("smoothLimiter", C.c_double),
                 ("extremaCoeff", C.c_double), ("boundaryExtrema", C.c_int32), ("device", C.c_int32),
@@ -68,6 +84,7 @@ def lib():
     L.tcif_launch_count.argtypes = [C.c_void_p]
     L.tcif_device_bytes.restype = C.c_int64
     L.tcif_device_bytes.argtypes = [C.c_void_p]
+    L.tcif_predictor_sweeps.argtypes = [C.c_void_p, C.c_int]
     L.tcif_destroy.argtypes = [C.c_void_p]
     L.tcif_destroy.restype = None
     L.tcif_group_destroy.argtypes = [C.c_void_p]
@@ -319,6 +336,42 @@ class Context:
             assert a.dtype == np.float64 and a.flags.c_contiguous
         self._ck(lib().tcif_stage_host(self.h, C.c_double(deltaT), _pp(alphas_i), _pp(alphas_b), _d(Ti), _d(Tb),
                                        _d(phii), _d(phib), _pp(phiAlpha_i), _pp(phiAlpha_b), _d(Fi), _d(Fb)))
+
+    # -- rest of solveAlphas
+    def set_cell_centres(self, Ccells, deltaBoundary):
+        a, b = _f64(Ccells), _f64(deltaBoundary)
+        assert a.shape == (self.nCells, 3) and b.shape == (self.nBF, 3)
+        self._ck(lib().tcif_set_cell_centres(self.h, _d(a), _d(b)))
+
+    def set_calpha(self, table):
+        t = _f64(table)
+        assert t.shape == (self.P, self.P)
+        self._ck(lib().tcif_set_calpha(self.h, _d(t)))
+
+    def set_rho(self, phase, uniform, internal=None, boundary=None):
+        i = _f64(internal) if internal is not None else None
+        b = _f64(boundary) if boundary is not None else None
+        self._ck(lib().tcif_set_rho(self.h, int(phase), C.c_double(uniform), _d(i), _d(b)))
+
+    def flux_assembly(self, schemePhi="vanLeer", schemePhir="linear"):
+        self._ck(lib().tcif_flux_assembly(self.h, SCHEMES[schemePhi], SCHEMES[schemePhir]))
+
+    def get_flux_assembly(self, phase):
+        a, b = np.empty(self.nIF), np.empty(self.nBF)
+        self._ck(lib().tcif_get_flux_assembly(self.h, int(phase), _d(a), _d(b)))
+        return a, b
+
+    def upwind_predictor(self, phase, deltaT, tol=1e-12, maxIter=200):
+        self._ck(lib().tcif_upwind_predictor(self.h, int(phase), C.c_double(deltaT), C.c_double(tol), int(maxIter)))
+        return int(lib().tcif_predictor_sweeps(self.h, int(phase)))
+
+    def solve_alphas(self, ctl: AlphaControls, deltaT):
+        self._ck(lib().tcif_solve_alphas(self.h, C.byref(ctl), C.c_double(deltaT)))
+
+    def get_rho_phi(self):
+        a, b = np.empty(self.nIF), np.empty(self.nBF)
+        self._ck(lib().tcif_get_rho_phi(self.h, _d(a), _d(b)))
+        return a, b
 
     def alpha_stats(self, phase):
         out = (C.c_double * 3)()

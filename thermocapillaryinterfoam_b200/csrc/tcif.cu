@@ -7,6 +7,7 @@
 // There is no CPU fallback: every entry point needs a CUDA device.
 #include "tcif_device.cuh"
 #include "tcif_volume.cuh"
+#include "tcif_alpha.cuh"
 #include "../../include/tcif.h"
 
 #include <dlfcn.h>
@@ -48,11 +49,11 @@ inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 // ---- timers ---------------------------------------------------------------------------
 enum TimerId {
     T_GRAD_TENSOR = 0, T_DIV_TENSOR, T_MULES_SETUP, T_MULES_ITER, T_MULES_FINAL, T_LIMIT_SUM,
-    T_BOUNDARY, T_HALO, T_CONVERT, T_STATS, T_COUNT
+    T_BOUNDARY, T_HALO, T_CONVERT, T_STATS, T_FLUX_ASSEMBLY, T_PREDICTOR, T_RHOPHI, T_COUNT
 };
 const char *kTimerNames[T_COUNT] = {
     "grad_tensor", "div_tensor", "mules_setup", "mules_iter", "mules_final", "limit_sum",
-    "boundary", "halo", "convert", "stats"};
+    "boundary", "halo", "convert", "stats", "flux_assembly", "predictor", "rho_phi"};
 
 struct EvPair { cudaEvent_t a, b; int id; double bytes; };
 
@@ -153,6 +154,16 @@ struct tcif_ctx {
     double *Su[4]{}, *Sp[4]{};
     bool haveSu[4]{}, haveSp[4]{};
     double *Tq = nullptr, *gBnd = nullptr, *TqHalo = nullptr, *G = nullptr, *Gb = nullptr, *F = nullptr, *Fb = nullptr;
+    // rest of solveAlphas (flux assembly, predictor, rhoPhi)
+    double *Cx = nullptr, *Cy = nullptr, *Cz = nullptr, *dbx = nullptr, *dby = nullptr, *dbz = nullptr;
+    double cAlpha[16];
+    double rhoU[4]{};
+    double *rho[4]{}, *rhob[4]{};
+    bool haveRho[4]{}, rhoSet[4]{};
+    double *rhoPhi = nullptr, *rhoPhib = nullptr;
+    double *predDiag[4]{}, *predRhs[4]{};
+    double *dmaxDev = nullptr;
+    int predictorSweeps[4]{};
     double deltaN = 0.0;
     bool deltaNValid = false;
     double *staging = nullptr;
@@ -367,6 +378,8 @@ void alloc_fields(tcif_ctx *c) {
     c->sendBuf = c->dalloc<double>(c->haloDoubles); c->recvBuf = c->dalloc<double>(c->haloDoubles);
     c->statsPart = c->dalloc<double>(1024 * 3); c->statsOut = c->dalloc<double>(16);
     CUDA_OK(cudaHostAlloc((void **)&c->h_small, 64 * sizeof(double), cudaHostAllocDefault));
+    for (int i = 0; i < 16; ++i) c->cAlpha[i] = 1.0;
+    c->dmaxDev = c->dalloc<double>(8);
     for (int q = 0; q < 6; ++q) { c->hSig[q].kind = SIGMA_CONSTANT; c->hSig[q].n = 1; memset(c->hSig[q].c, 0, sizeof c->hSig[q].c); }
 }
 
@@ -775,6 +788,157 @@ void do_explicit(tcif_ctx *c, const int *phases, int nPh, double deltaT, bool ad
     correct_alpha_bcs(c, phases, nPh);
 }
 
+// phiAlpha[p] += upwind<scalar>(mesh, phi).flux(alpha_p)
+void do_add_upwind(tcif_ctx *c, int phase) {
+    timed(c, T_MULES_SETUP, 0, [&] {
+        int grid = cdiv(c->nC, TCIF_TPB);
+        DISPATCH_K(k_add_upwind<KO><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, c->phi, c->alpha[phase], c->phiPsi[phase]));
+        c->launches++;
+        if (c->nBF) {
+            k_add_upwind_bnd<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->phib, c->alpha[phase], c->alphab[phase], c->phiPsib[phase]);
+            c->launches++;
+        }
+    });
+}
+
+void ensure_G(tcif_ctx *c) {
+    if (!c->G) { c->G = c->dalloc<double>((size_t)c->P * 3 * c->stride); c->Gb = c->dalloc<double>((size_t)c->P * 3 * std::max(c->nBF, 1)); }
+}
+
+// phic_k = min(pa[k]*phic0, pb[k]): closed form of the cumulative `phic = min(cAlpha*phic, max(phic))`
+// (multiphaseSystem.C:237) over the (phase1, phase2) visits of ALL correctors of one solveAlphas() call
+struct PhicState { double a = 1.0, b = 1e300, M0 = 0.0; bool trivial = true; };
+
+void phic_begin(tcif_ctx *c, PhicState &st) {
+    st = PhicState();
+    for (int p1 = 0; p1 < c->P; ++p1) for (int p2 = 0; p2 < c->P; ++p2) if (p1 != p2 && c->cAlpha[p1 * c->P + p2] != 1.0) st.trivial = false;
+    if (st.trivial) return;                       // cAlpha == 1 everywhere: min(phic, max(phic)) == phic
+    CUDA_OK(cudaMemsetAsync(c->dmaxDev, 0, sizeof(double) * 8, c->stream));
+    long long n = (long long)c->nFd + c->nBF;
+    k_phic_max<<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->phi, c->phib, c->dmaxDev);
+    c->launches++;
+    CUDA_OK(cudaMemcpyAsync(c->h_small, c->dmaxDev, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    double v[1] = {c->h_small[0]};
+    int ops[1] = {RED_MAX};
+    allreduce_host(c, v, ops, 1);
+    st.M0 = v[0];
+}
+
+// fvc::flux(phi, alpha_p, scheme) + interface compression for every phase -> phiHO[p] (multiphaseSystem.C:199-277)
+void do_flux_assembly(tcif_ctx *c, int schemePhi, int schemePhir, PhicState &st) {
+    for (int sc : {schemePhi, schemePhir}) {
+        if (sc < 0 || sc > 2) failf("unsupported convection scheme %d (upwind | linear | vanLeer)", sc);
+        if (sc == SCHEME_VANLEER && !c->Cx) failf("vanLeer needs cell centres: call tcif_set_cell_centres first");
+    }
+    require_comm(c);
+    ensure_deltaN(c);
+    ensure_G(c);
+    ForceArgs ga = force_args(c, false, true);
+    sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, false, true), [&] { launch_grad_tensor<false, true>(c, ga); }); },
+             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, ga); }); });
+    join(c);
+    if (c->nCoupled) {                            // neighbour-rank gradients on processor faces
+        const double *src[36]; double *dst[36];
+        for (int k = 0; k < c->P * 3; ++k) { src[k] = c->G + (size_t)k * c->stride; dst[k] = c->Gb + (size_t)k * c->nBF; }
+        halo_cells(c, c->P * 3, src, dst);
+    }
+    FluxArgs a{};
+    a.P = c->P; a.schemePhi = schemePhi; a.schemePhir = schemePhir;
+    for (int p = 0; p < c->P; ++p) { a.alpha[p] = c->alpha[p]; a.alphab[p] = c->alphab[p]; a.out[p] = c->phiHO[p]; a.outb[p] = c->phiHOb[p]; }
+    a.G = c->G; a.Gb = c->Gb; a.Cx = c->Cx; a.Cy = c->Cy; a.Cz = c->Cz; a.dbx = c->dbx; a.dby = c->dby; a.dbz = c->dbz;
+    a.phi = c->phi; a.phib = c->phib; a.deltaN = c->deltaN;
+    int step = 0;
+    for (int p1 = 0; p1 < c->P; ++p1)
+        for (int p2 = 0; p2 < c->P; ++p2) {
+            if (p1 == p2) continue;
+            if (!st.trivial) {
+                double cA = c->cAlpha[p1 * c->P + p2];
+                double M = std::min(st.a * st.M0, st.b);
+                st.b = std::min(cA * st.b, M);
+                st.a = cA * st.a;
+            }
+            a.pa[step] = st.a; a.pb[step] = st.b;
+            ++step;
+        }
+    double bytes = (double)c->nC * (8.0 * c->P + 24.0 * c->P + 4.0 * c->Ko + 8.0 * c->Ko * (5 + c->P) + (c->Cx ? 24 : 0));
+    timed(c, T_FLUX_ASSEMBLY, bytes, [&] {
+        int grid = cdiv(c->nC, TCIF_TPB);
+        DISPATCH_P(k_flux_assembly<PP><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, a));
+        c->launches++;
+        if (c->nBF) {
+            DISPATCH_P(k_flux_assembly_bnd<PP><<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a));
+            c->launches++;
+        }
+    });
+}
+
+// implicit upwind predictor for a batch of phases (multiphaseSystem.C:348-363): Jacobi on the M-matrix
+// EulerDdt + upwind fvmDiv == Su + Sp until max|dpsi| <= tol per phase; then psi.correctBoundaryConditions()
+// and phiAlpha += alpha1Eqn.flux().
+void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double tol, int maxIter) {
+    if (!(deltaT > 0)) failf("predictor: deltaT must be positive");
+    require_comm(c);
+    for (int k = 0; k < nPh; ++k) {
+        int p = phases[k];
+        if (!c->predDiag[p]) { c->predDiag[p] = c->dalloc<double>(c->stride); c->predRhs[p] = c->dalloc<double>(c->stride); }
+        c->predictorSweeps[p] = 0;
+    }
+    auto batch = [&](const bool *active) {
+        PredBatch b{};
+        b.nPh = nPh; b.phi = c->phi; b.phib = c->phib; b.rDeltaT = 1.0 / deltaT; b.dmax = c->dmaxDev;
+        for (int k = 0; k < nPh; ++k) {
+            int p = phases[k];
+            PredPh &ph = b.ph[k];
+            ph.psi0 = c->alpha0[p]; ph.Su = c->haveSu[p] ? c->Su[p] : nullptr; ph.Sp = c->haveSp[p] ? c->Sp[p] : nullptr;
+            ph.bc = c->bc[p]; ph.psib = c->alphab[p]; ph.diag = c->predDiag[p]; ph.rhs = c->predRhs[p];
+            ph.x = c->alpha[p]; ph.xn = c->alphaNew[p]; ph.active = active ? (active[k] ? 1 : 0) : 1;
+        }
+        return b;
+    };
+    int grid = cdiv(c->nC, TCIF_TPB) * nPh, gridB = cdiv(std::max(c->nBndCells, 1), TCIF_TPB) * nPh;
+    {
+        PredBatch b = batch(nullptr);
+        sweep(c, [&] { timed(c, T_PREDICTOR, (double)nPh * c->nC * (40.0 + 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko), [&] {
+                           k_pred_setup<false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b); c->launches++; }); },
+                 [&] { if (c->nBndCells) timed_on(c, c->side, T_BOUNDARY, 0, [&] {
+                           k_pred_setup<true><<<gridB, TCIF_TPB, 0, c->side>>>(c->dm, b); c->launches++; }); });
+    }
+    bool active[4] = {true, true, true, true};
+    for (int it = 0; it < maxIter; ++it) {
+        bool any = false;
+        for (int k = 0; k < nPh; ++k) any = any || active[k];
+        if (!any) break;
+        CUDA_OK(cudaMemsetAsync(c->dmaxDev, 0, sizeof(double) * 8, c->stream));
+        PredBatch b = batch(active);
+        sweep(c, [&] { timed(c, T_PREDICTOR, (double)nPh * c->nC * (32.0 + 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko), [&] {
+                           k_pred_jacobi<false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b); c->launches++; }); },
+                 [&] {
+                     if (c->nCoupled) {           // patchNeighbourField of the iterate
+                         const double *src[4]; double *dst[4]; int n = 0;
+                         for (int k = 0; k < nPh; ++k) if (active[k]) { src[n] = c->alpha[phases[k]]; dst[n] = c->alphab[phases[k]]; ++n; }
+                         halo_cells(c, n, src, dst, c->side);
+                     }
+                     if (c->nBndCells) timed_on(c, c->side, T_BOUNDARY, 0, [&] {
+                         k_pred_jacobi<true><<<gridB, TCIF_TPB, 0, c->side>>>(c->dm, b); c->launches++; });
+                 });
+        join(c);
+        CUDA_OK(cudaMemcpyAsync(c->h_small, c->dmaxDev, sizeof(double) * 4, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        double v[4]; int ops[4] = {RED_MAX, RED_MAX, RED_MAX, RED_MAX};
+        for (int k = 0; k < nPh; ++k) v[k] = c->h_small[k];
+        allreduce_host(c, v, ops, nPh);
+        for (int k = 0; k < nPh; ++k) {
+            if (!active[k]) continue;
+            std::swap(c->alpha[phases[k]], c->alphaNew[phases[k]]);
+            c->predictorSweeps[phases[k]]++;
+            if (v[k] <= tol) active[k] = false;
+        }
+    }
+    correct_alpha_bcs(c, phases, nPh);
+    for (int k = 0; k < nPh; ++k) do_add_upwind(c, phases[k]);
+}
+
 void store_old(tcif_ctx *c) {
     for (int p = 0; p < c->P; ++p)
         CUDA_OK(cudaMemcpyAsync(c->alpha0[p], c->alpha[p], sizeof(double) * c->nC, cudaMemcpyDeviceToDevice, c->stream));
@@ -788,6 +952,71 @@ void do_stage(tcif_ctx *c, double deltaT) {
     do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true);      // multiphaseSystem.C:296-319
     do_limit_sum(c);                                            // :321
     do_explicit(c, all, c->P, deltaT, true);                    // :346 (bounded flux) + :365-375
+}
+
+// rhoPhi_ (+)= sum_p interpolate(rho_p)*alphaPhi_p   (multiphaseSystem.C:397-406, 158)
+void do_rho_phi(tcif_ctx *c, double wgt, bool accumulate) {
+    for (int p = 0; p < c->P; ++p) if (!c->rhoSet[p]) failf("phase %d has no density: call tcif_set_rho first", p);
+    if (!c->rhoPhi) { c->rhoPhi = c->dalloc<double>(c->nFd); c->rhoPhib = c->dalloc<double>(std::max(c->nBF, 1)); }
+    RhoPhiArgs a{};
+    a.P = c->P; a.out = c->rhoPhi; a.outb = c->rhoPhib; a.wgt = wgt; a.accumulate = accumulate ? 1 : 0;
+    for (int p = 0; p < c->P; ++p) {
+        a.rhoU[p] = c->rhoU[p]; a.rho[p] = c->haveRho[p] ? c->rho[p] : nullptr; a.rhob[p] = c->haveRho[p] ? c->rhob[p] : nullptr;
+        a.aPhi[p] = c->phiPsi[p]; a.aPhib[p] = c->phiPsib[p];
+    }
+    timed(c, T_RHOPHI, (double)c->nC * (4.0 * c->Ko + 8.0 * c->Ko * (2 + c->P)), [&] {
+        k_rho_phi<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a);
+        c->launches++;
+        if (c->nBF) { k_rho_phi_bnd<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a); c->launches++; }
+    });
+}
+
+// alpha += alpha*(1 - sumAlpha), cells and patch values   (multiphaseSystem.C:414-426)
+void do_renormalise(tcif_ctx *c) {
+    RenormArgs r{};
+    r.P = c->P;
+    for (int p = 0; p < c->P; ++p) r.a[p] = c->alpha[p];
+    timed(c, T_RHOPHI, 16.0 * c->P * c->nC, [&] {
+        k_renormalise<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nC, r);
+        c->launches++;
+        if (c->nBF) {
+            RenormArgs rb{};
+            rb.P = c->P;
+            for (int p = 0; p < c->P; ++p) rb.a[p] = c->alphab[p];
+            k_renormalise<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nBF, rb);
+            c->launches++;
+        }
+    });
+}
+
+// multiphaseSystem::solve() (multiphaseSystem.C:128-168) = nAlphaSubCycles x solveAlphas() (:170-429)
+void do_solve_alphas(tcif_ctx *c, const tcif_alpha_controls *ctl, double deltaT) {
+    if (!ctl) failf("tcif_solve_alphas: null controls");
+    if (!(deltaT > 0)) failf("tcif_solve_alphas: deltaT must be positive");
+    if (ctl->nAlphaCorr < 1) failf("tcif_solve_alphas: nAlphaCorr must be >= 1");
+    int all[4] = {0, 1, 2, 3};
+    const int nSub = std::max(1, ctl->nAlphaSubCycles);
+    const double dt = deltaT / nSub;
+    for (int sub = 0; sub < nSub; ++sub) {
+        store_old(c);                                                     // subCycle refreshes oldTime()
+        PhicState st;
+        phic_begin(c, st);
+        for (int acorr = 0; acorr < ctl->nAlphaCorr; ++acorr) {
+            do_flux_assembly(c, ctl->schemePhi, ctl->schemePhir, st);     // :199-277
+            do_limit(c, all, c->P, 1.0 / dt, 0, false, true);             // :296-319
+            do_limit_sum(c);                                              // :321
+            if (ctl->implicitPredictor) {
+                do_predictor(c, all, c->P, dt, ctl->predictorTol, ctl->predictorMaxIter);   // :348-363
+                do_explicit(c, all, c->P, dt, false);                     // :365-375
+            } else {
+                do_explicit(c, all, c->P, dt, true);                      // :346 (the commented-out bounded flux)
+            }
+            if (acorr == ctl->nAlphaCorr - 1) {                           // :382-427
+                do_rho_phi(c, dt / deltaT, nSub > 1 && sub > 0);
+                do_renormalise(c);
+            }
+        }
+    }
 }
 
 // ---- host <-> device field transfers ----------------------------------------------------
@@ -1190,15 +1419,7 @@ int tcif_mules_limit_sum(tcif_ctx *c) {
 int tcif_add_upwind_flux(tcif_ctx *c, int phase) {
     API_BEGIN(c)
     check_phase(c, phase);
-    timed(c, T_MULES_SETUP, 0, [&] {
-        int grid = cdiv(c->nC, TCIF_TPB);
-        DISPATCH_K(k_add_upwind<KO><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, c->phi, c->alpha[phase], c->phiPsi[phase]));
-        c->launches++;
-        if (c->nBF) {
-            k_add_upwind_bnd<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->phib, c->alpha[phase], c->alphab[phase], c->phiPsib[phase]);
-            c->launches++;
-        }
-    });
+    do_add_upwind(c, phase);
     API_END(c)
 }
 
@@ -1232,6 +1453,98 @@ int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const
         down_faces(c, pai[p], c->phiPsi[p]);
         if (c->nBF) CUDA_OK(cudaMemcpyAsync(pab[p], c->phiPsib[p], sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
     }
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_set_cell_centres(tcif_ctx *c, const double *C, const double *deltaB) {
+    API_BEGIN(c)
+    if (!C || (c->nBF && !deltaB)) failf("tcif_set_cell_centres: null array");
+    if (!c->Cx) {
+        c->Cx = c->dalloc<double>(3 * (size_t)c->stride); c->Cy = c->Cx + c->stride; c->Cz = c->Cy + c->stride;
+        c->dbx = c->dalloc<double>(3 * (size_t)std::max(c->nBF, 1)); c->dby = c->dbx + std::max(c->nBF, 1); c->dbz = c->dby + std::max(c->nBF, 1);
+    }
+    CUDA_OK(cudaMemcpyAsync(c->staging, C, sizeof(double) * 3 * c->nC, cudaMemcpyDefault, c->stream));
+    k_aos3_to_soa<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nC, (size_t)c->stride, c->staging, c->Cx);
+    c->launches++;
+    if (c->nBF) {
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        CUDA_OK(cudaMemcpyAsync(c->staging, deltaB, sizeof(double) * 3 * c->nBF, cudaMemcpyDefault, c->stream));
+        k_aos3_to_soa<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nBF, (size_t)std::max(c->nBF, 1), c->staging, c->dbx);
+        c->launches++;
+    }
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_set_calpha(tcif_ctx *c, const double *cAlpha) {
+    API_BEGIN(c)
+    if (!cAlpha) failf("tcif_set_calpha: null table");
+    for (int i = 0; i < c->P * c->P; ++i) {
+        if (!(cAlpha[i] >= 0)) failf("tcif_set_calpha: negative or NaN entry %d", i);
+        c->cAlpha[i] = cAlpha[i];
+    }
+    API_END(c)
+}
+
+int tcif_set_rho(tcif_ctx *c, int phase, double uniform, const double *internal, const double *boundary) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    c->rhoU[phase] = uniform;
+    if (internal) {
+        if (c->nBF && !boundary) failf("tcif_set_rho: field without boundary values");
+        if (!c->rho[phase]) { c->rho[phase] = c->dalloc<double>(c->stride); c->rhob[phase] = c->dalloc<double>(std::max(c->nBF, 1)); }
+        up_cells(c, c->rho[phase], internal);
+        up_bnd(c, c->rhob[phase], boundary);
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+    }
+    c->haveRho[phase] = internal != nullptr;
+    c->rhoSet[phase] = true;
+    API_END(c)
+}
+
+int tcif_flux_assembly(tcif_ctx *c, int schemePhi, int schemePhir) {
+    API_BEGIN(c)
+    PhicState st;
+    phic_begin(c, st);
+    do_flux_assembly(c, schemePhi, schemePhir, st);
+    for (int p = 0; p < c->P; ++p) {      // becomes the input of tcif_mules_limit like tcif_set_phi_alpha does
+        CUDA_OK(cudaMemcpyAsync(c->phiPsi[p], c->phiHO[p], sizeof(double) * c->nFd, cudaMemcpyDeviceToDevice, c->stream));
+        if (c->nBF) CUDA_OK(cudaMemcpyAsync(c->phiPsib[p], c->phiHOb[p], sizeof(double) * c->nBF, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    API_END(c)
+}
+
+int tcif_get_flux_assembly(tcif_ctx *c, int phase, double *internal, double *boundary) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (internal) down_faces(c, internal, c->phiHO[phase]);
+    if (boundary && c->nBF) CUDA_OK(cudaMemcpyAsync(boundary, c->phiHOb[phase], sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_upwind_predictor(tcif_ctx *c, int phase, double deltaT, double tol, int maxIter) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (!(tol > 0) || maxIter < 1) failf("tcif_upwind_predictor: tol must be > 0 and maxIter >= 1");
+    do_predictor(c, &phase, 1, deltaT, tol, maxIter);
+    API_END(c)
+}
+
+int tcif_predictor_sweeps(const tcif_ctx *c, int phase) { return (c && phase >= 0 && phase < c->P) ? c->predictorSweeps[phase] : -1; }
+
+int tcif_solve_alphas(tcif_ctx *c, const tcif_alpha_controls *ctl, double deltaT) {
+    API_BEGIN(c)
+    do_solve_alphas(c, ctl, deltaT);
+    API_END(c)
+}
+
+int tcif_get_rho_phi(tcif_ctx *c, double *internal, double *boundary) {
+    API_BEGIN(c)
+    if (!c->rhoPhi) failf("tcif_get_rho_phi: rhoPhi has not been computed (tcif_solve_alphas)");
+    if (internal) down_faces(c, internal, c->rhoPhi);
+    if (boundary && c->nBF) CUDA_OK(cudaMemcpyAsync(boundary, c->rhoPhib, sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END(c)
 }
