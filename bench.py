@@ -279,12 +279,14 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- e2e: host buffers through tcif_stage_host ------------------------------------------
     e2e = None
+    extra = {}
     if not args.no_e2e:
         def pin(a):
             b = abi.pinned_empty(a.shape)
             b[...] = a
             return b
-        ai = [pin(a) for a in f["alpha_i"]]; ab = [pin(a) for a in f["alpha_b"]]
+        ai0 = [np.array(a) for a in f["alpha_i"]]; ab0 = [np.array(a) for a in f["alpha_b"]]
+        ai = [pin(a) for a in ai0]; ab = [pin(a) for a in ab0]
         pi0 = [pin(a) for a in f["phiAlpha_i"]]; pb0 = [pin(a) for a in f["phiAlpha_b"]]
         pi = [abi.pinned_empty(a.shape) for a in pi0]; pb = [abi.pinned_empty(a.shape) for a in pb0]
         Ti, Tb, phii, phib = pin(f["T_i"]), pin(f["T_b"]), pin(f["phi_i"]), pin(f["phi_b"])
@@ -292,23 +294,59 @@ def run_ours(args, rank, world, local_rank):
         h2d = 8 * (P * (nC + nBF) + (nC + nBF) + (nIF + nBF) + P * (nIF + nBF))
         d2h = 8 * (3 * (nC + nBF) + P * (nC + nBF) + P * (nIF + nBF))
 
-        def one():
-            for p in range(P):          # the HO flux is an input every step (alphaPhi overwrites the buffer)
-                pi[p][...] = pi0[p]; pb[p][...] = pb0[p]
-            ctx.stage_host(dt, ai, ab, Ti, Tb, phii, phib, pi, pb, Fi, Fb)
-        with torch.cuda.stream(stream):
-            one()
-            barrier()
-            tw = time.perf_counter()
-            for _ in range(args.e2e_steps):
-                one()
-            barrier()
-            e2e_s = max_over_ranks(time.perf_counter() - tw)
+        def timed_host(fn, n):
+            with torch.cuda.stream(stream):
+                fn()
+                barrier()
+                tw = time.perf_counter()
+                for _ in range(n):
+                    fn()
+                barrier()
+                return max_over_ranks(time.perf_counter() - tw)
+
+        # (1) exactly the stage the device-resident number times: every field it consumes comes from host
+        #     memory and every field it produces goes back, pipelined over separate copy streams
+        e2e_s = timed_host(lambda: ctx.stage_host(dt, ai, ab, Ti, Tb, phii, phib, pi0, pb0, pi, pb, Fi, Fb), args.e2e_steps)
         e2e = {"value": total_cells * args.e2e_steps / e2e_s / 1e6, "unit": UNIT,
                "h2d_bytes_per_step": int(sum_over_ranks(h2d)), "d2h_bytes_per_step": int(sum_over_ranks(d2h)),
                "steps": args.e2e_steps, "ms_per_step": 1e3 * e2e_s / args.e2e_steps,
-               "api": "tcif_stage_host (pinned host buffers; includes the host-side refresh of the HO-flux input)"}
-        del ai, ab, pi, pb, pi0, pb0, Ti, Tb, phii, phib, Fi, Fb
+               "api": "tcif_stage_host: H2D alpha[P],T,phi,phiAlphaCorr[P]; D2H F,alpha[P],alphaPhi[P]; pinned host "
+                      "buffers, uploads/compute/downloads pipelined"}
+        # (2) the reference's own call surface: fluid.solve() (flux assembly + implicit predictor + MULES + rhoPhi,
+        #     all on the device) then fluid.divCapillaryStress(): more work per step, fewer bytes over PCIe
+        ctx.set_cell_centres(np.asarray(f["C"]), np.asarray(f["deltab"]))
+        for p in range(P):
+            ctx.set_rho(p, (1000.0, 800.0, 1.2, 50.0)[p])
+        ctl = abi.alpha_controls(1, 1, "vanLeer", "linear", True, 1e-10, 100)
+        rpi, rpb = abi.pinned_empty((nIF,)), abi.pinned_empty((nBF,))
+
+        for p in range(P):
+            ai[p][...] = ai0[p]; ab[p][...] = ab0[p]
+        cs_s = timed_host(lambda: ctx.time_step_host(ctl, dt, ai, ab, Ti, Tb, phii, phib, rpi, rpb, Fi, Fb), args.e2e_steps)
+        sweeps = [int(abi.lib().tcif_predictor_sweeps(ctx.h, p)) for p in range(P)]
+        extra["e2e_call_surface"] = {
+            "value": total_cells * args.e2e_steps / cs_s / 1e6, "unit": UNIT, "ms_per_step": 1e3 * cs_s / args.e2e_steps,
+            "h2d_bytes_per_step": int(sum_over_ranks(8 * ((P + 1) * (nC + nBF) + nIF + nBF))),
+            "d2h_bytes_per_step": int(sum_over_ranks(8 * ((P + 3) * (nC + nBF) + nIF + nBF))),
+            "api": "tcif_time_step_host = multiphaseSystem::solve() (vanLeer + linear compression, implicit upwind "
+                   "predictor, nAlphaCorr 1) + divCapillaryStress(); H2D alpha[P],T,phi; D2H alpha[P],rhoPhi,F",
+            "predictor_sweeps": sweeps}
+        # device-resident cost of that call surface
+        with torch.cuda.stream(stream):
+            ctx.solve_alphas(ctl, dt)
+            barrier()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record(stream)
+            for _ in range(args.e2e_steps):
+                ctx.solve_alphas(ctl, dt)
+                ctx.div_capillary_stress()
+            s1.record(stream)
+            barrier()
+            sm = max_over_ranks(s0.elapsed_time(s1))
+        extra["solve_plus_force_device"] = {"value": total_cells * args.e2e_steps / (sm * 1e-3) / 1e6, "unit": UNIT,
+                                            "ms_per_step": sm / args.e2e_steps,
+                                            "what": "tcif_solve_alphas + tcif_div_capillary_stress on resident fields"}
+        del ai, ab, pi, pb, pi0, pb0, Ti, Tb, phii, phib, Fi, Fb, rpi, rpb
 
     stats = [ctx.alpha_stats(p) for p in range(P)]
     dev_bytes = ctx.device_bytes
@@ -334,7 +372,7 @@ def run_ours(args, rank, world, local_rank):
                            "l2": "inputs larger than L2 (no flush needed)" if dev_bytes > 4 * 126e6 else
                                  "L2-resident case: latency-bound, no roofline claim",
                            "device_bytes_per_gpu": dev_bytes, "setup_s": round(setup_s, 1)},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+                "clocks": clocks, "e2e": e2e, **extra, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
                 "alpha_stats": [{"sumValpha": s[0], "min": s[1], "max": s[2]} for s in stats]}
         print(json.dumps(line), flush=True)
     if world > 1:

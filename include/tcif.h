@@ -157,13 +157,17 @@ TCIF_API int tcif_mules_explicit_solve(tcif_ctx *ctx, int phase, double deltaT);
  * one solveAlphas corrector over all phases (limit(returnCorr) x P, limitSum, per phase
  * phiAlpha += upwind flux; explicitSolve).  alpha0 := alpha at entry. */
 TCIF_API int tcif_stage(tcif_ctx *ctx, double deltaT);
-/* Same through host buffers (uploads alpha[P], T, phi, phiAlpha[P]; downloads F, alpha[P],
- * alphaPhi[P]); boundary arrays may be NULL when nBoundaryFaces == 0. */
+/* Same through host buffers, pipelined: uploads (alpha[P], T first; phi, phiAlphaCorr[P] behind them), the
+ * force, the download of F, the MULES corrector and the downloads of alpha[P], alphaPhi[P] overlap on
+ * separate copy streams.  alpha is in/out; phiAlphaCorr (multiphaseSystem.C:203-216) is read-only and
+ * alphaPhi (phase.alphaPhi(), :377) a separate output, as in the reference.  Use pinned buffers
+ * (tcif_host_alloc) for the copies to be asynchronous.  Boundary arrays may be NULL when nBoundaryFaces == 0. */
 TCIF_API int tcif_stage_host(tcif_ctx *ctx, double deltaT,
                              double *const *alphaInternal, double *const *alphaBoundary,
                              const double *Tinternal, const double *Tboundary,
                              const double *phiInternal, const double *phiBoundary,
-                             double *const *phiAlphaInternal, double *const *phiAlphaBoundary,
+                             const double *const *phiAlphaCorrInternal, const double *const *phiAlphaCorrBoundary,
+                             double *const *alphaPhiInternal, double *const *alphaPhiBoundary,
                              double *Finternal, double *Fboundary);
 
 /* ---- rest of multiphaseSystem::solveAlphas() on the device --------- */
@@ -199,6 +203,16 @@ TCIF_API int tcif_predictor_sweeps(const tcif_ctx *ctx, int phase);
  * limitSum, predictor, explicitSolve, rhoPhi, renormalisation, on the resident alpha, phi, Su/Sp. */
 TCIF_API int tcif_solve_alphas(tcif_ctx *ctx, const tcif_alpha_controls *ctl, double deltaT);
 TCIF_API int tcif_get_rho_phi(tcif_ctx *ctx, double *internal, double *boundary);
+/* The reference's call surface in one pipelined host-buffer call: fluid.solve() (thermocapillaryInterFoam.C:105)
+ * followed by fluid.divCapillaryStress() on the new alpha (UEqn.H:29).  alpha in/out; T, phi in; rhoPhi, F out;
+ * alphaPhi optional (NULL = not downloaded).  Su/Sp, rho, cAlpha, sigma as set on the context. */
+TCIF_API int tcif_time_step_host(tcif_ctx *ctx, const tcif_alpha_controls *ctl, double deltaT,
+                                 double *const *alphaInternal, double *const *alphaBoundary,
+                                 const double *Tinternal, const double *Tboundary,
+                                 const double *phiInternal, const double *phiBoundary,
+                                 double *const *alphaPhiInternal, double *const *alphaPhiBoundary,
+                                 double *rhoPhiInternal, double *rhoPhiBoundary,
+                                 double *Finternal, double *Fboundary);
 
 /* Logging scalars of multiphaseSystem.C:408-425: sum(V*alpha), min, max (global over ranks). */
 TCIF_API int tcif_alpha_stats(tcif_ctx *ctx, int phase, double out3[3]);

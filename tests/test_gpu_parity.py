@@ -132,9 +132,12 @@ def test_stage_host_roundtrip():
     f = cases.synthetic_fields(spec, m)
     ctx = _ctx(m, spec, f)
     ai = [x.copy() for x in f["alpha_i"]]; ab = [x.copy() for x in f["alpha_b"]]
-    pi = [x.copy() for x in f["phiAlpha_i"]]; pb = [x.copy() for x in f["phiAlpha_b"]]
+    pi = [np.zeros(m.nIF) for _ in range(2)]; pb = [np.zeros(m.nBF) for _ in range(2)]
     Fi, Fb = np.zeros((m.nCells, 3)), np.zeros((m.nBF, 3))
-    ctx.stage_host(f["deltaT"], ai, ab, f["T_i"], f["T_b"], f["phi_i"], f["phi_b"], pi, pb, Fi, Fb)
+    ctx.stage_host(f["deltaT"], ai, ab, f["T_i"], f["T_b"], f["phi_i"], f["phi_b"], f["phiAlpha_i"], f["phiAlpha_b"],
+                   pi, pb, Fi, Fb)
+    ctx.stage_host(f["deltaT"], [x.copy() for x in f["alpha_i"]], [x.copy() for x in f["alpha_b"]], f["T_i"], f["T_b"],
+                   f["phi_i"], f["phi_b"], f["phiAlpha_i"], f["phiAlpha_b"], pi, pb, Fi, Fb)   # repeatable: inputs untouched
     ref = orc.stage(m, orc.mules_cfg(3), f["alpha_i"], f["alpha_b"], f["alphaBc"], f["sigma"], f["T_i"], f["T_b"],
                     f["phi_i"], f["phi_b"], f["phiAlpha_i"], f["phiAlpha_b"], f["deltaT"])
     assert_field_close(Fi, ref["F_i"], "force")

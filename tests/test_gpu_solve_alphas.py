@@ -182,3 +182,26 @@ def test_solve_alphas_decomposed_matches_serial():
     for c in ctxs:
         c.close()
     grp.close()
+
+
+def test_time_step_host_matches_oracle():
+    spec = cases.case(5, 12)
+    m = global_mesh(spec)
+    f = cases.synthetic_fields(spec, m)
+    ctx = _ctx(m, spec, f)
+    ctl = abi.alpha_controls(1, 1, "vanLeer", "linear", True, 1e-13, 300)
+    ai = [x.copy() for x in f["alpha_i"]]; ab = [x.copy() for x in f["alpha_b"]]
+    ri, rb, Fi, Fb = np.zeros(m.nIF), np.zeros(m.nBF), np.zeros((m.nCells, 3)), np.zeros((m.nBF, 3))
+    pi = [np.zeros(m.nIF) for _ in range(3)]; pb = [np.zeros(m.nBF) for _ in range(3)]
+    ctx.time_step_host(ctl, f["deltaT"], ai, ab, f["T_i"], f["T_b"], f["phi_i"], f["phi_b"], ri, rb, Fi, Fb, pi, pb)
+    ref = orc.solve(m, orc.mules_cfg(3), orc.alpha_ctl(1, 1, "vanLeer", "linear", True, 1e-13, 300), f["alpha_i"],
+                    f["alpha_b"], f["alphaBc"], f["phi_i"], f["phi_b"], f["deltaT"], RHO[:3])
+    Fr, Fbr = orc.div_capillary_stress(m, ref["alpha_i"], ref["alpha_b"], f["alphaBc"], f["sigma"], f["T_i"], f["T_b"])
+    for p in range(3):
+        assert_field_close(ai[p], ref["alpha_i"][p], f"alpha{p}")
+        assert_field_close(ab[p], ref["alpha_b"][p], f"alpha{p} boundary")
+        assert_field_close(pi[p], ref["alphaPhi_i"][p], f"alphaPhi{p}")
+    assert_field_close(ri, ref["rhoPhi_i"], "rhoPhi")
+    assert_field_close(Fi, Fr, "force on the new alpha")
+    assert_field_close(Fb, Fbr, "force boundary")
+    ctx.close()

@@ -330,12 +330,15 @@ class Context:
     def stage(self, deltaT):
         self._ck(lib().tcif_stage(self.h, C.c_double(deltaT)))
 
-    def stage_host(self, deltaT, alphas_i, alphas_b, Ti, Tb, phii, phib, phiAlpha_i, phiAlpha_b, Fi, Fb):
-        """In-place on the given float64 C-contiguous arrays (alphas and phiAlpha are in/out)."""
-        for a in list(alphas_i) + list(alphas_b) + list(phiAlpha_i) + list(phiAlpha_b) + [Fi, Fb]:
+    def stage_host(self, deltaT, alphas_i, alphas_b, Ti, Tb, phii, phib, phiAlpha_i, phiAlpha_b, alphaPhi_i, alphaPhi_b,
+                   Fi, Fb):
+        """alphas in/out, phiAlpha (HO flux) read-only, alphaPhi/F outputs; float64 C-contiguous arrays."""
+        for a in list(alphas_i) + list(alphas_b) + list(phiAlpha_i) + list(phiAlpha_b) + list(alphaPhi_i) + \
+                list(alphaPhi_b) + [Fi, Fb]:
             assert a.dtype == np.float64 and a.flags.c_contiguous
         self._ck(lib().tcif_stage_host(self.h, C.c_double(deltaT), _pp(alphas_i), _pp(alphas_b), _d(Ti), _d(Tb),
-                                       _d(phii), _d(phib), _pp(phiAlpha_i), _pp(phiAlpha_b), _d(Fi), _d(Fb)))
+                                       _d(phii), _d(phib), _pp(phiAlpha_i), _pp(phiAlpha_b), _pp(alphaPhi_i),
+                                       _pp(alphaPhi_b), _d(Fi), _d(Fb)))
 
     # -- rest of solveAlphas
     def set_cell_centres(self, Ccells, deltaBoundary):
@@ -367,6 +370,14 @@ class Context:
 
     def solve_alphas(self, ctl: AlphaControls, deltaT):
         self._ck(lib().tcif_solve_alphas(self.h, C.byref(ctl), C.c_double(deltaT)))
+
+    def time_step_host(self, ctl, deltaT, alphas_i, alphas_b, Ti, Tb, phii, phib, rhoPhi_i, rhoPhi_b, Fi, Fb,
+                       alphaPhi_i=None, alphaPhi_b=None):
+        """solve() + divCapillaryStress() with host buffers (alphas in/out; rhoPhi, F, optional alphaPhi out)."""
+        self._ck(lib().tcif_time_step_host(self.h, C.byref(ctl), C.c_double(deltaT), _pp(alphas_i), _pp(alphas_b), _d(Ti),
+                                           _d(Tb), _d(phii), _d(phib), _pp(alphaPhi_i) if alphaPhi_i else None,
+                                           _pp(alphaPhi_b) if alphaPhi_b else None, _d(rhoPhi_i), _d(rhoPhi_b), _d(Fi),
+                                           _d(Fb)))
 
     def get_rho_phi(self):
         a, b = np.empty(self.nIF), np.empty(self.nBF)

@@ -164,7 +164,11 @@ def synthetic_fields(spec: CaseSpec, mesh) -> dict:
             b[k] = phib[k] * (mesh.wb[k] * ai[p][fc[k]] + (1.0 - mesh.wb[k]) * ab[p][k])
         pab.append(b)
     bc = np.full((P, len(mesh.patchType)), BC_ZERO_GRADIENT, np.int32)
-    return dict(alpha_i=ai, alpha_b=ab, T_i=Ti, T_b=Tb, phi_i=phii, phi_b=phib, phiAlpha_i=pai, phiAlpha_b=pab,
+    deltab = (np.asarray(mesh.Cfb) - np.asarray(mesh.C)[fc]) if nBF else np.zeros((0, 3))      # fvPatch::delta()
+    if coupled.any():
+        k = np.nonzero(coupled)[0]
+        deltab[k] = np.asarray(mesh.nbrC)[k] - np.asarray(mesh.C)[fc[k]]
+    return dict(C=np.array(mesh.C), deltab=deltab, alpha_i=ai, alpha_b=ab, T_i=Ti, T_b=Tb, phi_i=phii, phi_b=phib, phiAlpha_i=pai, phiAlpha_b=pab,
                 alphaBc=bc, sigma=spec.sigma, deltaT=spec.deltaT)
 
 

@@ -124,6 +124,10 @@ struct tcif_ctx {
     // O(surface) work (halo exchange + boundary-cell kernels) runs on `side`, concurrently with the
     // O(volume) sweep on `stream`; evV/evB order the two (see sweep()).
     cudaStream_t side = nullptr;
+    // host-buffer entry points: uploads on sIn, downloads on sOut, overlapped with compute (PCIe is full duplex)
+    cudaStream_t sIn = nullptr, sOut = nullptr;
+    cudaEvent_t evIn[2]{}, evC[2]{};
+    double *stagingOut = nullptr;
     cudaEvent_t evV = nullptr, evB = nullptr;
     bool noOverlap = false;
     // host copy of the small mesh tables
@@ -944,10 +948,14 @@ void store_old(tcif_ctx *c) {
         CUDA_OK(cudaMemcpyAsync(c->alpha0[p], c->alpha[p], sizeof(double) * c->nC, cudaMemcpyDeviceToDevice, c->stream));
 }
 
+void do_mules_stage(tcif_ctx *c, double deltaT);
 void do_stage(tcif_ctx *c, double deltaT) {
     if (!(deltaT > 0)) failf("tcif_stage: deltaT must be positive");
-    int all[4] = {0, 1, 2, 3};
     do_force(c);
+    do_mules_stage(c, deltaT);
+}
+void do_mules_stage(tcif_ctx *c, double deltaT) {
+    int all[4] = {0, 1, 2, 3};
     store_old(c);
     do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true);      // multiphaseSystem.C:296-319
     do_limit_sum(c);                                            // :321
@@ -1151,6 +1159,9 @@ void tcif_destroy(tcif_ctx *c) {
     for (auto &e : c->evPool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (void *p : c->allocs) cudaFree(p);
     if (c->h_small) cudaFreeHost(c->h_small);
+    if (c->sIn) cudaStreamDestroy(c->sIn);
+    if (c->sOut) cudaStreamDestroy(c->sOut);
+    for (int i = 0; i < 2; ++i) { if (c->evIn[i]) cudaEventDestroy(c->evIn[i]); if (c->evC[i]) cudaEventDestroy(c->evC[i]); }
     if (c->evV) cudaEventDestroy(c->evV);
     if (c->evB) cudaEventDestroy(c->evB);
     if (c->side && !c->noOverlap) cudaStreamDestroy(c->side);
@@ -1436,24 +1447,162 @@ int tcif_stage(tcif_ctx *c, double deltaT) {
     API_END(c)
 }
 
+// Pipelined host-buffer stage: [H2D alpha,T] -> force -> [D2H F || H2D phi, phiAlpha] -> MULES -> [D2H alpha, alphaPhi]
 int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const *ab, const double *Ti, const double *Tb,
-                    const double *phii, const double *phib, double *const *pai, double *const *pab, double *Fi, double *Fb) {
+                    const double *phii, const double *phib, const double *const *pai, const double *const *pab,
+                    double *const *apo, double *const *apob, double *Fi, double *Fb) {
     API_BEGIN(c)
-    if (!ai || !pai || (c->nBF && (!ab || !pab))) failf("tcif_stage_host: null field lists");
-    for (int p = 0; p < c->P; ++p) { up_cells(c, c->alpha[p], ai[p]); if (c->nBF) up_bnd(c, c->alphab[p], ab[p]); }
-    if (Ti) { up_cells(c, c->Tc, Ti); up_bnd(c, c->Tb, Tb); c->haveT = true; }
-    if (phii || !c->nIF) { up_faces(c, c->phi, phii); up_bnd(c, c->phib, phib); }
-    for (int p = 0; p < c->P; ++p) { up_faces(c, c->phiHO[p], pai[p]); if (c->nBF) up_bnd(c, c->phiHOb[p], pab[p]); }
-    do_stage(c, deltaT);
-    down_vec(c, Fi, c->F, c->nC, c->stride);
-    if (Fb && c->nBF) down_vec(c, Fb, c->Fb, c->nBF, c->nBF);
-    for (int p = 0; p < c->P; ++p) {
-        CUDA_OK(cudaMemcpyAsync(ai[p], c->alpha[p], sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
-        if (c->nBF) CUDA_OK(cudaMemcpyAsync(ab[p], c->alphab[p], sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
-        down_faces(c, pai[p], c->phiPsi[p]);
-        if (c->nBF) CUDA_OK(cudaMemcpyAsync(pab[p], c->phiPsib[p], sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
+    if (!ai || !pai || !apo || (c->nBF && (!ab || !pab || !apob))) failf("tcif_stage_host: null field lists");
+    if (!(deltaT > 0)) failf("tcif_stage_host: deltaT must be positive");
+    if (!c->sIn) {
+        CUDA_OK(cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking));
+        CUDA_OK(cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            CUDA_OK(cudaEventCreateWithFlags(&c->evIn[i], cudaEventDisableTiming));
+            CUDA_OK(cudaEventCreateWithFlags(&c->evC[i], cudaEventDisableTiming));
+        }
+        c->stagingOut = c->dalloc<double>(c->stagingDoubles);
     }
+    join(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    const size_t cb = sizeof(double) * c->nC, bb = sizeof(double) * c->nBF, fb = sizeof(double) * c->nIF;
+    cudaStream_t in = c->sIn, out = c->sOut;
+    auto upFaces = [&](double *dst, const double *src) {
+        if (!c->nIF) return;
+        CUDA_OK(cudaMemcpyAsync(c->staging, src, fb, cudaMemcpyDefault, in));
+        k_face_scatter<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, in>>>(c->nIF, c->d_faceMap, c->staging, dst);
+        c->launches++;
+    };
+    // group A: what the force needs
+    for (int p = 0; p < c->P; ++p) {
+        CUDA_OK(cudaMemcpyAsync(c->alpha[p], ai[p], cb, cudaMemcpyDefault, in));
+        if (c->nBF) CUDA_OK(cudaMemcpyAsync(c->alphab[p], ab[p], bb, cudaMemcpyDefault, in));
+    }
+    if (Ti) {
+        CUDA_OK(cudaMemcpyAsync(c->Tc, Ti, cb, cudaMemcpyDefault, in));
+        if (c->nBF && Tb) CUDA_OK(cudaMemcpyAsync(c->Tb, Tb, bb, cudaMemcpyDefault, in));
+        c->haveT = true;
+    }
+    CUDA_OK(cudaEventRecord(c->evIn[0], in));
+    // group B: what MULES needs, streaming in while the force runs
+    if (phii || !c->nIF) { upFaces(c->phi, phii); if (c->nBF && phib) CUDA_OK(cudaMemcpyAsync(c->phib, phib, bb, cudaMemcpyDefault, in)); }
+    for (int p = 0; p < c->P; ++p) {
+        upFaces(c->phiHO[p], pai[p]);
+        if (c->nBF) CUDA_OK(cudaMemcpyAsync(c->phiHOb[p], pab[p], bb, cudaMemcpyDefault, in));
+    }
+    CUDA_OK(cudaEventRecord(c->evIn[1], in));
+    // force
+    CUDA_OK(cudaStreamWaitEvent(c->stream, c->evIn[0], 0));
+    do_force(c);
+    CUDA_OK(cudaEventRecord(c->evC[0], c->stream));
+    CUDA_OK(cudaStreamWaitEvent(out, c->evC[0], 0));
+    k_soa_to_aos3<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nC, (size_t)c->stride, c->F, c->stagingOut);
+    c->launches++;
+    CUDA_OK(cudaMemcpyAsync(Fi, c->stagingOut, 3 * cb, cudaMemcpyDefault, out));
+    if (Fb && c->nBF) {
+        k_soa_to_aos3<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nBF, (size_t)c->nBF, c->Fb, c->stagingOut);
+        c->launches++;
+        CUDA_OK(cudaMemcpyAsync(Fb, c->stagingOut, 3 * bb, cudaMemcpyDefault, out));
+    }
+    // MULES corrector
+    CUDA_OK(cudaStreamWaitEvent(c->stream, c->evIn[1], 0));
+    do_mules_stage(c, deltaT);
+    CUDA_OK(cudaEventRecord(c->evC[1], c->stream));
+    CUDA_OK(cudaStreamWaitEvent(out, c->evC[1], 0));
+    for (int p = 0; p < c->P; ++p) {
+        CUDA_OK(cudaMemcpyAsync(ai[p], c->alpha[p], cb, cudaMemcpyDefault, out));
+        if (c->nBF) CUDA_OK(cudaMemcpyAsync(ab[p], c->alphab[p], bb, cudaMemcpyDefault, out));
+    }
+    for (int p = 0; p < c->P; ++p) {
+        if (c->nIF) {
+            k_face_gather<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nIF, c->d_faceMap, c->phiPsi[p], c->stagingOut);
+            c->launches++;
+            CUDA_OK(cudaMemcpyAsync(apo[p], c->stagingOut, fb, cudaMemcpyDefault, out));
+        }
+        if (c->nBF) CUDA_OK(cudaMemcpyAsync(apob[p], c->phiPsib[p], bb, cudaMemcpyDefault, out));
+    }
+    CUDA_OK(cudaStreamSynchronize(out));
+    CUDA_OK(cudaStreamSynchronize(in));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    CUDA_OK(cudaGetLastError());
+    API_END(c)
+}
+
+// The reference's own call surface with host buffers: fluid.solve() (thermocapillaryInterFoam.C:105) then
+// fluid.divCapillaryStress() on the new alpha (UEqn.H:29 / thermocapillaryInterFoam.C:150), pipelined.
+int tcif_time_step_host(tcif_ctx *c, const tcif_alpha_controls *ctl, double deltaT, double *const *ai, double *const *ab,
+                        const double *Ti, const double *Tb, const double *phii, const double *phib,
+                        double *const *apo, double *const *apob, double *rpi, double *rpb, double *Fi, double *Fb) {
+    API_BEGIN(c)
+    if (!ai || (c->nBF && !ab) || !phii) failf("tcif_time_step_host: null field lists");
+    if (!c->sIn) {
+        CUDA_OK(cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking));
+        CUDA_OK(cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            CUDA_OK(cudaEventCreateWithFlags(&c->evIn[i], cudaEventDisableTiming));
+            CUDA_OK(cudaEventCreateWithFlags(&c->evC[i], cudaEventDisableTiming));
+        }
+        c->stagingOut = c->dalloc<double>(c->stagingDoubles);
+    }
+    join(c);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    const size_t cb = sizeof(double) * c->nC, bb = sizeof(double) * c->nBF, fb = sizeof(double) * c->nIF;
+    cudaStream_t in = c->sIn, out = c->sOut;
+    for (int p = 0; p < c->P; ++p) {
+        CUDA_OK(cudaMemcpyAsync(c->alpha[p], ai[p], cb, cudaMemcpyDefault, in));
+        if (c->nBF) CUDA_OK(cudaMemcpyAsync(c->alphab[p], ab[p], bb, cudaMemcpyDefault, in));
+    }
+    if (c->nIF) {
+        CUDA_OK(cudaMemcpyAsync(c->staging, phii, fb, cudaMemcpyDefault, in));
+        k_face_scatter<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, in>>>(c->nIF, c->d_faceMap, c->staging, c->phi);
+        c->launches++;
+    }
+    if (c->nBF && phib) CUDA_OK(cudaMemcpyAsync(c->phib, phib, bb, cudaMemcpyDefault, in));
+    CUDA_OK(cudaEventRecord(c->evIn[0], in));
+    if (Ti) {
+        CUDA_OK(cudaMemcpyAsync(c->Tc, Ti, cb, cudaMemcpyDefault, in));
+        if (c->nBF && Tb) CUDA_OK(cudaMemcpyAsync(c->Tb, Tb, bb, cudaMemcpyDefault, in));
+        c->haveT = true;
+    }
+    CUDA_OK(cudaEventRecord(c->evIn[1], in));
+    CUDA_OK(cudaStreamWaitEvent(c->stream, c->evIn[0], 0));
+    do_solve_alphas(c, ctl, deltaT);
+    CUDA_OK(cudaEventRecord(c->evC[0], c->stream));
+    CUDA_OK(cudaStreamWaitEvent(out, c->evC[0], 0));
+    for (int p = 0; p < c->P; ++p) {
+        CUDA_OK(cudaMemcpyAsync(ai[p], c->alpha[p], cb, cudaMemcpyDefault, out));
+        if (c->nBF) CUDA_OK(cudaMemcpyAsync(ab[p], c->alphab[p], bb, cudaMemcpyDefault, out));
+    }
+    auto downFaces = [&](double *dst, const double *src) {
+        if (!c->nIF || !dst) return;
+        k_face_gather<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nIF, c->d_faceMap, src, c->stagingOut);
+        c->launches++;
+        CUDA_OK(cudaMemcpyAsync(dst, c->stagingOut, fb, cudaMemcpyDefault, out));
+    };
+    downFaces(rpi, c->rhoPhi);
+    if (rpb && c->nBF) CUDA_OK(cudaMemcpyAsync(rpb, c->rhoPhib, bb, cudaMemcpyDefault, out));
+    if (apo) for (int p = 0; p < c->P; ++p) {
+        downFaces(apo[p], c->phiPsi[p]);
+        if (apob && c->nBF) CUDA_OK(cudaMemcpyAsync(apob[p], c->phiPsib[p], bb, cudaMemcpyDefault, out));
+    }
+    CUDA_OK(cudaStreamWaitEvent(c->stream, c->evIn[1], 0));
+    do_force(c);
+    CUDA_OK(cudaEventRecord(c->evC[1], c->stream));
+    CUDA_OK(cudaStreamWaitEvent(out, c->evC[1], 0));
+    if (Fi) {
+        k_soa_to_aos3<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nC, (size_t)c->stride, c->F, c->stagingOut);
+        c->launches++;
+        CUDA_OK(cudaMemcpyAsync(Fi, c->stagingOut, 3 * cb, cudaMemcpyDefault, out));
+    }
+    if (Fb && c->nBF) {
+        k_soa_to_aos3<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nBF, (size_t)c->nBF, c->Fb, c->stagingOut);
+        c->launches++;
+        CUDA_OK(cudaMemcpyAsync(Fb, c->stagingOut, 3 * bb, cudaMemcpyDefault, out));
+    }
+    CUDA_OK(cudaStreamSynchronize(out));
+    CUDA_OK(cudaStreamSynchronize(in));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    CUDA_OK(cudaGetLastError());
     API_END(c)
 }
 
