@@ -1,0 +1,53 @@
+"""Golden fixtures (tests/golden/*.npz, written by tests/golden/make_golden.py from the oracle):
+the oracle must keep reproducing them (CPU; 1e-13 -- the synthetic inputs go through numpy's tanh/sin, whose last
+bit may differ between host CPUs), and the CUDA path must match them within the 1e-12 contract (GPU)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+import make_golden as mg  # noqa: E402
+from thermocapillaryinterfoam_b200 import abi, cases  # noqa: E402
+from helpers import assert_field_close, global_mesh   # noqa: E402
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.mark.parametrize("name,config,n", mg.CASES)
+def test_oracle_reproduces_golden(name, config, n):
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    got = mg.build(config, n)
+    assert set(z.files) == set(got)
+    for k in z.files:
+        assert_field_close(got[k], z[k], k, rtol=1e-13)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,config,n", mg.CASES)
+def test_cuda_path_matches_golden(name, config, n):
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    spec = cases.case(config, n)
+    m = global_mesh(spec)
+    f = cases.synthetic_fields(spec, m)
+    P = spec.nPhases
+    ctx = abi.Context(m, P)
+    cases.load_case(ctx, spec, f)
+    ctx.stage(f["deltaT"])
+    assert_field_close(ctx.get_force()[0], z["stage_F_i"], "force")
+    for p in range(P):
+        assert_field_close(ctx.get_alpha(p)[0], z[f"stage_alpha_i{p}"], f"alpha{p}")
+        assert_field_close(ctx.get_phi_alpha(p)[0], z[f"stage_alphaPhi_i{p}"], f"alphaPhi{p}")
+    ctx.close()
+    ctx = abi.Context(m, P)
+    cases.load_case(ctx, spec, f)
+    ctx.set_cell_centres(f["C"], f["deltab"])
+    for p in range(P):
+        ctx.set_rho(p, mg.RHO[p])
+    ctx.solve_alphas(abi.alpha_controls(2, 1, "vanLeer", "linear", True, 1e-13, 300), f["deltaT"])
+    for p in range(P):
+        assert_field_close(ctx.get_alpha(p)[0], z[f"solve_alpha_i{p}"], f"solve alpha{p}")
+        assert_field_close(ctx.get_phi_alpha(p)[0], z[f"solve_alphaPhi_i{p}"], f"solve alphaPhi{p}")
+    assert_field_close(ctx.get_rho_phi()[0], z["solve_rhoPhi_i"], "rhoPhi")
+    ctx.close()
