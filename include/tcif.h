@@ -140,6 +140,14 @@ TCIF_API int tcif_get_force(tcif_ctx *ctx, double *internal, double *boundary);
 TCIF_API int tcif_div_capillary_stress_host(tcif_ctx *ctx, const double *const *alphaInternal,
                                             const double *const *alphaBoundary, const double *Tinternal,
                                             const double *Tboundary, double *Finternal, double *Fboundary);
+/* fvc::flux(fluid.divCapillaryStress()) = linear(F) & Sf, the form pEqn.H:31-38 consumes: [nInternalFaces],
+ * [nBoundaryFaces].  The force itself is re-evaluated only when alpha, T or sigma changed since the last
+ * evaluation: the solver asks for it 2-4 times per time step on unchanged fields (UEqn.H:29, pEqn.H:35 per
+ * corrector, thermocapillaryInterFoam.C:150) and the reference recomputes it from scratch every time. */
+TCIF_API int tcif_flux_of_force(tcif_ctx *ctx, double *internal, double *boundary);
+/* Switch that cache off/on (default on) and read how often F was computed vs served from the cache. */
+TCIF_API int tcif_set_force_cache(tcif_ctx *ctx, int on);
+TCIF_API int tcif_force_counters(const tcif_ctx *ctx, int64_t *evaluations, int64_t *cacheHits);
 /* fvc::grad(alpha.<phase>) with Gauss linear (phaseSystem.C:1076-1077): [nCells*3], [nBF*3]. */
 TCIF_API int tcif_grad_alpha(tcif_ctx *ctx, int phase, double *internal, double *boundary);
 

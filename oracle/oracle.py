@@ -395,3 +395,12 @@ def solve(m, cfg, ctl, alphas_i, alphas_b, alphaBc, phii, phib, deltaT, rho, cAl
                     _d(phii), _d(phib), _d(cA), _d(rho), None, None, _pp(su) if su else None, _pp(sp) if sp else None,
                     C.c_double(deltaT), _pp(pi), _pp(pb), _d(ri), _d(rb))
     return dict(alpha_i=ai, alpha_b=ab, alphaPhi_i=pi, alphaPhi_b=pb, rhoPhi_i=ri, rhoPhi_b=rb)
+
+
+def flux_of_vector(m, Fi, Fb):
+    """fvc::flux(F) = interpolate(F) & Sf."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    Fi, Fb = f64(Fi), f64(Fb)
+    oi, ob = np.zeros(h.s.nIF), np.zeros(h.s.nBF)
+    lib().orc_flux_of_vector(h.ref, _d(Fi), _d(Fb), _d(oi), _d(ob))
+    return oi, ob

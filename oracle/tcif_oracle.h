@@ -237,6 +237,9 @@ void orc_solve(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg, c
                const double *const *Su, const double *const *Sp, double deltaT,
                double *const *alphaPhii, double *const *alphaPhib, double *rhoPhii, double *rhoPhib);
 
+/* fvc::flux(volVectorField) with linear interpolation (pEqn.H:31-38 consumes divCapillaryStress() this way). */
+void orc_flux_of_vector(const orc_mesh *m, const double *Fi, const double *Fb, double *outi, double *outb);
+
 #ifdef __cplusplus
 }
 #endif

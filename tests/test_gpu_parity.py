@@ -188,3 +188,29 @@ def test_errors_are_loud():
     with pytest.raises(abi.TcifError):
         abi.Context(m, 7)
     ctx.close()
+
+
+def test_flux_of_force_and_cache():
+    """fvc::flux(divCapillaryStress()) as pEqn.H:35 consumes it; F is recomputed only when alpha/T/sigma change."""
+    spec = cases.case(5, 14)
+    m = global_mesh(spec)
+    f = cases.synthetic_fields(spec, m)
+    ctx = _ctx(m, spec, f)
+    Ri, Rb = orc.div_capillary_stress(m, f["alpha_i"], f["alpha_b"], f["alphaBc"], f["sigma"], f["T_i"], f["T_b"])
+    ri, rb = orc.flux_of_vector(m, Ri, Rb)
+    gi, gb = ctx.flux_of_force()
+    assert_field_close(gi, ri, "flux(F)")
+    assert_field_close(gb, rb, "flux(F) boundary")
+    assert ctx.force_counters() == (1, 0)
+    ctx.div_capillary_stress(); ctx.flux_of_force()
+    assert ctx.force_counters() == (1, 2)                     # same alpha, T: served from the cache
+    ctx.set_temperature(f["T_i"] + 1.0, f["T_b"] + 1.0)       # sigma(T) changed
+    ctx.div_capillary_stress()
+    assert ctx.force_counters() == (2, 2)
+    ctx.stage(f["deltaT"])                                    # its force is a hit; then MULES moves alpha
+    ctx.div_capillary_stress()
+    assert ctx.force_counters() == (3, 3)
+    ctx.set_force_cache(False)
+    ctx.div_capillary_stress()
+    assert ctx.force_counters() == (4, 3)
+    ctx.close()

@@ -329,3 +329,13 @@ def test_k7_limit_sum_hand_vectors():
     out, _ = orc.mules_limit_sum(m, c, zb)
     assert [o[0] for o in out] == [1.0, -0.75, -0.25]          # sum < 0: negatives scaled by -sumPos/sumNeg
     assert sum(o[0] for o in out) == 0.0
+
+
+def test_flux_of_vector_uniform_and_linear():
+    m = mo.box_mesh(5, 4, 3, (1.0, 1.0, 1.0), (0,) * 6, (2.0, None, 0.5))
+    F0 = np.array([0.3, -1.2, 0.7])
+    fi, fb = orc.flux_of_vector(m, np.tile(F0, (m.nCells, 1)), np.tile(F0, (m.nBF, 1)))
+    assert np.allclose(fi, m.Sf @ F0, rtol=1e-15, atol=1e-18) and np.allclose(fb, m.Sfb @ F0, rtol=1e-15, atol=1e-18)
+    A = np.array([[1.0, 2.0, 0.0], [0.0, -1.0, 3.0], [0.5, 0.0, 1.0]])
+    fi, _ = orc.flux_of_vector(m, m.C @ A.T, m.Cfb @ A.T)
+    assert np.allclose(fi, np.einsum("ij,ij->i", m.Cf @ A.T, m.Sf), rtol=1e-13, atol=1e-16)   # linear weights: exact

@@ -310,6 +310,19 @@ class Context:
         self._ck(lib().tcif_div_capillary_stress_host(self.h, _pp(ai), _pp(ab), _d(Ti), _d(Tb), _d(Fi), _d(Fb)))
         return Fi, Fb
 
+    def flux_of_force(self):
+        a, b = np.empty(self.nIF), np.empty(self.nBF)
+        self._ck(lib().tcif_flux_of_force(self.h, _d(a), _d(b)))
+        return a, b
+
+    def set_force_cache(self, on=True):
+        self._ck(lib().tcif_set_force_cache(self.h, int(bool(on))))
+
+    def force_counters(self):
+        e, h = C.c_int64(), C.c_int64()
+        self._ck(lib().tcif_force_counters(self.h, C.byref(e), C.byref(h)))
+        return int(e.value), int(h.value)
+
     def grad_alpha(self, phase):
         gi, gb = np.empty((self.nCells, 3)), np.empty((self.nBF, 3))
         self._ck(lib().tcif_grad_alpha(self.h, int(phase), _d(gi), _d(gb)))

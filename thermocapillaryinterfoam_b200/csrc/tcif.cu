@@ -168,6 +168,12 @@ struct tcif_ctx {
     double *predDiag[4]{}, *predRhs[4]{};
     double *dmaxDev = nullptr;
     int predictorSweeps[4]{};
+    // F is a pure function of (alpha, T, sigma): the solver evaluates it 2-4x per time step on unchanged
+    // fields (UEqn.H:29, pEqn.H:35 per corrector, thermocapillaryInterFoam.C:150); fieldsVersion counts
+    // every change of those inputs and forceVersion remembers which one F was computed from
+    uint64_t fieldsVersion = 1, forceVersion = 0;
+    bool cacheForce = true;
+    int64_t forceEvaluations = 0, forceCacheHits = 0;
     double deltaN = 0.0;
     bool deltaNValid = false;
     double *staging = nullptr;
@@ -573,6 +579,8 @@ double bytes_mules_final(const tcif_ctx *c, int nPh, int mode, bool first) {
     return nPh * (double)c->nC * perCell;
 }
 
+inline void touch(tcif_ctx *c) { ++c->fieldsVersion; }   // alpha / T / sigma changed: F is stale
+
 void do_force(tcif_ctx *c) {
     if (c->Q < 1) failf("divCapillaryStress needs at least two phases");
     for (int q = 0; q < c->Q; ++q) {
@@ -580,6 +588,8 @@ void do_force(tcif_ctx *c) {
         if (c->hSig[q].kind != SIGMA_CONSTANT && !c->haveT) failf("temperatureDependent sigma without a temperature field");
     }
     require_comm(c);
+    if (c->cacheForce && c->forceVersion == c->fieldsVersion) { c->forceCacheHits++; return; }
+    c->forceEvaluations++;
     ensure_deltaN(c);
     ForceArgs a = force_args(c, true, false);
     sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, true, false), [&] { launch_grad_tensor<false, false>(c, a); }); },
@@ -605,6 +615,7 @@ void do_force(tcif_ctx *c) {
             halo_cells(c, 3, src, dst);
         }
     }
+    c->forceVersion = c->fieldsVersion;
 }
 
 // fvc::grad(alpha_p) for every phase into G / Gb (Gauss linear + gaussGrad boundary correction)
@@ -636,6 +647,7 @@ void do_grad(tcif_ctx *c) {
 
 // psi.correctBoundaryConditions() for a set of phases: zeroGradient patches + processor halo
 void correct_alpha_bcs(tcif_ctx *c, const int *phases, int nPh) {
+    touch(c);
     if (!c->nBF) return;
     for (int k = 0; k < nPh; ++k) {
         int p = phases[k];
@@ -761,6 +773,7 @@ void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode,
     else {
         fin(std::integral_constant<int, 2>{});
         for (int k = 0; k < nPh; ++k) std::swap(c->alpha[phases[k]], c->alphaNew[phases[k]]);
+        touch(c);
     }
     join(c);
 }
@@ -935,6 +948,7 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
         for (int k = 0; k < nPh; ++k) {
             if (!active[k]) continue;
             std::swap(c->alpha[phases[k]], c->alphaNew[phases[k]]);
+            touch(c);
             c->predictorSweeps[phases[k]]++;
             if (v[k] <= tol) active[k] = false;
         }
@@ -981,6 +995,7 @@ void do_rho_phi(tcif_ctx *c, double wgt, bool accumulate) {
 
 // alpha += alpha*(1 - sumAlpha), cells and patch values   (multiphaseSystem.C:414-426)
 void do_renormalise(tcif_ctx *c) {
+    touch(c);
     RenormArgs r{};
     r.P = c->P;
     for (int p = 0; p < c->P; ++p) r.a[p] = c->alpha[p];
@@ -1263,6 +1278,7 @@ int tcif_comm_init_local(tcif_ctx *c, int rank, tcif_group *g) {
 // ---- fields ---------------------------------------------------------------------------------
 int tcif_set_alpha_bc(tcif_ctx *c, int phase, const int32_t *bcKind) {
     API_BEGIN(c)
+    touch(c);
     check_phase(c, phase);
     if (c->nPatches) {
         for (int p = 0; p < c->nPatches; ++p) if (bcKind[p] != TCIF_BC_ZERO_GRADIENT && bcKind[p] != TCIF_BC_FIXED_VALUE) failf("unsupported alpha boundary condition %d on patch %d", bcKind[p], p);
@@ -1274,6 +1290,7 @@ int tcif_set_alpha_bc(tcif_ctx *c, int phase, const int32_t *bcKind) {
 
 int tcif_set_alpha(tcif_ctx *c, int phase, const double *internal, const double *boundary) {
     API_BEGIN(c)
+    touch(c);
     check_phase(c, phase);
     if (!internal || (c->nBF && !boundary)) failf("tcif_set_alpha: null field");
     up_cells(c, c->alpha[phase], internal);
@@ -1308,6 +1325,7 @@ int tcif_set_alpha_old(tcif_ctx *c, int phase, const double *internal) {
 
 int tcif_set_temperature(tcif_ctx *c, const double *internal, const double *boundary) {
     API_BEGIN(c)
+    touch(c);
     if (!internal || (c->nBF && !boundary)) failf("tcif_set_temperature: null field");
     up_cells(c, c->Tc, internal);
     up_bnd(c, c->Tb, boundary);
@@ -1318,6 +1336,7 @@ int tcif_set_temperature(tcif_ctx *c, const double *internal, const double *boun
 
 int tcif_set_sigma(tcif_ctx *c, int phase1, int phase2, int kind, int n, const double *coeffs) {
     API_BEGIN(c)
+    touch(c);
     check_phase(c, phase1); check_phase(c, phase2);
     if (phase1 == phase2) failf("tcif_set_sigma: a pair needs two different phases");
     int q = pair_index(c->P, std::min(phase1, phase2), std::max(phase1, phase2));
@@ -1395,6 +1414,7 @@ int tcif_div_capillary_stress_host(tcif_ctx *c, const double *const *ai, const d
                                    const double *Tb, double *Fi, double *Fb) {
     API_BEGIN(c)
     if (!ai || (c->nBF && !ab)) failf("tcif_div_capillary_stress_host: null alpha lists");
+    touch(c);
     for (int p = 0; p < c->P; ++p) { up_cells(c, c->alpha[p], ai[p]); if (c->nBF) up_bnd(c, c->alphab[p], ab[p]); }
     if (Ti) { up_cells(c, c->Tc, Ti); up_bnd(c, c->Tb, Tb); c->haveT = true; }
     do_force(c);
@@ -1402,6 +1422,33 @@ int tcif_div_capillary_stress_host(tcif_ctx *c, const double *const *ai, const d
     if (Fb && c->nBF) down_vec(c, Fb, c->Fb, c->nBF, c->nBF);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END(c)
+}
+
+// fvc::flux(fluid.divCapillaryStress())  (pEqn.H:31-38): F is evaluated only if alpha/T/sigma changed since
+int tcif_flux_of_force(tcif_ctx *c, double *internal, double *boundary) {
+    API_BEGIN(c)
+    do_force(c);
+    double *fl = c->phiCorr[0], *flb = c->phiCorrb[0];       // scratch surface field (MULES work array, free between limits)
+    k_flux_of_force<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->F, fl);
+    c->launches++;
+    if (c->nBF) { k_flux_of_force_bnd<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->F, c->Fb, flb); c->launches++; }
+    if (internal) down_faces(c, internal, fl);
+    if (boundary && c->nBF) CUDA_OK(cudaMemcpyAsync(boundary, flb, sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_set_force_cache(tcif_ctx *c, int on) {
+    API_BEGIN(c)
+    c->cacheForce = on != 0;
+    API_END(c)
+}
+
+int tcif_force_counters(const tcif_ctx *c, int64_t *evaluations, int64_t *cacheHits) {
+    if (!c) return 1;
+    if (evaluations) *evaluations = c->forceEvaluations;
+    if (cacheHits) *cacheHits = c->forceCacheHits;
+    return 0;
 }
 
 int tcif_grad_alpha(tcif_ctx *c, int phase, double *internal, double *boundary) {
@@ -1454,6 +1501,7 @@ int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const
     API_BEGIN(c)
     if (!ai || !pai || !apo || (c->nBF && (!ab || !pab || !apob))) failf("tcif_stage_host: null field lists");
     if (!(deltaT > 0)) failf("tcif_stage_host: deltaT must be positive");
+    touch(c);
     if (!c->sIn) {
         CUDA_OK(cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking));
         CUDA_OK(cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking));
@@ -1535,6 +1583,7 @@ int tcif_time_step_host(tcif_ctx *c, const tcif_alpha_controls *ctl, double delt
                         double *const *apo, double *const *apob, double *rpi, double *rpb, double *Fi, double *Fb) {
     API_BEGIN(c)
     if (!ai || (c->nBF && !ab) || !phii) failf("tcif_time_step_host: null field lists");
+    touch(c);
     if (!c->sIn) {
         CUDA_OK(cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking));
         CUDA_OK(cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking));

@@ -351,4 +351,32 @@ k_phic_max(const __grid_constant__ DMesh m, const double *phi, const double *phi
     if ((threadIdx.x & 31) == 0 && v > 0.0) atomic_max_nonneg(out, v);
 }
 
+// ---- fvc::flux(F) = linear(F) & Sf  (pEqn.H:31-38) ------------------------------------------------------------
+__global__ void __launch_bounds__(TCIF_TPB)
+k_flux_of_force(const __grid_constant__ DMesh m, const double *F, double *out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= m.nC) return;
+    const double fx = F[c], fy = F[(size_t)m.stride + c], fz = F[(size_t)2 * m.stride + c];
+    for (int k = 0; k < m.Ko; ++k) {
+        const int fo = k * m.stride + c, n = m.nbrOwn[fo];
+        if (n < 0) continue;
+        const double w = m.w[fo];
+        const double gx = F[n], gy = F[(size_t)m.stride + n], gz = F[(size_t)2 * m.stride + n];
+        const double ix = w * (fx - gx) + gx, iy = w * (fy - gy) + gy, iz = w * (fz - gz) + gz;
+        out[fo] = ix * m.Sfx[fo] + iy * m.Sfy[fo] + iz * m.Sfz[fo];
+    }
+}
+__global__ void __launch_bounds__(TCIF_TPB)
+k_flux_of_force_bnd(const __grid_constant__ DMesh m, const double *F, const double *Fb, double *outb) {
+    const int bf = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bf >= m.nBF) return;
+    double ix = Fb[bf], iy = Fb[(size_t)m.nBF + bf], iz = Fb[(size_t)2 * m.nBF + bf];
+    if (m.bfType[bf] == PATCH_PROCESSOR) {
+        const int c = m.faceCells[bf];
+        const double w = m.wb[bf];
+        ix = w * F[c] + (1.0 - w) * ix; iy = w * F[(size_t)m.stride + c] + (1.0 - w) * iy; iz = w * F[(size_t)2 * m.stride + c] + (1.0 - w) * iz;
+    }
+    outb[bf] = ix * m.Sfbx[bf] + iy * m.Sfby[bf] + iz * m.Sfbz[bf];
+}
+
 }  // namespace tcif
