@@ -137,6 +137,7 @@ struct tcif_ctx {
     std::vector<int> cpPatch, cpOff;    // coupled patches: patch id, offset in coupled-face units
     double sumV = 0.0;
     DMesh dm{};
+    int tsum = 0;            // force kernels carry the pair-summed stress tensor (6 comps) instead of Q tensors
     int *d_faceMap = nullptr;           // host face f -> device slot
     std::vector<void *> allocs;
     int64_t devBytes = 0;
@@ -296,6 +297,7 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
         w[fd] = m->weights[f];
     }
     DMesh &d = c->dm;
+    { const char *e = getenv("TCIF_PF_AHEAD"); d.pfAhead = e ? atoi(e) : 0; }
     d.nC = nC; d.stride = stride; d.Ko = Ko; d.Kn = Kn; d.nFd = (int)c->nFd; d.nBF = nBF; d.nPatches = nP;
     d.nbrOwn = c->upload(nbrOwn); d.neiFace = c->upload(neiFace);
     d.Sfx = c->upload(sx); d.Sfy = c->upload(sy); d.Sfz = c->upload(sz); d.w = c->upload(w);
@@ -517,6 +519,7 @@ ForceArgs force_args(tcif_ctx *c, bool withTensor, bool withG) {
     a.T = c->Tc; a.Tb = c->Tb; a.sig = c->dSig; a.deltaN = c->deltaN;
     a.Tq = withTensor ? c->Tq : nullptr; a.gBnd = c->gBnd; a.TqHalo = c->TqHalo;
     a.G = withG ? c->G : nullptr; a.F = c->F;
+    a.tsum = c->tsum;
     return a;
 }
 
@@ -559,12 +562,12 @@ template <bool BND> void launch_div_tensor(tcif_ctx *c, const ForceArgs &a) {
 // compulsory HBM bytes of the volume sweeps (every array touched once; DESIGN.md "Kernels")
 double bytes_grad_tensor(const tcif_ctx *c, bool tensor, bool g) {
     double perCell = 8.0 * c->P + 8 /*V*/ + 4.0 * (c->Ko + c->Kn) + 32.0 * c->Ko;
-    if (tensor) perCell += 48.0 * c->Q + (c->haveT ? 8 : 0);
+    if (tensor) perCell += 48.0 * (c->tsum ? 1 : c->Q) + (c->haveT ? 8 : 0);
     if (g) perCell += 24.0 * c->P;
     return perCell * c->nC;
 }
 double bytes_div_tensor(const tcif_ctx *c) {
-    return (48.0 * c->Q + 8 + 4.0 * (c->Ko + c->Kn) + 32.0 * c->Ko + 24) * c->nC;
+    return (48.0 * (c->tsum ? 1 : c->Q) + 8 + 4.0 * (c->Ko + c->Kn) + 32.0 * c->Ko + 24) * c->nC;
 }
 double bytes_mules_setup(const tcif_ctx *c, int nPh) {
     return nPh * (double)c->nC * (8 + 8 + 8 /*psi psi0 V*/ + 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko * 3 /*phi phiIn phiCorr*/ + 48 /*Q+-,s+-,l+-*/);
@@ -598,8 +601,9 @@ void do_force(tcif_ctx *c) {
              [&] {
                  if (c->nCoupled) {      // neighbour-rank tensors of the processor faces: hidden behind the volume sweep
                      const double *src[36]; double *dst[36];
-                     for (int k = 0; k < c->Q * 6; ++k) { src[k] = c->Tq + (size_t)k * c->stride; dst[k] = c->TqHalo + (size_t)k * std::max(c->nBF, 1); }
-                     halo_cells(c, c->Q * 6, src, dst, c->side);
+                     const int nT = (c->tsum ? 1 : c->Q) * 6;
+                     for (int k = 0; k < nT; ++k) { src[k] = c->Tq + (size_t)k * c->stride; dst[k] = c->TqHalo + (size_t)k * std::max(c->nBF, 1); }
+                     halo_cells(c, nT, src, dst, c->side);
                  }
                  timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_div_tensor<true>(c, a); });
              });
@@ -684,11 +688,18 @@ MulesBatch mules_batch(tcif_ctx *c, const int *phases, int nPh, bool fromHO) {
     return b;
 }
 
+// experiment switch: phase-looped volume kernels (hex meshes, 3-phase batches)
+bool use_kvp(tcif_ctx *c, const MulesBatch &b) {
+    static const int on = [] { const char *e = getenv("TCIF_KVP"); return e ? atoi(e) : 0; }();
+    return on && kshape(c) == 3 && b.nPh == 3;
+}
+
 template <bool BND> void launch_setup(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm) {
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
     int grid = cdiv(n, TCIF_TPB) * b.nPh;
     if constexpr (!BND) {
+        if (use_kvp(c, b)) { kvp_mules_setup<3, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, prm); c->launches++; return; }
         DISPATCH_KV((kv_mules_setup<K><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)),
                     (k_mules_setup<0, 0, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)));
     } else {
@@ -701,6 +712,11 @@ template <bool BND> void launch_iter(tcif_ctx *c, const MulesBatch &b, int first
     if (n == 0) return;
     int grid = cdiv(n, TCIF_TPB) * b.nPh;
     if constexpr (!BND) {
+        if (use_kvp(c, b)) {
+            if (first) kvp_mules_iter<3, true, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, flip);
+            else       kvp_mules_iter<3, false, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, flip);
+            c->launches++; return;
+        }
         if (first) {
             DISPATCH_KV((kv_mules_iter<K, true><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, flip)),
                         (k_mules_iter<0, 0, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, first, flip)));
@@ -718,6 +734,11 @@ template <bool BND, int MODE> void launch_final(tcif_ctx *c, const MulesBatch &b
     if (n == 0) return;
     int grid = cdiv(n, TCIF_TPB) * b.nPh;
     if constexpr (!BND) {
+        if (use_kvp(c, b)) {
+            if (first) kvp_mules_final<3, MODE, true, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter);
+            else       kvp_mules_final<3, MODE, false, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter);
+            c->launches++; return;
+        }
         if (first) {
             DISPATCH_KV((kv_mules_final<K, MODE, true><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter)),
                         (k_mules_final<0, 0, false, MODE><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, first, flip, nIter)));
@@ -1129,6 +1150,8 @@ int tcif_create(const tcif_mesh_desc *mesh, const tcif_config *cfg, tcif_ctx **o
         if (cfg->boundaryExtrema != TCIF_BEXT_GLOBAL && cfg->boundaryExtrema != TCIF_BEXT_PATCHVALUE) failf("tcif_create: bad boundaryExtrema");
         c = new tcif_ctx();
         c->cfg = *cfg;
+        c->tsum = TCIF_FORCE_EXACT ? 0 : 1;
+        if (const char *e = getenv("TCIF_TSUM")) c->tsum = atoi(e) ? 1 : 0;
         cudaGetDevice(&prevDev);
         c->device = cfg->device >= 0 ? cfg->device : prevDev;
         if (c->device >= nDev) failf("tcif_create: device %d not present (%d visible)", c->device, nDev);

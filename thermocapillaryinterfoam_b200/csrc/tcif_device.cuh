@@ -55,6 +55,7 @@ struct SigmaModel { int kind, n; double c[64]; };
 struct DMesh {
     int nC, stride, Ko, Kn, nFd;
     int nBF, nBndCells, nPatches, nCoupled;
+    int pfAhead;            // L2 prefetch distance of the volume sweeps in cells (0 = off)
     const int *nbrOwn;      // [Ko*stride] neighbour cell of the k-th owner face (-1: none)
     const int *neiFace;     // [Kn*stride] device face index of the k-th neighbour-side face (-1: none)
     const double *Sfx, *Sfy, *Sfz, *w;   // [Ko*stride]
@@ -71,6 +72,9 @@ struct DMesh {
     const int *coupledOff;  // [nCoupled] offset (in coupled-face units) of the face's processor patch
     const int *coupledSize; // [nCoupled] size of the face's processor patch
 };
+
+// hint: pull the sector holding *p from HBM into L2 (no register destination, never faults on a valid mapping)
+__device__ __forceinline__ void pf_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 __device__ __forceinline__ bool is_bnd_cell(const DMesh &m, int c) { return (m.bndMask[c >> 5] >> (c & 31)) & 1u; }
 
@@ -121,6 +125,7 @@ struct ForceArgs {
     double *TqHalo;            // [(q*6+k)*nBF + bf]   neighbour-rank tensors on coupled faces
     double *G;                 // optional [(p*3+d)*stride + c] (tcif_grad_alpha / flux assembly)
     double *F;                 // [d*stride + c]
+    int tsum;                  // 1: Tq holds ONE tensor, the sum over pairs (div is linear), 0: one per pair
 };
 
 // T = (2|g|) * (sigma * (I - n n)),  g = a2*g1 - a1*g2,  n = g/(|g| + deltaN)
@@ -211,6 +216,7 @@ k_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
     }
     if (a.Tq) {
         double Tc = a.T ? a.T[c] : 0.0;
+        double Ts6[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
         int q = 0;
 #pragma unroll
         for (int p1 = 0; p1 < P; ++p1)
@@ -219,9 +225,18 @@ k_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
                 double T6[6];
                 double sg = sigma_eval(a.sig[q], Tc);
                 pair_tensor(aS[p1], aS[p2], g[p1], g[p2], sg, a.deltaN, T6);
+                if (a.tsum) {
 #pragma unroll
-                for (int k = 0; k < 6; ++k) a.Tq[(size_t)(q * 6 + k) * m.stride + c] = T6[k];
+                    for (int k = 0; k < 6; ++k) Ts6[k] += T6[k];
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) a.Tq[(size_t)(q * 6 + k) * m.stride + c] = T6[k];
+                }
             }
+        if (a.tsum) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) a.Tq[(size_t)k * m.stride + c] = Ts6[k];
+        }
     }
 }
 
@@ -249,8 +264,9 @@ k_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs 
     const int kn = KN ? KN : m.Kn, ko = KO ? KO : m.Ko;
     double rV = f_rcp(m.V[c]);
     double F[3] = {0.0, 0.0, 0.0};
+    const int nQ = a.tsum ? 1 : Q;
 #pragma unroll 1
-    for (int q = 0; q < Q; ++q) {
+    for (int q = 0; q < nQ; ++q) {
         const double *Tq = a.Tq + (size_t)q * 6 * m.stride;
         double Ts[6], acc[3] = {0.0, 0.0, 0.0};
 #pragma unroll
@@ -278,39 +294,50 @@ k_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs 
             }
         }
         if (BND) {
-            // pair (p1,p2) of index q
-            int p1 = 0, p2 = 1, qq = 0;
-            for (int x = 0; x < P; ++x) for (int y = x + 1; y < P; ++y, ++qq) if (qq == q) { p1 = x; p2 = y; }
             for (int j = m.bndCellStart[i]; j < m.bndCellStart[i + 1]; ++j) {
                 int bf = m.bndFaces[j];
                 double sx = m.Sfbx[bf], sy = m.Sfby[bf], sz = m.Sfbz[bf];
-                double t[6];
+                double t[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
                 if (m.bfType[bf] == PATCH_PROCESSOR) {
                     double wb = m.wb[bf];
 #pragma unroll
                     for (int kk = 0; kk < 6; ++kk)
                         t[kk] = wb * Ts[kk] + (1.0 - wb) * a.TqHalo[(size_t)(q * 6 + kk) * m.nBF + bf];
                 } else {
-                    // patch values: alpha_b, grad_b = g_c + n (snGrad - n.g_c), sigma(T_b)
+                    // patch values: alpha_b, grad_b = g_c + n (snGrad - n.g_c), sigma(T_b); pair q only, or
+                    // (tsum) all pairs summed in pair order
                     double mag = m.magSfb[bf];
                     double nx = sx / mag, ny = sy / mag, nz = sz / mag;
-                    double gb[2][3], ab[2];
-                    int pp[2] = {p1, p2};
+                    int qq = 0;
+                    for (int p1 = 0; p1 < P; ++p1)
+                        for (int p2 = p1 + 1; p2 < P; ++p2, ++qq) {
+                            if (!a.tsum && qq != q) continue;
+                            double gb[2][3], ab[2];
+                            int pp[2] = {p1, p2};
 #pragma unroll
-                    for (int s = 0; s < 2; ++s) {
-                        int p = pp[s];
-                        double gc0 = a.gBnd[(size_t)(p * 3 + 0) * m.nBndCells + i];
-                        double gc1 = a.gBnd[(size_t)(p * 3 + 1) * m.nBndCells + i];
-                        double gc2 = a.gBnd[(size_t)(p * 3 + 2) * m.nBndCells + i];
-                        ab[s] = a.alphab[p][bf];
-                        double sn = 0.0;
-                        if (a.bc[p][m.bfPatch[bf]] == BC_FIXED_VALUE) sn = m.dcb[bf] * (ab[s] - a.alpha[p][c]);
-                        double ng = nx * gc0 + ny * gc1 + nz * gc2;
-                        double sc = sn - ng;
-                        gb[s][0] = gc0 + nx * sc; gb[s][1] = gc1 + ny * sc; gb[s][2] = gc2 + nz * sc;
-                    }
-                    double sg = sigma_eval(a.sig[q], a.Tb ? a.Tb[bf] : 0.0);
-                    pair_tensor(ab[0], ab[1], gb[0], gb[1], sg, a.deltaN, t);
+                            for (int s = 0; s < 2; ++s) {
+                                int p = pp[s];
+                                double gc0 = a.gBnd[(size_t)(p * 3 + 0) * m.nBndCells + i];
+                                double gc1 = a.gBnd[(size_t)(p * 3 + 1) * m.nBndCells + i];
+                                double gc2 = a.gBnd[(size_t)(p * 3 + 2) * m.nBndCells + i];
+                                ab[s] = a.alphab[p][bf];
+                                double sn = 0.0;
+                                if (a.bc[p][m.bfPatch[bf]] == BC_FIXED_VALUE) sn = m.dcb[bf] * (ab[s] - a.alpha[p][c]);
+                                double ng = nx * gc0 + ny * gc1 + nz * gc2;
+                                double sc = sn - ng;
+                                gb[s][0] = gc0 + nx * sc; gb[s][1] = gc1 + ny * sc; gb[s][2] = gc2 + nz * sc;
+                            }
+                            double sg = sigma_eval(a.sig[qq], a.Tb ? a.Tb[bf] : 0.0);
+                            double tq[6];
+                            pair_tensor(ab[0], ab[1], gb[0], gb[1], sg, a.deltaN, tq);
+                            if (a.tsum) {
+#pragma unroll
+                                for (int kk = 0; kk < 6; ++kk) t[kk] += tq[kk];
+                            } else {
+#pragma unroll
+                                for (int kk = 0; kk < 6; ++kk) t[kk] = tq[kk];
+                            }
+                        }
                 }
                 acc[0] += sx * t[0] + sy * t[1] + sz * t[2];
                 acc[1] += sx * t[1] + sy * t[3] + sz * t[4];

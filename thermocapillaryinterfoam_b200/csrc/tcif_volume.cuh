@@ -57,6 +57,23 @@ struct Slots {
     }
 };
 
+// L2 prefetch of the contiguous (own-slot) streams a later CTA will read: cp = c + m.pfAhead.  The volume
+// sweeps are bound by memory latency (ncu: long-scoreboard stalls, ~45 % occupancy), and everything a cell
+// reads from HBM for the first time is one of these streams, so a prefetch issued one or two waves ahead
+// turns those misses into L2 hits.  No registers are tied up (prefetch has no destination).
+template <int K> __device__ __forceinline__ void pf_slots(const DMesh &m, int cp) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) { pf_l2(m.neiFace + k * m.stride + cp); pf_l2(m.nbrOwn + k * m.stride + cp); }
+}
+template <int K> __device__ __forceinline__ void pf_face(const double *a, int stride, int cp) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) pf_l2(a + k * stride + cp);
+}
+template <int K> __device__ __forceinline__ void pf_geom(const DMesh &m, int cp) {
+    pf_face<K>(m.w, m.stride, cp); pf_face<K>(m.Sfx, m.stride, cp); pf_face<K>(m.Sfy, m.stride, cp); pf_face<K>(m.Sfz, m.stride, cp);
+    pf_l2(m.V + cp);
+}
+
 // ---- K1: grad(alpha_p) for all phases + capillary stress tensors of all pairs ---------------------
 template <int P, int K>
 __global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
@@ -65,6 +82,15 @@ kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArg
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     Slots<K> s;
     s.load(m, c);
+    {
+        const int cp = c + m.pfAhead;
+        if (m.pfAhead > 0 && cp < m.nC) {
+            pf_slots<K>(m, cp); pf_geom<K>(m, cp);
+#pragma unroll
+            for (int p = 0; p < P; ++p) pf_l2(a.alpha[p] + cp);
+            if (a.T) pf_l2(a.T + cp);
+        }
+    }
     double aS[P], aO[K][P], aN[K][P];
 #pragma unroll
     for (int p = 0; p < P; ++p) aS[p] = a.alpha[p][c];
@@ -113,6 +139,7 @@ kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArg
             for (int d = 0; d < 3; ++d) a.G[(size_t)(p * 3 + d) * m.stride + c] = g[p][d];
     }
     if (a.Tq) {
+        double Ts6[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
         int q = 0;
 #pragma unroll
         for (int p1 = 0; p1 < P; ++p1)
@@ -121,9 +148,18 @@ kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArg
                 double T6[6];
                 double sg = sigma_eval(a.sig[q], Tc);
                 pair_tensor(aS[p1], aS[p2], g[p1], g[p2], sg, a.deltaN, T6);
+                if (a.tsum) {
 #pragma unroll
-                for (int k = 0; k < 6; ++k) a.Tq[(size_t)(q * 6 + k) * m.stride + c] = T6[k];
+                    for (int k = 0; k < 6; ++k) Ts6[k] += T6[k];
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) a.Tq[(size_t)(q * 6 + k) * m.stride + c] = T6[k];
+                }
             }
+        if (a.tsum) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) a.Tq[(size_t)k * m.stride + c] = Ts6[k];
+        }
     }
 }
 
@@ -136,6 +172,14 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     Slots<K> s;
     s.load(m, c);
+    {
+        const int cp = c + m.pfAhead;
+        if (m.pfAhead > 0 && cp < m.nC) {
+            pf_slots<K>(m, cp); pf_geom<K>(m, cp);
+#pragma unroll
+            for (int kk = 0; kk < 6; ++kk) pf_l2(a.Tq + (size_t)kk * m.stride + cp);
+        }
+    }
     double wN[K], sxN[K], syN[K], szN[K], wO[K], sxO[K], syO[K], szO[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -145,8 +189,9 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
     }
     const double rV = f_rcp(m.V[c]);
     double F[3] = {0.0, 0.0, 0.0};
+    const int nQ = a.tsum ? 1 : Q;
 #pragma unroll 1
-    for (int q = 0; q < Q; ++q) {
+    for (int q = 0; q < nQ; ++q) {
         const double *Tq = a.Tq + (size_t)q * 6 * m.stride;
         double Ts[6], To[K][6], Tn[K][6];
 #pragma unroll
@@ -339,6 +384,233 @@ kv_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
     if (MODE == 2) {
         double d = sum / V;
         ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
+    }
+}
+
+// =====================================================================================================
+// Phase-looped variants (kvp_*): one thread per cell, ALL phases of the batch handled by that thread.
+// The 2K slot indices are loaded once per cell instead of once per (cell, phase), which removes one of
+// the two dependent memory round trips (indices -> gathers) for every phase after the first, and the
+// per-phase pointers are compile-time offsets into the kernel parameters (NPH is a template argument).
+// Same arithmetic, same order as the kv_* kernels.
+// =====================================================================================================
+template <int K, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_SETUP)
+kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
+                const __grid_constant__ MulesParams prm) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    Slots<K> s;
+    s.load(m, c);
+    double phiN[K], phiO[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) { phiN[k] = prm.phi[s.fdN[k]]; phiO[k] = __ldcs(prm.phi + k * m.stride + c); }
+    const double V = m.V[c];
+    const int cp = c + m.pfAhead;
+    const bool pf = m.pfAhead > 0 && cp < m.nC;
+    if (pf) { pf_slots<K>(m, cp); pf_face<K>(prm.phi, m.stride, cp); pf_l2(m.V + cp); }
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) {
+        const MulesPh &ph = b.ph[p];
+        if (pf) {
+            pf_l2(ph.psi + cp); pf_l2(ph.psi0 + cp); pf_face<K>(ph.phiIn, m.stride, cp);
+            if (ph.Su) pf_l2(ph.Su + cp);
+            if (ph.Sp) pf_l2(ph.Sp + cp);
+        }
+        const double psiC = ph.psi[c];
+        double psiO[K], ppN[K], psiN[K], ppO[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int fo = k * m.stride + c;
+            psiO[k] = ph.psi[s.oN[k]]; ppN[k] = ph.phiIn[s.fdN[k]];
+            psiN[k] = ph.psi[s.nO[k]]; ppO[k] = ph.phiIn[fo];
+        }
+        const double psi0 = __ldcs(ph.psi0 + c);
+        const double Su = ph.Su ? __ldcs(ph.Su + c) : 0.0, Sp = ph.Sp ? __ldcs(ph.Sp + c) : 0.0;
+        double psiMaxn = prm.psiMin, psiMinn = prm.psiMax, sBD = 0.0, sP = 0.0, sM = 0.0;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (s.vN[k]) {
+                double bd = upwind_flux(phiN[k], psiO[k], psiC);
+                double pp = ppN[k];
+                if (prm.addUpwind) pp = pp + bd;
+                double pc = pp - bd;
+                psiMaxn = dmax(psiMaxn, psiO[k]); psiMinn = dmin(psiMinn, psiO[k]);
+                sBD -= bd;
+                if (pc > 0) sM += pc; else sP -= pc;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (s.vO[k]) {
+                double bd = upwind_flux(phiO[k], psiC, psiN[k]);
+                double pp = ppO[k];
+                if (prm.addUpwind) pp = pp + bd;
+                double pc = pp - bd;
+                ph.phiCorr[k * m.stride + c] = pc;
+                psiMaxn = dmax(psiMaxn, psiN[k]); psiMinn = dmin(psiMinn, psiN[k]);
+                sBD += bd;
+                if (pc > 0) sP += pc; else sM -= pc;
+            }
+        }
+        psiMaxn = dmin(psiMaxn + prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMax);
+        psiMinn = dmax(psiMinn - prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMin);
+        if (prm.smoothLimiter > TCIF_SMALL) {
+            double sl = prm.smoothLimiter;
+            psiMaxn = dmin(sl * psiC + (1.0 - sl) * psiMaxn, prm.psiMax);
+            psiMinn = dmax(sl * psiC + (1.0 - sl) * psiMinn, prm.psiMin);
+        }
+        double Qp = V * ((prm.rDeltaT - Sp) * psiMaxn - Su) - (V * prm.rDeltaT) * psi0 + sBD;
+        double Qm = V * (Su - (prm.rDeltaT - Sp) * psiMinn) + (V * prm.rDeltaT) * psi0 - sBD;
+        __stcs(ph.Qp + c, Qp); __stcs(ph.Qm + c, Qm); __stcs(ph.sP + c, sP); __stcs(ph.sM + c, sM);
+        ph.lmA[c] = dmax(dmin((sP + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
+        ph.lpA[c] = dmax(dmin((sM + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
+    }
+}
+
+template <int K, bool FIRST, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_ITER)
+kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, int flip) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    Slots<K> s;
+    s.load(m, c);
+    const int cp = c + m.pfAhead;
+    const bool pf = m.pfAhead > 0 && cp < m.nC;
+    if (pf) pf_slots<K>(m, cp);
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) {
+        const MulesPh &ph = b.ph[p];
+        const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
+        double *lpOut = flip ? ph.lpA : ph.lpB, *lmOut = flip ? ph.lmA : ph.lmB;
+        const double *lamIn = flip ? ph.lamB : ph.lamA;
+        double *lamOut = flip ? ph.lamA : ph.lamB;
+        if (pf) {
+            pf_face<K>(ph.phiCorr, m.stride, cp);
+            if (!FIRST) pf_face<K>(lamIn, m.stride, cp);
+            pf_l2(lpIn + cp); pf_l2(lmIn + cp); pf_l2(ph.Qp + cp); pf_l2(ph.Qm + cp); pf_l2(ph.sP + cp); pf_l2(ph.sM + cp);
+        }
+        const double lpC = lpIn[c], lmC = lmIn[c];
+        double pcN[K], laN[K], lpO[K], lmO[K], pcO[K], laO[K], lpN[K], lmN[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int fo = k * m.stride + c;
+            pcN[k] = ph.phiCorr[s.fdN[k]]; laN[k] = FIRST ? 1.0 : lamIn[s.fdN[k]];
+            lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
+            pcO[k] = ph.phiCorr[fo]; laO[k] = FIRST ? 1.0 : lamIn[fo];
+            lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
+        }
+        const double Qp = __ldcs(ph.Qp + c), Qm = __ldcs(ph.Qm + c), sP = __ldcs(ph.sP + c), sM = __ldcs(ph.sM + c);
+        double slp = 0.0, slm = 0.0;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (s.vN[k]) {
+                double lam = lambda_face(laN[k], pcN[k], lpO[k], lmO[k], lpC, lmC);
+                double l = lam * pcN[k];
+                if (l > 0) slm += l; else slp -= l;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (s.vO[k]) {
+                double lam = lambda_face(laO[k], pcO[k], lpC, lmC, lpN[k], lmN[k]);
+                lamOut[k * m.stride + c] = lam;
+                double l = lam * pcO[k];
+                if (l > 0) slp += l; else slm -= l;
+            }
+        }
+        lmOut[c] = dmax(dmin((slp + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
+        lpOut[c] = dmax(dmin((slm + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
+    }
+}
+
+template <int K, int MODE, bool FIRST, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
+kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
+                const __grid_constant__ MulesParams prm, int flip, int nIter) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    Slots<K> s;
+    s.load(m, c);
+    double phN[K], phO[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (MODE == 2) phN[k] = prm.phi[s.fdN[k]];
+        if (MODE >= 1) phO[k] = __ldcs(prm.phi + k * m.stride + c);
+    }
+    const double V = (MODE == 2) ? m.V[c] : 1.0;
+    const int cp = c + m.pfAhead;
+    const bool pf = m.pfAhead > 0 && cp < m.nC;
+    if (pf) {
+        pf_slots<K>(m, cp);
+        if (MODE >= 1) pf_face<K>(prm.phi, m.stride, cp);
+        if (MODE == 2) pf_l2(m.V + cp);
+    }
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) {
+        const MulesPh &ph = b.ph[p];
+        const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
+        const double *lamIn = flip ? ph.lamB : ph.lamA;
+        if (pf) {
+            pf_face<K>(ph.phiCorr, m.stride, cp);
+            if (!FIRST) pf_face<K>(lamIn, m.stride, cp);
+            pf_l2(lpIn + cp); pf_l2(lmIn + cp);
+            if (MODE >= 1) pf_l2(ph.psi + cp);
+            if (MODE == 2) {
+                pf_l2(ph.psi0 + cp);
+                if (ph.Su) pf_l2(ph.Su + cp);
+                if (ph.Sp) pf_l2(ph.Sp + cp);
+            }
+        }
+        const double lpC = lpIn[c], lmC = lmIn[c];
+        const double psiC = (MODE >= 1) ? ph.psi[c] : 0.0;
+        double pcN[K], laN[K], lpO[K], lmO[K], psO[K];
+        double pcO[K], laO[K], lpN[K], lmN[K], psN[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int fo = k * m.stride + c;
+            if (MODE == 2) {
+                pcN[k] = ph.phiCorr[s.fdN[k]]; laN[k] = FIRST ? 1.0 : lamIn[s.fdN[k]];
+                lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
+                psO[k] = ph.psi[s.oN[k]];
+            }
+            pcO[k] = ph.phiCorr[fo]; laO[k] = FIRST ? 1.0 : lamIn[fo];
+            lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
+            if (MODE >= 1) psN[k] = ph.psi[s.nO[k]];
+        }
+        double psi0 = 0.0, Su = 0.0, Sp = 0.0;
+        if (MODE == 2) {
+            psi0 = __ldcs(ph.psi0 + c);
+            Su = ph.Su ? __ldcs(ph.Su + c) : 0.0; Sp = ph.Sp ? __ldcs(ph.Sp + c) : 0.0;
+        }
+        double sum = 0.0;
+        if (MODE == 2) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                if (s.vN[k]) {
+                    double lam = laN[k];
+                    if (nIter > 0) lam = lambda_face(lam, pcN[k], lpO[k], lmO[k], lpC, lmC);
+                    double bd = upwind_flux(phN[k], psO[k], psiC);
+                    sum -= bd + lam * pcN[k];
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (s.vO[k]) {
+                double lam = laO[k];
+                if (nIter > 0) lam = lambda_face(lam, pcO[k], lpC, lmC, lpN[k], lmN[k]);
+                double fl;
+                if (MODE == 0) fl = pcO[k] * lam;
+                else           fl = upwind_flux(phO[k], psiC, psN[k]) + lam * pcO[k];
+                ph.phiPsi[k * m.stride + c] = fl;
+                sum += fl;
+            }
+        }
+        if (MODE == 2) {
+            double d = sum / V;
+            ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
+        }
     }
 }
 
