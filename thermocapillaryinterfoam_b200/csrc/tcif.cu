@@ -22,6 +22,7 @@
 #include <string>
 #include <type_traits>
 #include <vector>
+#include <map>
 
 using namespace tcif;
 
@@ -297,7 +298,7 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
         w[fd] = m->weights[f];
     }
     DMesh &d = c->dm;
-    { const char *e = getenv("TCIF_PF_AHEAD"); d.pfAhead = e ? atoi(e) : 0; }
+    { const char *e = getenv("TCIF_PF_AHEAD"); d.pfAhead = e ? atoi(e) : 148 * TCIF_TPB; }   // one CTA per SM ahead (profiles/r02_variants.md)
     d.nC = nC; d.stride = stride; d.Ko = Ko; d.Kn = Kn; d.nFd = (int)c->nFd; d.nBF = nBF; d.nPatches = nP;
     d.nbrOwn = c->upload(nbrOwn); d.neiFace = c->upload(neiFace);
     d.Sfx = c->upload(sx); d.Sfy = c->upload(sy); d.Sfz = c->upload(sz); d.w = c->upload(w);
@@ -688,10 +689,31 @@ MulesBatch mules_batch(tcif_ctx *c, const int *phases, int nPh, bool fromHO) {
     return b;
 }
 
-// experiment switch: phase-looped volume kernels (hex meshes, 3-phase batches)
+// Phase-looped volume kernels (kvp_*, tcif_volume.cuh): batches of 2 or 3 phases on fixed-K meshes.
+// TCIF_KVP=0 falls back to the (cell, phase)-per-thread kernels (A/B and debugging aid).
 bool use_kvp(tcif_ctx *c, const MulesBatch &b) {
-    static const int on = [] { const char *e = getenv("TCIF_KVP"); return e ? atoi(e) : 0; }();
-    return on && kshape(c) == 3 && b.nPh == 3;
+    static const int on = [] { const char *e = getenv("TCIF_KVP"); return e ? atoi(e) : 1; }();
+    return on && kshape(c) != 0 && (b.nPh == 2 || b.nPh == 3);
+}
+#define DISPATCH_KVP(CALL)                                                         \
+    switch (kshape(c) * 10 + b.nPh) {                                              \
+        case 22: { constexpr int K = 2, NPH = 2; CALL; } break;                    \
+        case 23: { constexpr int K = 2, NPH = 3; CALL; } break;                    \
+        case 32: { constexpr int K = 3, NPH = 2; CALL; } break;                    \
+        case 33: { constexpr int K = 3, NPH = 3; CALL; } break;                    \
+        case 42: { constexpr int K = 4, NPH = 2; CALL; } break;                    \
+        case 43: { constexpr int K = 4, NPH = 3; CALL; } break;                    \
+        default: failf("kvp dispatch: unsupported shape");                         \
+    }
+// ping-pong buffers of the limiter resolved for one sweep
+MulesBatch resolve_flip(const MulesBatch &b0, int flip) {
+    MulesBatch b = b0;
+    for (int k = 0; k < b.nPh; ++k) {
+        MulesPh &ph = b.ph[k];
+        ph.lpIn = flip ? ph.lpB : ph.lpA; ph.lmIn = flip ? ph.lmB : ph.lmA; ph.lamIn = flip ? ph.lamB : ph.lamA;
+        ph.lpOut = flip ? ph.lpA : ph.lpB; ph.lmOut = flip ? ph.lmA : ph.lmB; ph.lamOut = flip ? ph.lamA : ph.lamB;
+    }
+    return b;
 }
 
 template <bool BND> void launch_setup(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm) {
@@ -699,7 +721,10 @@ template <bool BND> void launch_setup(tcif_ctx *c, const MulesBatch &b, const Mu
     if (n == 0) return;
     int grid = cdiv(n, TCIF_TPB) * b.nPh;
     if constexpr (!BND) {
-        if (use_kvp(c, b)) { kvp_mules_setup<3, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, prm); c->launches++; return; }
+        if (use_kvp(c, b)) {
+            DISPATCH_KVP((kvp_mules_setup<K, NPH><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)));
+            c->launches++; return;
+        }
         DISPATCH_KV((kv_mules_setup<K><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)),
                     (k_mules_setup<0, 0, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)));
     } else {
@@ -713,8 +738,9 @@ template <bool BND> void launch_iter(tcif_ctx *c, const MulesBatch &b, int first
     int grid = cdiv(n, TCIF_TPB) * b.nPh;
     if constexpr (!BND) {
         if (use_kvp(c, b)) {
-            if (first) kvp_mules_iter<3, true, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, flip);
-            else       kvp_mules_iter<3, false, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, flip);
+            const MulesBatch br = resolve_flip(b, flip);
+            if (first) { DISPATCH_KVP((kvp_mules_iter<K, true, NPH><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, br))); }
+            else       { DISPATCH_KVP((kvp_mules_iter<K, false, NPH><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, br))); }
             c->launches++; return;
         }
         if (first) {
@@ -729,16 +755,20 @@ template <bool BND> void launch_iter(tcif_ctx *c, const MulesBatch &b, int first
     }
     c->launches++;
 }
-template <bool BND, int MODE> void launch_final(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm, int first, int flip, int nIter) {
+template <bool BND, int MODE, bool LSUM = false>
+void launch_final(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm, int first, int flip, int nIter) {
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
     int grid = cdiv(n, TCIF_TPB) * b.nPh;
     if constexpr (!BND) {
         if (use_kvp(c, b)) {
-            if (first) kvp_mules_final<3, MODE, true, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter);
-            else       kvp_mules_final<3, MODE, false, 3><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter);
+            const MulesBatch br = resolve_flip(b, flip);
+            constexpr bool LS = LSUM && MODE == 0;
+            if (first) { DISPATCH_KVP((kvp_mules_final<K, MODE, true, NPH, LS><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, br, prm, nIter))); }
+            else       { DISPATCH_KVP((kvp_mules_final<K, MODE, false, NPH, LS><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, br, prm, nIter))); }
             c->launches++; return;
         }
+        if (LSUM) failf("launch_final: fused limitSum needs the phase-looped kernels");
         if (first) {
             DISPATCH_KV((kv_mules_final<K, MODE, true><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter)),
                         (k_mules_final<0, 0, false, MODE><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, first, flip, nIter)));
@@ -764,7 +794,9 @@ void halo_lambda(tcif_ctx *c, const MulesBatch &b, int flip) {
 
 // MULES::limit for a batch of phases.  mode 0: returnCorr=true; 1: returnCorr=false;
 // 2: explicitSolve's limit fused with surfaceIntegrate + Euler update (psi -> alphaNew).
-void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode, bool addUpwind, bool fromHO) {
+// fuseLimitSum (mode 0, batch = all phases): limitSum of the interior cells' owner faces rides on the apply sweep;
+// the caller finishes with do_limit_sum_rest().
+void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode, bool addUpwind, bool fromHO, bool fuseLimitSum = false) {
     require_comm(c);
     MulesBatch b = mules_batch(c, phases, nPh, fromHO);
     MulesParams prm{};
@@ -789,7 +821,13 @@ void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode,
                  [&] { if (L > 0) halo_lambda(c, b, flip);
                        timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_final<true, MODE>(c, b, prm, first, flip, L); }); });
     };
-    if (mode == 0) fin(std::integral_constant<int, 0>{});
+    if (mode == 0 && fuseLimitSum) {
+        if (!use_kvp(c, b)) failf("do_limit: fused limitSum requested without the phase-looped kernels");
+        sweep(c, [&] { timed(c, T_MULES_FINAL, fb + 0.0, [&] { launch_final<false, 0, true>(c, b, prm, first, flip, L); }); },
+                 [&] { if (L > 0) halo_lambda(c, b, flip);
+                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_final<true, 0>(c, b, prm, first, flip, L); }); });
+    }
+    else if (mode == 0) fin(std::integral_constant<int, 0>{});
     else if (mode == 1) fin(std::integral_constant<int, 1>{});
     else {
         fin(std::integral_constant<int, 2>{});
@@ -807,6 +845,34 @@ void do_limit_sum(tcif_ctx *c) {
         k_limit_sum<<<cdiv((long long)c->nFd, TCIF_TPB), TCIF_TPB, 0, c->stream>>>((int)c->nFd, a);
         c->launches++;
     });
+    if (c->nCoupled) {
+        LimitSumArgs ab{};
+        ab.nPh = c->P;
+        for (int p = 0; p < c->P; ++p) ab.f[p] = c->phiPsib[p];
+        timed(c, T_BOUNDARY, 0, [&] {
+            k_limit_sum_coupled<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nCoupled, c->dm.coupledFaces, ab);
+            c->launches++;
+        });
+    }
+}
+
+// whether limit(all phases, returnCorr=true) + limitSum can run fused (do_limit(..., fuseLimitSum=true) + do_limit_sum_rest)
+bool can_fuse_limit_sum(tcif_ctx *c) {
+    MulesBatch b{};
+    b.nPh = c->P;
+    return use_kvp(c, b);
+}
+// the part of limitSum the fused volume sweep did not cover: owner faces of boundary-adjacent cells, coupled faces
+void do_limit_sum_rest(tcif_ctx *c) {
+    LimitSumArgs a{};
+    a.nPh = c->P;
+    for (int p = 0; p < c->P; ++p) a.f[p] = c->phiPsi[p];
+    if (c->nBndCells) {
+        timed(c, T_BOUNDARY, 0, [&] {
+            k_limit_sum_bndcells<<<cdiv(c->nBndCells * c->Ko, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a);
+            c->launches++;
+        });
+    }
     if (c->nCoupled) {
         LimitSumArgs ab{};
         ab.nPh = c->P;
@@ -992,8 +1058,9 @@ void do_stage(tcif_ctx *c, double deltaT) {
 void do_mules_stage(tcif_ctx *c, double deltaT) {
     int all[4] = {0, 1, 2, 3};
     store_old(c);
-    do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true);      // multiphaseSystem.C:296-319
-    do_limit_sum(c);                                            // :321
+    const bool fuse = can_fuse_limit_sum(c);
+    do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true, fuse); // multiphaseSystem.C:296-319
+    if (fuse) do_limit_sum_rest(c); else do_limit_sum(c);       // :321
     do_explicit(c, all, c->P, deltaT, true);                    // :346 (bounded flux) + :365-375
 }
 
@@ -1047,8 +1114,9 @@ void do_solve_alphas(tcif_ctx *c, const tcif_alpha_controls *ctl, double deltaT)
         phic_begin(c, st);
         for (int acorr = 0; acorr < ctl->nAlphaCorr; ++acorr) {
             do_flux_assembly(c, ctl->schemePhi, ctl->schemePhir, st);     // :199-277
-            do_limit(c, all, c->P, 1.0 / dt, 0, false, true);             // :296-319
-            do_limit_sum(c);                                              // :321
+            const bool fuse = can_fuse_limit_sum(c);
+            do_limit(c, all, c->P, 1.0 / dt, 0, false, true, fuse);       // :296-319
+            if (fuse) do_limit_sum_rest(c); else do_limit_sum(c);         // :321
             if (ctl->implicitPredictor) {
                 do_predictor(c, all, c->P, dt, ctl->predictorTol, ctl->predictorMaxIter);   // :348-363
                 do_explicit(c, all, c->P, dt, false);                     // :365-375

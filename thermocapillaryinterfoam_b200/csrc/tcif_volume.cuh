@@ -470,7 +470,7 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
 
 template <int K, bool FIRST, int NPH>
 __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_ITER)
-kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, int flip) {
+kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     Slots<K> s;
@@ -481,10 +481,8 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
         const MulesPh &ph = b.ph[p];
-        const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
-        double *lpOut = flip ? ph.lpA : ph.lpB, *lmOut = flip ? ph.lmA : ph.lmB;
-        const double *lamIn = flip ? ph.lamB : ph.lamA;
-        double *lamOut = flip ? ph.lamA : ph.lamB;
+        const double *lpIn = ph.lpIn, *lmIn = ph.lmIn, *lamIn = ph.lamIn;      // ping-pong resolved on the host
+        double *lpOut = ph.lpOut, *lmOut = ph.lmOut, *lamOut = ph.lamOut;
         if (pf) {
             pf_face<K>(ph.phiCorr, m.stride, cp);
             if (!FIRST) pf_face<K>(lamIn, m.stride, cp);
@@ -524,10 +522,30 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
     }
 }
 
-template <int K, int MODE, bool FIRST, int NPH>
+// MULES::limitSum on one face, all phases in registers (same operations as k_limit_sum)
+template <int NPH> __device__ __forceinline__ void limit_sum_face(double *v) {
+    double sumPos = 0.0, sumNeg = 0.0;
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) { if (v[p] > 0) sumPos += v[p]; else sumNeg += v[p]; }
+    const double sum = sumPos + sumNeg;
+    if (sum > 0 && sumPos > TCIF_VSMALL) {
+        const double lambda = -sumNeg / sumPos;
+#pragma unroll
+        for (int p = 0; p < NPH; ++p) if (v[p] > 0) v[p] = v[p] * lambda;
+    } else if (sum < 0 && sumNeg < -TCIF_VSMALL) {
+        const double lambda = -sumPos / sumNeg;
+#pragma unroll
+        for (int p = 0; p < NPH; ++p) if (v[p] < 0) v[p] = v[p] * lambda;
+    }
+}
+
+// LSUM (MODE 0 only, batch = all phases): MULES::limitSum of the owner-side faces applied in registers
+// before the store, which saves the separate read-modify-write sweep over the P flux arrays.
+template <int K, int MODE, bool FIRST, int NPH, bool LSUM>
 __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
 kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
-                const __grid_constant__ MulesParams prm, int flip, int nIter) {
+                const __grid_constant__ MulesParams prm, int nIter) {
+    static_assert(!LSUM || MODE == 0, "limitSum is fused into the returnCorr=true apply only");
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     Slots<K> s;
@@ -546,11 +564,11 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
         if (MODE >= 1) pf_face<K>(prm.phi, m.stride, cp);
         if (MODE == 2) pf_l2(m.V + cp);
     }
+    double flAll[LSUM ? K : 1][LSUM ? NPH : 1];
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
         const MulesPh &ph = b.ph[p];
-        const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
-        const double *lamIn = flip ? ph.lamB : ph.lamA;
+        const double *lpIn = ph.lpIn, *lmIn = ph.lmIn, *lamIn = ph.lamIn;      // ping-pong resolved on the host
         if (pf) {
             pf_face<K>(ph.phiCorr, m.stride, cp);
             if (!FIRST) pf_face<K>(lamIn, m.stride, cp);
@@ -603,13 +621,24 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 double fl;
                 if (MODE == 0) fl = pcO[k] * lam;
                 else           fl = upwind_flux(phO[k], psiC, psN[k]) + lam * pcO[k];
-                ph.phiPsi[k * m.stride + c] = fl;
+                if (LSUM) flAll[k][p] = fl;
+                else ph.phiPsi[k * m.stride + c] = fl;
                 sum += fl;
             }
         }
         if (MODE == 2) {
             double d = sum / V;
             ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
+        }
+    }
+    if (LSUM) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (s.vO[k]) {
+                limit_sum_face<NPH>(flAll[k]);
+#pragma unroll
+                for (int p = 0; p < NPH; ++p) b.ph[p].phiPsi[k * m.stride + c] = flAll[k][p];
+            }
         }
     }
 }
