@@ -570,17 +570,23 @@ double bytes_grad_tensor(const tcif_ctx *c, bool tensor, bool g) {
 double bytes_div_tensor(const tcif_ctx *c) {
     return (48.0 * (c->tsum ? 1 : c->Q) + 8 + 4.0 * (c->Ko + c->Kn) + 32.0 * c->Ko + 24) * c->nC;
 }
+// MULES sweeps: arrays shared by the phases of a batch (slot indices, V, phi) are counted once per launch
 double bytes_mules_setup(const tcif_ctx *c, int nPh) {
-    return nPh * (double)c->nC * (8 + 8 + 8 /*psi psi0 V*/ + 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko * 3 /*phi phiIn phiCorr*/ + 48 /*Q+-,s+-,l+-*/);
+    double shared = 4.0 * (c->Ko + c->Kn) + 8 /*V*/ + 8.0 * c->Ko /*phi*/;
+    double perPh = 8 + 8 /*psi psi0*/ + 8.0 * c->Ko * 2 /*phiIn phiCorr*/ + 48 /*Q+-,s+-,l+-*/;
+    return (double)c->nC * (shared + nPh * perPh);
 }
 double bytes_mules_iter(const tcif_ctx *c, int nPh, bool first) {
-    return nPh * (double)c->nC * (4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko * (first ? 2 : 3) + 16 + 16 + 32);
+    double shared = 4.0 * (c->Ko + c->Kn);
+    double perPh = 8.0 * c->Ko * (first ? 2 : 3) + 16 + 16 + 32;
+    return (double)c->nC * (shared + nPh * perPh);
 }
 double bytes_mules_final(const tcif_ctx *c, int nPh, int mode, bool first) {
-    double perCell = 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko * (first ? 2 : 3) + 16;
-    if (mode >= 1) perCell += 8.0 * c->Ko + 8;          // phi, psi
-    if (mode == 2) perCell += 24;                       // psi0, V, psiNew
-    return nPh * (double)c->nC * perCell;
+    double shared = 4.0 * (c->Ko + c->Kn);
+    double perPh = 8.0 * c->Ko * (first ? 2 : 3) + 16;
+    if (mode >= 1) { shared += 8.0 * c->Ko; perPh += 8; }      // phi; psi
+    if (mode == 2) { shared += 8; perPh += 16; }               // V; psi0, psiNew
+    return (double)c->nC * (shared + nPh * perPh);
 }
 
 inline void touch(tcif_ctx *c) { ++c->fieldsVersion; }   // alpha / T / sigma changed: F is stale
