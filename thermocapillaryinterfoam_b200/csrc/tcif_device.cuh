@@ -76,6 +76,29 @@ struct DMesh {
 // hint: pull the sector holding *p from HBM into L2 (no register destination, never faults on a valid mapping)
 __device__ __forceinline__ void pf_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
+// own-slot load of an array that neighbouring cells gather later in the same sweep: ask L2 to keep the line
+#ifndef TCIF_EVL
+#define TCIF_EVL 0
+#endif
+__device__ __forceinline__ double ld_keep(const double *p) {
+#if TCIF_EVL
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    double v;
+    asm volatile("ld.global.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+    return v;
+#else
+    return *p;
+#endif
+}
+__device__ __forceinline__ void pf_l2_keep(const void *p) {
+#if TCIF_EVL
+    asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(p));
+#else
+    pf_l2(p);
+#endif
+}
+
 __device__ __forceinline__ bool is_bnd_cell(const DMesh &m, int c) { return (m.bndMask[c >> 5] >> (c & 31)) & 1u; }
 
 __device__ __forceinline__ int owner_of(const DMesh &m, int fd) {

@@ -486,16 +486,16 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
         if (pf) {
             pf_face<K>(ph.phiCorr, m.stride, cp);
             if (!FIRST) pf_face<K>(lamIn, m.stride, cp);
-            pf_l2(lpIn + cp); pf_l2(lmIn + cp); pf_l2(ph.Qp + cp); pf_l2(ph.Qm + cp); pf_l2(ph.sP + cp); pf_l2(ph.sM + cp);
+            pf_l2_keep(lpIn + cp); pf_l2_keep(lmIn + cp); pf_l2(ph.Qp + cp); pf_l2(ph.Qm + cp); pf_l2(ph.sP + cp); pf_l2(ph.sM + cp);
         }
-        const double lpC = lpIn[c], lmC = lmIn[c];
+        const double lpC = ld_keep(lpIn + c), lmC = ld_keep(lmIn + c);
         double pcN[K], laN[K], lpO[K], lmO[K], pcO[K], laO[K], lpN[K], lmN[K];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             const int fo = k * m.stride + c;
             pcN[k] = ph.phiCorr[s.fdN[k]]; laN[k] = FIRST ? 1.0 : lamIn[s.fdN[k]];
             lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
-            pcO[k] = ph.phiCorr[fo]; laO[k] = FIRST ? 1.0 : lamIn[fo];
+            pcO[k] = ld_keep(ph.phiCorr + fo); laO[k] = FIRST ? 1.0 : ld_keep(lamIn + fo);
             lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
         }
         const double Qp = __ldcs(ph.Qp + c), Qm = __ldcs(ph.Qm + c), sP = __ldcs(ph.sP + c), sM = __ldcs(ph.sM + c);
@@ -572,16 +572,16 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
         if (pf) {
             pf_face<K>(ph.phiCorr, m.stride, cp);
             if (!FIRST) pf_face<K>(lamIn, m.stride, cp);
-            pf_l2(lpIn + cp); pf_l2(lmIn + cp);
-            if (MODE >= 1) pf_l2(ph.psi + cp);
+            pf_l2_keep(lpIn + cp); pf_l2_keep(lmIn + cp);
+            if (MODE >= 1) pf_l2_keep(ph.psi + cp);
             if (MODE == 2) {
                 pf_l2(ph.psi0 + cp);
                 if (ph.Su) pf_l2(ph.Su + cp);
                 if (ph.Sp) pf_l2(ph.Sp + cp);
             }
         }
-        const double lpC = lpIn[c], lmC = lmIn[c];
-        const double psiC = (MODE >= 1) ? ph.psi[c] : 0.0;
+        const double lpC = ld_keep(lpIn + c), lmC = ld_keep(lmIn + c);
+        const double psiC = (MODE >= 1) ? ld_keep(ph.psi + c) : 0.0;
         double pcN[K], laN[K], lpO[K], lmO[K], psO[K];
         double pcO[K], laO[K], lpN[K], lmN[K], psN[K];
 #pragma unroll
@@ -592,7 +592,7 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
                 psO[k] = ph.psi[s.oN[k]];
             }
-            pcO[k] = ph.phiCorr[fo]; laO[k] = FIRST ? 1.0 : lamIn[fo];
+            pcO[k] = ld_keep(ph.phiCorr + fo); laO[k] = FIRST ? 1.0 : ld_keep(lamIn + fo);
             lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
             if (MODE >= 1) psN[k] = ph.psi[s.nO[k]];
         }
