@@ -222,6 +222,38 @@ TCIF_API int tcif_time_step_host(tcif_ctx *ctx, const tcif_alpha_controls *ctl, 
                                  double *rhoPhiInternal, double *rhoPhiBoundary,
                                  double *Finternal, double *Fboundary);
 
+/* ---- Su/Sp of the phase-fraction equations on the device ----------------------------
+ * Replaces MassTransferPhaseSystem::alphaTransfer(Su, Sp) (MassTransferPhaseSystem.C:503-704, called through
+ * multiphaseSystem::calculateSuSp(), multiphaseSystem.C:122-125, 292), correctMassSources(T) (:447-497) with
+ * the Lee model (massTransferModels/Lee/Lee.C:52-167), and phaseSystem::addInterfacePorosity with
+ * VollerPrakash::S() (phaseSystem.C:1148-1183, VollerPrakash.C:66-72).  Needs tcif_set_rho for every phase
+ * (coeffs = 1/rho, phaseSystem.C:1139-1145). */
+enum { TCIF_VAR_T = 0, TCIF_VAR_ALPHA = 1 };          /* interfaceCompositionModel::modelVariable */
+typedef struct tcif_lee_model {                        /* massTransferModel ((from to) {type Lee; ...}) */
+    int32_t from, to;                                  /* phase indices of the ordered pair key */
+    double C, Tactivate, alphaMin;                     /* Lee.C:39-42 */
+    int32_t modelVariable;                             /* TCIF_VAR_*: KSu(alpha, .) is valid only for TCIF_VAR_ALPHA */
+    int32_t includeDivU;                               /* interfaceCompositionModel::includeDivU() */
+} tcif_lee_model;
+TCIF_API int tcif_mass_transfer_clear(tcif_ctx *ctx);
+TCIF_API int tcif_add_mass_transfer_lee(tcif_ctx *ctx, const tcif_lee_model *model);
+/* totalPhasePairs() in its HashTable iteration order as (phase1, phase2) index pairs; default: all i<j. */
+TCIF_API int tcif_set_phase_pairs(tcif_ctx *ctx, int nPairs, const int32_t *pairs);
+/* dmdt_[from to] as computed by the host (any model); NULL = zero field.  [nCells] */
+TCIF_API int tcif_set_dmdt(tcif_ctx *ctx, int from, int to, const double *internal);
+TCIF_API int tcif_get_dmdt(tcif_ctx *ctx, int from, int to, double *internal);
+/* correctMassSources(T): dmdt_[key] = Kexp(T) for every registered model, from the resident alpha, rho, T. */
+TCIF_API int tcif_correct_mass_sources(tcif_ctx *ctx);
+/* Su_ = Sp_ = 0; alphaTransfer(Su_, Sp_) from the resident alpha, phi, rho, dmdt: the result becomes the Su/Sp
+ * of the MULES entry points (as tcif_set_su_sp would).  ddtAlphaMax (:700-702) optional. */
+TCIF_API int tcif_alpha_transfer(tcif_ctx *ctx, double *ddtAlphaMax);
+/* on: tcif_solve_alphas / tcif_time_step_host call alphaTransfer inside every corrector where solveAlphas
+ * calls calculateSuSp() (multiphaseSystem.C:280-292). */
+TCIF_API int tcif_set_mass_transfer_in_solve(tcif_ctx *ctx, int on);
+TCIF_API int tcif_get_su_sp(tcif_ctx *ctx, int phase, double *Su, double *Sp);
+/* Udiag[nCells] += V * sum_models Cu*sqr(alpha_s)/(pow3(1-alpha_s)+1e-3)   (UEqn diagonal, host buffer in/out). */
+TCIF_API int tcif_interface_porosity(tcif_ctx *ctx, int nModels, const int32_t *solidPhase, const double *Cu, double *Udiag);
+
 /* Logging scalars of multiphaseSystem.C:408-425: sum(V*alpha), min, max (global over ranks). */
 TCIF_API int tcif_alpha_stats(tcif_ctx *ctx, int phase, double out3[3]);
 

@@ -61,7 +61,7 @@ class OrcComm(C.Structure):
 
 def build(force: bool = False) -> str:
     so = os.path.join(_HERE, "libtcif_oracle.so")
-    src = [os.path.join(_HERE, f) for f in ("tcif_oracle.c", "tcif_oracle.h")]
+    src = [os.path.join(_HERE, f) for f in ("tcif_oracle.c", "tcif_oracle.h", "tcif_oracle_alpha.inc", "tcif_oracle_mass.inc")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src if os.path.exists(s)):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
     return so
@@ -404,3 +404,101 @@ def flux_of_vector(m, Fi, Fb):
     oi, ob = np.zeros(h.s.nIF), np.zeros(h.s.nBF)
     lib().orc_flux_of_vector(h.ref, _d(Fi), _d(Fb), _d(oi), _d(ob))
     return oi, ob
+
+
+# ---- Su/Sp of the phase-fraction equations, porous interface drag --------------------
+VAR_T, VAR_ALPHA = 0, 1
+
+
+class OrcLee(C.Structure):
+    _fields_ = [("from_", C.c_int32), ("to", C.c_int32), ("C", C.c_double), ("Tactivate", C.c_double),
+                ("alphaMin", C.c_double), ("modelVariable", C.c_int32), ("includeDivU", C.c_int32)]
+
+
+class OrcMass(C.Structure):
+    _fields_ = [("nModels", C.c_int32), ("models", C.POINTER(OrcLee)), ("nPairs", C.c_int32), ("pairs", c_ip),
+                ("rhoUniform", c_dp), ("rhoi", C.POINTER(c_dp))]
+
+
+class MassHandle:
+    """orc_mass built from python values; keeps the arrays alive.  models: list of dicts (from, to, C, Tactivate,
+    alphaMin, modelVariable, includeDivU); pairs: [(p1, p2), ...]; rho: uniform per-phase densities; rho_fields:
+    optional per-phase arrays (None entries fall back to rho)."""
+
+    def __init__(self, models, pairs, rho, rho_fields=None):
+        self.models = (OrcLee * max(len(models), 1))()
+        for i, md in enumerate(models):
+            self.models[i] = OrcLee(md["from"], md["to"], md["C"], md["Tactivate"], md.get("alphaMin", 0.0),
+                                    md.get("modelVariable", VAR_T), int(md.get("includeDivU", True)))
+        self.pairs = i32(np.asarray(pairs, dtype=np.int32).reshape(-1))
+        self.rho = f64(rho)
+        self.rf = [None if r is None else f64(r) for r in rho_fields] if rho_fields is not None else None
+        self.rfp = None
+        if self.rf is not None:
+            self.rfp = (c_dp * len(self.rf))(*[(_d(r) if r is not None else None) for r in self.rf])
+        self.s = OrcMass(len(models), self.models, len(pairs), _i(self.pairs), _d(self.rho),
+                         C.cast(self.rfp, C.POINTER(c_dp)) if self.rfp is not None else None)
+
+    @property
+    def ref(self):
+        return C.byref(self.s)
+
+
+def div_phi(m, phii, phib):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    phii, phib = f64(phii), f64(phib)
+    out = np.zeros(h.s.nCells)
+    lib().orc_div_phi(h.ref, _d(phii), _d(phib), _d(out))
+    return out
+
+
+def correct_mass_sources(m, mass, alphas_i, T):
+    """dmdt[i] = Kexp(T) of model i (MassTransferPhaseSystem::correctMassSources)."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    ai = [f64(a) for a in alphas_i]
+    T = f64(T)
+    out = [np.zeros(h.s.nCells) for _ in range(mass.s.nModels)]
+    lib().orc_correct_mass_sources(h.ref, mass.ref, _pp(ai), _d(T), _pp(out))
+    return out
+
+
+def alpha_transfer(m, mass, alphas_i, dmdt, phii, phib, comm=None):
+    """alphaTransfer on zeroed Su/Sp.  Returns (Su[P], Sp[P], ddtAlphaMax)."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    P = len(alphas_i)
+    ai = [f64(a) for a in alphas_i]
+    dm = [f64(d) for d in dmdt] if dmdt else None
+    phii, phib = f64(phii), f64(phib)
+    Su = [np.zeros(h.s.nCells) for _ in range(P)]; Sp = [np.zeros(h.s.nCells) for _ in range(P)]
+    L = lib()
+    L.orc_alpha_transfer.restype = C.c_double
+    mx = L.orc_alpha_transfer(h.ref, C.byref(comm) if comm else None, mass.ref, P, _pp(ai), _pp(dm) if dm else None,
+                              _d(phii), _d(phib), _pp(Su), _pp(Sp))
+    return Su, Sp, float(mx)
+
+
+def interface_porosity(m, solidPhase, Cu, alphas_i):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    ai = [f64(a) for a in alphas_i]
+    sp, cu = i32(solidPhase), f64(Cu)
+    out = np.zeros(h.s.nCells)
+    lib().orc_interface_porosity(h.ref, len(sp), _i(sp), _d(cu), _pp(ai), _d(out))
+    return out
+
+
+def solve_mt(m, cfg, ctl, alphas_i, alphas_b, alphaBc, phii, phib, deltaT, rho, mass, dmdt, cAlpha=None, comm=None):
+    """multiphaseSystem::solve() with calculateSuSp() inside every corrector."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    P = len(alphas_i)
+    ai = [f64(a).copy() for a in alphas_i]; ab = [f64(a).copy() for a in alphas_b]
+    bc = i32(alphaBc).reshape(P, -1)
+    phii, phib = f64(phii), f64(phib)
+    cA = f64(np.ones((P, P)) if cAlpha is None else cAlpha)
+    rho = f64(rho)
+    dm = [f64(d) for d in dmdt] if dmdt else None
+    pi = [np.zeros(h.s.nIF) for _ in range(P)]; pb = [np.zeros(h.s.nBF) for _ in range(P)]
+    ri, rb = np.zeros(h.s.nIF), np.zeros(h.s.nBF)
+    lib().orc_solve_mt(h.ref, C.byref(comm) if comm else None, C.byref(cfg), C.byref(ctl), P, _pp(ai), _pp(ab), _i(bc),
+                       _d(phii), _d(phib), _d(cA), _d(rho), None, None, None, None,
+                       C.c_double(deltaT), _pp(pi), _pp(pb), _d(ri), _d(rb), mass.ref, _pp(dm) if dm else None)
+    return dict(alpha_i=ai, alpha_b=ab, alphaPhi_i=pi, alphaPhi_b=pb, rhoPhi_i=ri, rhoPhi_b=rb)

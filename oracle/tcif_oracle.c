@@ -703,4 +703,5 @@ double orc_stage_threads(int nDom, const orc_mesh *meshes, const orc_mules_cfg *
     free(sh.sendPtr); free(sh.redbuf); free(args); free(th);
     return tmax;
 }
+#include "tcif_oracle_mass.inc"
 #include "tcif_oracle_alpha.inc"

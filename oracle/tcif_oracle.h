@@ -240,6 +240,45 @@ void orc_solve(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg, c
 /* fvc::flux(volVectorField) with linear interpolation (pEqn.H:31-38 consumes divCapillaryStress() this way). */
 void orc_flux_of_vector(const orc_mesh *m, const double *Fi, const double *Fb, double *outi, double *outb);
 
+/* ---- Su/Sp of the phase-fraction equations and porous interface drag -------- */
+enum { ORC_VAR_T = 0, ORC_VAR_ALPHA = 1 };      /* interfaceCompositionModel::modelVariable */
+/* meltingEvaporationModels::Lee (Lee.C:35-45): one entry of massTransferModel (from to) */
+typedef struct orc_lee {
+    int32_t from, to;
+    double C, Tactivate, alphaMin;
+    int32_t modelVariable;     /* ORC_VAR_* */
+    int32_t includeDivU;
+} orc_lee;
+typedef struct orc_mass {
+    int32_t nModels; const orc_lee *models;
+    int32_t nPairs; const int32_t *pairs;       /* totalPhasePairs in iteration order: (phase1, phase2) */
+    const double *rhoUniform;                   /* [nPhases] used when rhoi == NULL or rhoi[p] == NULL */
+    const double *const *rhoi;                  /* thermo().rho() per phase, may be NULL */
+} orc_mass;
+void orc_div_phi(const orc_mesh *m, const double *phii, const double *phib, double *out);
+void orc_lee_kexp(int nC, const orc_lee *mdl, const double *alphaFrom, const double *rhoFrom, const double *T, double *out);
+int orc_lee_ksu(int nC, const orc_lee *mdl, int variable, const double *alphaFrom, const double *rhoFrom,
+                const double *refValue, double *out);
+/* MassTransferPhaseSystem::correctMassSources(T) (:447-497): dmdt[i] = Kexp(T) of model i */
+void orc_correct_mass_sources(const orc_mesh *m, const orc_mass *mt, const double *const *alphai, const double *T,
+                              double *const *dmdt);
+/* MassTransferPhaseSystem::alphaTransfer(Su, Sp) (:503-704); Su/Sp are added to; returns ddtAlphaMax */
+double orc_alpha_transfer(const orc_mesh *m, const orc_comm *c, const orc_mass *mt, int nPhases,
+                          const double *const *alphai, const double *const *dmdt,
+                          const double *phii, const double *phib, double *const *Su, double *const *Sp);
+/* phaseSystem::addInterfacePorosity (phaseSystem.C:1148-1183) with VollerPrakash::S() (VollerPrakash.C:66-72) */
+void orc_interface_porosity(const orc_mesh *m, int nModels, const int32_t *solidPhase, const double *Cu,
+                            const double *const *alphai, double *Udiag);
+/* orc_solve with calculateSuSp() inside every corrector (multiphaseSystem.C:280-292): Su/Sp zeroed, then
+ * alphaTransfer from the current alpha and the stored dmdt.  mt == NULL: identical to orc_solve. */
+void orc_solve_mt(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg, const orc_alpha_ctl *ctl,
+                  int nPhases, double *const *alphai, double *const *alphab, const int32_t *alphaBc,
+                  const double *phii, const double *phib, const double *cAlpha,
+                  const double *rhoUniform, const double *const *rhoi, const double *const *rhob,
+                  const double *const *Su, const double *const *Sp, double deltaT,
+                  double *const *alphaPhii, double *const *alphaPhib, double *rhoPhii, double *rhoPhib,
+                  const orc_mass *mt, const double *const *dmdt);
+
 #ifdef __cplusplus
 }
 #endif

@@ -39,6 +39,15 @@ class MeshDesc(C.Structure):
                 ("deltaCoeffsBoundary", c_dp), ("weightsBoundary", c_dp)]
 
 
+VAR_T, VAR_ALPHA = 0, 1
+
+
+class LeeModel(C.Structure):
+    """tcif_lee_model (include/tcif.h)"""
+    _fields_ = [("from_", C.c_int32), ("to", C.c_int32), ("C", C.c_double), ("Tactivate", C.c_double),
+                ("alphaMin", C.c_double), ("modelVariable", C.c_int32), ("includeDivU", C.c_int32)]
+
+
 class AlphaControls(C.Structure):
     """tcif_alpha_controls: fvSolution "alpha" controls of solve()/solveAlphas()."""
     _fields_ = [("nAlphaCorr", C.c_int32), ("nAlphaSubCycles", C.c_int32), ("schemePhi", C.c_int32),
@@ -290,6 +299,50 @@ class Context:
         su = _f64(Su) if Su is not None else None
         sp = _f64(Sp) if Sp is not None else None
         self._ck(lib().tcif_set_su_sp(self.h, int(phase), _d(su), _d(sp)))
+
+    # -- Su/Sp from the mass-transfer models (MassTransferPhaseSystem::alphaTransfer)
+    def mass_transfer_clear(self):
+        self._ck(lib().tcif_mass_transfer_clear(self.h))
+
+    def add_mass_transfer_lee(self, from_, to, C_, Tactivate, alphaMin=0.0, modelVariable=VAR_T, includeDivU=True):
+        mdl = LeeModel(int(from_), int(to), float(C_), float(Tactivate), float(alphaMin), int(modelVariable), int(includeDivU))
+        self._ck(lib().tcif_add_mass_transfer_lee(self.h, C.byref(mdl)))
+
+    def set_phase_pairs(self, pairs):
+        a = np.ascontiguousarray(np.asarray(pairs, dtype=np.int32).reshape(-1))
+        self._ck(lib().tcif_set_phase_pairs(self.h, len(a) // 2, a.ctypes.data_as(C.POINTER(C.c_int32))))
+
+    def set_dmdt(self, from_, to, internal):
+        a = _f64(internal) if internal is not None else None
+        self._ck(lib().tcif_set_dmdt(self.h, int(from_), int(to), _d(a)))
+
+    def get_dmdt(self, from_, to):
+        a = np.empty(self.nCells)
+        self._ck(lib().tcif_get_dmdt(self.h, int(from_), int(to), _d(a)))
+        return a
+
+    def correct_mass_sources(self):
+        self._ck(lib().tcif_correct_mass_sources(self.h))
+
+    def alpha_transfer(self):
+        mx = C.c_double(0.0)
+        self._ck(lib().tcif_alpha_transfer(self.h, C.byref(mx)))
+        return mx.value
+
+    def set_mass_transfer_in_solve(self, on=True):
+        self._ck(lib().tcif_set_mass_transfer_in_solve(self.h, int(on)))
+
+    def get_su_sp(self, phase):
+        su, sp = np.empty(self.nCells), np.empty(self.nCells)
+        self._ck(lib().tcif_get_su_sp(self.h, int(phase), _d(su), _d(sp)))
+        return su, sp
+
+    def interface_porosity(self, solidPhase, Cu, Udiag):
+        sp = np.ascontiguousarray(solidPhase, dtype=np.int32)
+        cu = _f64(Cu)
+        d = _f64(Udiag).copy()
+        self._ck(lib().tcif_interface_porosity(self.h, len(sp), sp.ctypes.data_as(C.POINTER(C.c_int32)), _d(cu), _d(d)))
+        return d
 
     # -- hot path
     def div_capillary_stress(self):

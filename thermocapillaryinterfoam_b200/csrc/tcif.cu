@@ -8,6 +8,7 @@
 #include "tcif_device.cuh"
 #include "tcif_volume.cuh"
 #include "tcif_alpha.cuh"
+#include "tcif_mass.cuh"
 #include "../../include/tcif.h"
 
 #include <dlfcn.h>
@@ -50,11 +51,11 @@ inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 // ---- timers ---------------------------------------------------------------------------
 enum TimerId {
     T_GRAD_TENSOR = 0, T_DIV_TENSOR, T_MULES_SETUP, T_MULES_ITER, T_MULES_FINAL, T_LIMIT_SUM,
-    T_BOUNDARY, T_HALO, T_CONVERT, T_STATS, T_FLUX_ASSEMBLY, T_PREDICTOR, T_RHOPHI, T_COUNT
+    T_BOUNDARY, T_HALO, T_CONVERT, T_STATS, T_FLUX_ASSEMBLY, T_PREDICTOR, T_RHOPHI, T_MASS, T_COUNT
 };
 const char *kTimerNames[T_COUNT] = {
     "grad_tensor", "div_tensor", "mules_setup", "mules_iter", "mules_final", "limit_sum",
-    "boundary", "halo", "convert", "stats", "flux_assembly", "predictor", "rho_phi"};
+    "boundary", "halo", "convert", "stats", "flux_assembly", "predictor", "rho_phi", "alpha_transfer"};
 
 struct EvPair { cudaEvent_t a, b; int id; double bytes; };
 
@@ -170,6 +171,13 @@ struct tcif_ctx {
     double *predDiag[4]{}, *predRhs[4]{};
     double *dmaxDev = nullptr;
     int predictorSweeps[4]{};
+    // Su/Sp from alphaTransfer
+    struct MassModel { int from, to, var, divU; double C, Tact, aMin; double *dmdt; bool haveDmdt; };
+    std::vector<MassModel> massModels;
+    std::vector<int> massPairs;              // totalPhasePairs order; empty = all (i<j) in phase order
+    bool massInSolve = false;                // calculateSuSp() inside every solveAlphas corrector
+    long long *ddtMaxDev = nullptr;
+    double ddtAlphaMax = 0.0;
     // F is a pure function of (alpha, T, sigma): the solver evaluates it 2-4x per time step on unchanged
     // fields (UEqn.H:29, pEqn.H:35 per corrector, thermocapillaryInterFoam.C:150); fieldsVersion counts
     // every change of those inputs and forceVersion remembers which one F was computed from
@@ -1106,6 +1114,81 @@ void do_renormalise(tcif_ctx *c) {
     });
 }
 
+// MassTransferPhaseSystem::correctMassSources(T) (:447-497): dmdt_[key] = Lee::Kexp(T) for every model
+void do_correct_mass_sources(tcif_ctx *c) {
+    if (!c->haveT) failf("tcif_correct_mass_sources: no temperature field (tcif_set_temperature)");
+    for (auto &mm : c->massModels) {
+        if (!c->rhoSet[mm.from]) failf("tcif_correct_mass_sources: phase %d has no density (tcif_set_rho)", mm.from);
+        if (!mm.dmdt) mm.dmdt = c->dalloc<double>(c->stride);
+        timed(c, T_MASS, 32.0 * c->nC, [&] {
+            k_lee_kexp<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nC, mm.C, mm.Tact, mm.aMin, c->alpha[mm.from],
+                c->haveRho[mm.from] ? c->rho[mm.from] : nullptr, c->rhoU[mm.from], c->Tc, mm.dmdt);
+            c->launches++;
+        });
+        mm.haveDmdt = true;
+    }
+}
+
+// Su_/Sp_ := 0; alphaTransfer(Su_, Sp_)   (multiphaseSystem.C:282-292, MassTransferPhaseSystem.C:503-704)
+void do_alpha_transfer(tcif_ctx *c) {
+    require_comm(c);
+    MassArgs a{};
+    a.P = c->P;
+    std::vector<int> pairs = c->massPairs;
+    if (pairs.empty()) for (int i = 0; i < c->P; ++i) for (int j = i + 1; j < c->P; ++j) { pairs.push_back(i); pairs.push_back(j); }
+    a.nPairs = (int)pairs.size() / 2;
+    if (a.nPairs > TCIF_MAX_PAIRS) failf("tcif_alpha_transfer: more than %d phase pairs", TCIF_MAX_PAIRS);
+    a.nModels = (int)c->massModels.size();
+    for (int i = 0; i < a.nModels; ++i) {
+        const auto &mm = c->massModels[i];
+        a.mFrom[i] = mm.from; a.mVar[i] = mm.var; a.mC[i] = mm.C; a.mTact[i] = mm.Tact; a.mAmin[i] = mm.aMin;
+        a.dmdt[i] = mm.haveDmdt ? mm.dmdt : nullptr;
+    }
+    int includeDivU = 1;                                                    // :512
+    for (int q = 0; q < a.nPairs; ++q) {
+        int p1 = pairs[2 * q], p2 = pairs[2 * q + 1];
+        if (p1 < 0 || p1 >= c->P || p2 < 0 || p2 >= c->P || p1 == p2) failf("tcif_alpha_transfer: bad phase pair (%d,%d)", p1, p2);
+        a.pairs[2 * q] = p1; a.pairs[2 * q + 1] = p2; a.m12[q] = -1; a.m21[q] = -1;
+        for (int i = 0; i < a.nModels; ++i) {
+            if (c->massModels[i].from == p1 && c->massModels[i].to == p2) a.m12[q] = i;
+            if (c->massModels[i].from == p2 && c->massModels[i].to == p1) a.m21[q] = i;
+        }
+        if (a.m12[q] >= 0) includeDivU = c->massModels[a.m12[q]].divU;    // :555
+        if (a.m21[q] >= 0) includeDivU = c->massModels[a.m21[q]].divU;    // :583
+        a.divU[q] = includeDivU;
+        a.anyDivU |= includeDivU;
+    }
+    for (int p = 0; p < c->P; ++p) {
+        if (!c->rhoSet[p]) failf("tcif_alpha_transfer: phase %d has no density (tcif_set_rho)", p);
+        a.alpha[p] = c->alpha[p]; a.rhoU[p] = c->rhoU[p]; a.rho[p] = c->haveRho[p] ? c->rho[p] : nullptr;
+        if (!c->Su[p]) c->Su[p] = c->dalloc<double>(c->stride);
+        if (!c->Sp[p]) c->Sp[p] = c->dalloc<double>(c->stride);
+        a.Su[p] = c->Su[p]; a.Sp[p] = c->Sp[p];
+        c->haveSu[p] = c->haveSp[p] = true;
+    }
+    a.phi = c->phi; a.phib = c->phib;
+    if (!c->ddtMaxDev) c->ddtMaxDev = c->dalloc<long long>(2);
+    const long long init[2] = {dbl_ord(-1e300), dbl_ord(-1e300)};
+    CUDA_OK(cudaMemcpyAsync(c->ddtMaxDev, init, sizeof init, cudaMemcpyHostToDevice, c->stream));
+    a.ddtMax = c->ddtMaxDev;
+    double bytes = (double)c->nC * (4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko + 8 + 8.0 * c->P + 8.0 * a.nModels + 16.0 * c->P);
+    timed(c, T_MASS, bytes, [&] {
+        k_alpha_transfer<false><<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a);
+        c->launches++;
+        if (c->nBndCells) {
+            k_alpha_transfer<true><<<cdiv(c->nBndCells, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a);
+            c->launches++;
+        }
+    });
+    long long h[2];
+    CUDA_OK(cudaMemcpyAsync(h, c->ddtMaxDev, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    double v[2] = {ord_dbl(h[0]), ord_dbl(h[1])};
+    const int ops[2] = {RED_MAX, RED_MAX};
+    allreduce_host(c, v, ops, 2);                                           // gMax
+    c->ddtAlphaMax = std::max(v[0], v[1]);
+}
+
 // multiphaseSystem::solve() (multiphaseSystem.C:128-168) = nAlphaSubCycles x solveAlphas() (:170-429)
 void do_solve_alphas(tcif_ctx *c, const tcif_alpha_controls *ctl, double deltaT) {
     if (!ctl) failf("tcif_solve_alphas: null controls");
@@ -1120,6 +1203,7 @@ void do_solve_alphas(tcif_ctx *c, const tcif_alpha_controls *ctl, double deltaT)
         phic_begin(c, st);
         for (int acorr = 0; acorr < ctl->nAlphaCorr; ++acorr) {
             do_flux_assembly(c, ctl->schemePhi, ctl->schemePhir, st);     // :199-277
+            if (c->massInSolve) do_alpha_transfer(c);                     // :280-292 calculateSuSp()
             const bool fuse = can_fuse_limit_sum(c);
             do_limit(c, all, c->P, 1.0 / dt, 0, false, true, fuse);       // :296-319
             if (fuse) do_limit_sum_rest(c); else do_limit_sum(c);         // :321
@@ -1488,6 +1572,109 @@ int tcif_set_su_sp(tcif_ctx *c, int phase, const double *Su, const double *Sp) {
     if (Su) { if (!c->Su[phase]) c->Su[phase] = c->dalloc<double>(c->stride); up_cells(c, c->Su[phase], Su); }
     if (Sp) { if (!c->Sp[phase]) c->Sp[phase] = c->dalloc<double>(c->stride); up_cells(c, c->Sp[phase], Sp); }
     c->haveSu[phase] = Su != nullptr; c->haveSp[phase] = Sp != nullptr;
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+// ---- Su/Sp from the mass-transfer models -----------------------------------------
+int tcif_mass_transfer_clear(tcif_ctx *c) {
+    API_BEGIN(c)
+    c->massModels.clear(); c->massPairs.clear(); c->massInSolve = false;
+    API_END(c)
+}
+
+int tcif_add_mass_transfer_lee(tcif_ctx *c, const tcif_lee_model *mdl) {
+    API_BEGIN(c)
+    if (!mdl) failf("tcif_add_mass_transfer_lee: null model");
+    check_phase(c, mdl->from); check_phase(c, mdl->to);
+    if (mdl->from == mdl->to) failf("tcif_add_mass_transfer_lee: from == to");
+    if (mdl->modelVariable != TCIF_VAR_T && mdl->modelVariable != TCIF_VAR_ALPHA) failf("tcif_add_mass_transfer_lee: bad modelVariable");
+    if (!(mdl->Tactivate != 0)) failf("tcif_add_mass_transfer_lee: Tactivate must be non-zero");
+    for (const auto &mm : c->massModels)
+        if (mm.from == mdl->from && mm.to == mdl->to) failf("massTransferModel (%d to %d) given twice", mdl->from, mdl->to);
+    if ((int)c->massModels.size() >= TCIF_MAX_MASS_MODELS) failf("too many mass transfer models");
+    c->massModels.push_back({mdl->from, mdl->to, mdl->modelVariable, mdl->includeDivU ? 1 : 0, mdl->C, mdl->Tactivate, mdl->alphaMin, nullptr, false});
+    API_END(c)
+}
+
+int tcif_set_phase_pairs(tcif_ctx *c, int nPairs, const int32_t *pairs) {
+    API_BEGIN(c)
+    if (nPairs < 0 || nPairs > TCIF_MAX_PAIRS || (nPairs && !pairs)) failf("tcif_set_phase_pairs: bad arguments");
+    for (int q = 0; q < nPairs; ++q) { check_phase(c, pairs[2 * q]); check_phase(c, pairs[2 * q + 1]); if (pairs[2 * q] == pairs[2 * q + 1]) failf("tcif_set_phase_pairs: pair of a phase with itself"); }
+    c->massPairs.assign(pairs, pairs + 2 * nPairs);
+    API_END(c)
+}
+
+static tcif_ctx::MassModel &find_mass_model(tcif_ctx *c, int from, int to) {
+    for (auto &mm : c->massModels) if (mm.from == from && mm.to == to) return mm;
+    failf("no massTransferModel (%d to %d)", from, to);
+    throw std::logic_error("unreachable");
+}
+
+int tcif_set_dmdt(tcif_ctx *c, int from, int to, const double *internal) {
+    API_BEGIN(c)
+    auto &mm = find_mass_model(c, from, to);
+    if (!internal) { mm.haveDmdt = false; }
+    else {
+        if (!mm.dmdt) mm.dmdt = c->dalloc<double>(c->stride);
+        up_cells(c, mm.dmdt, internal);
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        mm.haveDmdt = true;
+    }
+    API_END(c)
+}
+
+int tcif_get_dmdt(tcif_ctx *c, int from, int to, double *internal) {
+    API_BEGIN(c)
+    auto &mm = find_mass_model(c, from, to);
+    if (!internal) failf("tcif_get_dmdt: null output");
+    if (mm.haveDmdt) CUDA_OK(cudaMemcpyAsync(internal, mm.dmdt, sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
+    else memset(internal, 0, sizeof(double) * c->nC);          // dmdt(key) of an empty entry is a zero field (:127-151)
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_correct_mass_sources(tcif_ctx *c) {
+    API_BEGIN(c)
+    do_correct_mass_sources(c);
+    API_END(c)
+}
+
+int tcif_alpha_transfer(tcif_ctx *c, double *ddtAlphaMax) {
+    API_BEGIN(c)
+    do_alpha_transfer(c);
+    if (ddtAlphaMax) *ddtAlphaMax = c->ddtAlphaMax;
+    API_END(c)
+}
+
+int tcif_set_mass_transfer_in_solve(tcif_ctx *c, int on) {
+    API_BEGIN(c)
+    c->massInSolve = on != 0;
+    API_END(c)
+}
+
+int tcif_get_su_sp(tcif_ctx *c, int phase, double *Su, double *Sp) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (Su) { if (c->haveSu[phase]) CUDA_OK(cudaMemcpyAsync(Su, c->Su[phase], sizeof(double) * c->nC, cudaMemcpyDefault, c->stream)); else memset(Su, 0, sizeof(double) * c->nC); }
+    if (Sp) { if (c->haveSp[phase]) CUDA_OK(cudaMemcpyAsync(Sp, c->Sp[phase], sizeof(double) * c->nC, cudaMemcpyDefault, c->stream)); else memset(Sp, 0, sizeof(double) * c->nC); }
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_interface_porosity(tcif_ctx *c, int nModels, const int32_t *solidPhase, const double *Cu, double *Udiag) {
+    API_BEGIN(c)
+    if (nModels < 0 || nModels > 8 || (nModels && (!solidPhase || !Cu)) || !Udiag) failf("tcif_interface_porosity: bad arguments");
+    PorosityArgs a{};
+    a.n = nModels;
+    for (int i = 0; i < nModels; ++i) { check_phase(c, solidPhase[i]); a.alpha[i] = c->alpha[solidPhase[i]]; a.Cu[i] = Cu[i]; }
+    if (c->stagingDoubles < (size_t)c->nC) failf("tcif_interface_porosity: staging buffer too small");
+    up_cells(c, c->staging, Udiag);
+    timed(c, T_MASS, (16.0 + 8.0 * nModels + 8) * c->nC, [&] {
+        k_interface_porosity<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nC, c->dm.V, a, c->staging);
+        c->launches++;
+    });
+    CUDA_OK(cudaMemcpyAsync(Udiag, c->staging, sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END(c)
 }
