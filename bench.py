@@ -43,6 +43,9 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong: the SAME box split over N ranks (default, BASELINE configs[4]); weak: --n (default 200) cells "
+                         "per edge PER RANK, the box grows with the simple (px py pz) layout")
     ap.add_argument("--cpu-n", type=int, default=0, help="edge of the CPU-baseline sample box (0 = auto)")
     return ap.parse_args()
 
@@ -147,7 +150,7 @@ def cpu_sample_edge(args, cores):
     if args.cpu_n:
         return args.cpu_n
     full = args.n or {1: 64, 2: 512, 3: 128, 4: 200, 5: 400}[args.config]
-    return min(full, 128 if cores >= 8 else 96)
+    return min(full, 160 if cores >= 8 else 96)      # ~10-20 s of CPU work at 16 stages on 16 cores
 
 
 def run_reference(args, rank):
@@ -211,8 +214,16 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
-    spec = cases.case(args.config, args.n or None)
     procs = hm.procs_for(world)
+    if args.scaling == "weak":
+        import dataclasses
+        base = args.n or 200
+        spec = cases.case(args.config, base)
+        if spec.two_d:
+            raise SystemExit("bench.py: --scaling weak is for the 3-D configs")
+        spec = dataclasses.replace(spec, n=(base * procs[0], base * procs[1], base * procs[2]))
+    else:
+        spec = cases.case(args.config, args.n or None)
     t0 = time.time()
     m = hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, rank)
     f = cases.synthetic_fields(spec, m)
@@ -357,7 +368,7 @@ def run_ours(args, rank, world, local_rank):
     if world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
         edge = cpu_sample_edge(args, cores)
-        nst = 4
+        nst = 16
         rate, secs, nd, cprocs, cspec = cpu_stage_rate(args.config, edge, nst, cores)
         cpu = {"value": rate, "unit": UNIT, "cores": nd, "kind": "port", "host_cores": cores,
                "sample": f"{cspec.name} {edge}^3 = {cspec.nCells} cells, {cspec.nPhases} phases, {nst} stages, "
@@ -365,9 +376,11 @@ def run_ours(args, rank, world, local_rank):
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": workload_name(args), "phases": P, "pairs": len(spec.sigma), "nLimiterIter": 3,
+                "config": {"workload": workload_name(args) if args.scaling == "strong" else
+                           f"configs[{args.config - 1}] {spec.name} weak scaling {spec.n[0]}x{spec.n[1]}x{spec.n[2]} = {spec.nCells} cells, {spec.nPhases} phases",
+                           "phases": P, "pairs": len(spec.sigma), "nLimiterIter": 3,
                            "decomposition": f"simple {procs[0]}x{procs[1]}x{procs[2]}", "cells_per_gpu": nC,
                            "l2": "inputs larger than L2 (no flush needed)" if dev_bytes > 4 * 126e6 else
                                  "L2-resident case: latency-bound, no roofline claim",

@@ -49,7 +49,7 @@ class CaseSpec:
 
     @property
     def lengths(self):
-        return (1.0, 1.0, self.dx if self.two_d else 1.0 * self.n[2] / self.n[0])
+        return (1.0, 1.0 * self.n[1] / self.n[0], self.dx if self.two_d else 1.0 * self.n[2] / self.n[0])
 
     @property
     def patch_types(self):
