@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=5)
-    ap.add_argument("--n", type=int, default=0, help="cells per box edge (0 = BASELINE size)")
+    ap.add_argument("--n", "--edge", dest="n", type=int, default=0, help="cells per box edge (0 = BASELINE size); use --edge under torchrun, whose parser claims --n")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
