@@ -75,11 +75,12 @@ class ClockSampler:
         self.gpu = gpu_index
         self.proc = None
         self.lines = []
+        self.marks = {}
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -88,7 +89,11 @@ class ClockSampler:
 
     def _read(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.time(), ln.strip()))
+
+    def mark(self, name):
+        """wall-clock marks: 'load' (work starts, warm-up included), 't0'/'t1' (timed region)"""
+        self.marks[name] = time.time()
 
     def stop(self):
         if not self.proc:
@@ -100,7 +105,15 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons, pw = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        t0, t1 = self.marks.get("t0", 0.0), self.marks.get("t1", float("inf"))
+        lines = [ln for (t, ln) in self.lines if t0 <= t <= t1 + 0.05]
+        window = "timed region"
+        if len(lines) < 2:      # timed region shorter than the sampling period: widen to the warm-up steps before it
+            tl = self.marks.get("load", 0.0)
+            lines = [ln for (t, ln) in self.lines if tl <= t <= t1 + 0.05]
+            window = "warm-up + timed region (timed region shorter than the sampling period)"
+        self.window = window
+        for ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -114,7 +127,7 @@ class ClockSampler:
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "power_w_max": float(max(pw)), "samples": len(sm)}
+                "power_w_max": float(max(pw)), "samples": len(sm), "window": window}
 
 
 # ---- CPU arm: the oracle, domain-decomposed on the host cores ----------------------------------
@@ -245,21 +258,25 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- value: device-resident stages --------------------------------------------------------
     with torch.cuda.stream(stream):
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()
+            time.sleep(0.3)            # let nvidia-smi come up before the GPU gets busy
+        sampler.mark("load")
         for _ in range(args.warmup):
             ctx.stage(dt)
         ctx.timers_enable(True)
         ctx.timers_reset()
         launches0 = ctx.launch_count
-        sampler = ClockSampler(local_rank)
         barrier()
-        if rank == 0:
-            sampler.start()
+        sampler.mark("t0")
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(args.steps):
             ctx.stage(dt)
         e1.record(stream)
         barrier()
+        sampler.mark("t1")
         clocks = sampler.stop() if rank == 0 else None
         ms = max_over_ranks(e0.elapsed_time(e1))
         launches = ctx.launch_count - launches0
