@@ -139,6 +139,7 @@ struct tcif_ctx {
     std::vector<int> cpPatch, cpOff;    // coupled patches: patch id, offset in coupled-face units
     double sumV = 0.0;
     DMesh dm{};
+    int tileStrips = 0;      // 1: volume sweeps walk the tiles strip by strip (build_tile_order)
     int tsum = 0;            // force kernels carry the pair-summed stress tensor (6 comps) instead of Q tensors
     int *d_faceMap = nullptr;           // host face f -> device slot
     std::vector<void *> allocs;
@@ -271,6 +272,49 @@ void timers_collect(tcif_ctx *c) {
 }
 
 // ---- mesh upload: OpenFOAM ldu addressing -> owner-slot-major padded ELL ----------------
+// Traversal order of the 256-cell tiles for the volume sweeps (DMesh::tileOrder).  Any permutation is valid
+// (cells of one launch are independent); this one targets numberings that are banded like a structured
+// block (blockMesh / simple decomposition output): the modal neighbour offset of each owner slot gives the
+// strides (1, a, b) = (cell, row, plane).  Ascending order has a reuse distance of one plane (b cells) for the
+// +-z neighbours, which at 400^3 is more than L2 holds across all streams of a sweep; walking the mesh in
+// strips of H rows (all planes of strip 0, then strip 1, ...) shortens it to a*H cells at the price of one
+// extra row fetch per strip edge.  Returns empty (= ascending) when no such structure is found, when the
+// mesh is small enough for L2 anyway, or with TCIF_TILE_ORDER=0.  TCIF_STRIP_CELLS sets a*H (default 16384).
+std::vector<int> build_tile_order(int nC, int stride, int Ko, const std::vector<int> &nbrOwn) {
+    const char *e = getenv("TCIF_TILE_ORDER");
+    const int mode = e ? atoi(e) : 1;                  // 0 off, 1 auto, 2 force (also on small meshes)
+    if (mode == 0 || Ko < 3) return {};
+    if (mode == 1 && nC < (1 << 21)) return {};        // <= 2 M cells: a plane of all streams fits in L2
+    std::vector<long long> offs;
+    for (int k = 0; k < Ko; ++k) {
+        std::map<long long, long long> hist;
+        long long valid = 0;
+        for (int c = 0; c < nC; c += (nC > (1 << 20) ? 7 : 1)) {      // a sample is enough for the mode
+            int n = nbrOwn[(size_t)k * stride + c];
+            if (n >= 0) { ++hist[(long long)n - c]; ++valid; }
+        }
+        long long best = 0, cnt = 0;
+        for (auto &kv : hist) if (kv.second > cnt) { cnt = kv.second; best = kv.first; }
+        if (valid == 0 || cnt < 0.8 * valid || best <= 0) return {};
+        offs.push_back(best);
+    }
+    std::sort(offs.begin(), offs.end());
+    const long long a = offs[offs.size() - 2], b = offs[offs.size() - 1];
+    if (a < 2 || b <= a || b % a != 0) return {};
+    const long long R = b / a;                         // rows per plane
+    const char *sc = getenv("TCIF_STRIP_CELLS");
+    long long H = std::max<long long>(2, (sc ? atoll(sc) : 16384) / a);
+    if (H >= R) return {};
+    const long long nStrips = (R + H - 1) / H;
+    H = (R + nStrips - 1) / nStrips;                   // even strips
+    const int nTiles = cdiv(nC, 256);
+    std::vector<int> order(nTiles);
+    for (int t = 0; t < nTiles; ++t) order[t] = t;
+    auto strip_of = [&](int t) { long long c0 = (long long)t * 256; return ((c0 % b) / a) / H; };
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return strip_of(x) < strip_of(y); });
+    return order;
+}
+
 void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
     const int nC = m->nCells, nIF = m->nInternalFaces, nBF = m->nBoundaryFaces, nP = m->nPatches;
     if (nC <= 0 || nIF < 0 || nBF < 0 || nP < 0) failf("tcif_create: bad mesh sizes");
@@ -306,7 +350,13 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
         w[fd] = m->weights[f];
     }
     DMesh &d = c->dm;
-    { const char *e = getenv("TCIF_PF_AHEAD"); d.pfAhead = e ? atoi(e) : 148 * TCIF_TPB; }   // one CTA per SM ahead (profiles/r02_variants.md)
+    { const char *e = getenv("TCIF_PF_AHEAD"); d.pfTiles = (e ? atoi(e) : 148 * 256) / 256; }   // one CTA per SM ahead (profiles/r02_variants.md)
+    d.nTiles = cdiv(nC, 256);
+    {
+        std::vector<int> order = build_tile_order(nC, stride, Ko, nbrOwn);
+        d.tileOrder = order.empty() ? nullptr : c->upload(order);
+        c->tileStrips = order.empty() ? 0 : 1;
+    }
     d.nC = nC; d.stride = stride; d.Ko = Ko; d.Kn = Kn; d.nFd = (int)c->nFd; d.nBF = nBF; d.nPatches = nP;
     d.nbrOwn = c->upload(nbrOwn); d.neiFace = c->upload(neiFace);
     d.Sfx = c->upload(sx); d.Sfy = c->upload(sy); d.Sfz = c->upload(sz); d.w = c->upload(w);
@@ -541,12 +591,16 @@ ForceArgs force_args(tcif_ctx *c, bool withTensor, bool withG) {
         default: { OLD; } break;                               \
     }
 
+// the force sweeps gather few arrays (their +-z planes fit in L2): ascending tile order is faster for them
+// (profiles/r02_variants.md), the strip order is for the MULES sweeps
+DMesh dm_ascending(const tcif_ctx *c) { DMesh d = c->dm; d.tileOrder = nullptr; return d; }
+
 template <bool BND, bool WG> void launch_grad_tensor(tcif_ctx *c, const ForceArgs &a) {
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
     if constexpr (!BND) {
-        int gv = cdiv(n, TCIF_TPB_FORCE), go = cdiv(n, TCIF_TPB);
-        DISPATCH_P(DISPATCH_KV((kv_grad_tensor<PP, K><<<gv, TCIF_TPB_FORCE, 0, c->stream>>>(c->dm, a)),
+        int gv = cdiv(n, 256) * (256 / TCIF_TPB_FORCE), go = cdiv(n, TCIF_TPB);
+        DISPATCH_P(DISPATCH_KV((kv_grad_tensor<PP, K><<<gv, TCIF_TPB_FORCE, 0, c->stream>>>(dm_ascending(c), a)),
                                (k_grad_tensor<PP, 0, 0, false, WG><<<go, TCIF_TPB, 0, c->stream>>>(c->dm, a))));
     } else {
         int grid = cdiv(n, TCIF_TPB);
@@ -558,8 +612,8 @@ template <bool BND> void launch_div_tensor(tcif_ctx *c, const ForceArgs &a) {
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
     if constexpr (!BND) {
-        int gv = cdiv(n, TCIF_TPB_FORCE), go = cdiv(n, TCIF_TPB);
-        DISPATCH_P(DISPATCH_KV((kv_div_tensor<PP, K><<<gv, TCIF_TPB_FORCE, 0, c->stream>>>(c->dm, a)),
+        int gv = cdiv(n, 256) * (256 / TCIF_TPB_FORCE), go = cdiv(n, TCIF_TPB);
+        DISPATCH_P(DISPATCH_KV((kv_div_tensor<PP, K><<<gv, TCIF_TPB_FORCE, 0, c->stream>>>(dm_ascending(c), a)),
                                (k_div_tensor<PP, 0, 0, false><<<go, TCIF_TPB, 0, c->stream>>>(c->dm, a))));
     } else {
         int grid = cdiv(n, TCIF_TPB);

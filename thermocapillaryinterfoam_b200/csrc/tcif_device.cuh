@@ -55,7 +55,9 @@ struct SigmaModel { int kind, n; double c[64]; };
 struct DMesh {
     int nC, stride, Ko, Kn, nFd;
     int nBF, nBndCells, nPatches, nCoupled;
-    int pfAhead;            // L2 prefetch distance of the volume sweeps in cells (0 = off)
+    int pfTiles;            // L2 prefetch distance of the volume sweeps in 256-cell tiles (0 = off)
+    int nTiles;             // ceil(nC / 256)
+    const int *tileOrder;   // [nTiles] traversal order of the 256-cell tiles (null = ascending), see build_tile_order()
     const int *nbrOwn;      // [Ko*stride] neighbour cell of the k-th owner face (-1: none)
     const int *neiFace;     // [Kn*stride] device face index of the k-th neighbour-side face (-1: none)
     const double *Sfx, *Sfy, *Sfz, *w;   // [Ko*stride]

@@ -57,7 +57,29 @@ struct Slots {
     }
 };
 
-// L2 prefetch of the contiguous (own-slot) streams a later CTA will read: cp = c + m.pfAhead.  The volume
+// The volume sweeps visit the mesh in 256-cell tiles.  Within one launch cells are independent, so the ORDER in
+// which CTAs visit the tiles is free: m.tileOrder (host-built, build_tile_order() in tcif.cu) walks banded
+// numberings strip by strip so that the +-z neighbour planes are still in L2 when they are gathered
+// (profiles/r02_variants.md: at 400^3 one plane of all streams is 70-90 MB, more than L2 keeps).
+// vblock counts CTAs in units of TPB_ cells (TPB_ = 128 or 256); c = cell of this thread, cp = cell whose
+// own-slot streams this thread prefetches (-1: none).
+struct CellIdx { int c, cp; };
+template <int TPB_> __device__ __forceinline__ CellIdx cell_of(const DMesh &m, int vblock) {
+    static_assert(TPB_ == 128 || TPB_ == 256, "tiles are 256 cells");
+    const int tile = TPB_ == 256 ? vblock : (vblock >> 1);
+    const int sub = (TPB_ == 256 ? 0 : (vblock & 1) * 128) + threadIdx.x;
+    CellIdx r;
+    r.c = (m.tileOrder ? m.tileOrder[tile] : tile) * 256 + sub;
+    r.cp = -1;
+    const int tp = tile + m.pfTiles;
+    if (m.pfTiles > 0 && tp < m.nTiles) {
+        const int cp = (m.tileOrder ? m.tileOrder[tp] : tp) * 256 + sub;
+        if (cp < m.nC) r.cp = cp;
+    }
+    return r;
+}
+
+// L2 prefetch of the contiguous (own-slot) streams a later CTA will read (cp of cell_of()).  The volume
 // sweeps are bound by memory latency (ncu: long-scoreboard stalls, ~45 % occupancy), and everything a cell
 // reads from HBM for the first time is one of these streams, so a prefetch issued one or two waves ahead
 // turns those misses into L2 hits.  No registers are tied up (prefetch has no destination).
@@ -78,13 +100,14 @@ template <int K> __device__ __forceinline__ void pf_geom(const DMesh &m, int cp)
 template <int P, int K>
 __global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
 kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const CellIdx ci = cell_of<TCIF_TPB_FORCE>(m, blockIdx.x);
+    const int c = ci.c;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     Slots<K> s;
     s.load(m, c);
     {
-        const int cp = c + m.pfAhead;
-        if (m.pfAhead > 0 && cp < m.nC) {
+        const int cp = ci.cp;
+        if (cp >= 0) {
             pf_slots<K>(m, cp); pf_geom<K>(m, cp);
 #pragma unroll
             for (int p = 0; p < P; ++p) pf_l2(a.alpha[p] + cp);
@@ -168,13 +191,14 @@ template <int P, int K>
 __global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
 kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
     constexpr int Q = P * (P - 1) / 2;
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const CellIdx ci = cell_of<TCIF_TPB_FORCE>(m, blockIdx.x);
+    const int c = ci.c;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     Slots<K> s;
     s.load(m, c);
     {
-        const int cp = c + m.pfAhead;
-        if (m.pfAhead > 0 && cp < m.nC) {
+        const int cp = ci.cp;
+        if (cp >= 0) {
             pf_slots<K>(m, cp); pf_geom<K>(m, cp);
 #pragma unroll
             for (int kk = 0; kk < 6; ++kk) pf_l2(a.Tq + (size_t)kk * m.stride + cp);
@@ -221,7 +245,7 @@ __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_SETUP)
 kv_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                const __grid_constant__ MulesParams prm) {
     const int p = blockIdx.x % b.nPh;
-    const int c = (blockIdx.x / b.nPh) * blockDim.x + threadIdx.x;
+    const int c = cell_of<TCIF_TPB>(m, blockIdx.x / b.nPh).c;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     const MulesPh &ph = b.ph[p];
     Slots<K> s;
@@ -281,7 +305,7 @@ template <int K, bool FIRST>
 __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_ITER)
 kv_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, int flip) {
     const int p = blockIdx.x % b.nPh;
-    const int c = (blockIdx.x / b.nPh) * blockDim.x + threadIdx.x;
+    const int c = cell_of<TCIF_TPB>(m, blockIdx.x / b.nPh).c;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     const MulesPh &ph = b.ph[p];
     const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
@@ -329,7 +353,7 @@ __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
 kv_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                const __grid_constant__ MulesParams prm, int flip, int nIter) {
     const int p = blockIdx.x % b.nPh;
-    const int c = (blockIdx.x / b.nPh) * blockDim.x + threadIdx.x;
+    const int c = cell_of<TCIF_TPB>(m, blockIdx.x / b.nPh).c;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     const MulesPh &ph = b.ph[p];
     const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
@@ -398,7 +422,8 @@ template <int K, int NPH>
 __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_SETUP)
 kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                 const __grid_constant__ MulesParams prm) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const CellIdx ci = cell_of<TCIF_TPB>(m, blockIdx.x);
+    const int c = ci.c;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     Slots<K> s;
     s.load(m, c);
@@ -406,8 +431,8 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
 #pragma unroll
     for (int k = 0; k < K; ++k) { phiN[k] = prm.phi[s.fdN[k]]; phiO[k] = __ldcs(prm.phi + k * m.stride + c); }
     const double V = m.V[c];
-    const int cp = c + m.pfAhead;
-    const bool pf = m.pfAhead > 0 && cp < m.nC;
+    const int cp = ci.cp;
+    const bool pf = cp >= 0;
     if (pf) { pf_slots<K>(m, cp); pf_face<K>(prm.phi, m.stride, cp); pf_l2(m.V + cp); }
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
@@ -471,12 +496,13 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
 template <int K, bool FIRST, int NPH>
 __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_ITER)
 kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const CellIdx ci = cell_of<TCIF_TPB>(m, blockIdx.x);
+    const int c = ci.c;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     Slots<K> s;
     s.load(m, c);
-    const int cp = c + m.pfAhead;
-    const bool pf = m.pfAhead > 0 && cp < m.nC;
+    const int cp = ci.cp;
+    const bool pf = cp >= 0;
     if (pf) pf_slots<K>(m, cp);
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
@@ -546,7 +572,8 @@ __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
 kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                 const __grid_constant__ MulesParams prm, int nIter) {
     static_assert(!LSUM || MODE == 0, "limitSum is fused into the returnCorr=true apply only");
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const CellIdx ci = cell_of<TCIF_TPB>(m, blockIdx.x);
+    const int c = ci.c;
     if (c >= m.nC || is_bnd_cell(m, c)) return;
     Slots<K> s;
     s.load(m, c);
@@ -557,8 +584,8 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
         if (MODE >= 1) phO[k] = __ldcs(prm.phi + k * m.stride + c);
     }
     const double V = (MODE == 2) ? m.V[c] : 1.0;
-    const int cp = c + m.pfAhead;
-    const bool pf = m.pfAhead > 0 && cp < m.nC;
+    const int cp = ci.cp;
+    const bool pf = cp >= 0;
     if (pf) {
         pf_slots<K>(m, cp);
         if (MODE >= 1) pf_face<K>(prm.phi, m.stride, cp);
