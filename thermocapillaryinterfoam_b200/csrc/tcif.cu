@@ -1077,6 +1077,8 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
                            k_pred_setup<true><<<gridB, TCIF_TPB, 0, c->side>>>(c->dm, b); c->launches++; }); });
     }
     bool active[4] = {true, true, true, true};
+    bool kvpPred;
+    { MulesBatch mb{}; mb.nPh = nPh; kvpPred = use_kvp(c, mb); }
     for (int it = 0; it < maxIter; ++it) {
         bool any = false;
         for (int k = 0; k < nPh; ++k) any = any || active[k];
@@ -1084,7 +1086,9 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
         CUDA_OK(cudaMemsetAsync(c->dmaxDev, 0, sizeof(double) * 8, c->stream));
         PredBatch b = batch(active);
         sweep(c, [&] { timed(c, T_PREDICTOR, (double)nPh * c->nC * (32.0 + 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko), [&] {
-                           k_pred_jacobi<false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b); c->launches++; }); },
+                           if (kvpPred) { DISPATCH_KVP((kvp_pred_jacobi<K, NPH><<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b))); }
+                           else k_pred_jacobi<false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b);
+                           c->launches++; }); },
                  [&] {
                      if (c->nCoupled) {           // patchNeighbourField of the iterate
                          const double *src[4]; double *dst[4]; int n = 0;

@@ -671,3 +671,57 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
 }
 
 }  // namespace tcif
+#include "tcif_alpha.cuh"
+namespace tcif {
+
+// ---- Jacobi sweep of the implicit upwind predictor, phase-looped (see k_pred_jacobi, tcif_alpha.cuh) -----------
+// The matrix coefficients max(phi,0) / -min(phi,0) and the slot indices are shared by the phases of the batch:
+// loaded once per cell.  Same operations in the same order as k_pred_jacobi (bit-identical iterates).
+template <int K, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB, 4)
+kvp_pred_jacobi(const __grid_constant__ DMesh m, const __grid_constant__ PredBatch b) {
+    const CellIdx ci = cell_of<TCIF_TPB>(m, blockIdx.x);
+    const int c = ci.c;
+    const bool on = c < m.nC && !is_bnd_cell(m, c);
+    double dl[NPH];
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) dl[p] = 0.0;
+    if (on) {
+        Slots<K> s;
+        s.load(m, c);
+        double cN[K], cO[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            cN[k] = dmax(b.phi[s.fdN[k]], 0.0);
+            cO[k] = dmin(__ldcs(b.phi + k * m.stride + c), 0.0);
+        }
+        const int cp = ci.cp;
+        if (cp >= 0) { pf_slots<K>(m, cp); pf_face<K>(b.phi, m.stride, cp); }
+#pragma unroll
+        for (int p = 0; p < NPH; ++p) {
+            const PredPh &ph = b.ph[p];
+            if (!ph.active) continue;
+            if (cp >= 0) { pf_l2(ph.rhs + cp); pf_l2(ph.diag + cp); pf_l2(ph.x + cp); }
+            double xO[K], xN[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) { xO[k] = ph.x[s.oN[k]]; xN[k] = ph.x[s.nO[k]]; }
+            const double xC = ph.x[c], dg = __ldcs(ph.diag + c);
+            double acc = __ldcs(ph.rhs + c);
+#pragma unroll
+            for (int k = 0; k < K; ++k) if (s.vN[k]) acc += cN[k] * xO[k];
+#pragma unroll
+            for (int k = 0; k < K; ++k) if (s.vO[k]) acc -= cO[k] * xN[k];
+            const double xn = acc / dg;
+            ph.xn[c] = xn;
+            dl[p] = fabs(xn - xC);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) {
+        double d = dl[p];
+        for (int o = 16; o > 0; o >>= 1) d = dmax(d, __shfl_xor_sync(0xffffffffu, d, o));
+        if ((threadIdx.x & 31) == 0 && d > 0.0) atomic_max_nonneg(b.dmax + p, d);
+    }
+}
+
+}  // namespace tcif
