@@ -364,6 +364,8 @@ def run_ours(args, rank, world, local_rank):
             ctx.solve_alphas(ctl, dt)
             barrier()
             s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ctx.timers_enable(True)
+            ctx.timers_reset()
             s0.record(stream)
             for _ in range(args.e2e_steps):
                 ctx.solve_alphas(ctl, dt)
@@ -371,9 +373,12 @@ def run_ours(args, rank, world, local_rank):
             s1.record(stream)
             barrier()
             sm = max_over_ranks(s0.elapsed_time(s1))
+            st = ctx.timers_read()
+            ctx.timers_enable(False)
         extra["solve_plus_force_device"] = {"value": total_cells * args.e2e_steps / (sm * 1e-3) / 1e6, "unit": UNIT,
                                             "ms_per_step": sm / args.e2e_steps,
-                                            "what": "tcif_solve_alphas + tcif_div_capillary_stress on resident fields"}
+                                            "what": "tcif_solve_alphas + tcif_div_capillary_stress on resident fields",
+                                            "per_kernel_ms_per_step": {k: v["ms"] / args.e2e_steps for k, v in st.items() if v["launches"]}}
         del ai, ab, pi, pb, pi0, pb0, Ti, Tb, phii, phib, Fi, Fb, rpi, rpb
 
     stats = [ctx.alpha_stats(p) for p in range(P)]

@@ -1048,7 +1048,9 @@ void do_flux_assembly(tcif_ctx *c, int schemePhi, int schemePhir, PhicState &st)
 // implicit upwind predictor for a batch of phases (multiphaseSystem.C:348-363): Jacobi on the M-matrix
 // EulerDdt + upwind fvmDiv == Su + Sp until max|dpsi| <= tol per phase; then psi.correctBoundaryConditions()
 // and phiAlpha += alpha1Eqn.flux().
-void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double tol, int maxIter) {
+// addFlux=false leaves `phiAlpha += alpha1Eqn.flux()` to the caller (solve() folds it into explicitSolve's set-up
+// sweep, which evaluates the same upwind flux of the same psi anyway).
+void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double tol, int maxIter, bool addFlux = true) {
     if (!(deltaT > 0)) failf("predictor: deltaT must be positive");
     require_comm(c);
     for (int k = 0; k < nPh; ++k) {
@@ -1113,7 +1115,7 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
         }
     }
     correct_alpha_bcs(c, phases, nPh);
-    for (int k = 0; k < nPh; ++k) do_add_upwind(c, phases[k]);
+    if (addFlux) for (int k = 0; k < nPh; ++k) do_add_upwind(c, phases[k]);
 }
 
 void store_old(tcif_ctx *c) {
@@ -1266,8 +1268,8 @@ void do_solve_alphas(tcif_ctx *c, const tcif_alpha_controls *ctl, double deltaT)
             do_limit(c, all, c->P, 1.0 / dt, 0, false, true, fuse);       // :296-319
             if (fuse) do_limit_sum_rest(c); else do_limit_sum(c);         // :321
             if (ctl->implicitPredictor) {
-                do_predictor(c, all, c->P, dt, ctl->predictorTol, ctl->predictorMaxIter);   // :348-363
-                do_explicit(c, all, c->P, dt, false);                     // :365-375
+                do_predictor(c, all, c->P, dt, ctl->predictorTol, ctl->predictorMaxIter, false);   // :348-361
+                do_explicit(c, all, c->P, dt, true);                      // :363 (+= alpha1Eqn.flux()) and :365-375
             } else {
                 do_explicit(c, all, c->P, dt, true);                      // :346 (the commented-out bounded flux)
             }

@@ -716,11 +716,22 @@ kvp_pred_jacobi(const __grid_constant__ DMesh m, const __grid_constant__ PredBat
             dl[p] = fabs(xn - xC);
         }
     }
+    // max |dpsi| per phase: warp shuffle, then one CTA-level value, then at most one atomic per CTA and phase --
+    // and only if it can still raise the running maximum (one atomic per warp on three addresses serialised in
+    // L2 and cost more than the sweep itself)
+    __shared__ double red[NPH][TCIF_TPB / 32];
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
         double d = dl[p];
         for (int o = 16; o > 0; o >>= 1) d = dmax(d, __shfl_xor_sync(0xffffffffu, d, o));
-        if ((threadIdx.x & 31) == 0 && d > 0.0) atomic_max_nonneg(b.dmax + p, d);
+        if ((threadIdx.x & 31) == 0) red[p][threadIdx.x >> 5] = d;
+    }
+    __syncthreads();
+    if (threadIdx.x < NPH) {
+        double d = 0.0;
+#pragma unroll
+        for (int w = 0; w < TCIF_TPB / 32; ++w) d = dmax(d, red[threadIdx.x][w]);
+        if (d > 0.0 && d > *(volatile double *)(b.dmax + threadIdx.x)) atomic_max_nonneg(b.dmax + threadIdx.x, d);
     }
 }
 
