@@ -1035,8 +1035,8 @@ void do_flux_assembly(tcif_ctx *c, int schemePhi, int schemePhir, PhicState &st)
         }
     double bytes = (double)c->nC * (8.0 * c->P + 24.0 * c->P + 4.0 * c->Ko + 8.0 * c->Ko * (5 + c->P) + (c->Cx ? 24 : 0));
     timed(c, T_FLUX_ASSEMBLY, bytes, [&] {
-        int grid = cdiv(c->nC, TCIF_TPB);
-        DISPATCH_P(k_flux_assembly<PP><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, a));
+        int grid = cdiv(c->nC, TCIF_TPB_FLUX);
+        DISPATCH_P(k_flux_assembly<PP><<<grid, TCIF_TPB_FLUX, 0, c->stream>>>(c->dm, a));
         c->launches++;
         if (c->nBF) {
             DISPATCH_P(k_flux_assembly_bnd<PP><<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a));
