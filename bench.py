@@ -294,8 +294,15 @@ def run_ours(args, rank, world, local_rank):
     step_ms_sum = sum(v["ms"] for v in timers.values())
     stage_bytes_compulsory = sum(v["bytes"] for k, v in timers.items() if k not in ("convert", "stats")) / args.steps
     contract = contract_bytes(nC, nIF, nBF, P, QT, 3)
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")      # written by profiles/summarise_ncu.py from the committed capture
+    if os.path.exists(tp) and world == 1 and not args.n and args.config == 5 and args.scaling == "strong":
+        with open(tp) as fh:
+            tj = json.load(fh)
+        traffic = tj.get("bytes_per_launch", {}).get(top)
+        traffic_src = tj.get("source")
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                "traffic": None, "peak_source": how, "launches": tk["launches"],
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": how, "launches": tk["launches"],
                 "avg_launch_ms": tk["ms"] / tk["launches"], "kernel_share_of_step": tk["ms"] / step_ms_sum,
                 "bytes_per_launch": tk["bytes"] / tk["launches"],
                 "stage": {"compulsory_bytes_per_cell": stage_bytes_compulsory / nC,
