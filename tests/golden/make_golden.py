@@ -40,7 +40,43 @@ def build(config, n):
     return out
 
 
+# dmdt (Lee::Kexp), alphaTransfer Su/Sp, solve() with calculateSuSp() in the correctors
+MASS_CASE = ("mass_transfer_3d_n8", 5, 8)
+MASS_RHO = [7000.0, 1.2, 6500.0]
+MASS_PAIRS = [(0, 1), (0, 2), (1, 2)]
+MASS_MODELS = [{"from": 0, "to": 2, "C": 0.5, "Tactivate": 300.05, "alphaMin": 0.0},
+               {"from": 2, "to": 0, "C": -0.25, "Tactivate": 299.98, "alphaMin": 0.01},
+               {"from": 0, "to": 1, "C": 3.0, "Tactivate": 300.02, "alphaMin": 0.0}]
+
+
+def mass_inputs(config, n):
+    spec = cases.case(config, n)
+    m = global_mesh(spec)
+    f = cases.synthetic_fields(spec, m)
+    # deterministic non-solenoidal perturbation of phi so that div(phi) != 0
+    k = np.arange(m.nIF, dtype=np.float64)
+    f["phi_i"] = f["phi_i"] + 1e-3 * np.abs(f["phi_i"]).max() * np.sin(0.37 * k + 0.11 * k * k / max(m.nIF, 1))
+    return spec, m, f
+
+
+def build_mass(config, n):
+    spec, m, f = mass_inputs(config, n)
+    mass = orc.MassHandle(MASS_MODELS, MASS_PAIRS, MASS_RHO)
+    dm = orc.correct_mass_sources(m, mass, f["alpha_i"], f["T_i"])
+    Su, Sp, mx = orc.alpha_transfer(m, mass, f["alpha_i"], dm, f["phi_i"], f["phi_b"])
+    so = orc.solve_mt(m, orc.mules_cfg(3), orc.alpha_ctl(2, 1, "vanLeer", "linear", True, 1e-13, 300), f["alpha_i"],
+                      f["alpha_b"], f["alphaBc"], f["phi_i"], f["phi_b"], f["deltaT"], MASS_RHO, mass, dm)
+    out = dict(ddtAlphaMax=np.array([mx]))
+    for i in range(len(MASS_MODELS)):
+        out[f"dmdt{i}"] = dm[i]
+    for p in range(3):
+        out[f"Su{p}"] = Su[p]; out[f"Sp{p}"] = Sp[p]; out[f"solve_alpha_i{p}"] = so["alpha_i"][p]
+    return out
+
+
 if __name__ == "__main__":
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", MASS_CASE[0] + ".npz"), **build_mass(*MASS_CASE[1:]))
+    print("wrote", MASS_CASE[0])
     for name, config, n in CASES:
         np.savez_compressed(os.path.join(ROOT, "tests", "golden", name + ".npz"), **build(config, n))
         print("wrote", name)

@@ -51,3 +51,39 @@ def test_cuda_path_matches_golden(name, config, n):
         assert_field_close(ctx.get_phi_alpha(p)[0], z[f"solve_alphaPhi_i{p}"], f"solve alphaPhi{p}")
     assert_field_close(ctx.get_rho_phi()[0], z["solve_rhoPhi_i"], "rhoPhi")
     ctx.close()
+
+
+def test_oracle_reproduces_mass_transfer_golden():
+    z = np.load(os.path.join(GOLD, mg.MASS_CASE[0] + ".npz"))
+    got = mg.build_mass(*mg.MASS_CASE[1:])
+    assert set(z.files) == set(got)
+    for k in z.files:
+        assert_field_close(got[k], z[k], k, rtol=1e-13)
+
+
+@pytest.mark.gpu
+def test_cuda_path_matches_mass_transfer_golden():
+    z = np.load(os.path.join(GOLD, mg.MASS_CASE[0] + ".npz"))
+    spec, m, f = mg.mass_inputs(*mg.MASS_CASE[1:])
+    ctx = abi.Context(m, 3)
+    cases.load_case(ctx, spec, f)
+    ctx.set_cell_centres(f["C"], f["deltab"])
+    for p in range(3):
+        ctx.set_rho(p, mg.MASS_RHO[p])
+    for md in mg.MASS_MODELS:
+        ctx.add_mass_transfer_lee(md["from"], md["to"], md["C"], md["Tactivate"], md["alphaMin"])
+    ctx.set_phase_pairs(mg.MASS_PAIRS)
+    ctx.correct_mass_sources()
+    for i, md in enumerate(mg.MASS_MODELS):
+        assert_field_close(ctx.get_dmdt(md["from"], md["to"]), z[f"dmdt{i}"], f"dmdt{i}")
+    mx = ctx.alpha_transfer()
+    assert abs(mx - float(z["ddtAlphaMax"][0])) <= 1e-12 * abs(mx)
+    for p in range(3):
+        su, sp = ctx.get_su_sp(p)
+        assert_field_close(su, z[f"Su{p}"], f"Su{p}")
+        assert_field_close(sp, z[f"Sp{p}"], f"Sp{p}")
+    ctx.set_mass_transfer_in_solve(True)
+    ctx.solve_alphas(abi.alpha_controls(2, 1, "vanLeer", "linear", True, 1e-13, 300), f["deltaT"])
+    for p in range(3):
+        assert_field_close(ctx.get_alpha(p)[0], z[f"solve_alpha_i{p}"], f"solve alpha{p}", rtol=1e-11)
+    ctx.close()

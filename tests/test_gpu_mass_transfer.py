@@ -136,3 +136,67 @@ def test_errors():
     with pytest.raises(RuntimeError):
         ctx.set_dmdt(1, 2, np.zeros(m.nCells))               # no such model
     ctx.close()
+
+
+@pytest.mark.parametrize("procs", [(2, 1, 1), (2, 2, 2)])
+def test_decomposed_alpha_transfer_matches_serial(procs):
+    """Processor patches: div(phi) of a boundary-adjacent cell includes the processor-face fluxes, ddtAlphaMax is a
+    gMax over ranks.  Su/Sp are cell-local after that, so the decomposed result must be bit-identical to the serial
+    oracle up to the face-sum order of div(phi) (1e-12)."""
+    import threading
+    from thermocapillaryinterfoam_b200 import mesh as hm
+    spec = cases.case(5, 12)
+    g = global_mesh(spec)
+    fg = cases.synthetic_fields(spec, g)
+    rng = np.random.default_rng(11)
+    phig = fg["phi_i"] + 1e-3 * np.abs(fg["phi_i"]).max() * rng.standard_normal(g.nIF)
+    mass = orc.MassHandle(MODELS, PAIRS, RHO)
+    dm = orc.correct_mass_sources(g, mass, fg["alpha_i"], fg["T_i"])
+    Su, Sp, mxo = orc.alpha_transfer(g, mass, fg["alpha_i"], dm, phig, fg["phi_b"])
+    nd = procs[0] * procs[1] * procs[2]
+    meshes = [hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, r) for r in range(nd)]
+    fs = [cases.synthetic_fields(spec, m) for m in meshes]
+    grp = abi.Group(nd)
+    ctxs = [abi.Context(m, spec.nPhases) for m in meshes]
+    outs, errs = [None] * nd, []
+
+    def work(r):
+        try:
+            m, f, ctx = meshes[r], fs[r], ctxs[r]
+            ctx.comm_init_local(r, grp)
+            cases.load_case(ctx, spec, f)
+            # the perturbed global flux restricted to this rank (processor faces: sign by orientation)
+            fa = np.asarray(m.faceProcAddressing) - 1
+            phi_i = phig[fa]
+            phi_b = np.array(f["phi_b"])
+            for k in range(m.nPatches):
+                if m.patchType[k] == 3:
+                    sl = slice(int(m.patchStart[k]), int(m.patchStart[k] + m.patchSize[k]))
+                    a = np.asarray(m.bfaceProcAddressing)[sl]
+                    phi_b[sl] = np.sign(a) * phig[np.abs(a) - 1]
+            ctx.set_phi(phi_i, phi_b)
+            for p in range(3):
+                ctx.set_rho(p, RHO[p])
+            for md in MODELS:
+                ctx.add_mass_transfer_lee(md["from"], md["to"], md["C"], md["Tactivate"], md.get("alphaMin", 0.0))
+            ctx.set_phase_pairs(PAIRS)
+            ctx.correct_mass_sources()
+            mx = ctx.alpha_transfer()
+            outs[r] = dict(mx=mx, su=[ctx.get_su_sp(p) for p in range(3)], gid=np.asarray(m.cellGlobal))
+        except Exception as e:          # noqa: BLE001
+            errs.append((r, e))
+    ts = [threading.Thread(target=work, args=(r,), daemon=True) for r in range(nd)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(120)
+    assert not errs, errs
+    for r in range(nd):
+        gid = outs[r]["gid"]
+        assert outs[r]["mx"] == mxo
+        for p in range(3):
+            assert_field_close(outs[r]["su"][p][0], Su[p][gid], f"Su{p} rank {r}")
+            assert np.array_equal(outs[r]["su"][p][1], Sp[p][gid]), f"Sp{p} rank {r}"
+    for c in ctxs:
+        c.close()
+    grp.close()
