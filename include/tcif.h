@@ -254,6 +254,18 @@ TCIF_API int tcif_get_su_sp(tcif_ctx *ctx, int phase, double *Su, double *Sp);
 /* Udiag[nCells] += V * sum_models Cu*sqr(alpha_s)/(pow3(1-alpha_s)+1e-3)   (UEqn diagonal, host buffer in/out). */
 TCIF_API int tcif_interface_porosity(tcif_ctx *ctx, int nModels, const int32_t *solidPhase, const double *Cu, double *Udiag);
 
+/* MultiComponentPhaseModel::solveYi (phaseModel/MultiComponentPhaseModel/MultiComponentPhaseModel.C:182-388): the
+ * species MULES of one phase on the device -- flux assembly with interface compression (:199-297), MULES::limit
+ * (:299-311), implicit upwind predictor + explicitSolve (:321-378), inert species = max(1 - sum Yi, 0) (:383-384).
+ * Uses the resident alpha (all phases), phi, mesh geometry; Yinternal[i] [nCells] / Yboundary[i] [nBoundaryFaces]
+ * are host buffers in/out, Ybc [nSpecies*nPatches] the TCIF_BC_* kind per patch, Su/Sp[i] may be NULL (the
+ * massSpeciesTransfer sources); cYi, the two div schemes, nYiSubCycles (<= 1) and the Yi solver tolerance are the
+ * case's fvSolution/fvSchemes entries.  Overwrites nothing of the phase-fraction state. */
+TCIF_API int tcif_solve_yi(tcif_ctx *ctx, int phase, int nSpecies, int inertIndex,
+                           double *const *Yinternal, double *const *Yboundary, const int32_t *Ybc,
+                           const double *const *Su, const double *const *Sp, double cYi,
+                           int schemePhi, int schemePhir, int nYiSubCycles, double deltaT, double tol, int maxIter);
+
 /* Logging scalars of multiphaseSystem.C:408-425: sum(V*alpha), min, max (global over ranks). */
 TCIF_API int tcif_alpha_stats(tcif_ctx *ctx, int phase, double out3[3]);
 

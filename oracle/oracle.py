@@ -61,7 +61,7 @@ class OrcComm(C.Structure):
 
 def build(force: bool = False) -> str:
     so = os.path.join(_HERE, "libtcif_oracle.so")
-    src = [os.path.join(_HERE, f) for f in ("tcif_oracle.c", "tcif_oracle.h", "tcif_oracle_alpha.inc", "tcif_oracle_mass.inc")]
+    src = [os.path.join(_HERE, f) for f in ("tcif_oracle.c", "tcif_oracle.h", "tcif_oracle_alpha.inc", "tcif_oracle_mass.inc", "tcif_oracle_species.inc")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src if os.path.exists(s)):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
     return so
@@ -502,3 +502,23 @@ def solve_mt(m, cfg, ctl, alphas_i, alphas_b, alphaBc, phii, phib, deltaT, rho, 
                        _d(phii), _d(phib), _d(cA), _d(rho), None, None, None, None,
                        C.c_double(deltaT), _pp(pi), _pp(pb), _d(ri), _d(rb), mass.ref, _pp(dm) if dm else None)
     return dict(alpha_i=ai, alpha_b=ab, alphaPhi_i=pi, alphaPhi_b=pb, rhoPhi_i=ri, rhoPhi_b=rb)
+
+
+def solve_yi(m, cfg, alphas_i, alphas_b, alphaBc, ph, Y_i, Y_b, YBc, inertIndex, phii, phib, deltaT, cYi=1.0,
+             schemePhi="vanLeer", schemePhir="linear", Su=None, Sp=None, tol=1e-12, maxIter=200, comm=None):
+    """MultiComponentPhaseModel::solveYi for the species of phase `ph`.  Returns (Y_i, Y_b) lists."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    P, S = len(alphas_i), len(Y_i)
+    ai = [f64(a) for a in alphas_i]; ab = [f64(a) for a in alphas_b]
+    bc = i32(alphaBc).reshape(P, -1)
+    yi = [f64(a).copy() for a in Y_i]; yb = [f64(a).copy() for a in Y_b]
+    ybc = i32(YBc).reshape(S, -1)
+    phii, phib = f64(phii), f64(phib)
+    z = np.zeros(h.s.nCells)
+    su = [f64(x) if x is not None else z for x in Su] if Su is not None else None
+    sp = [f64(x) if x is not None else z for x in Sp] if Sp is not None else None
+    lib().orc_solve_yi(h.ref, C.byref(comm) if comm else None, C.byref(cfg), P, _pp(ai), _pp(ab), _i(bc), int(ph), S,
+                       int(inertIndex), _pp(yi), _pp(yb), _i(ybc), _d(phii), _d(phib), C.c_double(cYi),
+                       SCHEMES[schemePhi], SCHEMES[schemePhir], _pp(su) if su else None, _pp(sp) if sp else None,
+                       C.c_double(deltaT), C.c_double(tol), int(maxIter))
+    return yi, yb

@@ -279,6 +279,15 @@ void orc_solve_mt(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg
                   double *const *alphaPhii, double *const *alphaPhib, double *rhoPhii, double *rhoPhib,
                   const orc_mass *mt, const double *const *dmdt);
 
+/* MultiComponentPhaseModel::solveYi (MultiComponentPhaseModel.C:182-388): species MULES of phase `ph`.
+ * Y (internal, boundary) in/out [nSpecies]; YBc [nSpecies*nPatches]; Su/Sp per species may be NULL.
+ * cYi, nYiSubCycles <= 1, the two div schemes and the Yi linear-solver tolerance come from the case. */
+void orc_solve_yi(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg, int nPhases,
+                  const double *const *alphai, const double *const *alphab, const int32_t *alphaBc, int ph,
+                  int nSpecies, int inertIndex, double *const *Yi, double *const *Yb, const int32_t *YBc,
+                  const double *phii, const double *phib, double cYi, int schemePhi, int schemePhir,
+                  const double *const *Su, const double *const *Sp, double deltaT, double tol, int maxIter);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,82 @@
+"""GPU parity of the species MULES (MultiComponentPhaseModel::solveYi) against the CPU oracle.
+Tolerance 1e-11 relative + 1e-11*||.||inf (gradients use x*(1/V)+fma on the device, the predictor may stop one
+sweep apart); the phase-fraction state must come back untouched."""
+import threading
+
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+from thermocapillaryinterfoam_b200 import abi, cases, mesh as hm
+from helpers import assert_field_close, global_mesh
+
+pytestmark = pytest.mark.gpu
+
+
+def _species(m, nS, seed=3):
+    X = np.asarray(m.C)
+    rng = np.random.default_rng(seed)
+    raw = [0.2 + 0.15 * np.sin(5.0 * X[:, 0] + k) * np.cos(4.0 * X[:, 1] - k) + 0.02 * rng.standard_normal(m.nCells)
+           for k in range(nS)]
+    tot = sum(raw) + 0.3
+    Y = [r / tot for r in raw]
+    fc = np.asarray(m.faceCells, dtype=np.int64)
+    Yb = [y[fc].copy() for y in Y]
+    return Y, Yb
+
+
+def _delta_b(m):
+    fc = np.asarray(m.faceCells, dtype=np.int64)
+    return np.asarray(m.Cfb) - np.asarray(m.C)[fc]
+
+
+@pytest.mark.parametrize("config,n,ph,sphi,sphir,cYi", [(5, 12, 0, "vanLeer", "linear", 1.0), (5, 10, 2, "upwind", "vanLeer", 0.5),
+                                                      (3, 12, 1, "linear", "linear", 1.0), (2, 24, 0, "vanLeer", "vanLeer", 1.0)])
+def test_solve_yi_matches_oracle(config, n, ph, sphi, sphir, cYi):
+    spec = cases.case(config, n)
+    m = global_mesh(spec, grading=(1.5, None, None))
+    f = cases.synthetic_fields(spec, m)
+    nS = 3
+    Y, Yb = _species(m, nS)
+    ybc = np.zeros((nS, m.nPatches), np.int32)
+    ybc[0, 0] = abi.BC_FIXED_VALUE if hasattr(abi, "BC_FIXED_VALUE") else 1
+    Yb[0][int(m.patchStart[0]):int(m.patchStart[0] + m.patchSize[0])] = 0.25
+    rng = np.random.default_rng(9)
+    Su = [1e-2 * rng.uniform(0, 1, m.nCells), None, None]
+    Sp = [None, -1e-2 * rng.uniform(0, 1, m.nCells), None]
+    ctx = abi.Context(m, spec.nPhases)
+    cases.load_case(ctx, spec, f)
+    ctx.set_cell_centres(m.C, _delta_b(m))
+    a_before = [ctx.get_alpha(p) for p in range(spec.nPhases)]
+    yi, yb = ctx.solve_yi(ph, Y, Yb, ybc, 2, f["deltaT"], cYi=cYi, schemePhi=sphi, schemePhir=sphir, Su=Su, Sp=Sp)
+    ri, rb = orc.solve_yi(m, orc.mules_cfg(3), f["alpha_i"], f["alpha_b"], f["alphaBc"], ph, Y, Yb, ybc, 2,
+                          f["phi_i"], f["phi_b"], f["deltaT"], cYi=cYi, schemePhi=sphi, schemePhir=sphir, Su=Su, Sp=Sp)
+    for i in range(nS):
+        assert np.abs(ri[i] - Y[i]).max() > 1e-6                  # something happened
+        assert_field_close(yi[i], ri[i], f"Y{i}", rtol=1e-11)
+        assert_field_close(yb[i], rb[i], f"Y{i} boundary", rtol=1e-11)
+    for p in range(spec.nPhases):                                 # phase fractions untouched
+        ai, ab = ctx.get_alpha(p)
+        assert np.array_equal(ai, a_before[p][0]) and np.array_equal(ab, a_before[p][1])
+    # and the alpha path still works afterwards
+    ctx.stage(f["deltaT"])
+    ref = orc.stage(m, orc.mules_cfg(3), f["alpha_i"], f["alpha_b"], f["alphaBc"], f["sigma"], f["T_i"], f["T_b"],
+                    f["phi_i"], f["phi_b"], f["phiAlpha_i"], f["phiAlpha_b"], f["deltaT"])
+    for p in range(spec.nPhases):
+        assert_field_close(ctx.get_alpha(p)[0], ref["alpha_i"][p], f"alpha{p} after solve_yi")
+    ctx.close()
+
+
+def test_solve_yi_errors():
+    spec = cases.case(5, 8)
+    m = global_mesh(spec)
+    f = cases.synthetic_fields(spec, m)
+    Y, Yb = _species(m, 2)
+    ctx = abi.Context(m, 3)
+    cases.load_case(ctx, spec, f)
+    with pytest.raises(RuntimeError):      # vanLeer without cell centres
+        ctx.solve_yi(0, Y, Yb, np.zeros((2, m.nPatches), np.int32), 1, f["deltaT"])
+    with pytest.raises(RuntimeError):      # sub-cycling is not on the device path
+        ctx.solve_yi(0, Y, Yb, np.zeros((2, m.nPatches), np.int32), 1, f["deltaT"], schemePhi="upwind", schemePhir="upwind",
+                     nYiSubCycles=2)
+    ctx.close()

@@ -344,6 +344,28 @@ class Context:
         self._ck(lib().tcif_interface_porosity(self.h, len(sp), sp.ctypes.data_as(C.POINTER(C.c_int32)), _d(cu), _d(d)))
         return d
 
+    def solve_yi(self, phase, Y_i, Y_b, Ybc, inertIndex, deltaT, cYi=1.0, schemePhi="vanLeer", schemePhir="linear",
+                 Su=None, Sp=None, nYiSubCycles=1, tol=1e-12, maxIter=200):
+        """MultiComponentPhaseModel::solveYi for the species of `phase`; returns new (Y_i, Y_b) lists."""
+        S = len(Y_i)
+        yi = [_f64(a).copy() for a in Y_i]
+        yb = [_f64(a).copy() for a in Y_b]
+        bc = np.ascontiguousarray(np.asarray(Ybc, dtype=np.int32).reshape(S, -1))
+        dpp = C.POINTER(C.c_double) * S
+
+        def pp(arrs):
+            if arrs is None:
+                return None
+            keep = [(_f64(a) if a is not None else None) for a in arrs]
+            return dpp(*[(_d(a) if a is not None else None) for a in keep]), keep
+        su, sp = pp(Su), pp(Sp)
+        self._ck(lib().tcif_solve_yi(self.h, int(phase), S, int(inertIndex), dpp(*[_d(a) for a in yi]),
+                                     dpp(*[_d(a) for a in yb]), bc.ctypes.data_as(C.POINTER(C.c_int32)),
+                                     su[0] if su else None, sp[0] if sp else None, C.c_double(cYi),
+                                     SCHEMES[schemePhi], SCHEMES[schemePhir], int(nYiSubCycles), C.c_double(deltaT),
+                                     C.c_double(tol), int(maxIter)))
+        return yi, yb
+
     # -- hot path
     def div_capillary_stress(self):
         self._ck(lib().tcif_div_capillary_stress(self.h))

@@ -9,6 +9,7 @@
 #include "tcif_volume.cuh"
 #include "tcif_alpha.cuh"
 #include "tcif_mass.cuh"
+#include "tcif_species.cuh"
 #include "../../include/tcif.h"
 
 #include <dlfcn.h>
@@ -178,6 +179,11 @@ struct tcif_ctx {
     std::vector<int> massPairs;              // totalPhasePairs order; empty = all (i<j) in phase order
     bool massInSolve = false;                // calculateSuSp() inside every solveAlphas corrector
     long long *ddtMaxDev = nullptr;
+    // species MULES (solveYi): phase gradients kept aside + one species' working set swapped into a phase slot
+    double *GA = nullptr, *GAb = nullptr;
+    double *spY = nullptr, *spY0 = nullptr, *spYNew = nullptr, *spYb = nullptr, *spSu = nullptr, *spSp = nullptr;
+    double *spPhiPsi = nullptr, *spPhiPsib = nullptr, *spPhiHO = nullptr, *spPhiHOb = nullptr;
+    int *spBc = nullptr;
     double ddtAlphaMax = 0.0;
     // F is a pure function of (alpha, T, sigma): the solver evaluates it 2-4x per time step on unchanged
     // fields (UEqn.H:29, pEqn.H:35 per corrector, thermocapillaryInterFoam.C:150); fieldsVersion counts
@@ -1249,6 +1255,119 @@ void do_alpha_transfer(tcif_ctx *c) {
     c->ddtAlphaMax = std::max(v[0], v[1]);
 }
 
+void check_phase(tcif_ctx *c, int p);
+void up_cells(tcif_ctx *c, double *dst, const double *src);
+void up_bnd(tcif_ctx *c, double *dst, const double *src);
+
+// MultiComponentPhaseModel::solveYi (MultiComponentPhaseModel.C:182-388) for the species of phase `ph`.
+// Host buffers in/out: Yint[i] [nCells], Ybnd[i] [nBF]; the inert species receives max(1 - sum Yi, 0).
+// The species' working set (Yi, Yi.oldTime, patch values, BC kinds, Su/Sp, flux) is swapped into phase slot `ph`
+// so that the limiter / predictor / explicitSolve sweeps of the phase fractions run on it unchanged.
+void do_solve_yi(tcif_ctx *c, int ph, int nSpecies, int inertIndex, double *const *Yint, double *const *Ybnd,
+                 const int32_t *Ybc, const double *const *Su, const double *const *Sp, double cYi,
+                 int schemePhi, int schemePhir, int nYiSubCycles, double deltaT, double tol, int maxIter) {
+    check_phase(c, ph);
+    if (nSpecies < 1 || !Yint || (c->nBF && !Ybnd) || !Ybc) failf("tcif_solve_yi: bad arguments");
+    if (!(deltaT > 0)) failf("tcif_solve_yi: deltaT must be positive");
+    if (nYiSubCycles > 1) failf("tcif_solve_yi: nYiSubCycles > 1 is not supported by the device path");
+    for (int sc : {schemePhi, schemePhir}) {
+        if (sc < 0 || sc > 2) failf("unsupported convection scheme %d (upwind | linear | vanLeer)", sc);
+        if (sc == SCHEME_VANLEER && !c->Cx) failf("vanLeer needs cell centres: call tcif_set_cell_centres first");
+    }
+    require_comm(c);
+    ensure_deltaN(c);
+    const size_t cs = c->stride, bs = std::max(c->nBF, 1);
+    if (!c->GA) {
+        c->GA = c->dalloc<double>((size_t)c->P * 3 * cs); c->GAb = c->dalloc<double>((size_t)c->P * 3 * bs);
+        c->spY = c->dalloc<double>(cs); c->spY0 = c->dalloc<double>(cs); c->spYNew = c->dalloc<double>(cs);
+        c->spYb = c->dalloc<double>(bs); c->spSu = c->dalloc<double>(cs); c->spSp = c->dalloc<double>(cs);
+        c->spPhiPsi = c->dalloc<double>(c->nFd); c->spPhiPsib = c->dalloc<double>(bs);
+        c->spPhiHO = c->dalloc<double>(c->nFd); c->spPhiHOb = c->dalloc<double>(bs);
+        c->spBc = c->dalloc<int>(std::max(c->nPatches, 1));
+    }
+    // grad(alpha_p) of the phases (nHatf, vanLeer of alpha2), kept aside: G is re-used for grad(Yi)
+    do_grad(c);
+    CUDA_OK(cudaMemcpyAsync(c->GA, c->G, sizeof(double) * c->P * 3 * cs, cudaMemcpyDeviceToDevice, c->stream));
+    CUDA_OK(cudaMemcpyAsync(c->GAb, c->Gb, sizeof(double) * c->P * 3 * bs, cudaMemcpyDeviceToDevice, c->stream));
+    // max(phic) over all faces (:199-201)
+    CUDA_OK(cudaMemsetAsync(c->dmaxDev, 0, sizeof(double) * 8, c->stream));
+    {
+        long long n = (long long)c->nFd + c->nBF;
+        k_phic_max<<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->phi, c->phib, c->dmaxDev, 1);
+        c->launches++;
+    }
+    CUDA_OK(cudaMemcpyAsync(c->h_small, c->dmaxDev, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    double mx[1] = {c->h_small[0]};
+    { int ops[1] = {RED_MAX}; allreduce_host(c, mx, ops, 1); }
+
+    // the phase's own state, restored at the end
+    struct Saved { double *alpha, *alpha0, *alphaNew, *alphab, *Su, *Sp, *phiPsi, *phiPsib, *phiHO, *phiHOb; int *bc; bool haveSu, haveSp; } sv =
+        {c->alpha[ph], c->alpha0[ph], c->alphaNew[ph], c->alphab[ph], c->Su[ph], c->Sp[ph], c->phiPsi[ph], c->phiPsib[ph],
+         c->phiHO[ph], c->phiHOb[ph], c->bc[ph], c->haveSu[ph], c->haveSp[ph]};
+    const double *alphaPh = sv.alpha, *alphabPh = sv.alphab;
+    std::vector<double> Yt((size_t)c->nC, 0.0), Ytb((size_t)c->nBF, 0.0), tmp((size_t)std::max(c->nC, c->nBF));
+    double *yCur = c->spY, *yNew = c->spYNew;
+    auto restore = [&] {
+        c->alpha[ph] = sv.alpha; c->alpha0[ph] = sv.alpha0; c->alphaNew[ph] = sv.alphaNew; c->alphab[ph] = sv.alphab;
+        c->Su[ph] = sv.Su; c->Sp[ph] = sv.Sp; c->phiPsi[ph] = sv.phiPsi; c->phiPsib[ph] = sv.phiPsib; c->bc[ph] = sv.bc;
+        c->phiHO[ph] = sv.phiHO; c->phiHOb[ph] = sv.phiHOb;
+        c->haveSu[ph] = sv.haveSu; c->haveSp[ph] = sv.haveSp;
+        touch(c);
+    };
+    try {
+        for (int i = 0; i < nSpecies; ++i) {
+            if (i == inertIndex) continue;
+            if (!Yint[i] || (c->nBF && !Ybnd[i])) failf("tcif_solve_yi: species %d has no field", i);
+            up_cells(c, yCur, Yint[i]);
+            if (c->nBF) up_bnd(c, c->spYb, Ybnd[i]);
+            CUDA_OK(cudaMemcpyAsync(c->spBc, Ybc + (size_t)i * c->nPatches, sizeof(int) * c->nPatches, cudaMemcpyHostToDevice, c->stream));
+            const bool hsu = Su && Su[i], hsp = Sp && Sp[i];
+            if (hsu) up_cells(c, c->spSu, Su[i]);
+            if (hsp) up_cells(c, c->spSp, Sp[i]);
+            c->alpha[ph] = yCur; c->alpha0[ph] = c->spY0; c->alphaNew[ph] = yNew; c->alphab[ph] = c->spYb;
+            c->Su[ph] = c->spSu; c->Sp[ph] = c->spSp; c->haveSu[ph] = hsu; c->haveSp[ph] = hsp;
+            c->phiPsi[ph] = c->spPhiPsi; c->phiPsib[ph] = c->spPhiPsib; c->bc[ph] = c->spBc;
+            c->phiHO[ph] = c->spPhiHO; c->phiHOb[ph] = c->spPhiHOb;
+            correct_alpha_bcs(c, &ph, 1);
+            CUDA_OK(cudaMemcpyAsync(c->spY0, yCur, sizeof(double) * c->nC, cudaMemcpyDeviceToDevice, c->stream));   // Yi.oldTime()
+            do_grad(c);                                   // slot ph of G/Gb now holds grad(Yi)
+            YiFluxArgs a{};
+            a.P = c->P; a.ph = ph; a.schemePhi = schemePhi; a.schemePhir = schemePhir;
+            for (int p = 0; p < c->P; ++p) { a.alpha[p] = p == ph ? alphaPh : c->alpha[p]; a.alphab[p] = p == ph ? alphabPh : c->alphab[p]; }
+            a.GA = c->GA; a.GAb = c->GAb; a.Y = yCur; a.Yb = c->spYb;
+            a.GY = c->G + (size_t)ph * 3 * cs; a.GYb = c->Gb + (size_t)ph * 3 * c->nBF;
+            a.Cx = c->Cx; a.Cy = c->Cy; a.Cz = c->Cz; a.dbx = c->dbx; a.dby = c->dby; a.dbz = c->dbz;
+            a.phi = c->phi; a.phib = c->phib; a.deltaN = c->deltaN; a.cYi = cYi; a.maxPhic = mx[0];
+            a.out = c->phiHO[ph]; a.outb = c->phiHOb[ph];
+            timed(c, T_FLUX_ASSEMBLY, 0, [&] {
+                DISPATCH_P(k_flux_yi<PP><<<cdiv(c->nC, 128), 128, 0, c->stream>>>(c->dm, a));
+                c->launches++;
+                if (c->nBF) {
+                    DISPATCH_P(k_flux_yi_bnd<PP><<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a));
+                    c->launches++;
+                }
+            });
+            do_limit(c, &ph, 1, 1.0 / deltaT, 0, false, true);                        // :299-311
+            do_predictor(c, &ph, 1, deltaT, tol, maxIter, false);                      // :323-338
+            do_explicit(c, &ph, 1, deltaT, true);                                      // :343 (+= YiEqn.flux()) and :361-378
+            yCur = c->alpha[ph]; yNew = c->alphaNew[ph];                               // explicitSolve swapped the buffers
+            CUDA_OK(cudaMemcpyAsync(Yint[i], yCur, sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
+            if (c->nBF) CUDA_OK(cudaMemcpyAsync(Ybnd[i], c->spYb, sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
+            CUDA_OK(cudaStreamSynchronize(c->stream));
+            for (int k = 0; k < c->nC; ++k) Yt[k] += Yint[i][k];                       // Yt += Yi (:380)
+            for (int b = 0; b < c->nBF; ++b) Ytb[b] += Ybnd[i][b];
+        }
+    } catch (...) { restore(); throw; }
+    restore();
+    c->spY = yCur; c->spYNew = yNew;
+    if (inertIndex >= 0 && inertIndex < nSpecies) {                                    // :383-384
+        if (!Yint[inertIndex] || (c->nBF && !Ybnd[inertIndex])) failf("tcif_solve_yi: inert species has no field");
+        for (int k = 0; k < c->nC; ++k) Yint[inertIndex][k] = std::max(1.0 - Yt[k], 0.0);
+        for (int b = 0; b < c->nBF; ++b) Ybnd[inertIndex][b] = std::max(1.0 - Ytb[b], 0.0);
+    }
+}
+
 // multiphaseSystem::solve() (multiphaseSystem.C:128-168) = nAlphaSubCycles x solveAlphas() (:170-429)
 void do_solve_alphas(tcif_ctx *c, const tcif_alpha_controls *ctl, double deltaT) {
     if (!ctl) failf("tcif_solve_alphas: null controls");
@@ -1736,6 +1855,15 @@ int tcif_interface_porosity(tcif_ctx *c, int nModels, const int32_t *solidPhase,
     });
     CUDA_OK(cudaMemcpyAsync(Udiag, c->staging, sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_solve_yi(tcif_ctx *c, int phase, int nSpecies, int inertIndex, double *const *Yinternal, double *const *Yboundary,
+                  const int32_t *Ybc, const double *const *Su, const double *const *Sp, double cYi,
+                  int schemePhi, int schemePhir, int nYiSubCycles, double deltaT, double tol, int maxIter) {
+    API_BEGIN(c)
+    do_solve_yi(c, phase, nSpecies, inertIndex, Yinternal, Yboundary, Ybc, Su, Sp, cYi, schemePhi, schemePhir, nYiSubCycles,
+                deltaT, tol, maxIter);
     API_END(c)
 }
 

@@ -339,7 +339,7 @@ k_renormalise(int n, const __grid_constant__ RenormArgs r) {
 
 // max over all face slots / boundary faces of phic0 = |phi|/|Sf| (multiphaseSystem.C:181, 237)
 __global__ void __launch_bounds__(TCIF_TPB)
-k_phic_max(const __grid_constant__ DMesh m, const double *phi, const double *phib, double *out) {
+k_phic_max(const __grid_constant__ DMesh m, const double *phi, const double *phib, double *out, int allPatches = 0) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     double v = 0.0;
     if (i < m.nFd) {
@@ -348,7 +348,7 @@ k_phic_max(const __grid_constant__ DMesh m, const double *phi, const double *phi
         if (mg > 0.0) v = fabs(phi[i] / mg);
     } else if (i - m.nFd < m.nBF) {
         int bf = i - m.nFd;
-        if (m.bfType[bf] == PATCH_PROCESSOR) v = fabs(phib[bf] / m.magSfb[bf]);
+        if (allPatches || m.bfType[bf] == PATCH_PROCESSOR) v = fabs(phib[bf] / m.magSfb[bf]);
     }
     for (int o = 16; o > 0; o >>= 1) v = dmax(v, __shfl_xor_sync(0xffffffffu, v, o));
     if ((threadIdx.x & 31) == 0 && v > 0.0) atomic_max_nonneg(out, v);
