@@ -80,3 +80,51 @@ def test_solve_yi_errors():
         ctx.solve_yi(0, Y, Yb, np.zeros((2, m.nPatches), np.int32), 1, f["deltaT"], schemePhi="upwind", schemePhir="upwind",
                      nYiSubCycles=2)
     ctx.close()
+
+
+@pytest.mark.parametrize("procs", [(2, 1, 1), (2, 2, 2)])
+def test_decomposed_solve_yi_matches_serial(procs):
+    """Processor patches: halo of Yi, grad(Yi), grad(alpha) and the coupled form of the face interpolation."""
+    spec = cases.case(5, 12)
+    g = global_mesh(spec)
+    fg = cases.synthetic_fields(spec, g)
+    nS = 3
+    Y, Yb = _species(g, nS)
+    ybc = np.zeros((nS, g.nPatches), np.int32)
+    ri, rb = orc.solve_yi(g, orc.mules_cfg(3), fg["alpha_i"], fg["alpha_b"], fg["alphaBc"], 0, Y, Yb, ybc, 2,
+                          fg["phi_i"], fg["phi_b"], fg["deltaT"])
+    nd = procs[0] * procs[1] * procs[2]
+    meshes = [hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, r) for r in range(nd)]
+    fs = [cases.synthetic_fields(spec, m) for m in meshes]
+    grp = abi.Group(nd)
+    ctxs = [abi.Context(m, spec.nPhases) for m in meshes]
+    outs, errs = [None] * nd, []
+
+    def work(r):
+        try:
+            m, f, ctx = meshes[r], fs[r], ctxs[r]
+            ctx.comm_init_local(r, grp)
+            cases.load_case(ctx, spec, f)
+            ctx.set_cell_centres(f["C"], f["deltab"])
+            gid = np.asarray(m.cellGlobal)
+            fc = np.asarray(m.faceCells, dtype=np.int64)
+            yl = [y[gid] for y in Y]
+            ybl = [y[fc].copy() for y in yl]                      # walls zeroGradient; processor values come from the halo
+            bc = np.zeros((nS, m.nPatches), np.int32)
+            yi, yb = ctx.solve_yi(0, yl, ybl, bc, 2, f["deltaT"])
+            outs[r] = (gid, yi)
+        except Exception as e:          # noqa: BLE001
+            errs.append((r, e))
+    ts = [threading.Thread(target=work, args=(r,), daemon=True) for r in range(nd)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(120)
+    assert not errs, errs
+    for r in range(nd):
+        gid, yi = outs[r]
+        for i in range(nS):
+            assert_field_close(yi[i], ri[i][gid], f"Y{i} rank {r}", rtol=1e-11)
+    for c in ctxs:
+        c.close()
+    grp.close()
