@@ -284,13 +284,12 @@ void timers_collect(tcif_ctx *c) {
 // strides (1, a, b) = (cell, row, plane).  Ascending order has a reuse distance of one plane (b cells) for the
 // +-z neighbours, which at 400^3 is more than L2 holds across all streams of a sweep; walking the mesh in
 // strips of H rows (all planes of strip 0, then strip 1, ...) shortens it to a*H cells at the price of one
-// extra row fetch per strip edge.  Returns empty (= ascending) when no such structure is found, when the
-// mesh is small enough for L2 anyway, or with TCIF_TILE_ORDER=0.  TCIF_STRIP_CELLS sets a*H (default 16384).
+// extra row fetch per strip edge.  Returns empty (= ascending) when no such structure is found, when one
+// plane is small enough for L2 anyway (< 64 K cells), or with TCIF_TILE_ORDER=0.  TCIF_STRIP_CELLS sets a*H (default 16384).
 std::vector<int> build_tile_order(int nC, int stride, int Ko, const std::vector<int> &nbrOwn) {
     const char *e = getenv("TCIF_TILE_ORDER");
     const int mode = e ? atoi(e) : 1;                  // 0 off, 1 auto, 2 force (also on small meshes)
     if (mode == 0 || Ko < 3) return {};
-    if (mode == 1 && nC < (1 << 21)) return {};        // <= 2 M cells: a plane of all streams fits in L2
     std::vector<long long> offs;
     for (int k = 0; k < Ko; ++k) {
         std::map<long long, long long> hist;
@@ -307,6 +306,7 @@ std::vector<int> build_tile_order(int nC, int stride, int Ko, const std::vector<
     std::sort(offs.begin(), offs.end());
     const long long a = offs[offs.size() - 2], b = offs[offs.size() - 1];
     if (a < 2 || b <= a || b % a != 0) return {};
+    if (mode == 1 && b * 512 < (32 << 20)) return {};  // a plane of all streams of a sweep (~0.5 KB/cell) fits in L2 anyway
     const long long R = b / a;                         // rows per plane
     const char *sc = getenv("TCIF_STRIP_CELLS");
     long long H = std::max<long long>(2, (sc ? atoll(sc) : 16384) / a);
