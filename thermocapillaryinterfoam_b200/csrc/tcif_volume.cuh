@@ -11,6 +11,7 @@
 // use evict-first loads/stores (__ldcs/__stcs) so that L2 keeps the arrays neighbours gather from.
 #pragma once
 #include "tcif_device.cuh"
+#include "tcif_alpha.cuh"      // PredBatch (kvp_pred_jacobi)
 
 namespace tcif {
 
@@ -670,9 +671,6 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
     }
 }
 
-}  // namespace tcif
-#include "tcif_alpha.cuh"
-namespace tcif {
 
 // ---- Jacobi sweep of the implicit upwind predictor, phase-looped (see k_pred_jacobi, tcif_alpha.cuh) -----------
 // The matrix coefficients max(phi,0) / -min(phi,0) and the slot indices are shared by the phases of the batch:
