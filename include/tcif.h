@@ -266,6 +266,42 @@ TCIF_API int tcif_solve_yi(tcif_ctx *ctx, int phase, int nSpecies, int inertInde
                            const double *const *Su, const double *const *Sp, double cYi,
                            int schemePhi, int schemePhir, int nYiSubCycles, double deltaT, double tol, int maxIter);
 
+/* ---- laserDTRM: the discrete-ray laser heat source -----------------------------------------
+ * Replaces radiation::laserDTRM::calculate() (laserDTRM/laserDTRM.C:542-735) with DTRMParticle::move
+ * (laserDTRM/DTRMParticle/DTRMParticle.C:94-266): reflecting-cell marking from grad(alpha) (:596-652), the cell
+ * walk of the cloud with absorption/emission per cell crossed and Fresnel reflection at the interface, Q /= V.
+ * The seeds (initialise(), :169-331: polar disk, Function1s, findCell) stay with the solver.  Single domain:
+ * a mesh with processor patches is refused. */
+/* polyMesh data of the cell walk and of interpolationCellPoint(nHat): mesh.faceCentres() (internal [nIF*3],
+ * boundary [nBF*3]), mesh.points(), mesh.faces() as CSR over internal then boundary faces, mesh.tetBasePtIs(),
+ * mesh.bounds().mag().  Needs tcif_set_cell_centres first. */
+TCIF_API int tcif_laser_set_polymesh(tcif_ctx *ctx, const double *Cf, const double *Cfb, int32_t nPoints,
+                                     const double *points, const int32_t *fpStart, const int32_t *fpPts,
+                                     const int32_t *tetBasePt, double boundsMag);
+enum { TCIF_REFL_NONE = 0, TCIF_REFL_FRESNEL = 1, TCIF_REFL_FRESNEL_LASER = 2 };
+/* one entry of the `reflectionModel` table (laserDTRM.C:137-166) in the table's iteration order:
+ * noReflection (noReflection.C:58-73), Fresnel (Fresnel.C:57-58: nk1, nk2), FresnelLaser (FresnelLaser.C:57: epsilon) */
+typedef struct tcif_reflection_model {
+    int32_t kind, from, to;
+    double nk1[2], nk2[2], epsilon;
+} tcif_reflection_model;
+TCIF_API int tcif_laser_set_reflection(tcif_ctx *ctx, int32_t nModels, const tcif_reflection_model *models, double alphaCut);
+/* localDensityAbsorptionEmission (localDensityAbsorptionEmission.C:86-186): a/e/E = sum_i max(alpha_i,0)*coeff_i */
+TCIF_API int tcif_laser_set_local_density_absorption(tcif_ctx *ctx, int32_t nNames, const int32_t *phases,
+                                                     const double *aCoeff, const double *eCoeff, const double *ECoeff);
+/* a(), e(), E() of any other absorptionEmissionModel as host fields [nCells] (laserDTRM.C:583-585) */
+TCIF_API int tcif_laser_set_absorption_fields(tcif_ctx *ctx, const double *a, const double *e, const double *E);
+/* calculate(): seeds p0/p1 [n*3], Ip, dA [n], cell [n] (-1: findCell missed, not seeded); sigmaSB =
+ * physicoChemical::sigma; maxParticles = capacity of the cloud incl. reflected particles (0: 64 per seed).
+ * Uses the resident alpha and T.  Q [nCells] (= Ru(), W/m^3) may be NULL (read it with tcif_laser_get). */
+TCIF_API int tcif_laser_calculate(tcif_ctx *ctx, int32_t nParticles, const double *p0, const double *p1, const double *I,
+                                  const double *dA, const int32_t *cell, double sigmaSB, int32_t maxParticles,
+                                  double *Q, int32_t *nParticlesFinal);
+/* Q, reflectingCellsVol (:556), nHat (:576) [nCells*3] and its point interpolation [nPoints*3]; any may be NULL */
+TCIF_API int tcif_laser_get(tcif_ctx *ctx, double *Q, int32_t *reflectingCells, double *nHat, double *nHatPoints);
+/* launches of the walk kernel in the last calculate() = depth of the reflection cascade + 1 */
+TCIF_API int tcif_laser_generations(const tcif_ctx *ctx);
+
 /* Logging scalars of multiphaseSystem.C:408-425: sum(V*alpha), min, max (global over ranks). */
 TCIF_API int tcif_alpha_stats(tcif_ctx *ctx, int phase, double out3[3]);
 

@@ -61,7 +61,7 @@ class OrcComm(C.Structure):
 
 def build(force: bool = False) -> str:
     so = os.path.join(_HERE, "libtcif_oracle.so")
-    src = [os.path.join(_HERE, f) for f in ("tcif_oracle.c", "tcif_oracle.h", "tcif_oracle_alpha.inc", "tcif_oracle_mass.inc", "tcif_oracle_species.inc")]
+    src = [os.path.join(_HERE, f) for f in ("tcif_oracle.c", "tcif_oracle.h", "tcif_oracle_alpha.inc", "tcif_oracle_mass.inc", "tcif_oracle_species.inc", "tcif_oracle_laser.inc")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src if os.path.exists(s)):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
     return so
@@ -75,6 +75,8 @@ def lib():
         _LIB.orc_sigma_eval.restype = C.c_double
         _LIB.orc_stage_threads.restype = C.c_double
         _LIB.orc_upwind_predictor.restype = C.c_int
+        _LIB.orc_laser_calculate.restype = C.c_int
+        _LIB.orc_find_cell.restype = C.c_int
     return _LIB
 
 
@@ -522,3 +524,98 @@ def solve_yi(m, cfg, alphas_i, alphas_b, alphaBc, ph, Y_i, Y_b, YBc, inertIndex,
                        SCHEMES[schemePhi], SCHEMES[schemePhir], _pp(su) if su else None, _pp(sp) if sp else None,
                        C.c_double(deltaT), C.c_double(tol), int(maxIter))
     return yi, yb
+
+
+# ---- laserDTRM -----------------------------------------------------------------------------
+REFL_KINDS = {"noReflection": 0, "Fresnel": 1, "FresnelLaser": 2}
+PD_MODES = {"Gaussian": 0, "uniform": 2, "GaussianPeak": 3}
+SIGMA_SB = 5.670374419e-8          # physicoChemical::sigma
+
+
+class OrcLaserGeom(C.Structure):
+    _fields_ = [("Cf", c_dp), ("Cfb", c_dp), ("nPoints", C.c_int32), ("points", c_dp), ("fpStart", c_ip),
+                ("fpPts", c_ip), ("tetBasePt", c_ip), ("boundsMag", C.c_double)]
+
+
+class OrcReflection(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("from_", C.c_int32), ("to", C.c_int32), ("nk1", C.c_double * 2),
+                ("nk2", C.c_double * 2), ("epsilon", C.c_double)]
+
+
+class OrcLaserCfg(C.Structure):
+    _fields_ = [("nModels", C.c_int32), ("models", C.POINTER(OrcReflection)), ("alphaCut", C.c_double),
+                ("sigmaSB", C.c_double), ("maxParticles", C.c_int32)]
+
+
+class LaserGeomHandle:
+    """geom: dict(points [nP,3], fpStart [nIF+nBF+1], fpPts, tetBasePt [nIF+nBF], boundsMag) + the mesh's Cf/Cfb."""
+
+    def __init__(self, m, geom):
+        self.keep = dict(Cf=f64(m.Cf), Cfb=f64(m.Cfb), points=f64(geom["points"]), fpStart=i32(geom["fpStart"]),
+                         fpPts=i32(geom["fpPts"]), tetBasePt=i32(geom["tetBasePt"]))
+        k = self.keep
+        self.s = OrcLaserGeom(_d(k["Cf"]), _d(k["Cfb"]), len(k["points"]), _d(k["points"]), _i(k["fpStart"]),
+                              _i(k["fpPts"]), _i(k["tetBasePt"]), float(geom["boundsMag"]))
+
+    @property
+    def ref(self):
+        return C.byref(self.s)
+
+
+def reflection_array(models):
+    """models: list of dict(kind, from, to, nk1, nk2, epsilon) in the reflectionModel table's iteration order."""
+    arr = (OrcReflection * max(len(models), 1))()
+    for i, md in enumerate(models):
+        arr[i].kind = REFL_KINDS[md["kind"]]; arr[i].from_ = md["from"]; arr[i].to = md["to"]
+        arr[i].nk1[:] = md.get("nk1", (1.0, 0.0)); arr[i].nk2[:] = md.get("nk2", (1.0, 0.0))
+        arr[i].epsilon = md.get("epsilon", 0.0)
+    return arr
+
+
+def laser_seed(lPosition, lDir, rArea, nr, nTheta, focalLaserRadius, maxTrackLength, mode="Gaussian", power=1.0,
+               sigma=1.0, I0=0.0):
+    n = nr * nTheta
+    p0, p1, Ip, dA = np.zeros((n, 3)), np.zeros((n, 3)), np.zeros(n), np.zeros(n)
+    v3 = lambda v: (C.c_double * 3)(*[float(x) for x in v])
+    lib().orc_laser_seed(v3(lPosition), v3(lDir), v3(rArea), int(nr), int(nTheta), C.c_double(focalLaserRadius),
+                         C.c_double(maxTrackLength), PD_MODES[mode], C.c_double(power), C.c_double(sigma), C.c_double(I0),
+                         _d(p0), _d(p1), _d(Ip), _d(dA))
+    return p0, p1, Ip, dA
+
+
+def find_cells(m, geom, pts):
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    g = geom if isinstance(geom, LaserGeomHandle) else LaserGeomHandle(h.m, geom)
+    pts = f64(pts).reshape(-1, 3)
+    return np.array([lib().orc_find_cell(h.ref, g.ref, (C.c_double * 3)(*p)) for p in pts], np.int32)
+
+
+def local_density(alphas_i, coeff):
+    ai = [f64(a) for a in alphas_i]
+    out = np.zeros(len(ai[0]))
+    lib().orc_local_density(len(out), len(ai), _pp(ai), _d(f64(coeff)), _d(out))
+    return out
+
+
+def laser_calculate(m, geom, models, alphas_i, alphas_b, alphaBc, a, e, E, T, p0, p1, I, dA, cell, alphaCut=0.5,
+                    sigmaSB=SIGMA_SB, maxParticles=0, comm=None):
+    """laserDTRM::calculate().  Returns dict(Q, reflectingCells, nHat, nHatPoints, nParticles)."""
+    h = m if isinstance(m, MeshHandle) else MeshHandle(m)
+    g = geom if isinstance(geom, LaserGeomHandle) else LaserGeomHandle(h.m, geom)
+    P = len(alphas_i)
+    ai = [f64(x) for x in alphas_i]; ab = [f64(x) for x in alphas_b]
+    bc = i32(alphaBc).reshape(P, -1)
+    arr = reflection_array(models)
+    n = len(I)
+    cfg = OrcLaserCfg(len(models), arr, float(alphaCut), float(sigmaSB), int(maxParticles or 64 * max(n, 1)))
+    nC = h.s.nCells
+    Q = np.zeros(nC); refl = np.zeros(nC, np.int32); nHat = np.zeros((nC, 3)); nPts = np.zeros((g.s.nPoints, 3))
+    nFinal = C.c_int32(0)
+    p0, p1, I, dA, cell = f64(p0), f64(p1), f64(I), f64(dA), i32(cell)
+    a, e, E, T = f64(a), f64(e), f64(E), f64(T)
+    rc = lib().orc_laser_calculate(h.ref, C.byref(comm) if comm else None, g.ref, C.byref(cfg), P, _pp(ai), _pp(ab), _i(bc),
+                                   _d(a), _d(e), _d(E), _d(T), n, _d(p0), _d(p1), _d(I), _d(dA), _i(cell), _d(Q), _i(refl),
+                                   _d(nHat), _d(nPts), C.byref(nFinal))
+    if rc:
+        raise RuntimeError(f"orc_laser_calculate failed: rc={rc}")
+    return dict(Q=Q, reflectingCells=refl, nHat=nHat, nHatPoints=nPts, nParticles=nFinal.value)

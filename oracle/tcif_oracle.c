@@ -706,3 +706,4 @@ double orc_stage_threads(int nDom, const orc_mesh *meshes, const orc_mules_cfg *
 #include "tcif_oracle_mass.inc"
 #include "tcif_oracle_alpha.inc"
 #include "tcif_oracle_species.inc"
+#include "tcif_oracle_laser.inc"

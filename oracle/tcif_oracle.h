@@ -288,6 +288,52 @@ void orc_solve_yi(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg
                   const double *phii, const double *phib, double cYi, int schemePhi, int schemePhir,
                   const double *const *Su, const double *const *Sp, double deltaT, double tol, int maxIter);
 
+/* ---- laserDTRM: discrete-ray laser heat source ---------------------------------------- */
+/* polyMesh data the cell walk and interpolationCellPoint need on top of orc_mesh */
+typedef struct orc_laser_geom {
+    const double *Cf;          /* [nIF*3] mesh.faceCentres(), internal faces  */
+    const double *Cfb;         /* [nBF*3] boundary faces                      */
+    int32_t nPoints;
+    const double *points;      /* [nPoints*3] mesh.points()                   */
+    const int32_t *fpStart;    /* [nIF+nBF+1] CSR of mesh.faces(): internal faces, then boundary faces */
+    const int32_t *fpPts;
+    const int32_t *tetBasePt;  /* [nIF+nBF] mesh.tetBasePtIs()                */
+    double boundsMag;          /* mesh.bounds().mag()                         */
+} orc_laser_geom;
+enum { ORC_REFL_NONE = 0, ORC_REFL_FRESNEL = 1, ORC_REFL_FRESNEL_LASER = 2 };
+/* one entry of the reflectionModel table, in the table's iteration order (laserDTRM.C:137-166) */
+typedef struct orc_reflection {
+    int32_t kind, from, to;
+    double nk1[2], nk2[2];     /* Fresnel (Fresnel.C:57-58)   */
+    double epsilon;            /* FresnelLaser (FresnelLaser.C:57) */
+} orc_reflection;
+typedef struct orc_laser_cfg {
+    int32_t nModels; const orc_reflection *models;
+    double alphaCut;           /* laserDTRM.C:379 (default 0.5)  */
+    double sigmaSB;            /* physicoChemical::sigma          */
+    int32_t maxParticles;      /* capacity of the cloud incl. reflected particles */
+} orc_laser_cfg;
+enum { ORC_PD_GAUSSIAN = 0, ORC_PD_UNIFORM = 2, ORC_PD_GAUSSIAN_PEAK = 3 };
+/* laserDTRM::initialise() (laserDTRM.C:169-331) without findCell: the polar disk of seeds.  rArea is the unit
+ * vector normal to lDir the reference derives from Random(1234) (:186-197); out arrays [nr*nTheta]. */
+void orc_laser_seed(const double lPosition[3], const double lDir[3], const double rArea[3], int nr, int nTheta,
+                    double focalLaserRadius, double maxTrackLength, int mode, double power, double sigma, double I0,
+                    double *p0, double *p1, double *Ip, double *dA);
+/* mesh.findCell(p) for convex cells with planar faces (brute force); -1 if outside */
+int orc_find_cell(const orc_mesh *m, const orc_laser_geom *g, const double p[3]);
+/* localDensityAbsorptionEmission::aCont/eCont/ECont (localDensityAbsorptionEmission.C:86-186):
+ * out = sum_i max(alpha_i, 0)*coeff_i over the listed phases */
+void orc_local_density(int nC, int nNames, const double *const *alphai, const double *coeff, double *out);
+/* laserDTRM::calculate() (laserDTRM.C:542-735) with DTRMParticle::move (DTRMParticle.C:94-266): marks the
+ * reflecting cells, walks the particles cell to cell, deposits Q and divides by V.  Single domain (a particle
+ * reaching a processor patch returns 2; cloud overflow returns 3).  Optional outputs may be NULL. */
+int orc_laser_calculate(const orc_mesh *m, const orc_comm *c, const orc_laser_geom *g, const orc_laser_cfg *cfg,
+                        int nPhases, const double *const *alphai, const double *const *alphab, const int32_t *alphaBc,
+                        const double *a, const double *e, const double *E, const double *T,
+                        int nParticles, const double *p0, const double *p1, const double *I, const double *dA,
+                        const int32_t *cell, double *Q, int32_t *reflectingCells, double *nHat, double *nHatPoints,
+                        int32_t *nParticlesFinal);
+
 #ifdef __cplusplus
 }
 #endif

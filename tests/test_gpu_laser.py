@@ -1,0 +1,149 @@
+"""GPU parity of laserDTRM through the C ABI against the CPU oracle: reflecting cells and nHat
+(bit-identical: same operations, fmad off), the point interpolation, the cell walk with absorption and Fresnel
+reflection.  Q is summed with fp64 atomics on the device, in seed order on the CPU: tolerance 1e-11 of max|Q|;
+sin/cos/tan/cbrt of the Fresnel model and of the insertion offset differ by ulps between libm and CUDA."""
+import numpy as np
+import pytest
+
+from oracle import oracle as orc, mesh_oracle as mo
+from thermocapillaryinterfoam_b200 import abi, cases, mesh as hm
+
+pytestmark = pytest.mark.gpu
+
+MODELS = [dict(kind="FresnelLaser", **{"from": 2, "to": 0}, epsilon=0.25),
+          dict(kind="Fresnel", **{"from": 2, "to": 1}, nk1=(1.0, 0.0), nk2=(3.6, 5.0))]
+
+
+def _setup(n=16, grading=(1.4, None, 0.8), config=5):
+    spec = cases.case(config, n)
+    g = grading or (None, None, None)
+    m = mo.box_mesh(*spec.n, spec.lengths, spec.patch_types, grading)
+    xs, ys, zs = (hm.vertices(spec.n[d], spec.lengths[d], g[d]) for d in range(3))
+    geom = cases.box_polymesh(m, xs, ys, zs)
+    f = cases.synthetic_fields(spec, m)
+    ctx = abi.Context(m, spec.nPhases)
+    cases.load_case(ctx, spec, f)
+    fc = np.asarray(m.faceCells, dtype=np.int64)
+    ctx.set_cell_centres(m.C, np.asarray(m.Cfb) - np.asarray(m.C)[fc])
+    ctx.laser_set_polymesh(m.Cf, m.Cfb, geom)
+    return spec, m, (xs, ys, zs), geom, f, ctx
+
+
+def _seeds(spec, v, geom, pos, d, nr=8, nTheta=16, R=0.18):
+    d = np.asarray(d, float); d /= np.linalg.norm(d)
+    r = np.cross(d, [0.0, 0.0, 1.0]); r /= np.linalg.norm(r)
+    p0, p1, Ip, dA = cases.laser_seeds(pos, d, r, nr, nTheta, R, geom["boundsMag"], mode="Gaussian", power=200.0, sigma=0.08)
+    return p0, p1, Ip, dA, cases.find_cells_box(spec.n, *v, p0)
+
+
+def _close(a, b, what, rtol=1e-11):
+    scale = max(np.abs(a).max(), np.abs(b).max(), 1e-300)
+    err = np.abs(a - b).max()
+    assert err <= rtol * scale, f"{what}: max err {err:.3e} (scale {scale:.3e})"
+
+
+@pytest.mark.parametrize("aC", [(60.0, 25.0, 0.3), (4.0, 2.0, 0.05)])
+def test_calculate_matches_oracle(aC):
+    spec, m, v, geom, f, ctx = _setup()
+    eC, EC = (0.2, 0.1, 0.0), (0.0, 0.0, 0.0)
+    ctx.laser_set_reflection(MODELS, alphaCut=0.5)
+    ctx.laser_set_local_density_absorption([0, 1, 2], aC, eC, EC)
+    p0, p1, Ip, dA, cell = _seeds(spec, v, geom, (0.5, 0.93, 0.5), (0.25, -1.0, 0.1))
+    assert (cell >= 0).all()
+    Q, nPart = ctx.laser_calculate(p0, p1, Ip, dA, cell)
+    got = ctx.laser_get()
+    al = f["alpha_i"]
+    ref = orc.laser_calculate(m, geom, MODELS, al, f["alpha_b"], f["alphaBc"], orc.local_density(al, aC), orc.local_density(al, eC),
+                              orc.local_density(al, EC), f["T_i"], p0, p1, Ip, dA, cell)
+    assert (ref["reflectingCells"] >= 0).sum() > 20 and len(np.unique(ref["reflectingCells"])) == 3
+    assert np.array_equal(got["reflectingCells"], ref["reflectingCells"])
+    _close(got["nHat"], ref["nHat"], "nHat", 1e-12)
+    _close(got["nHatPoints"], ref["nHatPoints"], "nHatPoints", 1e-12)
+    assert ref["nParticles"] > len(Ip), "the case must exercise reflection"
+    assert nPart == ref["nParticles"]
+    assert ctx.laser_generations >= 2
+    assert np.array_equal(Q, got["Q"])
+    _close(Q, ref["Q"], "Q")
+    assert np.array_equal(Q != 0, ref["Q"] != 0)
+    ctx.close()
+
+
+def test_no_reflection_and_host_absorption_fields():
+    spec, m, v, geom, f, ctx = _setup(n=12, grading=None)
+    rng = np.random.default_rng(4)
+    a, e, E = rng.uniform(0.5, 8.0, m.nCells), rng.uniform(0, 0.5, m.nCells), rng.uniform(0, 3.0, m.nCells)
+    ctx.laser_set_reflection([])
+    ctx.laser_set_absorption_fields(a, e, E)
+    p0, p1, Ip, dA, cell = _seeds(spec, v, geom, (0.4, 0.5, 1.2), (0.3, 0.2, -1.0), nr=6, nTheta=12, R=0.3)
+    assert (cell < 0).all()            # seeded outside the box: findCell misses, nothing is tracked
+    Q, nPart = ctx.laser_calculate(p0, p1, Ip, dA, cell)
+    assert nPart == 0 and not Q.any()
+    p0, p1, Ip, dA, cell = _seeds(spec, v, geom, (0.4, 0.5, 0.97), (0.3, 0.2, -1.0), nr=6, nTheta=12, R=0.3)
+    assert (cell >= 0).any()
+    Q, nPart = ctx.laser_calculate(p0, p1, Ip, dA, cell)
+    al = f["alpha_i"]
+    ref = orc.laser_calculate(m, geom, [], al, f["alpha_b"], f["alphaBc"], a, e, E, f["T_i"], p0, p1, Ip, dA, cell)
+    assert nPart == ref["nParticles"] == (cell >= 0).sum()
+    _close(Q, ref["Q"], "Q")
+    assert (ctx.laser_get()["reflectingCells"] == -1).all()
+    ctx.close()
+
+
+def test_noReflection_model_marks_but_does_not_spawn():
+    spec, m, v, geom, f, ctx = _setup(n=12, grading=None)
+    models = [dict(kind="noReflection", **{"from": 2, "to": 0})]
+    ctx.laser_set_reflection(models, alphaCut=0.4)
+    ctx.laser_set_local_density_absorption([0, 2], (30.0, 0.1), (0.0, 0.0), (0.0, 0.0))
+    p0, p1, Ip, dA, cell = _seeds(spec, v, geom, (0.35, 0.93, 0.5), (0.0, -1.0, 0.0), nr=5, nTheta=8, R=0.1)
+    Q, nPart = ctx.laser_calculate(p0, p1, Ip, dA, cell)
+    al = f["alpha_i"]
+    a = orc.local_density([al[0], al[2]], (30.0, 0.1)); z = np.zeros(m.nCells)
+    ref = orc.laser_calculate(m, geom, models, al, f["alpha_b"], f["alphaBc"], a, z, z, f["T_i"], p0, p1, Ip, dA, cell, alphaCut=0.4)
+    assert nPart == ref["nParticles"] == len(Ip)
+    assert (ref["reflectingCells"] == 0).any()
+    assert np.array_equal(ctx.laser_get()["reflectingCells"], ref["reflectingCells"])
+    _close(Q, ref["Q"], "Q")
+    ctx.close()
+
+
+def test_energy_is_linear_in_the_seed_intensity_on_the_device():
+    spec, m, v, geom, f, ctx = _setup(n=12, grading=None)
+    ctx.laser_set_reflection(MODELS)
+    ctx.laser_set_local_density_absorption([0, 1, 2], (20.0, 10.0, 0.2), (0, 0, 0), (0, 0, 0))
+    p0, p1, Ip, dA, cell = _seeds(spec, v, geom, (0.5, 0.93, 0.5), (0.1, -1.0, 0.0))
+    Q1, n1 = ctx.laser_calculate(p0, p1, Ip, dA, cell)
+    Q2, n2 = ctx.laser_calculate(p0, p1, 4.0 * Ip, dA, cell)
+    assert n1 == n2
+    _close(Q2, 4.0 * Q1, "linearity")
+    assert (Q1 >= 0).all() and (Q1 * m.V).sum() <= (Ip * dA).sum() * (1 + 1e-12)
+    ctx.close()
+
+
+def test_errors():
+    spec = cases.case(5, 8)
+    m = mo.box_mesh(*spec.n, spec.lengths, spec.patch_types)
+    xs = ys = zs = hm.vertices(8, 1.0)
+    geom = cases.box_polymesh(m, xs, ys, zs)
+    f = cases.synthetic_fields(spec, m)
+    ctx = abi.Context(m, spec.nPhases)
+    cases.load_case(ctx, spec, f)
+    one = (np.array([[0.5, 0.9, 0.5]]), np.array([[0.5, -1.0, 0.5]]), [1.0], [1.0], [0])
+    with pytest.raises(RuntimeError):
+        ctx.laser_calculate(*one)                           # no polymesh
+    with pytest.raises(RuntimeError):
+        ctx.laser_set_polymesh(m.Cf, m.Cfb, geom)           # no cell centres
+    fc = np.asarray(m.faceCells, dtype=np.int64)
+    ctx.set_cell_centres(m.C, np.asarray(m.Cfb) - np.asarray(m.C)[fc])
+    ctx.laser_set_polymesh(m.Cf, m.Cfb, geom)
+    with pytest.raises(RuntimeError):
+        ctx.laser_calculate(*one)                           # no absorption model
+    with pytest.raises(RuntimeError):
+        ctx.laser_set_reflection([dict(kind="Fresnel", **{"from": 1, "to": 1})])
+    ctx.laser_set_local_density_absorption([0, 1, 2], (5.0, 5.0, 0.5), (0, 0, 0), (0, 0, 0))
+    ctx.laser_set_reflection(MODELS)
+    p0, p1, Ip, dA, cell = _seeds(spec, (xs, ys, zs), geom, (0.5, 0.93, 0.5), (0.25, -1.0, 0.1))
+    with pytest.raises(RuntimeError):
+        ctx.laser_calculate(p0, p1, Ip, dA, cell, maxParticles=len(Ip))     # reflected particles do not fit
+    Q, n = ctx.laser_calculate(p0, p1, Ip, dA, cell)        # the context is usable afterwards
+    assert n > len(Ip) and Q.max() > 0
+    ctx.close()

@@ -48,6 +48,16 @@ class LeeModel(C.Structure):
                 ("alphaMin", C.c_double), ("modelVariable", C.c_int32), ("includeDivU", C.c_int32)]
 
 
+class ReflectionModel(C.Structure):
+    """tcif_reflection_model (include/tcif.h)"""
+    _fields_ = [("kind", C.c_int32), ("from_", C.c_int32), ("to", C.c_int32), ("nk1", C.c_double * 2),
+                ("nk2", C.c_double * 2), ("epsilon", C.c_double)]
+
+
+REFL_KINDS = {"noReflection": 0, "Fresnel": 1, "FresnelLaser": 2}
+SIGMA_SB = 5.670374419e-8       # physicoChemical::sigma
+
+
 class AlphaControls(C.Structure):
     """tcif_alpha_controls: fvSolution "alpha" controls of solve()/solveAlphas()."""
     _fields_ = [("nAlphaCorr", C.c_int32), ("nAlphaSubCycles", C.c_int32), ("schemePhi", C.c_int32),
@@ -343,6 +353,51 @@ class Context:
         d = _f64(Udiag).copy()
         self._ck(lib().tcif_interface_porosity(self.h, len(sp), sp.ctypes.data_as(C.POINTER(C.c_int32)), _d(cu), _d(d)))
         return d
+
+    # ---- laserDTRM ----
+    def laser_set_polymesh(self, Cf, Cfb, geom):
+        """geom: dict(points, fpStart, fpPts, tetBasePt, boundsMag) as cases.box_polymesh builds it."""
+        cf, cfb, pts = _f64(Cf), _f64(Cfb), _f64(geom["points"])
+        fs, fp, tb = _i32(geom["fpStart"]), _i32(geom["fpPts"]), _i32(geom["tetBasePt"])
+        self._nPoints = len(pts.reshape(-1, 3))
+        self._ck(lib().tcif_laser_set_polymesh(self.h, _d(cf), _d(cfb), self._nPoints, _d(pts), _i(fs), _i(fp), _i(tb),
+                                               C.c_double(geom["boundsMag"])))
+
+    def laser_set_reflection(self, models, alphaCut=0.5):
+        arr = (ReflectionModel * max(len(models), 1))()
+        for i, md in enumerate(models):
+            arr[i].kind = REFL_KINDS[md["kind"]]; arr[i].from_ = md["from"]; arr[i].to = md["to"]
+            arr[i].nk1[:] = md.get("nk1", (1.0, 0.0)); arr[i].nk2[:] = md.get("nk2", (1.0, 0.0))
+            arr[i].epsilon = md.get("epsilon", 0.0)
+        self._ck(lib().tcif_laser_set_reflection(self.h, len(models), arr, C.c_double(alphaCut)))
+
+    def laser_set_local_density_absorption(self, phases, aCoeff, eCoeff, ECoeff):
+        ph = _i32(phases)
+        a, e, E = _f64(aCoeff), _f64(eCoeff), _f64(ECoeff)
+        self._ck(lib().tcif_laser_set_local_density_absorption(self.h, len(ph), _i(ph), _d(a), _d(e), _d(E)))
+
+    def laser_set_absorption_fields(self, a, e, E):
+        a, e, E = _f64(a), _f64(e), _f64(E)
+        self._ck(lib().tcif_laser_set_absorption_fields(self.h, _d(a), _d(e), _d(E)))
+
+    def laser_calculate(self, p0, p1, I, dA, cell, sigmaSB=SIGMA_SB, maxParticles=0):
+        """laserDTRM::calculate(); returns (Q [nCells], particles in the cloud at the end)."""
+        p0, p1, I, dA, cell = _f64(p0), _f64(p1), _f64(I), _f64(dA), _i32(cell)
+        Q = np.zeros(self.nCells)
+        n = C.c_int32(0)
+        self._ck(lib().tcif_laser_calculate(self.h, len(I), _d(p0), _d(p1), _d(I), _d(dA), _i(cell), C.c_double(sigmaSB),
+                                            int(maxParticles), _d(Q), C.byref(n)))
+        return Q, n.value
+
+    def laser_get(self):
+        Q = np.zeros(self.nCells); refl = np.zeros(self.nCells, np.int32)
+        nHat = np.zeros((self.nCells, 3)); nPts = np.zeros((self._nPoints, 3))
+        self._ck(lib().tcif_laser_get(self.h, _d(Q), _i(refl), _d(nHat), _d(nPts)))
+        return dict(Q=Q, reflectingCells=refl, nHat=nHat, nHatPoints=nPts)
+
+    @property
+    def laser_generations(self):
+        return lib().tcif_laser_generations(self.h)
 
     def solve_yi(self, phase, Y_i, Y_b, Ybc, inertIndex, deltaT, cYi=1.0, schemePhi="vanLeer", schemePhir="linear",
                  Su=None, Sp=None, nYiSubCycles=1, tol=1e-12, maxIter=200):

@@ -187,3 +187,82 @@ def load_case(ctx, spec: CaseSpec, f: dict):
     ctx.set_temperature(f["T_i"], f["T_b"])
     ctx.set_phi(f["phi_i"], f["phi_b"])
     ctx.store_old_alphas()
+
+
+# ---- laserDTRM inputs -----------------------------------------------------------------------
+def box_polymesh(mesh, xs, ys, zs) -> dict:
+    """mesh.points(), mesh.faces() and tetBasePtIs of a rectilinear hex box whose vertex coordinates are xs, ys, zs
+    (what blockMesh would write; the shim reads them off the polyMesh).  Faces are ordered internal, then boundary;
+    the vertices of a face turn right-handed about its area vector.  Vertex id = i + (nx+1)*(j + (ny+1)*k)."""
+    xs, ys, zs = (np.asarray(v, np.float64) for v in (xs, ys, zs))
+    co = (xs, ys, zs)
+    nvx, nvy = len(xs), len(ys)
+    Cf = np.concatenate([np.asarray(mesh.Cf).reshape(-1, 3), np.asarray(mesh.Cfb).reshape(-1, 3)])
+    Sf = np.concatenate([np.asarray(mesh.Sf).reshape(-1, 3), np.asarray(mesh.Sfb).reshape(-1, 3)])
+    nF = len(Cf)
+    ax = np.argmax(np.abs(Sf), axis=1)
+    idx = np.zeros((nF, 3), np.int64)
+    for d in range(3):
+        mid = 0.5 * (co[d][1:] + co[d][:-1])
+        plane = np.searchsorted(mid, Cf[:, d])                       # nearest vertex plane
+        cellidx = np.clip(np.searchsorted(co[d], Cf[:, d]) - 1, 0, len(co[d]) - 2)
+        idx[:, d] = np.where(ax == d, plane, cellidx)
+    # the two in-plane axes (e1, e2) with e1 x e2 = +normal
+    e1 = (ax + 1) % 3
+    e2 = (ax + 2) % 3
+    corners = np.zeros((nF, 4, 3), np.int64)
+    for k, (s1, s2) in enumerate(((0, 0), (1, 0), (1, 1), (0, 1))):
+        c = idx.copy()
+        c[np.arange(nF), e1] += s1
+        c[np.arange(nF), e2] += s2
+        corners[:, k] = c
+    neg = Sf[np.arange(nF), ax] < 0
+    corners[neg] = corners[neg][:, [0, 3, 2, 1]]
+    vid = corners[..., 0] + nvx * (corners[..., 1] + nvy * corners[..., 2])
+    Z, Y, X = np.meshgrid(zs, ys, xs, indexing="ij")
+    points = np.stack([X.ravel(), Y.ravel(), Z.ravel()], axis=1)
+    ext = np.array([xs[-1] - xs[0], ys[-1] - ys[0], zs[-1] - zs[0]])
+    return dict(points=points, fpStart=(4 * np.arange(nF + 1)).astype(np.int32), fpPts=vid.reshape(-1).astype(np.int32),
+                tetBasePt=np.zeros(nF, np.int32), boundsMag=float(np.sqrt(np.dot(ext, ext))))
+
+
+def find_cells_box(n, xs, ys, zs, pts) -> np.ndarray:
+    """mesh.findCell on the rectilinear box (cell id = i + nx*(j + ny*k)); -1 outside."""
+    pts = np.asarray(pts, np.float64).reshape(-1, 3)
+    ijk, ok = [], np.ones(len(pts), bool)
+    for d, v in enumerate((xs, ys, zs)):
+        i = np.searchsorted(np.asarray(v), pts[:, d], side="right") - 1
+        ok &= (i >= 0) & (i < n[d])
+        ijk.append(np.clip(i, 0, n[d] - 1))
+    return np.where(ok, ijk[0] + n[0] * (ijk[1] + n[1] * ijk[2]), -1).astype(np.int32)
+
+
+def laser_seeds(lPosition, lDir, rArea, nr, nTheta, focalLaserRadius, maxTrackLength, mode="Gaussian", power=1.0,
+                sigma=1.0, I0=0.0):
+    """The polar disk of DTRM seeds, laserDTRM::initialise() (laserDTRM.C:199-283): p0, p1, Ip, dA [nr*nTheta].
+    In the drop-in the solver's own initialise() produces these (it also owns findCell and the Function1s)."""
+    SMALL = 1e-15
+    lPosition, lDir, rArea = (np.asarray(v, np.float64) for v in (lPosition, lDir, rArea))
+    dr, dTheta = focalLaserRadius / nr, 2.0 * np.pi / nTheta
+    r1 = SMALL + dr * np.arange(nr)
+    r2 = r1 + dr
+    rP = (r1 + r2) / 2
+    th1 = SMALL + dTheta * np.arange(nTheta)
+    th2 = th1 + dTheta
+    thP = (th1 + th2) / 2.0
+    # quaternion(lDir, thetaP).R() & (rP*rArea): Rodrigues rotation about the unit axis lDir
+    c, s = np.cos(thP)[None, :, None], np.sin(thP)[None, :, None]
+    v = (rP[:, None, None] * rArea[None, None, :])
+    rot = v * c + np.cross(lDir, v) * s + lDir * np.einsum("k,ijk->ij", lDir, v)[..., None] * (1 - c)
+    p0 = (lPosition + rot).reshape(-1, 3)
+    p1 = p0 + 0.5 * maxTrackLength * lDir
+    if mode == "GaussianPeak":
+        Ip = I0 * np.exp(-2.0 * rP ** 2 / sigma ** 2)
+    elif mode == "Gaussian":
+        Ip = power / (2.0 * np.pi * sigma ** 2) * np.exp(-rP ** 2 / 2.0 / sigma ** 2)
+    elif mode == "uniform":
+        Ip = np.full(nr, power / (np.pi * focalLaserRadius ** 2))
+    else:
+        raise ValueError(mode)
+    dA = ((r2 ** 2 - r1 ** 2)[:, None] * (th2 - th1)[None, :] / 2.0)
+    return p0, p1, np.repeat(Ip, nTheta), dA.reshape(-1)

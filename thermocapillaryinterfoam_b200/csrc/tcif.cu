@@ -10,6 +10,7 @@
 #include "tcif_alpha.cuh"
 #include "tcif_mass.cuh"
 #include "tcif_species.cuh"
+#include "tcif_laser.cuh"
 #include "../../include/tcif.h"
 
 #include <dlfcn.h>
@@ -52,11 +53,11 @@ inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 // ---- timers ---------------------------------------------------------------------------
 enum TimerId {
     T_GRAD_TENSOR = 0, T_DIV_TENSOR, T_MULES_SETUP, T_MULES_ITER, T_MULES_FINAL, T_LIMIT_SUM,
-    T_BOUNDARY, T_HALO, T_CONVERT, T_STATS, T_FLUX_ASSEMBLY, T_PREDICTOR, T_RHOPHI, T_MASS, T_COUNT
+    T_BOUNDARY, T_HALO, T_CONVERT, T_STATS, T_FLUX_ASSEMBLY, T_PREDICTOR, T_RHOPHI, T_MASS, T_LASER, T_COUNT
 };
 const char *kTimerNames[T_COUNT] = {
     "grad_tensor", "div_tensor", "mules_setup", "mules_iter", "mules_final", "limit_sum",
-    "boundary", "halo", "convert", "stats", "flux_assembly", "predictor", "rho_phi", "alpha_transfer"};
+    "boundary", "halo", "convert", "stats", "flux_assembly", "predictor", "rho_phi", "alpha_transfer", "laser_dtrm"};
 
 struct EvPair { cudaEvent_t a, b; int id; double bytes; };
 
@@ -185,6 +186,19 @@ struct tcif_ctx {
     double *spPhiPsi = nullptr, *spPhiPsib = nullptr, *spPhiHO = nullptr, *spPhiHOb = nullptr;
     int *spBc = nullptr;
     double ddtAlphaMax = 0.0;
+    // laserDTRM
+    LaserGeo lg{};
+    bool laserGeoSet = false;
+    std::vector<LaserRefl> lzModels;
+    double lzAlphaCut = 0.5;
+    int lzNAbs = 0, lzAbsPhase[4]{};
+    double lzA[4]{}, lzE[4]{}, lzEE[4]{};
+    bool lzAbsFields = false;
+    double *lzAF = nullptr;                 // a, e, E fields [3*stride] when the host supplies them
+    int *lzRefl = nullptr, *lzCounters = nullptr;
+    double *lzNHat = nullptr, *lzNHatPts = nullptr, *lzQ = nullptr;
+    LaserPart *lzCloud = nullptr;
+    int lzCap = 0, lzParticles = 0, lzGenerations = 0;
     // F is a pure function of (alpha, T, sigma): the solver evaluates it 2-4x per time step on unchanged
     // fields (UEqn.H:29, pEqn.H:35 per corrector, thermocapillaryInterFoam.C:150); fieldsVersion counts
     // every change of those inputs and forceVersion remembers which one F was computed from
@@ -1440,6 +1454,189 @@ int pair_index(int P, int p1, int p2) {
     return -1;
 }
 
+// ---- laserDTRM, kernels in tcif_laser.cuh ------------------------------------------------
+// polyMesh data of the cell walk: face centres in the slot layout, mesh.points()/faces()/tetBasePtIs and the
+// point -> cell weights of volPointInterpolation (built once on the host from the faces' vertices).
+void do_laser_set_polymesh(tcif_ctx *c, const double *Cf, const double *Cfb, int nPoints, const double *points,
+                           const int32_t *fpStart, const int32_t *fpPts, const int32_t *tetBasePt, double boundsMag) {
+    const int nIF = c->nIF, nBF = c->nBF, nC = c->nC, nF = nIF + nBF;
+    if ((nIF && !Cf) || (nBF && !Cfb) || nPoints <= 0 || !points || !fpStart || !fpPts || !tetBasePt || !(boundsMag > 0))
+        failf("tcif_laser_set_polymesh: bad arguments");
+    if (!c->Cx) failf("tcif_laser_set_polymesh: cell centres needed, call tcif_set_cell_centres first");
+    if (fpStart[0] != 0) failf("tcif_laser_set_polymesh: fpStart[0] must be 0");
+    for (int f = 0; f < nF; ++f) {
+        if (fpStart[f + 1] - fpStart[f] < 3) failf("tcif_laser_set_polymesh: face %d has fewer than 3 vertices", f);
+        if (tetBasePt[f] >= fpStart[f + 1] - fpStart[f]) failf("tcif_laser_set_polymesh: tetBasePt[%d] out of range", f);
+    }
+    const int nFP = fpStart[nF];
+    for (int j = 0; j < nFP; ++j) if (fpPts[j] < 0 || fpPts[j] >= nPoints) failf("tcif_laser_set_polymesh: vertex label out of range");
+    LaserGeo &g = c->lg;
+    g = LaserGeo{};
+    const size_t bs = std::max(nBF, 1);
+    // face centres: internal faces scattered into the slots of Sf, boundary faces as SoA
+    {
+        double *cf = c->dalloc<double>(3 * c->nFd);
+        g.Cfx = cf; g.Cfy = cf + c->nFd; g.Cfz = cf + 2 * c->nFd;
+        double *cb = c->dalloc<double>(3 * bs);
+        g.Cfbx = cb; g.Cfby = cb + bs; g.Cfbz = cb + 2 * bs;
+        double *tmp = nullptr;
+        CUDA_OK(cudaMalloc(&tmp, sizeof(double) * 3 * (size_t)std::max(std::max(nIF, nBF), 1)));
+        if (nIF) {
+            CUDA_OK(cudaMemcpyAsync(tmp, Cf, sizeof(double) * 3 * nIF, cudaMemcpyDefault, c->stream));
+            k_face_scatter_vec<<<cdiv(nIF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(nIF, c->d_faceMap, tmp, cf, cf + c->nFd, cf + 2 * c->nFd);
+            CUDA_OK(cudaStreamSynchronize(c->stream));
+        }
+        if (nBF) {
+            CUDA_OK(cudaMemcpyAsync(tmp, Cfb, sizeof(double) * 3 * nBF, cudaMemcpyDefault, c->stream));
+            k_aos3_to_soa<<<cdiv(nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(nBF, bs, tmp, cb);
+            CUDA_OK(cudaStreamSynchronize(c->stream));
+        }
+        CUDA_OK(cudaFree(tmp));
+        c->launches += 2;
+    }
+    g.Cx = c->Cx; g.Cy = c->Cy; g.Cz = c->Cz;
+    {
+        int *bi = c->dalloc<int>(nC, false);
+        CUDA_OK(cudaMemsetAsync(bi, 0xff, sizeof(int) * nC, c->stream));
+        if (c->nBndCells) k_laser_bnd_index<<<cdiv(c->nBndCells, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nBndCells, c->dm.bndCells, bi);
+        int *ff = c->dalloc<int>(c->nFd, false);
+        CUDA_OK(cudaMemsetAsync(ff, 0xff, sizeof(int) * c->nFd, c->stream));
+        if (nIF) k_laser_fd_to_face<<<cdiv(nIF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(nIF, c->d_faceMap, ff);
+        g.bndIdx = bi; g.fdToFace = ff;
+        c->launches += 2;
+    }
+    g.nIF = nIF; g.nPoints = nPoints; g.boundsMag = boundsMag;
+    g.points = c->upload(std::vector<double>(points, points + 3 * (size_t)nPoints));
+    g.fpStart = c->upload(std::vector<int>(fpStart, fpStart + nF + 1));
+    g.fpPts = c->upload(std::vector<int>(fpPts, fpPts + nFP));
+    g.tetBasePt = c->upload(std::vector<int>(tetBasePt, tetBasePt + nF));
+    // owner / neighbour / faceCells back from the device tables
+    std::vector<int> faceMap(nIF), nbrOwn(c->nFd), fc(nBF);
+    if (nIF) CUDA_OK(cudaMemcpy(faceMap.data(), c->d_faceMap, sizeof(int) * nIF, cudaMemcpyDeviceToHost));
+    CUDA_OK(cudaMemcpy(nbrOwn.data(), c->dm.nbrOwn, sizeof(int) * c->nFd, cudaMemcpyDeviceToHost));
+    if (nBF) CUDA_OK(cudaMemcpy(fc.data(), c->dm.faceCells, sizeof(int) * nBF, cudaMemcpyDeviceToHost));
+    std::vector<double> Cc(3 * (size_t)nC);
+    {
+        std::vector<double> soa(3 * (size_t)c->stride);
+        CUDA_OK(cudaMemcpy(soa.data(), c->Cx, sizeof(double) * 3 * c->stride, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < nC; ++i) for (int d = 0; d < 3; ++d) Cc[3 * (size_t)i + d] = soa[(size_t)d * c->stride + i];
+    }
+    // point -> cells (ascending, unique) with weights (1/|x_p - C_c|)/sum   [volPointInterpolation::makeWeights]
+    std::vector<int> cnt(nPoints + 1, 0);
+    for (int f = 0; f < nF; ++f)
+        for (int j = fpStart[f]; j < fpStart[f + 1]; ++j) cnt[fpPts[j] + 1] += f < nIF ? 2 : 1;
+    for (int p = 0; p < nPoints; ++p) cnt[p + 1] += cnt[p];
+    std::vector<int> tmp(cnt[nPoints]), fill(cnt.begin(), cnt.end() - 1);
+    for (int f = 0; f < nF; ++f)
+        for (int j = fpStart[f]; j < fpStart[f + 1]; ++j) {
+            const int p = fpPts[j];
+            if (f < nIF) { tmp[fill[p]++] = faceMap[f] % c->stride; tmp[fill[p]++] = nbrOwn[faceMap[f]]; }
+            else tmp[fill[p]++] = fc[f - nIF];
+        }
+    std::vector<int> pcStart(nPoints + 1), pc;
+    std::vector<double> pw;
+    pc.reserve(tmp.size() / 2); pw.reserve(tmp.size() / 2);
+    for (int p = 0; p < nPoints; ++p) {
+        pcStart[p] = (int)pc.size();
+        std::sort(tmp.begin() + cnt[p], tmp.begin() + cnt[p + 1]);
+        double sum = 0.0;
+        const size_t first = pc.size();
+        for (int i = cnt[p]; i < cnt[p + 1]; ++i) {
+            if (i > cnt[p] && tmp[i] == tmp[i - 1]) continue;
+            const double *C = &Cc[3 * (size_t)tmp[i]], *x = points + 3 * (size_t)p;
+            const double d[3] = {x[0] - C[0], x[1] - C[1], x[2] - C[2]};
+            const double w = 1.0 / std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+            pc.push_back(tmp[i]); pw.push_back(w);
+            sum += w;
+        }
+        for (size_t i = first; i < pc.size(); ++i) pw[i] /= sum;
+    }
+    pcStart[nPoints] = (int)pc.size();
+    std::vector<unsigned char> isPatch(nPoints, 0);
+    for (int pa = 0; pa < c->nPatches; ++pa) {
+        if (c->patchType[pa] == TCIF_PATCH_EMPTY || c->patchType[pa] == TCIF_PATCH_PROCESSOR) continue;
+        for (int i = 0; i < c->patchSize[pa]; ++i) {
+            const int f = nIF + c->patchStart[pa] + i;
+            for (int j = fpStart[f]; j < fpStart[f + 1]; ++j) isPatch[fpPts[j]] = 1;
+        }
+    }
+    g.pcStart = c->upload(pcStart); g.pc = c->upload(pc); g.pw = c->upload(pw); g.isPatchPoint = c->upload(isPatch);
+    c->lzRefl = c->dalloc<int>(nC);
+    c->lzNHat = c->dalloc<double>(3 * (size_t)c->stride);
+    c->lzNHatPts = c->dalloc<double>(3 * (size_t)nPoints);
+    c->lzQ = c->dalloc<double>(nC);
+    c->lzCounters = c->dalloc<int>(4);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    c->laserGeoSet = true;
+}
+
+// laserDTRM::calculate(): mark the reflecting cells, interpolate nHat to the points, walk the cloud generation by
+// generation (reflected particles are appended by the walk), Q /= V
+int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const double *p1, const double *I, const double *dA,
+                       const int32_t *cell, double sigmaSB, int maxParticles) {
+    if (!c->laserGeoSet) failf("tcif_laser_calculate: call tcif_laser_set_polymesh first");
+    if (!c->haveT) failf("tcif_laser_calculate: temperature not set");
+    if (!c->lzAbsFields && c->lzNAbs == 0) failf("tcif_laser_calculate: no absorption model set");
+    if (nParticles < 0 || (nParticles && (!p0 || !p1 || !I || !dA || !cell))) failf("tcif_laser_calculate: bad arguments");
+    if (c->nCoupled > 0) failf("tcif_laser_calculate: processor patches are not supported by the device cell walk yet");
+    LaserArgs a{};
+    a.nModels = (int)c->lzModels.size(); a.P = c->P;
+    for (int i = 0; i < a.nModels; ++i) a.models[i] = c->lzModels[i];
+    a.alphaCut = c->lzAlphaCut; a.sigmaSB = sigmaSB;
+    a.deltaN = 1e-7 / cbrt(c->sumV / (double)c->nC);                                   // laserDTRM.C:121-125
+    for (int p = 0; p < c->P; ++p) a.alpha[p] = c->alpha[p];
+    a.refl = c->lzRefl; a.nHat = c->lzNHat; a.nHatPts = c->lzNHatPts; a.Q = c->lzQ; a.T = c->Tc;
+    a.nAbs = c->lzNAbs;
+    for (int i = 0; i < c->lzNAbs; ++i) { a.absPhase[i] = c->lzAbsPhase[i]; a.aCoeff[i] = c->lzA[i]; a.eCoeff[i] = c->lzE[i]; a.ECoeff[i] = c->lzEE[i]; }
+    if (c->lzAbsFields) { a.aF = c->lzAF; a.eF = c->lzAF + c->stride; a.EF = c->lzAF + 2 * (size_t)c->stride; }
+    // the seeds that found a cell (laserDTRM.C:287-296)
+    std::vector<LaserPart> seeds;
+    seeds.reserve(nParticles);
+    for (int k = 0; k < nParticles; ++k) {
+        if (cell[k] < 0) continue;
+        if (cell[k] >= c->nC) failf("tcif_laser_calculate: cell[%d] out of range", k);
+        LaserPart q{};
+        for (int d = 0; d < 3; ++d) { q.pos[d] = q.p0[d] = p0[3 * (size_t)k + d]; q.p1[d] = p1[3 * (size_t)k + d]; }
+        q.I0 = q.I = I[k]; q.dA = dA[k]; q.frac = 0; q.cell = cell[k]; q.tid = -1; q.face = -1; q.keep = 1;
+        seeds.push_back(q);
+    }
+    const int nSeeds = (int)seeds.size();
+    const int cap = std::max(maxParticles > 0 ? maxParticles : 64 * std::max(nSeeds, 1), nSeeds);
+    if (cap > c->lzCap) {
+        if (c->lzCloud) CUDA_OK(cudaFree(c->lzCloud));
+        CUDA_OK(cudaMalloc((void **)&c->lzCloud, sizeof(LaserPart) * (size_t)cap));
+        c->lzCap = cap;
+    }
+    a.cloud = c->lzCloud; a.cap = cap; a.counters = c->lzCounters;
+    if (nSeeds) CUDA_OK(cudaMemcpyAsync(c->lzCloud, seeds.data(), sizeof(LaserPart) * nSeeds, cudaMemcpyHostToDevice, c->stream));
+    int cnt[4] = {nSeeds, 0, 0, 0};
+    CUDA_OK(cudaMemcpyAsync(c->lzCounters, cnt, sizeof(cnt), cudaMemcpyHostToDevice, c->stream));
+    CUDA_OK(cudaMemsetAsync(c->lzQ, 0, sizeof(double) * c->nC, c->stream));
+    if (a.nModels) { do_grad(c); a.G = c->G; }
+    timed(c, T_LASER, (16.0 * a.nModels * 4 + 28.0) * c->nC, [&] {
+        k_laser_mark<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a);
+        k_laser_points<<<cdiv(c->lg.nPoints, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->lg, c->lzNHat, c->lzNHatPts);
+        c->launches += 2;
+    });
+    int done = 0, total = nSeeds, generations = 0;
+    while (done < total) {
+        timed(c, T_LASER, 0.0, [&] {
+            k_laser_move<<<cdiv(total - done, 128), 128, 0, c->stream>>>(c->dm, c->lg, a, done, total);
+            c->launches++;
+        });
+        CUDA_OK(cudaMemcpyAsync(cnt, c->lzCounters, sizeof(int) * 2, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        if (cnt[1] == LASER_ERR_PROCESSOR) failf("tcif_laser_calculate: a particle reached a processor patch");
+        if (cnt[1] == LASER_ERR_OVERFLOW || cnt[0] > cap) failf("tcif_laser_calculate: cloud overflow (more than %d particles), raise maxParticles", cap);
+        done = total; total = cnt[0];
+        if (++generations > 10000) failf("tcif_laser_calculate: reflection cascade does not end");
+    }
+    k_laser_finish<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nC, c->dm.V, c->lzQ);
+    c->launches++;
+    c->lzParticles = total; c->lzGenerations = generations;
+    return total;
+}
+
 }  // namespace
 
 // ========================================================================================
@@ -1533,6 +1730,7 @@ void tcif_destroy(tcif_ctx *c) {
     for (auto &e : c->evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (auto &e : c->evPool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (void *p : c->allocs) cudaFree(p);
+    if (c->lzCloud) cudaFree(c->lzCloud);
     if (c->h_small) cudaFreeHost(c->h_small);
     if (c->sIn) cudaStreamDestroy(c->sIn);
     if (c->sOut) cudaStreamDestroy(c->sOut);
@@ -1868,6 +2066,79 @@ int tcif_solve_yi(tcif_ctx *c, int phase, int nSpecies, int inertIndex, double *
 }
 
 // ---- hot path ---------------------------------------------------------------------------------
+// ---- laserDTRM ----------------------------------------------------------------------------
+int tcif_laser_set_polymesh(tcif_ctx *c, const double *Cf, const double *Cfb, int32_t nPoints, const double *points,
+                            const int32_t *fpStart, const int32_t *fpPts, const int32_t *tetBasePt, double boundsMag) {
+    API_BEGIN(c)
+    do_laser_set_polymesh(c, Cf, Cfb, nPoints, points, fpStart, fpPts, tetBasePt, boundsMag);
+    API_END(c)
+}
+
+int tcif_laser_set_reflection(tcif_ctx *c, int32_t nModels, const tcif_reflection_model *models, double alphaCut) {
+    API_BEGIN(c)
+    if (nModels < 0 || nModels > 8 || (nModels && !models)) failf("tcif_laser_set_reflection: 0..8 models");
+    std::vector<LaserRefl> v;
+    for (int i = 0; i < nModels; ++i) {
+        const tcif_reflection_model &m = models[i];
+        if (m.kind < 0 || m.kind > 2) failf("tcif_laser_set_reflection: unknown reflection model %d", m.kind);
+        check_phase(c, m.from); check_phase(c, m.to);
+        if (m.from == m.to) failf("tcif_laser_set_reflection: pair (%d %d)", m.from, m.to);
+        LaserRefl r{m.kind, m.from, m.to, {m.nk1[0], m.nk1[1]}, {m.nk2[0], m.nk2[1]}, m.epsilon};
+        v.push_back(r);
+    }
+    c->lzModels = v; c->lzAlphaCut = alphaCut;
+    API_END(c)
+}
+
+int tcif_laser_set_local_density_absorption(tcif_ctx *c, int32_t nNames, const int32_t *phases, const double *aCoeff,
+                                            const double *eCoeff, const double *ECoeff) {
+    API_BEGIN(c)
+    if (nNames < 1 || nNames > 4 || !phases || !aCoeff || !eCoeff || !ECoeff) failf("tcif_laser_set_local_density_absorption: bad arguments");
+    for (int i = 0; i < nNames; ++i) {
+        check_phase(c, phases[i]);
+        c->lzAbsPhase[i] = phases[i]; c->lzA[i] = aCoeff[i]; c->lzE[i] = eCoeff[i]; c->lzEE[i] = ECoeff[i];
+    }
+    c->lzNAbs = nNames; c->lzAbsFields = false;
+    API_END(c)
+}
+
+int tcif_laser_set_absorption_fields(tcif_ctx *c, const double *a, const double *e, const double *E) {
+    API_BEGIN(c)
+    if (!a || !e || !E) failf("tcif_laser_set_absorption_fields: null array");
+    if (!c->lzAF) c->lzAF = c->dalloc<double>(3 * (size_t)c->stride);
+    up_cells(c, c->lzAF, a); up_cells(c, c->lzAF + c->stride, e); up_cells(c, c->lzAF + 2 * (size_t)c->stride, E);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    c->lzAbsFields = true;
+    API_END(c)
+}
+
+int tcif_laser_calculate(tcif_ctx *c, int32_t nParticles, const double *p0, const double *p1, const double *I, const double *dA,
+                         const int32_t *cell, double sigmaSB, int32_t maxParticles, double *Q, int32_t *nParticlesFinal) {
+    API_BEGIN(c)
+    const int n = do_laser_calculate(c, nParticles, p0, p1, I, dA, cell, sigmaSB, maxParticles);
+    if (Q) CUDA_OK(cudaMemcpyAsync(Q, c->lzQ, sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    if (nParticlesFinal) *nParticlesFinal = n;
+    API_END(c)
+}
+
+int tcif_laser_get(tcif_ctx *c, double *Q, int32_t *reflectingCells, double *nHat, double *nHatPoints) {
+    API_BEGIN(c)
+    if (!c->laserGeoSet) failf("tcif_laser_get: call tcif_laser_set_polymesh first");
+    if (Q) CUDA_OK(cudaMemcpyAsync(Q, c->lzQ, sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
+    if (reflectingCells) CUDA_OK(cudaMemcpyAsync(reflectingCells, c->lzRefl, sizeof(int) * c->nC, cudaMemcpyDefault, c->stream));
+    if (nHat) {
+        k_soa_to_aos3<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nC, (size_t)c->stride, c->lzNHat, c->staging);
+        c->launches++;
+        CUDA_OK(cudaMemcpyAsync(nHat, c->staging, sizeof(double) * 3 * c->nC, cudaMemcpyDefault, c->stream));
+    }
+    if (nHatPoints) CUDA_OK(cudaMemcpyAsync(nHatPoints, c->lzNHatPts, sizeof(double) * 3 * c->lg.nPoints, cudaMemcpyDefault, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_laser_generations(const tcif_ctx *c) { return c ? c->lzGenerations : -1; }
+
 int tcif_div_capillary_stress(tcif_ctx *c) {
     API_BEGIN(c)
     do_force(c);
