@@ -74,7 +74,41 @@ def build_mass(config, n):
     return out
 
 
+# laserDTRM::calculate() - reflecting cells, nHat, Q of a Gaussian beam onto the first blob
+LASER_CASE = ("laser_dtrm_3d_n10", 5, 10)
+LASER_MODELS = [{"kind": "FresnelLaser", "from": 2, "to": 0, "epsilon": 0.25},
+                {"kind": "Fresnel", "from": 2, "to": 1, "nk1": (1.0, 0.0), "nk2": (3.6, 5.0)}]
+LASER_ABS = dict(a=(30.0, 12.0, 0.2), e=(0.3, 0.1, 0.0), E=(0.0, 0.0, 0.0))
+
+
+def laser_inputs(config, n):
+    from thermocapillaryinterfoam_b200 import mesh as hm
+    spec = cases.case(config, n)
+    m = global_mesh(spec)
+    v = tuple(hm.vertices(spec.n[d], spec.lengths[d]) for d in range(3))
+    geom = cases.box_polymesh(m, *v)
+    f = cases.synthetic_fields(spec, m)
+    d = np.array([0.2, -1.0, 0.1]); d /= np.linalg.norm(d)
+    r = np.cross(d, [0.0, 0.0, 1.0]); r /= np.linalg.norm(r)
+    p0, p1, Ip, dA = cases.laser_seeds((0.45, 0.93, 0.5), d, r, 6, 12, 0.2, geom["boundsMag"], mode="Gaussian", power=150.0,
+                                       sigma=0.09)
+    seeds = dict(p0=p0, p1=p1, I=Ip, dA=dA, cell=cases.find_cells_box(spec.n, *v, p0))
+    return spec, m, geom, f, seeds
+
+
+def build_laser(config, n):
+    spec, m, geom, f, s = laser_inputs(config, n)
+    al = f["alpha_i"]
+    a, e, E = (orc.local_density(al, LASER_ABS[k]) for k in ("a", "e", "E"))
+    r = orc.laser_calculate(m, geom, LASER_MODELS, al, f["alpha_b"], f["alphaBc"], a, e, E, f["T_i"], s["p0"], s["p1"], s["I"],
+                            s["dA"], s["cell"])
+    return dict(Q=r["Q"], reflectingCells=r["reflectingCells"], nHat=r["nHat"], nHatPoints=r["nHatPoints"],
+                nParticles=np.array([r["nParticles"]]))
+
+
 if __name__ == "__main__":
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", LASER_CASE[0] + ".npz"), **build_laser(*LASER_CASE[1:]))
+    print("wrote", LASER_CASE[0])
     np.savez_compressed(os.path.join(ROOT, "tests", "golden", MASS_CASE[0] + ".npz"), **build_mass(*MASS_CASE[1:]))
     print("wrote", MASS_CASE[0])
     for name, config, n in CASES:

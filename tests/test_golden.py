@@ -87,3 +87,35 @@ def test_cuda_path_matches_mass_transfer_golden():
     for p in range(3):
         assert_field_close(ctx.get_alpha(p)[0], z[f"solve_alpha_i{p}"], f"solve alpha{p}", rtol=1e-11)
     ctx.close()
+
+
+def test_oracle_reproduces_laser_golden():
+    z = np.load(os.path.join(GOLD, mg.LASER_CASE[0] + ".npz"))
+    got = mg.build_laser(*mg.LASER_CASE[1:])
+    assert set(z.files) == set(got)
+    assert int(z["nParticles"][0]) > 72                     # the fixture exercises reflection
+    for k in z.files:
+        if k in ("reflectingCells", "nParticles"):
+            assert np.array_equal(got[k], z[k]), k
+        else:
+            assert_field_close(got[k], z[k], k, rtol=1e-13)
+
+
+@pytest.mark.gpu
+def test_cuda_path_matches_laser_golden():
+    z = np.load(os.path.join(GOLD, mg.LASER_CASE[0] + ".npz"))
+    spec, m, geom, f, s = mg.laser_inputs(*mg.LASER_CASE[1:])
+    ctx = abi.Context(m, 3)
+    cases.load_case(ctx, spec, f)
+    ctx.set_cell_centres(f["C"], f["deltab"])
+    ctx.laser_set_polymesh(m.Cf, m.Cfb, geom)
+    ctx.laser_set_reflection(mg.LASER_MODELS)
+    ctx.laser_set_local_density_absorption([0, 1, 2], mg.LASER_ABS["a"], mg.LASER_ABS["e"], mg.LASER_ABS["E"])
+    Q, n = ctx.laser_calculate(s["p0"], s["p1"], s["I"], s["dA"], s["cell"])
+    got = ctx.laser_get()
+    assert n == int(z["nParticles"][0])
+    assert np.array_equal(got["reflectingCells"], z["reflectingCells"])
+    assert_field_close(got["nHat"], z["nHat"], "nHat")
+    assert_field_close(got["nHatPoints"], z["nHatPoints"], "nHatPoints")
+    assert np.abs(Q - z["Q"]).max() <= 1e-11 * np.abs(z["Q"]).max()
+    ctx.close()
