@@ -270,8 +270,7 @@ TCIF_API int tcif_solve_yi(tcif_ctx *ctx, int phase, int nSpecies, int inertInde
  * Replaces radiation::laserDTRM::calculate() (laserDTRM/laserDTRM.C:542-735) with DTRMParticle::move
  * (laserDTRM/DTRMParticle/DTRMParticle.C:94-266): reflecting-cell marking from grad(alpha) (:596-652), the cell
  * walk of the cloud with absorption/emission per cell crossed and Fresnel reflection at the interface, Q /= V.
- * The seeds (initialise(), :169-331: polar disk, Function1s, findCell) stay with the solver.  Single domain:
- * a mesh with processor patches is refused. */
+ * The seeds (initialise(), :169-331: polar disk, Function1s, findCell) stay with the solver. */
 /* polyMesh data of the cell walk and of interpolationCellPoint(nHat): mesh.faceCentres() (internal [nIF*3],
  * boundary [nBF*3]), mesh.points(), mesh.faces() as CSR over internal then boundary faces, mesh.tetBasePtIs(),
  * mesh.bounds().mag().  Needs tcif_set_cell_centres first. */
@@ -293,12 +292,20 @@ TCIF_API int tcif_laser_set_local_density_absorption(tcif_ctx *ctx, int32_t nNam
 TCIF_API int tcif_laser_set_absorption_fields(tcif_ctx *ctx, const double *a, const double *e, const double *E);
 /* calculate(): seeds p0/p1 [n*3], Ip, dA [n], cell [n] (-1: findCell missed, not seeded); sigmaSB =
  * physicoChemical::sigma; maxParticles = capacity of the cloud incl. reflected particles (0: 64 per seed).
- * Uses the resident alpha and T.  Q [nCells] (= Ru(), W/m^3) may be NULL (read it with tcif_laser_get). */
+ * Uses the resident alpha and T.  Q [nCells] (= Ru(), W/m^3) may be NULL (read it with tcif_laser_get);
+ * nParticlesFinal = particles created on this rank (its seeds + the reflected particles it spawned). */
 TCIF_API int tcif_laser_calculate(tcif_ctx *ctx, int32_t nParticles, const double *p0, const double *p1, const double *I,
                                   const double *dA, const int32_t *cell, double sigmaSB, int32_t maxParticles,
                                   double *Q, int32_t *nParticlesFinal);
 /* Q, reflectingCellsVol (:556), nHat (:576) [nCells*3] and its point interpolation [nPoints*3]; any may be NULL */
 TCIF_API int tcif_laser_get(tcif_ctx *ctx, double *Q, int32_t *reflectingCells, double *nHat, double *nHatPoints);
+/* Decomposed meshes: the points of processor patches are shared by ranks, and volPointInterpolation sums weights and
+ * weighted values over all ranks holding a point.  localPoint [n]: every local point lying on a processor patch,
+ * globalPoint [n]: its global label (globalMeshData).  Collective over the communicator; call after
+ * tcif_laser_set_polymesh.  Particles reaching a processor patch are then handed to the neighbour rank between the
+ * launches of the walk (hitProcessorPatch, DTRMParticle.C:268-275); tcif_laser_calculate is collective, every rank
+ * passes the seeds whose cell it owns (cell = -1 for the others) and gets back Q of its own cells. */
+TCIF_API int tcif_laser_set_shared_points(tcif_ctx *ctx, int32_t nShared, const int32_t *localPoint, const int64_t *globalPoint);
 /* launches of the walk kernel in the last calculate() = depth of the reflection cascade + 1 */
 TCIF_API int tcif_laser_generations(const tcif_ctx *ctx);
 

@@ -147,3 +147,72 @@ def test_errors():
     Q, n = ctx.laser_calculate(p0, p1, Ip, dA, cell)        # the context is usable afterwards
     assert n > len(Ip) and Q.max() > 0
     ctx.close()
+
+
+@pytest.mark.parametrize("procs", [(2, 1, 1), (1, 2, 1), (2, 2, 2)])
+def test_decomposed_matches_serial_oracle(procs):
+    """Processor patches: grad(alpha) with halos, point interpolation summed over the ranks sharing a point,
+    particles handed to the neighbour rank when they reach a processor patch (in-process group, one thread per
+    rank).  Against the SERIAL oracle on the undecomposed mesh: the point weights are re-associated (1e-10)."""
+    import threading
+    n = 16
+    spec = cases.case(5, n)
+    g = mo.box_mesh(*spec.n, spec.lengths, spec.patch_types)
+    xs, ys, zs = (hm.vertices(spec.n[d], spec.lengths[d]) for d in range(3))
+    geomG = cases.box_polymesh(g, xs, ys, zs)
+    fg = cases.synthetic_fields(spec, g)
+    aC, eC, EC = (25.0, 10.0, 0.3), (0.1, 0.0, 0.0), (0.0, 0.0, 0.0)
+    d = np.array([0.5, -1.0, 0.2]); d /= np.linalg.norm(d)
+    r = np.cross(d, [0.0, 0.0, 1.0]); r /= np.linalg.norm(r)
+    p0, p1, Ip, dA = cases.laser_seeds((0.3, 0.93, 0.45), d, r, 8, 16, 0.15, geomG["boundsMag"], sigma=0.07, power=200.0)
+    cellG = cases.find_cells_box(spec.n, xs, ys, zs, p0)
+    assert (cellG >= 0).all()
+    al = fg["alpha_i"]
+    ref = orc.laser_calculate(g, geomG, MODELS, al, fg["alpha_b"], fg["alphaBc"], orc.local_density(al, aC),
+                              orc.local_density(al, eC), orc.local_density(al, EC), fg["T_i"], p0, p1, Ip, dA, cellG)
+    assert ref["nParticles"] > len(Ip)
+    nd = procs[0] * procs[1] * procs[2]
+    meshes = [hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, rk) for rk in range(nd)]
+    fs = [cases.synthetic_fields(spec, m) for m in meshes]
+    grp = abi.Group(nd)
+    ctxs = [abi.Context(m, spec.nPhases) for m in meshes]
+    outs, errs = [None] * nd, []
+
+    def work(rk):
+        try:
+            m, f, ctx = meshes[rk], fs[rk], ctxs[rk]
+            ctx.comm_init_local(rk, grp)
+            cases.load_case(ctx, spec, f)
+            ctx.set_cell_centres(f["C"], f["deltab"])
+            geom = cases.box_block_polymesh(spec.n, xs, ys, zs, procs, rk, m)
+            ctx.laser_set_polymesh(m.Cf, m.Cfb, geom)
+            ctx.laser_set_shared_points(geom["sharedLocal"], geom["sharedGlobal"])
+            ctx.laser_set_reflection(MODELS)
+            ctx.laser_set_local_density_absorption([0, 1, 2], aC, eC, EC)
+            gid = np.asarray(m.cellGlobal)
+            g2l = np.full(g.nCells, -1, np.int32); g2l[gid] = np.arange(len(gid), dtype=np.int32)
+            Q, created = ctx.laser_calculate(p0, p1, Ip, dA, g2l[cellG])
+            got = ctx.laser_get()
+            outs[rk] = dict(Q=Q, created=created, gid=gid, refl=got["reflectingCells"], nHat=got["nHat"],
+                            nPts=got["nHatPoints"], pgid=geom["pointGlobal"])
+        except Exception as e:          # noqa: BLE001
+            errs.append((rk, e))
+    ts = [threading.Thread(target=work, args=(rk,), daemon=True) for rk in range(nd)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(180)
+    assert not errs, errs
+    assert all(o is not None for o in outs), "a rank did not finish"
+    assert sum(o["created"] for o in outs) == ref["nParticles"]
+    scale = np.abs(ref["Q"]).max()
+    for rk, o in enumerate(outs):
+        assert np.array_equal(o["refl"], ref["reflectingCells"][o["gid"]]), f"reflectingCells rank {rk}"
+        assert np.abs(o["nHat"] - ref["nHat"][o["gid"]]).max() <= 1e-12, f"nHat rank {rk}"
+        assert np.abs(o["nPts"] - ref["nHatPoints"][o["pgid"]]).max() <= 1e-12, f"nHatPoints rank {rk}"
+        err = np.abs(o["Q"] - ref["Q"][o["gid"]]).max()
+        assert err <= 1e-10 * scale, f"Q rank {rk}: {err:.3e} of {scale:.3e}"
+    assert sum((o["Q"] != 0).sum() for o in outs) == (ref["Q"] != 0).sum()
+    for c in ctxs:
+        c.close()
+    grp.close()

@@ -363,6 +363,12 @@ class Context:
         self._ck(lib().tcif_laser_set_polymesh(self.h, _d(cf), _d(cfb), self._nPoints, _d(pts), _i(fs), _i(fp), _i(tb),
                                                C.c_double(geom["boundsMag"])))
 
+    def laser_set_shared_points(self, localPoint, globalPoint):
+        """Collective: the local points on processor patches and their global labels."""
+        lp = _i32(localPoint)
+        gp = np.ascontiguousarray(globalPoint, dtype=np.int64)
+        self._ck(lib().tcif_laser_set_shared_points(self.h, len(lp), _i(lp), gp.ctypes.data_as(C.POINTER(C.c_int64))))
+
     def laser_set_reflection(self, models, alphaCut=0.5):
         arr = (ReflectionModel * max(len(models), 1))()
         for i, md in enumerate(models):

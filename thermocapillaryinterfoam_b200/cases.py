@@ -266,3 +266,34 @@ def laser_seeds(lPosition, lDir, rArea, nr, nTheta, focalLaserRadius, maxTrackLe
         raise ValueError(mode)
     dA = ((r2 ** 2 - r1 ** 2)[:, None] * (th2 - th1)[None, :] / 2.0)
     return p0, p1, np.repeat(Ip, nTheta), dA.reshape(-1)
+
+
+def box_block_polymesh(n, xs, ys, zs, procs, rank, mesh) -> dict:
+    """box_polymesh of processor sub-mesh `rank` of the `simple procs` decomposition (mesh: that sub-mesh), plus
+    what tcif_laser_set_shared_points needs: the local points on processor patches and their global labels."""
+    co = (np.asarray(xs, np.float64), np.asarray(ys, np.float64), np.asarray(zs, np.float64))
+    b = (rank % procs[0], (rank // procs[0]) % procs[1], rank // (procs[0] * procs[1]))
+    lo, sub = [], []
+    for d in range(3):
+        own = np.nonzero(np.arange(n[d]) * procs[d] // n[d] == b[d])[0]
+        lo.append(int(own[0]))
+        sub.append(co[d][own[0]:own[-1] + 2])
+    geom = box_polymesh(mesh, *sub)
+    nvx, nvy = len(sub[0]), len(sub[1])
+    pid = np.arange(len(geom["points"]))
+    i, j, k = pid % nvx, (pid // nvx) % nvy, pid // (nvx * nvy)
+    gid = (i + lo[0]) + (n[0] + 1) * ((j + lo[1]) + (n[1] + 1) * (k + lo[2]))
+    nIF = len(np.asarray(mesh.owner))
+    fp = geom["fpPts"].reshape(-1, 4)
+    shared = []
+    for p in range(len(mesh.patchType)):
+        if mesh.patchType[p] == 3:
+            s, e = int(mesh.patchStart[p]), int(mesh.patchStart[p] + mesh.patchSize[p])
+            shared.append(fp[nIF + s:nIF + e].reshape(-1))
+    shared = np.unique(np.concatenate(shared)) if shared else np.zeros(0, np.int64)
+    geom["sharedLocal"] = shared.astype(np.int32)
+    geom["sharedGlobal"] = gid[shared].astype(np.int64)
+    geom["pointGlobal"] = gid.astype(np.int64)
+    ext = np.array([co[d][-1] - co[d][0] for d in range(3)])
+    geom["boundsMag"] = float(np.sqrt(np.dot(ext, ext)))          # mesh.bounds() is global (reduced over ranks)
+    return geom

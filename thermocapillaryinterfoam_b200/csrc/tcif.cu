@@ -24,6 +24,7 @@
 #include <stdexcept>
 #include <string>
 #include <type_traits>
+#include <unordered_map>
 #include <vector>
 #include <map>
 
@@ -113,6 +114,7 @@ struct tcif_group {
     long generation = 0;
     std::vector<tcif_ctx *> members;
     std::vector<double> red;     // n * 16 doubles
+    std::vector<const double *> gatherPtr;   // n pointers (allgather_host)
     void barrier() {
         std::unique_lock<std::mutex> lk(mu);
         long gen = generation;
@@ -199,6 +201,22 @@ struct tcif_ctx {
     double *lzNHat = nullptr, *lzNHatPts = nullptr, *lzQ = nullptr;
     LaserPart *lzCloud = nullptr;
     int lzCap = 0, lzParticles = 0, lzGenerations = 0;
+    // decomposed runs: point weights kept on the host for the global normalisation, shared points, mailboxes
+    std::vector<double> lzPwRaw;
+    std::vector<int> lzPcStart;
+    std::vector<unsigned char> lzIsPatch;
+    double *lzPw = nullptr;
+    unsigned char *lzIsPatchDev = nullptr;
+    int lzNShared = 0, lzMaxShared = 0;
+    bool lzSharedSet = false;
+    int *lzSharedPts = nullptr;
+    double *lzSharedBuf = nullptr;
+    std::vector<std::vector<int>> lzSharedSrc;      // per shared point: indices rank*maxShared + j of its copies (all ranks)
+    LaserPart *lzOutbox = nullptr, *lzInbox = nullptr;
+    int lzMailCap = 0;
+    int *lzPatchInfo = nullptr;
+    double lzDeltaN = 0.0;
+    long long lzCreated = 0;
     // F is a pure function of (alpha, T, sigma): the solver evaluates it 2-4x per time step on unchanged
     // fields (UEqn.H:29, pEqn.H:35 per corrector, thermocapillaryInterFoam.C:150); fieldsVersion counts
     // every change of those inputs and forceVersion remembers which one F was computed from
@@ -506,6 +524,31 @@ void allreduce_host(tcif_ctx *c, double *v, const int *ops, int n) {
             }
             v[i] = r;
         }
+    }
+}
+
+// all-gather of n doubles per rank (same n everywhere) into all[rank*n + i]; host buffers
+void allgather_host(tcif_ctx *c, const double *send, int n, std::vector<double> &all) {
+    all.resize((size_t)c->nRanks * std::max(n, 0));
+    if (n <= 0) return;
+    if (c->group) {
+        tcif_group *g = c->group;
+        g->barrier();
+        g->gatherPtr[c->rank] = send;
+        g->barrier();
+        for (int r = 0; r < g->n; ++r) memcpy(&all[(size_t)r * n], g->gatherPtr[r], sizeof(double) * n);
+        g->barrier();
+    } else if (c->nccl) {
+        double *ds = nullptr, *dr = nullptr;
+        CUDA_OK(cudaMalloc((void **)&ds, sizeof(double) * n));
+        CUDA_OK(cudaMalloc((void **)&dr, sizeof(double) * n * c->nRanks));
+        CUDA_OK(cudaMemcpyAsync(ds, send, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+        NCCL_OK(g_nccl.AllGather(ds, dr, n, kNcclDouble, c->nccl, c->stream));
+        CUDA_OK(cudaMemcpyAsync(all.data(), dr, sizeof(double) * n * c->nRanks, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        CUDA_OK(cudaFree(ds)); CUDA_OK(cudaFree(dr));
+    } else {
+        memcpy(all.data(), send, sizeof(double) * n);
     }
 }
 
@@ -1534,6 +1577,7 @@ void do_laser_set_polymesh(tcif_ctx *c, const double *Cf, const double *Cfb, int
             else tmp[fill[p]++] = fc[f - nIF];
         }
     std::vector<int> pcStart(nPoints + 1), pc;
+    c->lzPwRaw.clear();
     std::vector<double> pw;
     pc.reserve(tmp.size() / 2); pw.reserve(tmp.size() / 2);
     for (int p = 0; p < nPoints; ++p) {
@@ -1550,6 +1594,7 @@ void do_laser_set_polymesh(tcif_ctx *c, const double *Cf, const double *Cfb, int
             sum += w;
         }
         for (size_t i = first; i < pc.size(); ++i) pw[i] /= sum;
+        c->lzPwRaw.push_back(sum);           // local sum of the raw weights of point p
     }
     pcStart[nPoints] = (int)pc.size();
     std::vector<unsigned char> isPatch(nPoints, 0);
@@ -1560,36 +1605,138 @@ void do_laser_set_polymesh(tcif_ctx *c, const double *Cf, const double *Cfb, int
             for (int j = fpStart[f]; j < fpStart[f + 1]; ++j) isPatch[fpPts[j]] = 1;
         }
     }
-    g.pcStart = c->upload(pcStart); g.pc = c->upload(pc); g.pw = c->upload(pw); g.isPatchPoint = c->upload(isPatch);
+    g.pcStart = c->upload(pcStart); g.pc = c->upload(pc);
+    c->lzPw = c->upload(pw); c->lzIsPatchDev = c->upload(isPatch);
+    g.pw = c->lzPw; g.isPatchPoint = c->lzIsPatchDev;
+    c->lzPcStart = pcStart; c->lzIsPatch = isPatch;
+    {
+        std::vector<int> info(2 * (size_t)std::max(c->nPatches, 1), -1);
+        for (int pa = 0; pa < c->nPatches; ++pa) info[2 * pa + 1] = c->patchStart[pa];
+        for (size_t i = 0; i < c->cpPatch.size(); ++i) info[2 * c->cpPatch[i]] = (int)i;
+        c->lzPatchInfo = c->upload(info);
+    }
+    c->lzSharedSet = false;
     c->lzRefl = c->dalloc<int>(nC);
     c->lzNHat = c->dalloc<double>(3 * (size_t)c->stride);
     c->lzNHatPts = c->dalloc<double>(3 * (size_t)nPoints);
     c->lzQ = c->dalloc<double>(nC);
-    c->lzCounters = c->dalloc<int>(4);
+    c->lzCounters = c->dalloc<int>(4 + 64);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     c->laserGeoSet = true;
 }
 
+// Points on processor patches are shared by ranks: volPointInterpolation sums weights and weighted values over
+// all ranks holding the point (syncUntransformedData with plusEqOp).  The solver hands over the global label of
+// every such local point (globalMeshData); collective over the ranks.
+void do_laser_set_shared_points(tcif_ctx *c, int nShared, const int32_t *localPoint, const int64_t *globalPoint) {
+    if (!c->laserGeoSet) failf("tcif_laser_set_shared_points: call tcif_laser_set_polymesh first");
+    if (nShared < 0 || (nShared && (!localPoint || !globalPoint))) failf("tcif_laser_set_shared_points: bad arguments");
+    require_comm(c);
+    const int nPoints = c->lg.nPoints;
+    for (int i = 0; i < nShared; ++i) if (localPoint[i] < 0 || localPoint[i] >= nPoints) failf("tcif_laser_set_shared_points: local point out of range");
+    double mx[1] = {(double)nShared};
+    { int ops[1] = {RED_MAX}; allreduce_host(c, mx, ops, 1); }
+    const int maxS = (int)mx[0];
+    c->lzNShared = nShared; c->lzMaxShared = maxS;
+    c->lzSharedSrc.assign(nShared, {});
+    if (maxS > 0) {
+        // (global label, local sum of raw weights, on-a-patch flag) of every shared point of every rank
+        std::vector<double> mine(3 * (size_t)maxS, -1.0), all;
+        for (int i = 0; i < nShared; ++i) {
+            mine[3 * i] = (double)globalPoint[i];
+            mine[3 * i + 1] = c->lzPwRaw[localPoint[i]];
+            mine[3 * i + 2] = c->lzIsPatch[localPoint[i]] ? 1.0 : 0.0;
+        }
+        allgather_host(c, mine.data(), 3 * maxS, all);
+        std::unordered_map<long long, int> idx;
+        for (int i = 0; i < nShared; ++i) idx[(long long)globalPoint[i]] = i;
+        std::vector<double> sumW(nShared, 0.0);
+        std::vector<int> flag(nShared, 0);
+        for (int r = 0; r < c->nRanks; ++r)
+            for (int j = 0; j < maxS; ++j) {
+                const double id = all[((size_t)r * maxS + j) * 3];
+                if (id < 0) continue;
+                auto it = idx.find((long long)id);
+                if (it == idx.end()) continue;
+                c->lzSharedSrc[it->second].push_back(r * maxS + j);
+                sumW[it->second] += all[((size_t)r * maxS + j) * 3 + 1];
+                if (all[((size_t)r * maxS + j) * 3 + 2] > 0) flag[it->second] = 1;
+            }
+        // renormalise the weights of the shared points by the global sum, OR the patch flags
+        std::vector<double> pw(c->lzPcStart[nPoints]);
+        CUDA_OK(cudaMemcpy(pw.data(), c->lzPw, sizeof(double) * pw.size(), cudaMemcpyDeviceToHost));
+        for (int i = 0; i < nShared; ++i) {
+            const int p = localPoint[i];
+            const double f = c->lzPwRaw[p] / sumW[i];
+            for (int k = c->lzPcStart[p]; k < c->lzPcStart[p + 1]; ++k) pw[k] *= f;
+            c->lzPwRaw[p] = sumW[i];
+            if (flag[i]) c->lzIsPatch[p] = 1;
+        }
+        CUDA_OK(cudaMemcpy(c->lzPw, pw.data(), sizeof(double) * pw.size(), cudaMemcpyHostToDevice));
+        CUDA_OK(cudaMemcpy(c->lzIsPatchDev, c->lzIsPatch.data(), nPoints, cudaMemcpyHostToDevice));
+        c->lzSharedPts = c->upload(std::vector<int>(localPoint, localPoint + nShared));
+        c->lzSharedBuf = c->dalloc<double>(3 * (size_t)std::max(nShared, 1));
+    }
+    c->lzSharedSet = true;
+}
+
+// sum the partial point values of the shared points over the ranks, in rank order on every rank
+void laser_sync_points(tcif_ctx *c) {
+    const int nS = c->lzNShared, maxS = c->lzMaxShared;
+    if (maxS == 0) return;
+    std::vector<double> mine(3 * (size_t)maxS, 0.0), all;
+    if (nS) {
+        k_laser_points_gather<<<cdiv(nS, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(nS, c->lzSharedPts, c->lzNHatPts, c->lzSharedBuf);
+        c->launches++;
+        CUDA_OK(cudaMemcpyAsync(mine.data(), c->lzSharedBuf, sizeof(double) * 3 * nS, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+    }
+    allgather_host(c, mine.data(), 3 * maxS, all);
+    if (!nS) return;
+    for (int i = 0; i < nS; ++i)
+        for (int d = 0; d < 3; ++d) {
+            double v = 0.0;
+            for (int src : c->lzSharedSrc[i]) v += all[(size_t)src * 3 + d];
+            mine[3 * i + d] = v;
+        }
+    CUDA_OK(cudaMemcpyAsync(c->lzSharedBuf, mine.data(), sizeof(double) * 3 * nS, cudaMemcpyHostToDevice, c->stream));
+    k_laser_points_scatter<<<cdiv(nS, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(nS, c->lzSharedPts, c->lzSharedBuf, c->lzNHatPts);
+    c->launches++;
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+}
+
 // laserDTRM::calculate(): mark the reflecting cells, interpolate nHat to the points, walk the cloud generation by
-// generation (reflected particles are appended by the walk), Q /= V
+// generation (reflected particles are appended by the walk, particles reaching a processor patch are handed to the
+// neighbour rank between generations), Q /= V
 int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const double *p1, const double *I, const double *dA,
                        const int32_t *cell, double sigmaSB, int maxParticles) {
     if (!c->laserGeoSet) failf("tcif_laser_calculate: call tcif_laser_set_polymesh first");
     if (!c->haveT) failf("tcif_laser_calculate: temperature not set");
     if (!c->lzAbsFields && c->lzNAbs == 0) failf("tcif_laser_calculate: no absorption model set");
     if (nParticles < 0 || (nParticles && (!p0 || !p1 || !I || !dA || !cell))) failf("tcif_laser_calculate: bad arguments");
-    if (c->nCoupled > 0) failf("tcif_laser_calculate: processor patches are not supported by the device cell walk yet");
+    const int nCp = (int)c->cpPatch.size();
+    const bool par = c->nCoupled > 0;
+    if (par) {
+        require_comm(c);
+        if (!c->lzSharedSet) failf("tcif_laser_calculate: mesh has processor patches, call tcif_laser_set_shared_points first");
+        if (nCp > 64) failf("tcif_laser_calculate: more than 64 processor patches");
+    }
+    if (c->lzDeltaN == 0.0) {
+        double v[2] = {c->sumV, (double)c->nC};
+        int ops[2] = {RED_SUM, RED_SUM};
+        if (c->nRanks > 1) allreduce_host(c, v, ops, 2);
+        c->lzDeltaN = 1e-7 / cbrt(v[0] / v[1]);                                        // laserDTRM.C:121-125
+    }
     LaserArgs a{};
     a.nModels = (int)c->lzModels.size(); a.P = c->P;
     for (int i = 0; i < a.nModels; ++i) a.models[i] = c->lzModels[i];
-    a.alphaCut = c->lzAlphaCut; a.sigmaSB = sigmaSB;
-    a.deltaN = 1e-7 / cbrt(c->sumV / (double)c->nC);                                   // laserDTRM.C:121-125
+    a.alphaCut = c->lzAlphaCut; a.sigmaSB = sigmaSB; a.deltaN = c->lzDeltaN;
     for (int p = 0; p < c->P; ++p) a.alpha[p] = c->alpha[p];
     a.refl = c->lzRefl; a.nHat = c->lzNHat; a.nHatPts = c->lzNHatPts; a.Q = c->lzQ; a.T = c->Tc;
     a.nAbs = c->lzNAbs;
     for (int i = 0; i < c->lzNAbs; ++i) { a.absPhase[i] = c->lzAbsPhase[i]; a.aCoeff[i] = c->lzA[i]; a.eCoeff[i] = c->lzE[i]; a.ECoeff[i] = c->lzEE[i]; }
     if (c->lzAbsFields) { a.aF = c->lzAF; a.eF = c->lzAF + c->stride; a.EF = c->lzAF + 2 * (size_t)c->stride; }
-    // the seeds that found a cell (laserDTRM.C:287-296)
+    // the seeds that found a cell on this rank (laserDTRM.C:287-296)
     std::vector<LaserPart> seeds;
     seeds.reserve(nParticles);
     for (int k = 0; k < nParticles; ++k) {
@@ -1601,15 +1748,29 @@ int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const doub
         seeds.push_back(q);
     }
     const int nSeeds = (int)seeds.size();
-    const int cap = std::max(maxParticles > 0 ? maxParticles : 64 * std::max(nSeeds, 1), nSeeds);
+    // on a decomposed mesh any rank may end up walking every ray: capacity from the full seed list
+    const int base = par ? std::max(nParticles, 1) : std::max(nSeeds, 1);
+    const int cap = std::max(maxParticles > 0 ? maxParticles : 64 * base, nSeeds);
     if (cap > c->lzCap) {
         if (c->lzCloud) CUDA_OK(cudaFree(c->lzCloud));
+        c->lzCloud = nullptr; c->lzCap = 0;
         CUDA_OK(cudaMalloc((void **)&c->lzCloud, sizeof(LaserPart) * (size_t)cap));
         c->lzCap = cap;
     }
+    const int mailCap = par ? std::max(4 * nParticles, 1024) : 0;
+    if (par && mailCap > c->lzMailCap) {
+        if (c->lzOutbox) CUDA_OK(cudaFree(c->lzOutbox));
+        if (c->lzInbox) CUDA_OK(cudaFree(c->lzInbox));
+        c->lzOutbox = c->lzInbox = nullptr; c->lzMailCap = 0;
+        CUDA_OK(cudaMalloc((void **)&c->lzOutbox, sizeof(LaserPart) * (size_t)mailCap * nCp));
+        CUDA_OK(cudaMalloc((void **)&c->lzInbox, sizeof(LaserPart) * (size_t)mailCap * nCp));
+        c->lzMailCap = mailCap;
+    }
     a.cloud = c->lzCloud; a.cap = cap; a.counters = c->lzCounters;
+    a.outbox = par ? c->lzOutbox : nullptr; a.mailCap = c->lzMailCap; a.patchInfo = c->lzPatchInfo;
     if (nSeeds) CUDA_OK(cudaMemcpyAsync(c->lzCloud, seeds.data(), sizeof(LaserPart) * nSeeds, cudaMemcpyHostToDevice, c->stream));
-    int cnt[4] = {nSeeds, 0, 0, 0};
+    int cnt[4 + 64] = {0};
+    cnt[0] = nSeeds;
     CUDA_OK(cudaMemcpyAsync(c->lzCounters, cnt, sizeof(cnt), cudaMemcpyHostToDevice, c->stream));
     CUDA_OK(cudaMemsetAsync(c->lzQ, 0, sizeof(double) * c->nC, c->stream));
     if (a.nModels) { do_grad(c); a.G = c->G; }
@@ -1618,23 +1779,95 @@ int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const doub
         k_laser_points<<<cdiv(c->lg.nPoints, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->lg, c->lzNHat, c->lzNHatPts);
         c->launches += 2;
     });
+    if (par) laser_sync_points(c);
     int done = 0, total = nSeeds, generations = 0;
-    while (done < total) {
-        timed(c, T_LASER, 0.0, [&] {
-            k_laser_move<<<cdiv(total - done, 128), 128, 0, c->stream>>>(c->dm, c->lg, a, done, total);
-            c->launches++;
-        });
-        CUDA_OK(cudaMemcpyAsync(cnt, c->lzCounters, sizeof(int) * 2, cudaMemcpyDeviceToHost, c->stream));
+    long long created = nSeeds;
+    std::string error;
+    for (;;) {
+        if (total > done) {
+            timed(c, T_LASER, 0.0, [&] {
+                k_laser_move<<<cdiv(total - done, 128), 128, 0, c->stream>>>(c->dm, c->lg, a, done, total);
+                c->launches++;
+            });
+        }
+        CUDA_OK(cudaMemcpyAsync(cnt, c->lzCounters, sizeof(int) * (4 + nCp), cudaMemcpyDeviceToHost, c->stream));
         CUDA_OK(cudaStreamSynchronize(c->stream));
-        if (cnt[1] == LASER_ERR_PROCESSOR) failf("tcif_laser_calculate: a particle reached a processor patch");
-        if (cnt[1] == LASER_ERR_OVERFLOW || cnt[0] > cap) failf("tcif_laser_calculate: cloud overflow (more than %d particles), raise maxParticles", cap);
-        done = total; total = cnt[0];
-        if (++generations > 10000) failf("tcif_laser_calculate: reflection cascade does not end");
+        if (cnt[1] == LASER_ERR_PROCESSOR) error = "a particle reached a processor patch of a context without mailboxes";
+        if (cnt[1] == LASER_ERR_OVERFLOW || cnt[0] > cap) error = "cloud overflow, raise maxParticles";
+        created += cnt[0] - total;
+        done = total; total = std::min(cnt[0], cap);
+        if (++generations > 10000) error = "reflection cascade does not end";
+        if (!par) {
+            if (!error.empty()) failf("tcif_laser_calculate: %s (capacity %d)", error.c_str(), cap);
+            if (done == total) break;
+            continue;
+        }
+        // hand-over: every rank learns how many particles each rank sends to each rank, who failed, who still has work
+        std::vector<double> mine(c->nRanks + 2, 0.0), all;
+        for (int i = 0; i < nCp; ++i) mine[c->patchNbr[c->cpPatch[i]]] += cnt[4 + i];
+        mine[c->nRanks] = error.empty() ? 0.0 : 1.0;
+        mine[c->nRanks + 1] = total - done;
+        allgather_host(c, mine.data(), c->nRanks + 2, all);
+        const int W = c->nRanks + 2;
+        bool anyErr = false;
+        double pending = 0.0;
+        for (int r = 0; r < c->nRanks; ++r) {
+            anyErr = anyErr || all[(size_t)r * W + c->nRanks] != 0.0;
+            pending += all[(size_t)r * W + c->nRanks + 1];
+            for (int e = 0; e < c->nRanks; ++e) pending += all[(size_t)r * W + e];
+        }
+        if (anyErr) failf("tcif_laser_calculate: %s", error.empty() ? "another rank failed" : error.c_str());
+        if (pending == 0.0) break;
+        std::vector<int> inCount(nCp, 0);
+        for (int i = 0; i < nCp; ++i) inCount[i] = (int)all[(size_t)c->patchNbr[c->cpPatch[i]] * W + c->rank];
+        if (c->group) {
+            tcif_group *g = c->group;
+            g->barrier();
+            for (int i = 0; i < nCp; ++i) {
+                if (!inCount[i]) continue;
+                tcif_ctx *o = g->members[c->patchNbr[c->cpPatch[i]]];
+                int peer = -1;
+                for (size_t j = 0; j < o->cpPatch.size(); ++j) if (o->patchNbr[o->cpPatch[j]] == c->rank) { peer = (int)j; break; }
+                if (peer < 0) failf("tcif_laser_calculate: neighbour rank has no patch facing this rank");
+                CUDA_OK(cudaMemcpyAsync(c->lzInbox + (size_t)i * c->lzMailCap, o->lzOutbox + (size_t)peer * o->lzMailCap,
+                                        sizeof(LaserPart) * inCount[i], cudaMemcpyDeviceToDevice, c->stream));
+            }
+            CUDA_OK(cudaStreamSynchronize(c->stream));
+            g->barrier();
+        } else {
+            static_assert(sizeof(LaserPart) % sizeof(double) == 0, "LaserPart is sent as doubles");
+            const size_t dpp = sizeof(LaserPart) / sizeof(double);
+            NCCL_OK(g_nccl.GroupStart());
+            for (int i = 0; i < nCp; ++i) {
+                const int e = c->patchNbr[c->cpPatch[i]];
+                if (cnt[4 + i]) NCCL_OK(g_nccl.Send(c->lzOutbox + (size_t)i * c->lzMailCap, cnt[4 + i] * dpp, kNcclDouble, e, c->nccl, c->stream));
+                if (inCount[i]) NCCL_OK(g_nccl.Recv(c->lzInbox + (size_t)i * c->lzMailCap, inCount[i] * dpp, kNcclDouble, e, c->nccl, c->stream));
+            }
+            NCCL_OK(g_nccl.GroupEnd());
+        }
+        int got = 0;
+        for (int i = 0; i < nCp; ++i) got += inCount[i];
+        if (total + got > cap) failf("tcif_laser_calculate: cloud overflow on hand-over, raise maxParticles (capacity %d)", cap);
+        for (int i = 0; i < nCp; ++i) {
+            if (!inCount[i]) continue;
+            k_laser_receive<<<cdiv(inCount[i], TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->lg, inCount[i], c->lzInbox + (size_t)i * c->lzMailCap,
+                                                                                c->patchStart[c->cpPatch[i]], c->lzCloud + total, c->lzCounters);
+            c->launches++;
+            total += inCount[i];
+        }
+        // reflected particles located here on behalf of a neighbour count as created on this rank
+        CUDA_OK(cudaMemcpyAsync(cnt, c->lzCounters, sizeof(int) * 4, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+        created += cnt[2];
+        cnt[0] = total; cnt[1] = 0; cnt[2] = 0;
+        for (int i = 0; i < nCp; ++i) cnt[4 + i] = 0;
+        CUDA_OK(cudaMemcpyAsync(c->lzCounters, cnt, sizeof(int) * (4 + nCp), cudaMemcpyHostToDevice, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
     }
     k_laser_finish<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nC, c->dm.V, c->lzQ);
     c->launches++;
-    c->lzParticles = total; c->lzGenerations = generations;
-    return total;
+    c->lzParticles = total; c->lzGenerations = generations; c->lzCreated = created;
+    return (int)created;
 }
 
 }  // namespace
@@ -1731,6 +1964,8 @@ void tcif_destroy(tcif_ctx *c) {
     for (auto &e : c->evPool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (void *p : c->allocs) cudaFree(p);
     if (c->lzCloud) cudaFree(c->lzCloud);
+    if (c->lzOutbox) cudaFree(c->lzOutbox);
+    if (c->lzInbox) cudaFree(c->lzInbox);
     if (c->h_small) cudaFreeHost(c->h_small);
     if (c->sIn) cudaStreamDestroy(c->sIn);
     if (c->sOut) cudaStreamDestroy(c->sOut);
@@ -1814,6 +2049,7 @@ int tcif_group_create(int nRanks, tcif_group **out) {
     if (!out || nRanks < 1) return 1;
     tcif_group *g = new tcif_group();
     g->n = nRanks; g->members.assign(nRanks, nullptr); g->red.assign((size_t)nRanks * 16, 0.0);
+    g->gatherPtr.assign(nRanks, nullptr);
     *out = g;
     return 0;
 }
@@ -2138,6 +2374,12 @@ int tcif_laser_get(tcif_ctx *c, double *Q, int32_t *reflectingCells, double *nHa
 }
 
 int tcif_laser_generations(const tcif_ctx *c) { return c ? c->lzGenerations : -1; }
+
+int tcif_laser_set_shared_points(tcif_ctx *c, int32_t nShared, const int32_t *localPoint, const int64_t *globalPoint) {
+    API_BEGIN(c)
+    do_laser_set_shared_points(c, nShared, localPoint, globalPoint);
+    API_END(c)
+}
 
 int tcif_div_capillary_stress(tcif_ctx *c) {
     API_BEGIN(c)

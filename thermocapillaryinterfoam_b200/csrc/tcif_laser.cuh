@@ -59,7 +59,11 @@ struct LaserArgs {
     const double *T;
     double *Q;
     LaserPart *cloud;
-    int *counters;                      // [0] particles in the cloud, [1] error code
+    int *counters;                      // [0] particles in the cloud, [1] error code, [4 + i] outbox fill of coupled patch i
+    // processor patches: a particle reaching one is handed to the neighbour rank (hitProcessorPatch, DTRMParticle.C:268-275)
+    LaserPart *outbox;                  // [nCoupledPatches * mailCap], null on a single domain
+    int mailCap;
+    const int *patchInfo;               // [nPatches*2]: coupled-patch slot (-1: none), first boundary face of the patch
 };
 
 __device__ __forceinline__ double l_dot(const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
@@ -147,7 +151,7 @@ template <class Fn> __device__ __forceinline__ void l_for_faces(const DMesh &m, 
 
 // particle::trackToAndHitFace as a walk over the face planes; returns an error code or 0
 __device__ int l_track(const DMesh &m, const LaserGeo &g, LaserPart &p, const double disp[3], double f) {
-    if (!p.keep) return 0;
+    if (p.keep != 1) return 0;
     double lam = TCIF_VGREAT;
     int hit = -1, other = -1;
     l_for_faces(m, g, p.cell, [&](int F, double sg, int oc) {
@@ -174,25 +178,31 @@ __device__ int l_track(const DMesh &m, const LaserGeo &g, LaserPart &p, const do
     p.face = hit;
     if (hit < m.nFd) p.cell = other;
     else {
-        if (m.bfType[hit - m.nFd] == PATCH_PROCESSOR) return LASER_ERR_PROCESSOR;
-        p.keep = 0;         // hitWallPatch (DTRMParticle.C:278-285); other non-coupled patches remove it as well
+        // hitProcessorPatch: switchProcessor (DTRMParticle.C:268-275); hitWallPatch (:278-285) and the other
+        // non-coupled patches remove the particle
+        p.keep = m.bfType[hit - m.nFd] == PATCH_PROCESSOR ? 2 : 0;
     }
     return 0;
 }
 
-// mesh.findCell for the reflected particle: walk from cell c through the first violated face plane
-__device__ int l_walk_find(const DMesh &m, const LaserGeo &g, int c, const double pt[3]) {
+// mesh.findCell for the reflected particle: walk from cell c through the first violated face plane.
+// -1: outside the mesh; *procFace = boundary face when the walk stopped at a processor patch
+__device__ int l_walk_find(const DMesh &m, const LaserGeo &g, int c, const double pt[3], int *procFace) {
+    *procFace = -1;
     for (int step = 0; step < 1000; ++step) {
-        int next = -2;
+        int next = -2, via = -1;
         l_for_faces(m, g, c, [&](int F, double sg, int oc) {
             double S[3], Cf[3];
             l_face_geom(m, g, F, S, Cf);
             const double d[3] = {pt[0] - Cf[0], pt[1] - Cf[1], pt[2] - Cf[2]};
-            if (sg * l_dot(d, S) > 0) { next = oc; return true; }
+            if (sg * l_dot(d, S) > 0) { next = oc; via = F; return true; }
             return false;
         });
         if (next == -2) return c;
-        if (next < 0) return -1;
+        if (next < 0) {
+            if (m.bfType[via - m.nFd] == PATCH_PROCESSOR) *procFace = via - m.nFd;
+            return -1;
+        }
         c = next;
     }
     return -1;
@@ -344,6 +354,7 @@ k_laser_move(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g
     if (ip >= last) return;
     const double pi = 3.14159265358979323846;
     LaserPart p = a.cloud[ip];
+    if (p.keep != 1) return;            // a received particle whose insertion point was not found on this rank
     int err = 0;
     do {
         const double pos0[3] = {p.pos[0], p.pos[1], p.pos[2]};
@@ -393,11 +404,10 @@ k_laser_move(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g
                     const double delaM = cbrt(m.V[cell1]);
                     double insertP[3];
                     for (int d = 0; d < 3; ++d) insertP[d] = p.pos[d] - pDir[d] * 0.1 * delaM;
-                    const int cellI = l_walk_find(m, g, cell1, insertP);
+                    int procFace;
+                    const int cellI = l_walk_find(m, g, cell1, insertP, &procFace);
                     // noReflection: R() = 0 and rho = 0, the new particle would deposit exactly nothing
-                    if (cellI > -1 && r.kind != REFL_NONE) {
-                        const int slot = atomicAdd(a.counters, 1);
-                        if (slot >= a.cap) { err = LASER_ERR_OVERFLOW; break; }
+                    if ((cellI > -1 || (procFace >= 0 && a.outbox)) && r.kind != REFL_NONE) {
                         const double s2 = 2.0 * (-l_dot(pDir, nh));                   // R(i, n) = i + 2(-i & n) n
                         LaserPart q;
                         for (int d = 0; d < 3; ++d) {
@@ -406,7 +416,20 @@ k_laser_move(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g
                             q.p1[d] = insertP[d] + nd * g.boundsMag;                  // :196-198
                         }
                         q.I0 = q.I = p.I * rho; q.dA = p.dA; q.frac = 0; q.cell = cellI; q.tid = -1; q.face = -1; q.keep = 1;
-                        a.cloud[slot] = q;
+                        if (cellI > -1) {
+                            const int slot = atomicAdd(a.counters, 1);
+                            if (slot >= a.cap) { err = LASER_ERR_OVERFLOW; break; }
+                            a.cloud[slot] = q;
+                        } else {
+                            // the insertion point lies behind a processor patch: the neighbour rank locates it
+                            // (the reference's local findCell would drop the particle on a decomposed mesh only)
+                            const int pa = m.bfPatch[procFace], slot = a.patchInfo[2 * pa];
+                            const int k = atomicAdd(a.counters + 4 + slot, 1);
+                            if (k >= a.mailCap) { err = LASER_ERR_OVERFLOW; break; }
+                            q.keep = 3;
+                            q.face = procFace - a.patchInfo[2 * pa + 1];
+                            a.outbox[(size_t)slot * a.mailCap + k] = q;
+                        }
                     }
                 }
             }
@@ -422,9 +445,56 @@ k_laser_move(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g
             p.I = I1;
             if (p.I <= 0.01 * p.I0) { p.frac = 1.0; break; }
         }
-    } while (p.keep && p.frac < 1);
+    } while (p.keep == 1 && p.frac < 1);
+    if (!err && p.keep == 2 && p.frac < 1) {
+        // hand the live particle to the rank behind the patch; `face` carries its index within the patch
+        const int bf = p.face - m.nFd, pa = m.bfPatch[bf];
+        const int slot = a.outbox ? a.patchInfo[2 * pa] : -1;
+        if (slot < 0) err = LASER_ERR_PROCESSOR;
+        else {
+            const int k = atomicAdd(a.counters + 4 + slot, 1);
+            if (k >= a.mailCap) err = LASER_ERR_OVERFLOW;
+            else {
+                LaserPart q = p;
+                q.face = bf - a.patchInfo[2 * pa + 1];
+                a.outbox[(size_t)slot * a.mailCap + k] = q;
+            }
+        }
+    }
     if (err) atomicMax(a.counters + 1, err);
     a.cloud[ip] = p;
+}
+
+// particles received through a coupled patch: continue in the cell behind the same face of this rank; a reflected
+// particle still to be located (keep == 3) walks from that cell to its insertion point
+__global__ void k_laser_receive(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g, int n, const LaserPart *inbox,
+                                int patchStart, LaserPart *dst, int *counters) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    LaserPart q = inbox[i];
+    const int bf = patchStart + q.face;
+    if (q.keep == 3) {
+        int procFace;
+        q.cell = l_walk_find(m, g, m.faceCells[bf], q.pos, &procFace);
+        q.face = -1;
+        q.keep = q.cell >= 0 ? 1 : 0;
+        if (q.keep) atomicAdd(counters + 2, 1);
+        else q.frac = 1.0;
+    } else {
+        q.cell = m.faceCells[bf];
+        q.face = m.nFd + bf;
+        q.keep = 1;
+    }
+    dst[i] = q;
+}
+
+__global__ void k_laser_points_gather(int n, const int *pts, const double *pv, double *out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const int p = pts[i]; out[3 * i] = pv[3 * (size_t)p]; out[3 * i + 1] = pv[3 * (size_t)p + 1]; out[3 * i + 2] = pv[3 * (size_t)p + 2]; }
+}
+__global__ void k_laser_points_scatter(int n, const int *pts, const double *in, double *pv) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const int p = pts[i]; pv[3 * (size_t)p] = in[3 * i]; pv[3 * (size_t)p + 1] = in[3 * i + 1]; pv[3 * (size_t)p + 2] = in[3 * i + 2]; }
 }
 
 __global__ void k_laser_finish(int n, const double *V, double *Q) {
