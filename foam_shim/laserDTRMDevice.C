@@ -17,6 +17,9 @@
 #include "noReflection.H"
 #include "localDensityAbsorptionEmission.H"
 #include "physicoChemicalConstants.H"
+#include "globalIndex.H"
+#include "syncTools.H"
+#include "processorPolyPatch.H"
 #include "tcifFoamBridge.H"
 
 namespace Foam
@@ -53,6 +56,29 @@ void laserDTRM::registerDevice()
         ),
         "tcif_laser_set_polymesh"
     );
+
+    if (Pstream::parRun())
+    {
+        // points of the processor patches and their global labels: volPointInterpolation sums over the ranks
+        // sharing a point (syncUntransformedData); the device does the same sum with these labels
+        const globalIndex globalPoints(mesh_.nPoints());          // any labelling unique per physical point will do:
+        labelList gid(mesh_.nPoints());                           // here the minimum over the ranks holding the point
+        forAll(gid, p) { gid[p] = globalPoints.toGlobal(p); }
+        syncTools::syncPointList(mesh_, gid, minEqOp<label>(), labelMax);
+        bitSet onProc(mesh_.nPoints());
+        for (const polyPatch& pp : mesh_.boundaryMesh())
+        {
+            if (isA<processorPolyPatch>(pp)) { onProc.set(pp.meshPoints()); }
+        }
+        const labelList localPts(onProc.toc());
+        List<int64_t> globalPts(localPts.size());
+        forAll(localPts, i) { globalPts[i] = gid[localPts[i]]; }
+        dev.call
+        (
+            tcif_laser_set_shared_points(dev.ctx(), localPts.size(), localPts.cdata(), globalPts.cdata()),
+            "tcif_laser_set_shared_points"
+        );
+    }
 
     // reflections_ in iteration order = the reflectionModelId of calculate() (:596-650)
     List<tcif_reflection_model> models(reflections_.size());

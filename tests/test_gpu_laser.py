@@ -216,3 +216,78 @@ def test_decomposed_matches_serial_oracle(procs):
     for c in ctxs:
         c.close()
     grp.close()
+
+
+# ---- NCCL, one process per GPU: hand-over by ncclSend/ncclRecv, point sums and counts by ncclAllGather ---------------
+_NCCL_ABS = ((25.0, 10.0, 0.3), (0.1, 0.0, 0.0), (0.0, 0.0, 0.0))
+
+
+def _nccl_case(n):
+    spec = cases.case(5, n)
+    xs, ys, zs = (hm.vertices(spec.n[d], spec.lengths[d]) for d in range(3))
+    d = np.array([0.5, -1.0, 0.2]); d /= np.linalg.norm(d)
+    r = np.cross(d, [0.0, 0.0, 1.0]); r /= np.linalg.norm(r)
+    p0, p1, Ip, dA = cases.laser_seeds((0.3, 0.93, 0.45), d, r, 8, 16, 0.15, float(np.sqrt(3.0)), sigma=0.07, power=200.0)
+    return spec, (xs, ys, zs), (p0, p1, Ip, dA), cases.find_cells_box(spec.n, xs, ys, zs, p0)
+
+
+def _nccl_laser_worker(rank, world, n, out):
+    import os, time
+    spec, v, (p0, p1, Ip, dA), cellG = _nccl_case(n)
+    procs = hm.procs_for(world)
+    m = hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, rank)
+    f = cases.synthetic_fields(spec, m)
+    idfile = os.path.join(out, "nccl_id")
+    if rank == 0:
+        with open(idfile + ".tmp", "wb") as fh:
+            fh.write(abi.nccl_unique_id())
+        os.rename(idfile + ".tmp", idfile)
+    t0 = time.time()
+    while not os.path.exists(idfile):
+        if time.time() - t0 > 120:
+            raise RuntimeError("no NCCL id")
+        time.sleep(0.05)
+    ctx = abi.Context(m, spec.nPhases, device=rank)
+    ctx.comm_init_nccl(rank, world, open(idfile, "rb").read())
+    cases.load_case(ctx, spec, f)
+    ctx.set_cell_centres(f["C"], f["deltab"])
+    geom = cases.box_block_polymesh(spec.n, *v, procs, rank, m)
+    ctx.laser_set_polymesh(m.Cf, m.Cfb, geom)
+    ctx.laser_set_shared_points(geom["sharedLocal"], geom["sharedGlobal"])
+    ctx.laser_set_reflection(MODELS)
+    ctx.laser_set_local_density_absorption([0, 1, 2], *_NCCL_ABS)
+    gid = np.asarray(m.cellGlobal)
+    g2l = np.full(spec.nCells, -1, np.int32); g2l[gid] = np.arange(len(gid), dtype=np.int32)
+    Q, created = ctx.laser_calculate(p0, p1, Ip, dA, g2l[cellG])
+    np.savez(os.path.join(out, f"rank{rank}.npz"), Q=Q, created=np.array([created]), gid=gid)
+    ctx.close()
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_nccl_ranks_match_serial_oracle(world):
+    if abi.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import multiprocessing as mp
+    import os
+    import tempfile
+    n = 16
+    spec, v, (p0, p1, Ip, dA), cellG = _nccl_case(n)
+    g = mo.box_mesh(*spec.n, spec.lengths, spec.patch_types)
+    geomG = cases.box_polymesh(g, *v)
+    fg = cases.synthetic_fields(spec, g)
+    al = fg["alpha_i"]
+    ref = orc.laser_calculate(g, geomG, MODELS, al, fg["alpha_b"], fg["alphaBc"], *(orc.local_density(al, c) for c in _NCCL_ABS),
+                              fg["T_i"], p0, p1, Ip, dA, cellG)
+    ctxm = mp.get_context("spawn")
+    with tempfile.TemporaryDirectory() as out:
+        ps = [ctxm.Process(target=_nccl_laser_worker, args=(r, world, n, out)) for r in range(world)]
+        [p.start() for p in ps]
+        [p.join(timeout=500) for p in ps]
+        assert all(p.exitcode == 0 for p in ps), [p.exitcode for p in ps]
+        zs = [np.load(os.path.join(out, f"rank{r}.npz")) for r in range(world)]
+    assert sum(int(z["created"][0]) for z in zs) == ref["nParticles"]
+    scale = np.abs(ref["Q"]).max()
+    for r, z in enumerate(zs):
+        err = np.abs(z["Q"] - ref["Q"][z["gid"]]).max()
+        assert err <= 1e-10 * scale, f"Q rank {r}: {err:.3e} of {scale:.3e}"
