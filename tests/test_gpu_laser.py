@@ -291,3 +291,20 @@ def test_nccl_ranks_match_serial_oracle(world):
     for r, z in enumerate(zs):
         err = np.abs(z["Q"] - ref["Q"][z["gid"]]).max()
         assert err <= 1e-10 * scale, f"Q rank {r}: {err:.3e} of {scale:.3e}"
+
+
+def test_walk_table_and_ell_gathers_agree(monkeypatch):
+    """The per-cell face records (default) and the gathers through the ELL tables (TCIF_LASER_TABLE=0, also the path
+    of meshes with more than 8 faces per cell) walk the same faces in the same order."""
+    res = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("TCIF_LASER_TABLE", flag)
+        spec, m, v, geom, f, ctx = _setup()
+        ctx.laser_set_reflection(MODELS)
+        ctx.laser_set_local_density_absorption([0, 1, 2], (8.0, 4.0, 0.1), (0, 0, 0), (0, 0, 0))
+        p0, p1, Ip, dA, cell = _seeds(spec, v, geom, (0.5, 0.93, 0.5), (0.25, -1.0, 0.1))
+        res.append(ctx.laser_calculate(p0, p1, Ip, dA, cell))
+        ctx.close()
+    assert res[0][1] == res[1][1] > 128
+    _close(res[0][0], res[1][0], "Q table vs ELL", 1e-13)
+    assert np.array_equal(res[0][0] != 0, res[1][0] != 0)

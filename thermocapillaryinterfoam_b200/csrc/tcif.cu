@@ -1616,6 +1616,23 @@ void do_laser_set_polymesh(tcif_ctx *c, const double *Cf, const double *Cfb, int
         c->lzPatchInfo = c->upload(info);
     }
     c->lzSharedSet = false;
+    // walk table: one contiguous record of all face planes per cell (TCIF_LASER_TABLE=0 keeps the ELL gathers)
+    {
+        std::vector<int> nf(nC, 0);
+        for (int f = 0; f < nIF; ++f) { nf[faceMap[f] % c->stride]++; nf[nbrOwn[faceMap[f]]]++; }
+        for (int b = 0; b < nBF; ++b) nf[fc[b]]++;
+        int W = 0;
+        for (int i = 0; i < nC; ++i) W = std::max(W, nf[i]);
+        const char *e = getenv("TCIF_LASER_TABLE");
+        if (W > 0 && W <= 8 && nC < 0x40000000 && !(e && atoi(e) == 0)) {
+            double *wd = c->dalloc<double>((size_t)nC * W * 6, false);
+            int *wi = c->dalloc<int>((size_t)nC * W * 2, false);
+            k_laser_build_walk<<<cdiv(nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, g, W, wd, wi);
+            c->launches++;
+            CUDA_OK(cudaStreamSynchronize(c->stream));
+            g.W = W; g.wd = wd; g.wi = wi;
+        }
+    }
     c->lzRefl = c->dalloc<int>(nC);
     c->lzNHat = c->dalloc<double>(3 * (size_t)c->stride);
     c->lzNHatPts = c->dalloc<double>(3 * (size_t)nPoints);

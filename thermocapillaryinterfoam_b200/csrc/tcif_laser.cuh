@@ -42,6 +42,12 @@ struct LaserGeo {
     const double *pw;
     const unsigned char *isPatchPoint;
     double boundsMag;
+    // walk table (W > 0): per cell W face records in the walk's order - outward area vector and face centre
+    // [(c*W + j)*6 doubles], device face id and the cell behind it [(c*W + j)*2 ints, -1: padding / boundary]:
+    // one contiguous read per cell crossed instead of gathers through the ELL tables
+    int W;
+    const double *wd;
+    const int *wi;
 };
 
 struct LaserArgs {
@@ -133,20 +139,87 @@ __device__ __forceinline__ int l_mesh_face(const DMesh &m, const LaserGeo &g, in
     return F < m.nFd ? g.fdToFace[F] : g.nIF + (F - m.nFd);
 }
 
-// visits the faces of cell c in the oracle's order; fn(F, sign, otherCell) returns true to stop
-template <class Fn> __device__ __forceinline__ void l_for_faces(const DMesh &m, const LaserGeo &g, int c, Fn &&fn) {
+// visits the faces of cell c in the oracle's order; fn(F, sign, otherCell, Sout, Cf) returns true to stop.
+// Sout = sign*Sf points out of the cell (the sign is exact, so dot(x, Sout) == sign*dot(x, Sf) bit for bit).
+template <class Fn> __device__ __forceinline__ void l_for_faces_ell(const DMesh &m, const LaserGeo &g, int c, Fn &&fn) {
+    double S[3], Cf[3];
     for (int k = 0; k < m.Ko; ++k) {
         const int fd = k * m.stride + c, n = m.nbrOwn[fd];
-        if (n >= 0 && fn(fd, 1.0, n)) return;
+        if (n < 0) continue;
+        l_face_geom(m, g, fd, S, Cf);
+        if (fn(fd, 1.0, n, S, Cf)) return;
     }
     for (int k = 0; k < m.Kn; ++k) {
         const int fd = m.neiFace[k * m.stride + c];
-        if (fd >= 0 && fn(fd, -1.0, owner_of(m, fd))) return;
+        if (fd < 0) continue;
+        l_face_geom(m, g, fd, S, Cf);
+        S[0] = -S[0]; S[1] = -S[1]; S[2] = -S[2];
+        if (fn(fd, -1.0, owner_of(m, fd), S, Cf)) return;
     }
     const int bi = g.bndIdx[c];
     if (bi >= 0)
-        for (int j = m.bndCellStart[bi]; j < m.bndCellStart[bi + 1]; ++j)
-            if (fn(m.nFd + m.bndFaces[j], 1.0, -1)) return;
+        for (int j = m.bndCellStart[bi]; j < m.bndCellStart[bi + 1]; ++j) {
+            const int F = m.nFd + m.bndFaces[j];
+            l_face_geom(m, g, F, S, Cf);
+            if (fn(F, 1.0, -1, S, Cf)) return;
+        }
+}
+
+template <int WW, class Fn> __device__ __forceinline__ void l_for_faces_table(const LaserGeo &g, int c, int W, Fn &&fn) {
+    const double2 *rd = reinterpret_cast<const double2 *>(g.wd + (size_t)c * W * 6);
+    const int2 *ri = reinterpret_cast<const int2 *>(g.wi + (size_t)c * W * 2);
+    if (WW > 0) {
+        double2 r[WW > 0 ? WW : 1][3];
+        int2 id[WW > 0 ? WW : 1];
+#pragma unroll
+        for (int j = 0; j < WW; ++j) { id[j] = ri[j]; r[j][0] = rd[3 * j]; r[j][1] = rd[3 * j + 1]; r[j][2] = rd[3 * j + 2]; }
+#pragma unroll
+        for (int j = 0; j < WW; ++j) {
+            if (id[j].x < 0) return;
+            const double S[3] = {r[j][0].x, r[j][0].y, r[j][1].x}, Cf[3] = {r[j][1].y, r[j][2].x, r[j][2].y};
+            const bool nei = (id[j].y & 0x40000000) != 0 && id[j].y >= 0;
+            if (fn(id[j].x, nei ? -1.0 : 1.0, nei ? (id[j].y & 0x3fffffff) : id[j].y, S, Cf)) return;
+        }
+    } else {
+        for (int j = 0; j < W; ++j) {
+            const int2 idj = ri[j];
+            if (idj.x < 0) return;
+            const double2 a = rd[3 * j], b = rd[3 * j + 1], cc = rd[3 * j + 2];
+            const double S[3] = {a.x, a.y, b.x}, Cf[3] = {b.y, cc.x, cc.y};
+            const bool nei = (idj.y & 0x40000000) != 0 && idj.y >= 0;
+            if (fn(idj.x, nei ? -1.0 : 1.0, nei ? (idj.y & 0x3fffffff) : idj.y, S, Cf)) return;
+        }
+    }
+}
+
+template <class Fn> __device__ __forceinline__ void l_for_faces(const DMesh &m, const LaserGeo &g, int c, Fn &&fn) {
+    if (g.W == 6) l_for_faces_table<6>(g, c, 6, fn);
+    else if (g.W > 0) l_for_faces_table<0>(g, c, g.W, fn);
+    else l_for_faces_ell(m, g, c, fn);
+}
+
+// fills the walk table of cell c (slot j: face j of the ELL enumeration; bit 30 of `other` marks a face seen from
+// its neighbour side, which interpolation in the cell's tets needs for the orientation of the face triangle)
+__global__ void __launch_bounds__(TCIF_TPB)
+k_laser_build_walk(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g, int W, double *wd, int *wi) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= m.nC) return;
+    int j = 0;
+    l_for_faces_ell(m, g, c, [&](int F, double sg, int oc, const double *S, const double *Cf) {
+        if (j < W) {
+            double *r = wd + ((size_t)c * W + j) * 6;
+            r[0] = S[0]; r[1] = S[1]; r[2] = S[2]; r[3] = Cf[0]; r[4] = Cf[1]; r[5] = Cf[2];
+            wi[((size_t)c * W + j) * 2] = F;
+            wi[((size_t)c * W + j) * 2 + 1] = (sg < 0 && oc >= 0) ? (oc | 0x40000000) : oc;
+        }
+        ++j;
+        return false;
+    });
+    for (; j < W; ++j) {
+        double *r = wd + ((size_t)c * W + j) * 6;
+        for (int k = 0; k < 6; ++k) r[k] = 0.0;
+        wi[((size_t)c * W + j) * 2] = -1; wi[((size_t)c * W + j) * 2 + 1] = -1;
+    }
 }
 
 // particle::trackToAndHitFace as a walk over the face planes; returns an error code or 0
@@ -154,13 +227,11 @@ __device__ int l_track(const DMesh &m, const LaserGeo &g, LaserPart &p, const do
     if (p.keep != 1) return 0;
     double lam = TCIF_VGREAT;
     int hit = -1, other = -1;
-    l_for_faces(m, g, p.cell, [&](int F, double sg, int oc) {
-        double S[3], Cf[3];
-        l_face_geom(m, g, F, S, Cf);
-        const double dn = sg * l_dot(disp, S);
+    l_for_faces(m, g, p.cell, [&](int F, double, int oc, const double *S, const double *Cf) {
+        const double dn = l_dot(disp, S);
         if (dn > 0) {
             const double d[3] = {Cf[0] - p.pos[0], Cf[1] - p.pos[1], Cf[2] - p.pos[2]};
-            double l = (sg * l_dot(d, S)) / dn;
+            double l = l_dot(d, S) / dn;
             if (l < 0) l = 0;
             if (l < lam) { lam = l; hit = F; other = oc; }
         }
@@ -191,11 +262,9 @@ __device__ int l_walk_find(const DMesh &m, const LaserGeo &g, int c, const doubl
     *procFace = -1;
     for (int step = 0; step < 1000; ++step) {
         int next = -2, via = -1;
-        l_for_faces(m, g, c, [&](int F, double sg, int oc) {
-            double S[3], Cf[3];
-            l_face_geom(m, g, F, S, Cf);
+        l_for_faces(m, g, c, [&](int F, double, int oc, const double *S, const double *Cf) {
             const double d[3] = {pt[0] - Cf[0], pt[1] - Cf[1], pt[2] - Cf[2]};
-            if (sg * l_dot(d, S) > 0) { next = oc; via = F; return true; }
+            if (l_dot(d, S) > 0) { next = oc; via = F; return true; }
             return false;
         });
         if (next == -2) return c;
@@ -284,7 +353,7 @@ __device__ void l_interp_in_cell(const DMesh &m, const LaserGeo &g, int c, const
     const double C[3] = {g.Cx[c], g.Cy[c], g.Cz[c]};
     double best = TCIF_VGREAT, bw[4] = {1, 0, 0, 0};
     int bv[3] = {0, 0, 0};
-    l_for_faces(m, g, c, [&](int F, double sg, int) {
+    l_for_faces(m, g, c, [&](int F, double sg, int, const double *, const double *) {
         const int f = l_mesh_face(m, g, F), n = g.fpStart[f + 1] - g.fpStart[f];
         for (int tp = 1; tp < n - 1; ++tp) {
             int v[3];
@@ -362,15 +431,7 @@ k_laser_move(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g
         const double f = 1 - p.frac;
         double disp[3];
         for (int d = 0; d < 3; ++d) disp[d] = f * (p.p1[d] - p.p0[d]);                 // :110-111
-        if ((err = l_track(m, g, p, disp, f))) break;
-        const double p1[3] = {p.pos[0], p.pos[1], p.pos[2]};
-        double dsv[3] = {p1[0] - pos0[0], p1[1] - pos0[1], p1[2] - pos0[2]};
-        double ds = l_mag(dsv);
-        if (ds == 0) {                                                                // :127-132
-            if ((err = l_track(m, g, p, disp, f))) break;
-            for (int d = 0; d < 3; ++d) dsv[d] = p1[d] - p.pos[d];
-            ds = l_mag(dsv);
-        }
+        // cell data first: these loads overlap the face records of the track
         const int zone = a.refl[cell1];
         double ac, ec, Ec;                                                            // interpolationCell of a, e, E, T
         if (a.aF) { ac = a.aF[cell1]; ec = a.eF[cell1]; Ec = a.EF[cell1]; }
@@ -383,6 +444,15 @@ k_laser_move(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g
         }
         const double Tc = a.T[cell1];
         const double emit = ec * a.sigmaSB * ((Tc * Tc) * (Tc * Tc)) / pi + Ec;
+        if ((err = l_track(m, g, p, disp, f))) break;
+        const double p1[3] = {p.pos[0], p.pos[1], p.pos[2]};
+        double dsv[3] = {p1[0] - pos0[0], p1[1] - pos0[1], p1[2] - pos0[2]};
+        double ds = l_mag(dsv);
+        if (ds == 0) {                                                                // :127-132
+            if ((err = l_track(m, g, p, disp, f))) break;
+            for (int d = 0; d < 3; ++d) dsv[d] = p1[d] - p.pos[d];
+            ds = l_mag(dsv);
+        }
         if (zone > -1 && (p.tid == -1 || p.tid != zone)) {                            // :139-146
             double rho = 0;
             if (p.I > 0.01 * p.I0 && ds > 0) {                                        // :151
