@@ -214,3 +214,38 @@ def test_cloud_overflow_is_reported():
     with pytest.raises(RuntimeError):
         orc.laser_calculate(m, geom, models, al, ab, np.ones((2, 6), np.int32), z + 1.0, z, z, z + 300, p0, p1, [1.0], [1.0],
                             cell, maxParticles=1)
+
+
+@pytest.mark.parametrize("procs", [(2, 1, 1), (2, 2, 1), (2, 2, 2)])
+def test_block_polymesh_and_shared_points_of_processor_sub_meshes(procs):
+    """Host side of the decomposed laser walk: every sub-mesh's points/faces reproduce its own geometry, the points of
+    processor patches carry global labels that at least two ranks hold, and all other points are private."""
+    spec = cases.case(5, 8)
+    xs, ys, zs = (hm.vertices(spec.n[d], spec.lengths[d], g) for d, g in enumerate((1.3, None, None)))
+    gm = mo.box_mesh(*spec.n, spec.lengths, spec.patch_types, (1.3, None, None))
+    geomG = cases.box_polymesh(gm, xs, ys, zs)
+    nd = procs[0] * procs[1] * procs[2]
+    holders = {}
+    for rk in range(nd):
+        m = hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, rk, grading=(1.3, None, None))
+        geom = cases.box_block_polymesh(spec.n, xs, ys, zs, procs, rk, m)
+        assert np.allclose(geom["points"], geomG["points"][geom["pointGlobal"]], atol=0)
+        P, fp = geom["points"], geom["fpPts"].reshape(-1, 4)
+        Cf = np.concatenate([m.Cf, m.Cfb]); Sf = np.concatenate([m.Sf, m.Sfb])
+        assert np.allclose(P[fp].mean(axis=1), Cf, atol=1e-14)
+        assert np.allclose(0.5 * np.cross(P[fp[:, 2]] - P[fp[:, 0]], P[fp[:, 3]] - P[fp[:, 1]]), Sf, atol=1e-15)
+        assert geom["boundsMag"] == geomG["boundsMag"]
+        assert np.array_equal(geom["pointGlobal"][geom["sharedLocal"]], geom["sharedGlobal"])
+        for gpt in geom["pointGlobal"]:
+            holders.setdefault(int(gpt), set()).add(rk)
+        geom_shared = set(int(x) for x in geom["sharedGlobal"])
+        for gpt in geom["pointGlobal"]:
+            holders.setdefault(("shared", int(gpt)), set())
+            if int(gpt) in geom_shared:
+                holders[("shared", int(gpt))].add(rk)
+    assert len([k for k in holders if not isinstance(k, tuple)]) == len(geomG["points"])
+    for k, ranks in holders.items():
+        if isinstance(k, tuple):
+            continue
+        # a point held by several ranks is declared shared by each of them, a private point by none
+        assert holders[("shared", k)] == (ranks if len(ranks) > 1 else set()), (k, ranks)
