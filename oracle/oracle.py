@@ -619,3 +619,35 @@ def laser_calculate(m, geom, models, alphas_i, alphas_b, alphaBc, a, e, E, T, p0
     if rc:
         raise RuntimeError(f"orc_laser_calculate failed: rc={rc}")
     return dict(Q=Q, reflectingCells=refl, nHat=nHat, nHatPoints=nPts, nParticles=nFinal.value)
+
+
+def laser_calculate_ranks(meshes, geoms, models, refl, nHat, pointGlobal, a, e, E, T, p0, p1, I, dA, cells, alphaCut=0.5,
+                          sigmaSB=SIGMA_SB, maxParticles=0):
+    """The decomposed laser walk with all ranks on one CPU (orc_laser_calculate_ranks).  Per-rank lists: meshes, geoms,
+    refl/nHat (the marking restricted to the rank's cells), pointGlobal, a/e/E/T, cells (local cell of each seed or -1).
+    Returns dict(Q=[...], created=[...], nHatPoints=[...])."""
+    R = len(meshes)
+    hs = [m if isinstance(m, MeshHandle) else MeshHandle(m) for m in meshes]
+    gs = [g if isinstance(g, LaserGeomHandle) else LaserGeomHandle(h.m, g) for h, g in zip(hs, geoms)]
+    arr = reflection_array(models)
+    n = len(I)
+    cfg = OrcLaserCfg(len(models), arr, float(alphaCut), float(sigmaSB), int(maxParticles or 64 * max(n, 1)))
+    mp = (C.POINTER(OrcMesh) * R)(*[C.pointer(h.s) for h in hs])
+    gp = (C.POINTER(OrcLaserGeom) * R)(*[C.pointer(g.s) for g in gs])
+    refl = [i32(x) for x in refl]; nHat = [f64(x) for x in nHat]
+    pg = [np.ascontiguousarray(x, dtype=np.int64) for x in pointGlobal]
+    a, e, E, T = ([f64(x) for x in v] for v in (a, e, E, T))
+    cells = [i32(x) for x in cells]
+    Q = [np.zeros(h.s.nCells) for h in hs]
+    nPts = [np.zeros((g.s.nPoints, 3)) for g in gs]
+    created = np.zeros(R, np.int32)
+    ipp = lambda xs: (c_ip * R)(*[_i(x) for x in xs])
+    lpp = (C.POINTER(C.c_int64) * R)(*[x.ctypes.data_as(C.POINTER(C.c_int64)) for x in pg])
+    p0, p1, I, dA = f64(p0), f64(p1), f64(I), f64(dA)
+    fn = lib().orc_laser_calculate_ranks
+    fn.restype = C.c_int
+    rc = fn(R, mp, gp, C.byref(cfg), ipp(refl), _pp(nHat), lpp, _pp(a), _pp(e), _pp(E), _pp(T), n, _d(p0), _d(p1), _d(I), _d(dA),
+            ipp(cells), _pp(Q), _i(created), _pp(nPts))
+    if rc:
+        raise RuntimeError(f"orc_laser_calculate_ranks failed: rc={rc}")
+    return dict(Q=Q, created=created, nHatPoints=nPts)

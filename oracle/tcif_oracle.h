@@ -334,6 +334,15 @@ int orc_laser_calculate(const orc_mesh *m, const orc_comm *c, const orc_laser_ge
                         const int32_t *cell, double *Q, int32_t *reflectingCells, double *nHat, double *nHatPoints,
                         int32_t *nParticlesFinal);
 
+/* The decomposed run restated on one CPU: all ranks in lock-step rounds, particles handed over at processor
+ * patches, point values summed over the ranks sharing a point (pointGlobal: global point labels per rank).
+ * refl / nHat per rank are the marking of laserDTRM.C:596-652 for the rank's cells; created [nRanks] out. */
+int orc_laser_calculate_ranks(int nRanks, const orc_mesh *const *ms, const orc_laser_geom *const *gs, const orc_laser_cfg *cfg,
+                              const int32_t *const *refl, const double *const *nHat, const int64_t *const *pointGlobal,
+                              const double *const *a, const double *const *e, const double *const *E, const double *const *T,
+                              int nParticles, const double *p0, const double *p1, const double *I, const double *dA,
+                              const int32_t *const *cell, double *const *Q, int32_t *created, double *const *nHatPointsOut);
+
 #ifdef __cplusplus
 }
 #endif

@@ -249,3 +249,43 @@ def test_block_polymesh_and_shared_points_of_processor_sub_meshes(procs):
             continue
         # a point held by several ranks is declared shared by each of them, a private point by none
         assert holders[("shared", k)] == (ranks if len(ranks) > 1 else set()), (k, ranks)
+
+
+@pytest.mark.parametrize("procs", [(2, 1, 1), (1, 2, 1), (2, 2, 2)])
+def test_decomposed_walk_on_cpu_matches_the_serial_walk(procs):
+    """N > 1 on the CPU: all ranks in lock-step rounds (orc_laser_calculate_ranks) - hand-over at processor patches,
+    point values summed over the ranks sharing a point, reflected particles located across ranks - against the serial
+    walk on the undecomposed mesh.  The same algorithm the device runs over NCCL (tests/test_gpu_laser.py)."""
+    n = 16
+    spec = cases.case(5, n)
+    xs, ys, zs = (hm.vertices(spec.n[d], spec.lengths[d]) for d in range(3))
+    g = mo.box_mesh(*spec.n, spec.lengths, spec.patch_types)
+    geomG = cases.box_polymesh(g, xs, ys, zs)
+    fg = cases.synthetic_fields(spec, g)
+    models = [dict(kind="FresnelLaser", **{"from": 2, "to": 0}, epsilon=0.25),
+              dict(kind="Fresnel", **{"from": 2, "to": 1}, nk1=(1.0, 0.0), nk2=(3.6, 5.0))]
+    d = np.array([0.5, -1.0, 0.2]); d /= np.linalg.norm(d)
+    r = np.cross(d, [0.0, 0.0, 1.0]); r /= np.linalg.norm(r)
+    p0, p1, Ip, dA = cases.laser_seeds((0.3, 0.93, 0.45), d, r, 8, 16, 0.15, geomG["boundsMag"], sigma=0.07, power=200.0)
+    cellG = cases.find_cells_box(spec.n, xs, ys, zs, p0)
+    al = fg["alpha_i"]
+    a, e, E = (orc.local_density(al, c) for c in ((25.0, 10.0, 0.3), (0.1, 0.0, 0.0), (0.0, 0.0, 0.0)))
+    ref = orc.laser_calculate(g, geomG, models, al, fg["alpha_b"], fg["alphaBc"], a, e, E, fg["T_i"], p0, p1, Ip, dA, cellG)
+    nd = procs[0] * procs[1] * procs[2]
+    meshes = [hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, rk) for rk in range(nd)]
+    geoms = [cases.box_block_polymesh(spec.n, xs, ys, zs, procs, rk, m) for rk, m in enumerate(meshes)]
+    gids = [np.asarray(m.cellGlobal) for m in meshes]
+    cells = []
+    for gid in gids:
+        g2l = np.full(g.nCells, -1, np.int32); g2l[gid] = np.arange(len(gid), dtype=np.int32)
+        cells.append(g2l[cellG])
+    out = orc.laser_calculate_ranks(meshes, geoms, models, [ref["reflectingCells"][i] for i in gids], [ref["nHat"][i] for i in gids],
+                                    [gm["pointGlobal"] for gm in geoms], [a[i] for i in gids], [e[i] for i in gids],
+                                    [E[i] for i in gids], [fg["T_i"][i] for i in gids], p0, p1, Ip, dA, cells)
+    assert int(out["created"].sum()) == ref["nParticles"] > len(Ip)
+    assert sum(1 for q in out["Q"] if q.any()) >= 2           # the beam crosses the processor planes
+    scale = np.abs(ref["Q"]).max()
+    for rk in range(nd):
+        assert np.abs(out["nHatPoints"][rk] - ref["nHatPoints"][geoms[rk]["pointGlobal"]]).max() <= 1e-12
+        assert np.abs(out["Q"][rk] - ref["Q"][gids[rk]]).max() <= 1e-10 * scale, rk
+    assert sum((q != 0).sum() for q in out["Q"]) == (ref["Q"] != 0).sum()
