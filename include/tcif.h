@@ -259,7 +259,7 @@ TCIF_API int tcif_interface_porosity(tcif_ctx *ctx, int nModels, const int32_t *
  * (:299-311), implicit upwind predictor + explicitSolve (:321-378), inert species = max(1 - sum Yi, 0) (:383-384).
  * Uses the resident alpha (all phases), phi, mesh geometry; Yinternal[i] [nCells] / Yboundary[i] [nBoundaryFaces]
  * are host buffers in/out, Ybc [nSpecies*nPatches] the TCIF_BC_* kind per patch, Su/Sp[i] may be NULL (the
- * massSpeciesTransfer sources); cYi, the two div schemes, nYiSubCycles (<= 1) and the Yi solver tolerance are the
+ * massSpeciesTransfer sources); cYi, the two div schemes, nYiSubCycles and the Yi solver tolerance are the
  * case's fvSolution/fvSchemes entries.  Overwrites nothing of the phase-fraction state. */
 TCIF_API int tcif_solve_yi(tcif_ctx *ctx, int phase, int nSpecies, int inertIndex,
                            double *const *Yinternal, double *const *Yboundary, const int32_t *Ybc,

@@ -507,7 +507,7 @@ def solve_mt(m, cfg, ctl, alphas_i, alphas_b, alphaBc, phii, phib, deltaT, rho, 
 
 
 def solve_yi(m, cfg, alphas_i, alphas_b, alphaBc, ph, Y_i, Y_b, YBc, inertIndex, phii, phib, deltaT, cYi=1.0,
-             schemePhi="vanLeer", schemePhir="linear", Su=None, Sp=None, tol=1e-12, maxIter=200, comm=None):
+             schemePhi="vanLeer", schemePhir="linear", Su=None, Sp=None, tol=1e-12, maxIter=200, comm=None, nYiSubCycles=1):
     """MultiComponentPhaseModel::solveYi for the species of phase `ph`.  Returns (Y_i, Y_b) lists."""
     h = m if isinstance(m, MeshHandle) else MeshHandle(m)
     P, S = len(alphas_i), len(Y_i)
@@ -522,7 +522,7 @@ def solve_yi(m, cfg, alphas_i, alphas_b, alphaBc, ph, Y_i, Y_b, YBc, inertIndex,
     lib().orc_solve_yi(h.ref, C.byref(comm) if comm else None, C.byref(cfg), P, _pp(ai), _pp(ab), _i(bc), int(ph), S,
                        int(inertIndex), _pp(yi), _pp(yb), _i(ybc), _d(phii), _d(phib), C.c_double(cYi),
                        SCHEMES[schemePhi], SCHEMES[schemePhir], _pp(su) if su else None, _pp(sp) if sp else None,
-                       C.c_double(deltaT), C.c_double(tol), int(maxIter))
+                       C.c_double(deltaT), C.c_double(tol), int(maxIter), int(nYiSubCycles))
     return yi, yb
 
 

@@ -281,12 +281,13 @@ void orc_solve_mt(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg
 
 /* MultiComponentPhaseModel::solveYi (MultiComponentPhaseModel.C:182-388): species MULES of phase `ph`.
  * Y (internal, boundary) in/out [nSpecies]; YBc [nSpecies*nPatches]; Su/Sp per species may be NULL.
- * cYi, nYiSubCycles <= 1, the two div schemes and the Yi linear-solver tolerance come from the case. */
+ * cYi, nYiSubCycles, the two div schemes and the Yi linear-solver tolerance come from the case. */
 void orc_solve_yi(const orc_mesh *m, const orc_comm *c, const orc_mules_cfg *cfg, int nPhases,
                   const double *const *alphai, const double *const *alphab, const int32_t *alphaBc, int ph,
                   int nSpecies, int inertIndex, double *const *Yi, double *const *Yb, const int32_t *YBc,
                   const double *phii, const double *phib, double cYi, int schemePhi, int schemePhir,
-                  const double *const *Su, const double *const *Sp, double deltaT, double tol, int maxIter);
+                  const double *const *Su, const double *const *Sp, double deltaT, double tol, int maxIter,
+                  int nYiSubCycles);
 
 /* ---- laserDTRM: discrete-ray laser heat source ---------------------------------------- */
 /* polyMesh data the cell walk and interpolationCellPoint need on top of orc_mesh */

@@ -76,9 +76,8 @@ def test_solve_yi_errors():
     cases.load_case(ctx, spec, f)
     with pytest.raises(RuntimeError):      # vanLeer without cell centres
         ctx.solve_yi(0, Y, Yb, np.zeros((2, m.nPatches), np.int32), 1, f["deltaT"])
-    with pytest.raises(RuntimeError):      # sub-cycling is not on the device path
-        ctx.solve_yi(0, Y, Yb, np.zeros((2, m.nPatches), np.int32), 1, f["deltaT"], schemePhi="upwind", schemePhir="upwind",
-                     nYiSubCycles=2)
+    with pytest.raises(RuntimeError):      # deltaT must be positive
+        ctx.solve_yi(0, Y, Yb, np.zeros((2, m.nPatches), np.int32), 1, -1.0, schemePhi="upwind", schemePhir="upwind")
     ctx.close()
 
 
@@ -128,3 +127,30 @@ def test_decomposed_solve_yi_matches_serial(procs):
     for c in ctxs:
         c.close()
     grp.close()
+
+
+@pytest.mark.parametrize("nSub", [2, 3])
+def test_solve_yi_sub_cycles_match_oracle(nSub):
+    """nYiSubCycles > 1 (MultiComponentPhaseModel.C:345-364): n explicitSolve calls with deltaT/n, Yi.oldTime() re-stored
+    from the current Yi at every sub-cycle, the flux left in place by the previous limit()."""
+    spec = cases.case(5, 12)
+    m = global_mesh(spec, grading=(1.5, None, None))
+    f = cases.synthetic_fields(spec, m)
+    nS = 3
+    Y, Yb = _species(m, nS)
+    ybc = np.zeros((nS, m.nPatches), np.int32)
+    rng = np.random.default_rng(2)
+    Su = [1e-2 * rng.uniform(0, 1, m.nCells), None, None]
+    ctx = abi.Context(m, spec.nPhases)
+    cases.load_case(ctx, spec, f)
+    ctx.set_cell_centres(m.C, _delta_b(m))
+    yi, yb = ctx.solve_yi(0, Y, Yb, ybc, 2, f["deltaT"], Su=Su, nYiSubCycles=nSub)
+    ri, rb = orc.solve_yi(m, orc.mules_cfg(3), f["alpha_i"], f["alpha_b"], f["alphaBc"], 0, Y, Yb, ybc, 2,
+                          f["phi_i"], f["phi_b"], f["deltaT"], Su=Su, nYiSubCycles=nSub)
+    r1, _ = orc.solve_yi(m, orc.mules_cfg(3), f["alpha_i"], f["alpha_b"], f["alphaBc"], 0, Y, Yb, ybc, 2,
+                         f["phi_i"], f["phi_b"], f["deltaT"], Su=Su)
+    assert max(np.abs(ri[i] - r1[i]).max() for i in range(nS)) > 1e-9      # sub-cycling changes the result
+    for i in range(nS):
+        assert_field_close(yi[i], ri[i], f"Y{i}", rtol=1e-11)
+        assert_field_close(yb[i], rb[i], f"Y{i} boundary", rtol=1e-11)
+    ctx.close()

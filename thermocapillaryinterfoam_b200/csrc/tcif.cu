@@ -236,6 +236,8 @@ struct tcif_ctx {
     tcif_group *group = nullptr;
     ncclComm_t nccl = nullptr;
     double *d_gather = nullptr;         // nRanks*16 doubles (nccl scalar reductions)
+    double *agBuf = nullptr;            // allgather_host staging
+    int agCap = 0;
     // timers
     bool timersOn = false;
     std::vector<EvPair> evs;
@@ -539,14 +541,17 @@ void allgather_host(tcif_ctx *c, const double *send, int n, std::vector<double> 
         for (int r = 0; r < g->n; ++r) memcpy(&all[(size_t)r * n], g->gatherPtr[r], sizeof(double) * n);
         g->barrier();
     } else if (c->nccl) {
-        double *ds = nullptr, *dr = nullptr;
-        CUDA_OK(cudaMalloc((void **)&ds, sizeof(double) * n));
-        CUDA_OK(cudaMalloc((void **)&dr, sizeof(double) * n * c->nRanks));
+        if (n > c->agCap) {             // grow-only device buffers: [n] to send, [n*nRanks] to receive
+            if (c->agBuf) CUDA_OK(cudaFree(c->agBuf));
+            c->agBuf = nullptr; c->agCap = 0;
+            CUDA_OK(cudaMalloc((void **)&c->agBuf, sizeof(double) * (size_t)n * (c->nRanks + 1)));
+            c->agCap = n;
+        }
+        double *ds = c->agBuf, *dr = c->agBuf + n;
         CUDA_OK(cudaMemcpyAsync(ds, send, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
         NCCL_OK(g_nccl.AllGather(ds, dr, n, kNcclDouble, c->nccl, c->stream));
         CUDA_OK(cudaMemcpyAsync(all.data(), dr, sizeof(double) * n * c->nRanks, cudaMemcpyDeviceToHost, c->stream));
         CUDA_OK(cudaStreamSynchronize(c->stream));
-        CUDA_OK(cudaFree(ds)); CUDA_OK(cudaFree(dr));
     } else {
         memcpy(all.data(), send, sizeof(double) * n);
     }
@@ -1326,7 +1331,6 @@ void do_solve_yi(tcif_ctx *c, int ph, int nSpecies, int inertIndex, double *cons
     check_phase(c, ph);
     if (nSpecies < 1 || !Yint || (c->nBF && !Ybnd) || !Ybc) failf("tcif_solve_yi: bad arguments");
     if (!(deltaT > 0)) failf("tcif_solve_yi: deltaT must be positive");
-    if (nYiSubCycles > 1) failf("tcif_solve_yi: nYiSubCycles > 1 is not supported by the device path");
     for (int sc : {schemePhi, schemePhir}) {
         if (sc < 0 || sc > 2) failf("unsupported convection scheme %d (upwind | linear | vanLeer)", sc);
         if (sc == SCHEME_VANLEER && !c->Cx) failf("vanLeer needs cell centres: call tcif_set_cell_centres first");
@@ -1407,7 +1411,16 @@ void do_solve_yi(tcif_ctx *c, int ph, int nSpecies, int inertIndex, double *cons
             });
             do_limit(c, &ph, 1, 1.0 / deltaT, 0, false, true);                        // :299-311
             do_predictor(c, &ph, 1, deltaT, tol, maxIter, false);                      // :323-338
-            do_explicit(c, &ph, 1, deltaT, true);                                      // :343 (+= YiEqn.flux()) and :361-378
+            if (nYiSubCycles > 1) {
+                // subCycle<volScalarField> (:345-364): the first sub-cycle keeps the real old-time field (the
+                // constructor advances the field's time index), from the second one on Yi.oldTime() is re-stored
+                // from the current Yi; deltaT/n; the flux left in place by the previous explicitSolve
+                for (int k = 0; k < nYiSubCycles; ++k) {
+                    if (k) CUDA_OK(cudaMemcpyAsync(c->spY0, c->alpha[ph], sizeof(double) * c->nC, cudaMemcpyDeviceToDevice, c->stream));
+                    do_explicit(c, &ph, 1, deltaT / nYiSubCycles, k == 0);
+                }
+            } else
+                do_explicit(c, &ph, 1, deltaT, true);                                  // :343 (+= YiEqn.flux()) and :361-378
             yCur = c->alpha[ph]; yNew = c->alphaNew[ph];                               // explicitSolve swapped the buffers
             CUDA_OK(cudaMemcpyAsync(Yint[i], yCur, sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
             if (c->nBF) CUDA_OK(cudaMemcpyAsync(Ybnd[i], c->spYb, sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
@@ -1980,6 +1993,7 @@ void tcif_destroy(tcif_ctx *c) {
     for (auto &e : c->evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (auto &e : c->evPool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (void *p : c->allocs) cudaFree(p);
+    if (c->agBuf) cudaFree(c->agBuf);
     if (c->lzCloud) cudaFree(c->lzCloud);
     if (c->lzOutbox) cudaFree(c->lzOutbox);
     if (c->lzInbox) cudaFree(c->lzInbox);
