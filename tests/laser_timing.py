@@ -1,6 +1,7 @@
 """Timing of laserDTRM::calculate() on the device against the CPU oracle, outside bench.py
-(whose one JSON line is the surface-force + MULES stage).  Usage on a B200:
-    python profiles/laser_timing.py [--n 200] [--nr 100] [--ntheta 200] [--reps 5] > gpurun_out/laser.json
+(whose one JSON line is the surface-force + MULES stage).  Lives under tests/ because it runs the oracle as the
+checker and CPU baseline; not collected by pytest.  Usage on a B200:
+    python tests/laser_timing.py [--n 200] [--nr 100] [--ntheta 200] [--reps 5] > gpurun_out/laser.json
 The workload: BASELINE configs[3] (3-phase melt pool box, n^3 cells), a Gaussian beam of nr x ntheta rays pointing
 down onto the first metal blob, FresnelLaser reflection at both metal surfaces, local-density absorption."""
 import argparse
