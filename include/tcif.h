@@ -299,6 +299,10 @@ TCIF_API int tcif_laser_calculate(tcif_ctx *ctx, int32_t nParticles, const doubl
                                   double *Q, int32_t *nParticlesFinal);
 /* Q, reflectingCellsVol (:556), nHat (:576) [nCells*3] and its point interpolation [nPoints*3]; any may be NULL */
 TCIF_API int tcif_laser_get(tcif_ctx *ctx, double *Q, int32_t *reflectingCells, double *nHat, double *nHatPoints);
+/* Q of the last calculate() as (cell, value) pairs of the cells that hold energy, unordered: the beam touches a small
+ * part of the mesh, the solver zeroes Q_ anyway (laserDTRM.C:580) and scatters these instead of reading nCells
+ * doubles back.  *n = number of such cells; fails (with *n set) when capacity is too small. */
+TCIF_API int tcif_laser_get_sparse(tcif_ctx *ctx, int32_t capacity, int32_t *cells, double *values, int32_t *n);
 /* Decomposed meshes: the points of processor patches are shared by ranks, and volPointInterpolation sums weights and
  * weighted values over all ranks holding a point.  localPoint [n]: every local point lying on a processor patch,
  * globalPoint [n]: its global label (globalMeshData).  Collective over the communicator; call after

@@ -57,10 +57,19 @@ def main():
         Q, nPart = ctx.laser_calculate(p0, p1, Ip, dA, cell)
     wall = (time.perf_counter() - t0) / a.reps
     tm = ctx.timers_read()
+    launches = (ctx.launch_count - l0) / a.reps
+    t0 = time.perf_counter()
+    for _ in range(a.reps):
+        _, _ = ctx.laser_calculate(p0, p1, Ip, dA, cell, dense=False)
+        cs, vs = ctx.laser_get_sparse(1 << 20)
+    wall_sparse = (time.perf_counter() - t0) / a.reps
+    Qs = np.zeros(m.nCells); Qs[cs] = vs
     out = dict(what="laserDTRM::calculate()", cells=int(m.nCells), seeds=int(len(Ip)), particles=int(nPart),
                generations=int(ctx.laser_generations), wall_ms_per_call=1e3 * wall,
+               wall_ms_per_call_sparse_readback=1e3 * wall_sparse, cells_with_energy=int(len(cs)),
+               sparse_vs_dense_max_dev_rel=float(np.abs(Qs - Q).max() / np.abs(Q).max()),
                device_ms_per_call={k: v["ms"] / a.reps for k, v in tm.items() if v["ms"] > 0},
-               launches_per_call=(ctx.launch_count - l0) / a.reps, polymesh_setup_s=t_setup,
+               launches_per_call=launches, polymesh_setup_s=t_setup,
                absorbed_W=float((Q * m.V).sum()), beam_W=float((Ip * dA)[cell >= 0].sum()))
     if not a.no_cpu:
         al = f["alpha_i"]

@@ -63,6 +63,10 @@ def test_calculate_matches_oracle(aC):
     assert nPart == ref["nParticles"]
     assert ctx.laser_generations >= 2
     assert np.array_equal(Q, got["Q"])
+    cells, vals = ctx.laser_get_sparse(capacity=16)          # grows to what is needed
+    assert len(cells) == (Q != 0).sum() > 16 and len(np.unique(cells)) == len(cells)
+    Qs = np.zeros(m.nCells); Qs[cells] = vals
+    assert np.array_equal(Qs, Q)
     _close(Q, ref["Q"], "Q")
     assert np.array_equal(Q != 0, ref["Q"] != 0)
     ctx.close()

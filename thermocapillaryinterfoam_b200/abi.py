@@ -386,14 +386,26 @@ class Context:
         a, e, E = _f64(a), _f64(e), _f64(E)
         self._ck(lib().tcif_laser_set_absorption_fields(self.h, _d(a), _d(e), _d(E)))
 
-    def laser_calculate(self, p0, p1, I, dA, cell, sigmaSB=SIGMA_SB, maxParticles=0):
-        """laserDTRM::calculate(); returns (Q [nCells], particles in the cloud at the end)."""
+    def laser_calculate(self, p0, p1, I, dA, cell, sigmaSB=SIGMA_SB, maxParticles=0, dense=True):
+        """laserDTRM::calculate(); returns (Q [nCells], particles created on this rank).  dense=False leaves Q on the
+        device (read it with laser_get_sparse / laser_get) and returns (None, particles)."""
         p0, p1, I, dA, cell = _f64(p0), _f64(p1), _f64(I), _f64(dA), _i32(cell)
-        Q = np.zeros(self.nCells)
+        Q = np.zeros(self.nCells) if dense else None
         n = C.c_int32(0)
         self._ck(lib().tcif_laser_calculate(self.h, len(I), _d(p0), _d(p1), _d(I), _d(dA), _i(cell), C.c_double(sigmaSB),
                                             int(maxParticles), _d(Q), C.byref(n)))
         return Q, n.value
+
+    def laser_get_sparse(self, capacity=1 << 16):
+        """(cells, values) of the cells that hold energy after the last laser_calculate, unordered."""
+        while True:
+            cells, vals, n = np.empty(capacity, np.int32), np.empty(capacity), C.c_int32(0)
+            rc = lib().tcif_laser_get_sparse(self.h, int(capacity), _i(cells), _d(vals), C.byref(n))
+            if rc and n.value > capacity:
+                capacity = int(n.value)
+                continue
+            self._ck(rc)
+            return cells[:n.value].copy(), vals[:n.value].copy()
 
     def laser_get(self):
         Q = np.zeros(self.nCells); refl = np.zeros(self.nCells, np.int32)

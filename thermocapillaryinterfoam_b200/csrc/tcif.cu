@@ -217,6 +217,9 @@ struct tcif_ctx {
     int *lzPatchInfo = nullptr;
     double lzDeltaN = 0.0;
     long long lzCreated = 0;
+    int *lzSpCells = nullptr;
+    double *lzSpVals = nullptr;
+    int lzSpCap = 0;
     // F is a pure function of (alpha, T, sigma): the solver evaluates it 2-4x per time step on unchanged
     // fields (UEqn.H:29, pEqn.H:35 per corrector, thermocapillaryInterFoam.C:150); fieldsVersion counts
     // every change of those inputs and forceVersion remembers which one F was computed from
@@ -1996,6 +1999,8 @@ void tcif_destroy(tcif_ctx *c) {
     if (c->agBuf) cudaFree(c->agBuf);
     if (c->lzCloud) cudaFree(c->lzCloud);
     if (c->lzOutbox) cudaFree(c->lzOutbox);
+    if (c->lzSpCells) cudaFree(c->lzSpCells);
+    if (c->lzSpVals) cudaFree(c->lzSpVals);
     if (c->lzInbox) cudaFree(c->lzInbox);
     if (c->h_small) cudaFreeHost(c->h_small);
     if (c->sIn) cudaStreamDestroy(c->sIn);
@@ -2401,6 +2406,34 @@ int tcif_laser_get(tcif_ctx *c, double *Q, int32_t *reflectingCells, double *nHa
     }
     if (nHatPoints) CUDA_OK(cudaMemcpyAsync(nHatPoints, c->lzNHatPts, sizeof(double) * 3 * c->lg.nPoints, cudaMemcpyDefault, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_laser_get_sparse(tcif_ctx *c, int32_t capacity, int32_t *cells, double *values, int32_t *n) {
+    API_BEGIN(c)
+    if (!c->laserGeoSet) failf("tcif_laser_get_sparse: call tcif_laser_set_polymesh first");
+    if (capacity < 0 || (capacity && (!cells || !values)) || !n) failf("tcif_laser_get_sparse: bad arguments");
+    if (capacity > c->lzSpCap) {
+        if (c->lzSpCells) CUDA_OK(cudaFree(c->lzSpCells));
+        if (c->lzSpVals) CUDA_OK(cudaFree(c->lzSpVals));
+        c->lzSpCells = nullptr; c->lzSpVals = nullptr; c->lzSpCap = 0;
+        CUDA_OK(cudaMalloc((void **)&c->lzSpCells, sizeof(int) * (size_t)capacity));
+        CUDA_OK(cudaMalloc((void **)&c->lzSpVals, sizeof(double) * (size_t)capacity));
+        c->lzSpCap = capacity;
+    }
+    CUDA_OK(cudaMemsetAsync(c->lzCounters + 3, 0, sizeof(int), c->stream));
+    k_laser_compact<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nC, c->lzQ, capacity, c->lzSpCells, c->lzSpVals, c->lzCounters + 3);
+    c->launches++;
+    int found = 0;
+    CUDA_OK(cudaMemcpyAsync(&found, c->lzCounters + 3, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    *n = found;
+    if (found > capacity) failf("tcif_laser_get_sparse: %d cells hold energy, capacity is %d", found, capacity);
+    if (found) {
+        CUDA_OK(cudaMemcpyAsync(cells, c->lzSpCells, sizeof(int) * found, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_OK(cudaMemcpyAsync(values, c->lzSpVals, sizeof(double) * found, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_OK(cudaStreamSynchronize(c->stream));
+    }
     API_END(c)
 }
 

@@ -572,6 +572,18 @@ __global__ void k_laser_finish(int n, const double *V, double *Q) {
     if (c < n) Q[c] /= V[c];                                                          // laserDTRM.C:671
 }
 
+// the cells the beam deposited in, unordered: Q is zero almost everywhere, the host zeroes its field anyway
+// (laserDTRM.C:580) and scatters these
+__global__ void k_laser_compact(int n, const double *Q, int cap, int *cells, double *vals, int *counter) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    const double q = Q[c];
+    if (q != 0.0) {
+        const int k = atomicAdd(counter, 1);
+        if (k < cap) { cells[k] = c; vals[k] = q; }
+    }
+}
+
 __global__ void k_laser_bnd_index(int nBndCells, const int *bndCells, int *bndIdx) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < nBndCells) bndIdx[bndCells[i]] = i;
