@@ -156,6 +156,9 @@ void laserDTRM::calculate()
         p0[k] = p.p0(); p1[k] = p.p1(); I[k] = p.I(); dA[k] = p.dA(); cell[k] = p.cell(); ++k;
     }
 
+    // Reset the field (:580); the device returns the cells that hold energy, a small part of the mesh
+    Q_ == dimensionedScalar(Q_.dimensions(), Zero);
+
     label nFinal = 0;
     dev.call
     (
@@ -164,10 +167,22 @@ void laserDTRM::calculate()
             dev.ctx(), n,
             reinterpret_cast<const double*>(p0.cdata()), reinterpret_cast<const double*>(p1.cdata()),
             I.cdata(), dA.cdata(), cell.cdata(), constant::physicoChemical::sigma.value(), 0,
-            Q_.primitiveFieldRef().data(), &nFinal
+            nullptr, &nFinal
         ),
         "tcif_laser_calculate"
     );
+    labelList hit(sparseCapacity_);
+    scalarField val(sparseCapacity_);
+    label nHit = 0;
+    if (tcif_laser_get_sparse(dev.ctx(), hit.size(), hit.data(), val.data(), &nHit) && nHit > hit.size())
+    {
+        sparseCapacity_ = 2*nHit;                    // grow once, the beam footprint changes slowly
+        hit.resize(sparseCapacity_); val.resize(sparseCapacity_);
+        dev.call(tcif_laser_get_sparse(dev.ctx(), hit.size(), hit.data(), val.data(), &nHit), "tcif_laser_get_sparse");
+    }
+    scalarField& Q = Q_.primitiveFieldRef();
+    for (label i = 0; i < nHit; ++i) { Q[hit[i]] = val[i]; }         // already divided by V (:671)
+
     Info<< "Move particles..." << n << " (" << nFinal << " with reflections)" << endl;
 
     initialise();                    // :734, seeds the cloud of the next call
