@@ -174,12 +174,14 @@ void laserDTRM::calculate()
     labelList hit(sparseCapacity_);
     scalarField val(sparseCapacity_);
     label nHit = 0;
-    if (tcif_laser_get_sparse(dev.ctx(), hit.size(), hit.data(), val.data(), &nHit) && nHit > hit.size())
+    int rc = tcif_laser_get_sparse(dev.ctx(), hit.size(), hit.data(), val.data(), &nHit);
+    if (rc && nHit > hit.size())                     // the one recoverable failure: more cells hold energy than fit
     {
         sparseCapacity_ = 2*nHit;                    // grow once, the beam footprint changes slowly
         hit.resize(sparseCapacity_); val.resize(sparseCapacity_);
-        dev.call(tcif_laser_get_sparse(dev.ctx(), hit.size(), hit.data(), val.data(), &nHit), "tcif_laser_get_sparse");
+        rc = tcif_laser_get_sparse(dev.ctx(), hit.size(), hit.data(), val.data(), &nHit);
     }
+    dev.call(rc, "tcif_laser_get_sparse");           // anything else (CUDA error, no polyMesh) is fatal, never Q = 0
     scalarField& Q = Q_.primitiveFieldRef();
     for (label i = 0; i < nHit; ++i) { Q[hit[i]] = val[i]; }         // already divided by V (:671)
 

@@ -35,7 +35,8 @@ void multiphaseSystem::solve()
     const tcifFoamBridge& dev = device_();                      // created by divCapillaryStress() (createFields.H:168)
     const label P = phases_.size();
 
-    // one-off: geometry for the NVD limiter, cAlphas table, phase densities
+    // once per bridge (static mesh, fvSolution read once): geometry for the NVD limiter and the cAlphas table
+    if (!dev.staticInputsSet())
     {
         vectorField deltaB(dev.nBoundaryFaces());
         // fvPatch::delta() patch by patch, flattened like every other boundary field
@@ -69,6 +70,7 @@ void multiphaseSystem::solve()
             ++p1;
         }
         dev.call(tcif_set_calpha(dev.ctx(), cA.cdata()), "tcif_set_calpha");
+        dev.staticInputsSet(true);
     }
 
     tcif_alpha_controls ctl;
@@ -96,8 +98,8 @@ void multiphaseSystem::solve()
             if (&other == &phase) continue;
             ctl.schemePhir = tcifScheme(mesh_, "div(phir," + other.name() + ',' + n + ')');
         }
-        dev.setAlphaBc(p, phase);
-        dev.setAlpha(p, phase);
+        dev.setAlphaBc(p, phase);              // re-uploaded only if a patch changed its kind
+        dev.setAlpha(p, phase);                // no bytes move unless the solver touched alpha since getAlpha() below
         const volScalarField& rho = phase.rho()();
         const scalarField rb(dev.flatBoundary(rho));
         dev.call(tcif_set_rho(dev.ctx(), p, 0, rho.primitiveField().cdata(), rb.cdata()), "tcif_set_rho");

@@ -93,6 +93,8 @@ tmp<volVectorField> phaseSystem::divCapillaryStress() const
     }
     const tcifFoamBridge& dev = device_();
 
+    // stamped: after solve() left the newest alpha on the device (and getAlpha() marked it) nothing is uploaded
+    // here, the device keeps F cached, and the 2nd..5th evaluation of a time step is one download of F
     label p = 0;
     forAllConstIters(phaseModels_, iter)
     {

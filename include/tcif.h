@@ -146,6 +146,22 @@ TCIF_API int tcif_div_capillary_stress_host(tcif_ctx *ctx, const double *const *
  * corrector, thermocapillaryInterFoam.C:150) and the reference recomputes it from scratch every time. */
 TCIF_API int tcif_flux_of_force(tcif_ctx *ctx, double *internal, double *boundary);
 /* Switch that cache off/on (default on) and read how often F was computed vs served from the cache. */
+/* ---- residency: keep fields on the device between calls ---------------------------------------------------
+ * The solver evaluates divCapillaryStress() 3-5 times per time step (UEqn.H:29, pEqn.H:35 per corrector,
+ * thermocapillaryInterFoam.C:150) and solve() once (:105), always on the SAME registered fields alpha.<phase>
+ * and T.  The device copy of a field carries the caller's modification stamp (OpenFOAM: regIOobject::eventNo()
+ * of the field, which every non-const access advances); a stamped set uploads -- and invalidates the cached
+ * force -- only when the stamp differs from the one the device copy carries.  stamp 0 = "unknown": always
+ * uploads.  Whatever changes alpha on the device (explicitSolve, the predictor, renormalisation, an unstamped
+ * set) resets the stamp to 0; after tcif_get_alpha the caller tells the device which host state now equals its
+ * copy with tcif_mark_alpha.  *uploaded (may be NULL) reports whether bytes moved. */
+TCIF_API int tcif_set_alpha_stamped(tcif_ctx *ctx, int phase, uint64_t stamp, const double *internal,
+                                    const double *boundary, int32_t *uploaded);
+TCIF_API int tcif_set_temperature_stamped(tcif_ctx *ctx, uint64_t stamp, const double *internal,
+                                          const double *boundary, int32_t *uploaded);
+TCIF_API int tcif_mark_alpha(tcif_ctx *ctx, int phase, uint64_t stamp);
+/* uploads[0] alpha fields uploaded, [1] alpha uploads skipped (stamp matched), [2] T uploaded, [3] T skipped */
+TCIF_API int tcif_transfer_counters(const tcif_ctx *ctx, int64_t uploads[4]);
 TCIF_API int tcif_set_force_cache(tcif_ctx *ctx, int on);
 TCIF_API int tcif_force_counters(const tcif_ctx *ctx, int64_t *evaluations, int64_t *cacheHits);
 /* fvc::grad(alpha.<phase>) with Gauss linear (phaseSystem.C:1076-1077): [nCells*3], [nBF*3]. */
@@ -329,6 +345,11 @@ TCIF_API int tcif_timers_read(tcif_ctx *ctx, double *ms, int64_t *launches, doub
 TCIF_API int64_t tcif_launch_count(const tcif_ctx *ctx);
 /* Bytes of HBM the context holds. */
 TCIF_API int64_t tcif_device_bytes(const tcif_ctx *ctx);
+/* How the mesh was laid out on the device (tests assert the benchmarked code path with it):
+ * out[0] Ko, [1] Kn (slot counts), [2] compile-time slot count of the fixed-K sweeps (0: generic-K kernels),
+ * [3] 1 when the volume sweeps walk the 256-cell tiles strip-wise, [4] L2 prefetch distance in tiles,
+ * [5] cells with patch faces, [6] of those deferred to the O(surface) launches, [7] processor faces. */
+TCIF_API int tcif_mesh_info(const tcif_ctx *ctx, int32_t out[8]);
 
 #ifdef __cplusplus
 }

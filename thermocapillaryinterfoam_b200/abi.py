@@ -103,6 +103,11 @@ def lib():
     L.tcif_launch_count.argtypes = [C.c_void_p]
     L.tcif_device_bytes.restype = C.c_int64
     L.tcif_device_bytes.argtypes = [C.c_void_p]
+    L.tcif_mesh_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+    L.tcif_set_alpha_stamped.argtypes = [C.c_void_p, C.c_int, C.c_uint64, c_dp, c_dp, C.POINTER(C.c_int32)]
+    L.tcif_set_temperature_stamped.argtypes = [C.c_void_p, C.c_uint64, c_dp, c_dp, C.POINTER(C.c_int32)]
+    L.tcif_mark_alpha.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
+    L.tcif_transfer_counters.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
     L.tcif_predictor_sweeps.argtypes = [C.c_void_p, C.c_int]
     L.tcif_destroy.argtypes = [C.c_void_p]
     L.tcif_destroy.restype = None
@@ -267,6 +272,29 @@ class Context:
         a, b = np.empty(self.nCells), np.empty(self.nBF)
         self._ck(lib().tcif_get_alpha(self.h, int(phase), _d(a), _d(b)))
         return a, b
+
+    def set_alpha_stamped(self, phase, stamp, internal, boundary):
+        """tcif_set_alpha_stamped: uploads only when `stamp` differs from the device copy's; returns whether bytes moved."""
+        a, b = _f64(internal), _f64(boundary)
+        assert a.shape[0] == self.nCells and b.shape[0] == self.nBF
+        up = C.c_int32(0)
+        self._ck(lib().tcif_set_alpha_stamped(self.h, int(phase), C.c_uint64(int(stamp)), _d(a), _d(b), C.byref(up)))
+        return bool(up.value)
+
+    def mark_alpha(self, phase, stamp):
+        self._ck(lib().tcif_mark_alpha(self.h, int(phase), C.c_uint64(int(stamp))))
+
+    def set_temperature_stamped(self, stamp, internal, boundary):
+        a, b = _f64(internal), _f64(boundary)
+        up = C.c_int32(0)
+        self._ck(lib().tcif_set_temperature_stamped(self.h, C.c_uint64(int(stamp)), _d(a), _d(b), C.byref(up)))
+        return bool(up.value)
+
+    @property
+    def transfer_counters(self):
+        out = (C.c_int64 * 4)()
+        self._ck(lib().tcif_transfer_counters(self.h, out))
+        return dict(alphaUploads=int(out[0]), alphaSkipped=int(out[1]), TUploads=int(out[2]), TSkipped=int(out[3]))
 
     def store_old_alphas(self):
         self._ck(lib().tcif_store_old_alphas(self.h))
@@ -570,3 +598,14 @@ class Context:
     @property
     def device_bytes(self):
         return int(lib().tcif_device_bytes(self.h))
+
+    @property
+    def mesh_info(self):
+        out = (C.c_int32 * 8)()
+        self._ck(lib().tcif_mesh_info(self.h, out))
+        return dict(Ko=out[0], Kn=out[1], fixedK=out[2], tileStrips=out[3], prefetchTiles=out[4], boundaryCells=out[5],
+                    deferredCells=out[6], processorFaces=out[7])
+
+    @property
+    def tile_strips(self):
+        return self.mesh_info["tileStrips"]

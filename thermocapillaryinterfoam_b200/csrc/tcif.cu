@@ -6,7 +6,7 @@
 //   multiphaseSystem::solveAlphas() MULES  /root/reference/phasesSystem/multiphaseSystem/multiphaseSystem.C:296-375
 // There is no CPU fallback: every entry point needs a CUDA device.
 #include "tcif_device.cuh"
-#include "tcif_volume.cuh"
+#include "tcif_sweeps.h"
 #include "tcif_alpha.cuh"
 #include "tcif_mass.cuh"
 #include "tcif_species.cuh"
@@ -15,6 +15,7 @@
 
 #include <dlfcn.h>
 #include <algorithm>
+#include <atomic>
 #include <condition_variable>
 #include <cmath>
 #include <cstdarg>
@@ -115,6 +116,9 @@ struct tcif_group {
     std::vector<tcif_ctx *> members;
     std::vector<double> red;     // n * 16 doubles
     std::vector<const double *> gatherPtr;   // n pointers (allgather_host)
+    // set by a member that found an error inside a collective section; every member checks it after the closing
+    // barrier of that section and fails too, so that nobody is left waiting in the next barrier
+    std::atomic<int> failed{0};
     void barrier() {
         std::unique_lock<std::mutex> lk(mu);
         long gen = generation;
@@ -136,6 +140,8 @@ struct tcif_ctx {
     double *stagingOut = nullptr;
     cudaEvent_t evV = nullptr, evB = nullptr;
     bool noOverlap = false;
+    int *bndIdentity = nullptr;   // [nBndCells] 0, 1, 2, ...: the deferred list of the one sweep that defers every boundary cell
+    int nDef = 0;            // cells deferred to the O(surface) launches (fixed-K meshes: the cells next to a processor patch)
     // host copy of the small mesh tables
     int nC = 0, nIF = 0, nBF = 0, nPatches = 0, stride = 0, Ko = 0, Kn = 0, nBndCells = 0, nCoupled = 0;
     size_t nFd = 0;
@@ -225,6 +231,10 @@ struct tcif_ctx {
     // every change of those inputs and forceVersion remembers which one F was computed from
     uint64_t fieldsVersion = 1, forceVersion = 0;
     bool cacheForce = true;
+    // residency (tcif_set_alpha_stamped & co.): the caller's modification stamp of the host field each device copy equals
+    uint64_t alphaStamp[4]{}, tStamp = 0;
+    int64_t xfer[4]{};                  // alpha uploaded / skipped, T uploaded / skipped
+    std::vector<int> bcHost[4];         // last alpha BC kinds uploaded (tcif_set_alpha_bc re-uploads only on change)
     int64_t forceEvaluations = 0, forceCacheHits = 0;
     double deltaN = 0.0;
     bool deltaNValid = false;
@@ -292,7 +302,10 @@ template <class F> void timed(tcif_ctx *c, int id, double bytes, F &&launch) { t
 // side stream, the halo exchange it does NOT need plus the O(surface) kernel over the boundary-adjacent
 // cells (which consumes the halo).  Sweep k's volume kernel reads sweep k-1's boundary results and
 // vice versa, hence the two events; the exchange and the boundary kernel hide behind the volume kernel.
-template <class FV, class FB> void sweep(tcif_ctx *c, FV &&volume, FB &&boundary) {
+// side = false: the volume launch covers every cell (fixed-K mesh without processor patches: patch faces are handled
+// inline, nothing is deferred), the side stream stays idle.
+template <class FV, class FB> void sweep(tcif_ctx *c, FV &&volume, FB &&boundary, bool side = true) {
+    if (!side) { volume(); return; }
     CUDA_OK(cudaEventRecord(c->evV, c->stream));
     CUDA_OK(cudaStreamWaitEvent(c->side, c->evV, 0));
     CUDA_OK(cudaStreamWaitEvent(c->stream, c->evB, 0));
@@ -450,6 +463,31 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
     for (int bc : bndCells) mask[bc >> 5] |= 1u << (bc & 31);
     d.bndMask = c->upload(mask);
     d.bndCells = c->upload(bndCells); d.bndCellStart = c->upload(bndStart); d.bndFaces = c->upload(order);
+    {
+        // fixed-K sweeps (tcif_volume.cuh): rank of a mask bit -> index in bndCells, and the cells whose patch faces
+        // must wait for the halo exchange (>= 1 processor face).  TCIF_INLINE_BND=0 defers every boundary-adjacent
+        // cell instead (the round-1 split, kept for A/B runs); generic-K meshes always use the k_* twin kernels.
+        std::vector<int> rank((size_t)stride / 32, 0);
+        int acc = 0;
+        for (size_t wd = 0; wd < rank.size(); ++wd) { rank[wd] = acc; acc += __builtin_popcount(mask[wd]); }
+        d.bndWordRank = c->upload(rank);
+        const char *e = getenv("TCIF_INLINE_BND");
+        const bool inl = !(e && atoi(e) == 0);
+        std::vector<int> def;
+        std::vector<unsigned> dmask((size_t)stride / 32, 0u);
+        for (int k = 0; k < (int)bndCells.size(); ++k) {
+            bool defer = !inl;
+            for (int j = bndStart[k]; j < bndStart[k + 1] && !defer; ++j) defer = bfType[order[j]] == TCIF_PATCH_PROCESSOR;
+            if (defer) { def.push_back(k); dmask[bndCells[k] >> 5] |= 1u << (bndCells[k] & 31); }
+        }
+        std::vector<int> ident(bndCells.size());
+        for (size_t k = 0; k < ident.size(); ++k) ident[k] = (int)k;
+        c->bndIdentity = c->upload(ident);
+        c->nDef = (int)def.size();
+        d.nDef = c->nDef;
+        d.defCells = c->upload(def);
+        d.defMask = def.empty() ? nullptr : c->upload(dmask);
+    }
     d.faceCells = c->upload(fc); d.bfPatch = c->upload(bfPatch); d.bfType = c->upload(bfType);
     std::vector<double> bx(nBF), by(nBF), bz(nBF), mag(nBF), dc(nBF), wb(nBF);
     for (int b = 0; b < nBF; ++b) {
@@ -582,19 +620,25 @@ void exchange(tcif_ctx *c, int ncomp, cudaStream_t st) {
         tcif_group *g = c->group;
         CUDA_OK(cudaStreamSynchronize(st));
         g->barrier();
-        for (size_t i = 0; i < c->cpPatch.size(); ++i) {
+        std::string bad;                 // a rank-local throw between the barriers would leave the other ranks waiting
+        for (size_t i = 0; i < c->cpPatch.size() && bad.empty(); ++i) {
             int p = c->cpPatch[i], e = c->patchNbr[p], n = c->patchSize[p];
-            if (e < 0 || e >= g->n || !g->members[e]) failf("processor patch %d: neighbour rank %d not in group", p, e);
+            if (e < 0 || e >= g->n || !g->members[e]) { bad = "processor patch " + std::to_string(p) + ": neighbour rank " + std::to_string(e) + " not in group"; break; }
             tcif_ctx *o = g->members[e];
             int peerOff = -1;
             for (size_t j = 0; j < o->cpPatch.size(); ++j)
-                if (o->patchNbr[o->cpPatch[j]] == c->rank) { peerOff = o->cpOff[j]; if (o->patchSize[o->cpPatch[j]] != n) failf("processor patch size mismatch"); break; }
-            if (peerOff < 0) failf("rank %d has no patch facing rank %d", e, c->rank);
-            CUDA_OK(cudaMemcpyAsync(c->recvBuf + (size_t)c->cpOff[i] * ncomp, o->sendBuf + (size_t)peerOff * ncomp,
-                                    sizeof(double) * (size_t)n * ncomp, cudaMemcpyDeviceToDevice, st));
+                if (o->patchNbr[o->cpPatch[j]] == c->rank) { peerOff = o->cpOff[j]; if (o->patchSize[o->cpPatch[j]] != n) bad = "processor patch size mismatch"; break; }
+            if (peerOff < 0) bad = "rank " + std::to_string(e) + " has no patch facing rank " + std::to_string(c->rank);
+            if (!bad.empty()) break;
+            if (cudaMemcpyAsync(c->recvBuf + (size_t)c->cpOff[i] * ncomp, o->sendBuf + (size_t)peerOff * ncomp,
+                                sizeof(double) * (size_t)n * ncomp, cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+                bad = std::string("halo copy failed: ") + cudaGetErrorString(cudaGetLastError());
         }
-        CUDA_OK(cudaStreamSynchronize(st));
+        if (cudaStreamSynchronize(st) != cudaSuccess && bad.empty()) bad = std::string("halo copy failed: ") + cudaGetErrorString(cudaGetLastError());
+        if (!bad.empty()) g->failed.store(1);
         g->barrier();
+        if (!bad.empty()) failf("%s", bad.c_str());
+        if (g->failed.load()) failf("processor-patch exchange failed on another rank of the group");
     } else if (c->nccl) {
         NCCL_OK(g_nccl.GroupStart());
         for (size_t i = 0; i < c->cpPatch.size(); ++i) {
@@ -628,13 +672,19 @@ void halo_cells(tcif_ctx *c, int ncomp, const double *const *src, double *const 
 // ---- kernel dispatch ----------------------------------------------------------------------
 int kshape(const tcif_ctx *c) { return (c->Ko == c->Kn && c->Ko >= 2 && c->Ko <= 4) ? c->Ko : 0; }
 
-#define DISPATCH_K(...)                                      \
-    switch (kshape(c)) {                                     \
-        case 3: { constexpr int KO = 3, KN = 3; (void)KO; (void)KN; __VA_ARGS__; } break; \
-        case 2: { constexpr int KO = 2, KN = 2; (void)KO; (void)KN; __VA_ARGS__; } break; \
-        case 4: { constexpr int KO = 4, KN = 4; (void)KO; (void)KN; __VA_ARGS__; } break; \
-        default: { constexpr int KO = 0, KN = 0; (void)KO; (void)KN; __VA_ARGS__; } break; \
+// fixed-K meshes: the sweeps of tcif_volume.cuh (one body for the volume launch and the deferred launch);
+// other meshes: the generic-K kernels k_* of tcif_device.cuh (volume launch + BND twin over all boundary cells)
+const SweepFns *fns(const tcif_ctx *c) {
+    switch (kshape(c)) {
+        case 2: return sweep_fns_k2();
+        case 3: return sweep_fns_k3();
+        case 4: return sweep_fns_k4();
+        default: return nullptr;
     }
+}
+// does a sweep have O(surface) work for the side stream?
+bool side_needed(const tcif_ctx *c) { return fns(c) ? (c->nDef > 0 || c->nCoupled > 0) : (c->nBndCells > 0 || c->nCoupled > 0); }
+
 #define DISPATCH_P(...)                                      \
     switch (c->P) {                                          \
         case 2: { constexpr int PP = 2; __VA_ARGS__; } break; \
@@ -653,43 +703,39 @@ ForceArgs force_args(tcif_ctx *c, bool withTensor, bool withG) {
     return a;
 }
 
-// volume sweeps (BND == false): fixed-K kernels of tcif_volume.cuh, generic-K fallback otherwise
-#define DISPATCH_KV(NEW, OLD)                                  \
-    switch (kshape(c)) {                                       \
-        case 2: { constexpr int K = 2; NEW; } break;           \
-        case 3: { constexpr int K = 3; NEW; } break;           \
-        case 4: { constexpr int K = 4; NEW; } break;           \
-        default: { OLD; } break;                               \
-    }
-
 // the force sweeps gather few arrays (their +-z planes fit in L2): ascending tile order is faster for them
 // (profiles/r02_variants.md), the strip order is for the MULES sweeps
 DMesh dm_ascending(const tcif_ctx *c) { DMesh d = c->dm; d.tileOrder = nullptr; return d; }
+// kv_div_tensor defers every boundary-adjacent cell (see tcif_volume.cuh): deferred list = bndCells
+DMesh dm_div(const tcif_ctx *c) {
+    DMesh d = c->dm;
+    d.tileOrder = nullptr; d.defMask = c->nBndCells ? d.bndMask : nullptr; d.defCells = c->bndIdentity; d.nDef = c->nBndCells;
+    return d;
+}
 
+// BND: the O(surface) launch on the side stream (deferred cells / generic-K twin)
 template <bool BND, bool WG> void launch_grad_tensor(tcif_ctx *c, const ForceArgs &a) {
+    if (const SweepFns *f = fns(c)) {
+        if (BND && !c->nDef) return;
+        f->grad_tensor(c->P, BND, BND ? c->side : c->stream, BND ? c->dm : dm_ascending(c), a);
+        c->launches++;
+        return;
+    }
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    if constexpr (!BND) {
-        int gv = cdiv(n, 256) * (256 / TCIF_TPB_FORCE), go = cdiv(n, TCIF_TPB);
-        DISPATCH_P(DISPATCH_KV((kv_grad_tensor<PP, K><<<gv, TCIF_TPB_FORCE, 0, c->stream>>>(dm_ascending(c), a)),
-                               (k_grad_tensor<PP, 0, 0, false, WG><<<go, TCIF_TPB, 0, c->stream>>>(c->dm, a))));
-    } else {
-        int grid = cdiv(n, TCIF_TPB);
-        DISPATCH_P(DISPATCH_K(k_grad_tensor<PP, KO, KN, true, WG><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, a)));
-    }
+    DISPATCH_P(k_grad_tensor<PP, 0, 0, BND, WG><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, a));
     c->launches++;
 }
 template <bool BND> void launch_div_tensor(tcif_ctx *c, const ForceArgs &a) {
+    if (const SweepFns *f = fns(c)) {
+        if (BND && !c->nBndCells) return;
+        f->div_tensor(c->P, BND, BND ? c->side : c->stream, dm_div(c), a);
+        c->launches++;
+        return;
+    }
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    if constexpr (!BND) {
-        int gv = cdiv(n, 256) * (256 / TCIF_TPB_FORCE), go = cdiv(n, TCIF_TPB);
-        DISPATCH_P(DISPATCH_KV((kv_div_tensor<PP, K><<<gv, TCIF_TPB_FORCE, 0, c->stream>>>(dm_ascending(c), a)),
-                               (k_div_tensor<PP, 0, 0, false><<<go, TCIF_TPB, 0, c->stream>>>(c->dm, a))));
-    } else {
-        int grid = cdiv(n, TCIF_TPB);
-        DISPATCH_P(DISPATCH_K(k_div_tensor<PP, KO, KN, true><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, a)));
-    }
+    DISPATCH_P(k_div_tensor<PP, 0, 0, BND><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, a));
     c->launches++;
 }
 
@@ -704,8 +750,9 @@ double bytes_div_tensor(const tcif_ctx *c) {
     return (48.0 * (c->tsum ? 1 : c->Q) + 8 + 4.0 * (c->Ko + c->Kn) + 32.0 * c->Ko + 24) * c->nC;
 }
 // MULES sweeps: arrays shared by the phases of a batch (slot indices, V, phi) are counted once per launch
-double bytes_mules_setup(const tcif_ctx *c, int nPh) {
+double bytes_mules_setup(const tcif_ctx *c, int nPh, bool storeOld = false) {
     double shared = 4.0 * (c->Ko + c->Kn) + 8 /*V*/ + 8.0 * c->Ko /*phi*/;
+    (void)storeOld;      // psi0 is one 8 B stream either way: read, or (storeOld) written
     double perPh = 8 + 8 /*psi psi0*/ + 8.0 * c->Ko * 2 /*phiIn phiCorr*/ + 48 /*Q+-,s+-,l+-*/;
     return (double)c->nC * (shared + nPh * perPh);
 }
@@ -723,6 +770,12 @@ double bytes_mules_final(const tcif_ctx *c, int nPh, int mode, bool first) {
 }
 
 inline void touch(tcif_ctx *c) { ++c->fieldsVersion; }   // alpha / T / sigma changed: F is stale
+// the device changed alpha_p: F is stale and no host field equals the device copy any more
+inline void alpha_changed(tcif_ctx *c, int p) { ++c->fieldsVersion; c->alphaStamp[p] = 0; }
+inline bool sigma_needs_T(const tcif_ctx *c) {
+    for (int q = 0; q < c->Q; ++q) if (!c->sigSet[q] || c->hSig[q].kind != SIGMA_CONSTANT) return true;
+    return false;
+}
 
 void do_force(tcif_ctx *c) {
     if (c->Q < 1) failf("divCapillaryStress needs at least two phases");
@@ -736,7 +789,7 @@ void do_force(tcif_ctx *c) {
     ensure_deltaN(c);
     ForceArgs a = force_args(c, true, false);
     sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, true, false), [&] { launch_grad_tensor<false, false>(c, a); }); },
-             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, false>(c, a); }); });
+             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, false>(c, a); }); }, side_needed(c));
     sweep(c, [&] { timed(c, T_DIV_TENSOR, bytes_div_tensor(c), [&] { launch_div_tensor<false>(c, a); }); },
              [&] {
                  if (c->nCoupled) {      // neighbour-rank tensors of the processor faces: hidden behind the volume sweep
@@ -746,7 +799,7 @@ void do_force(tcif_ctx *c) {
                      halo_cells(c, nT, src, dst, c->side);
                  }
                  timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_div_tensor<true>(c, a); });
-             });
+             }, c->nBndCells > 0 || c->nCoupled > 0);
     join(c);
     if (c->nBF) {
         timed(c, T_BOUNDARY, 0, [&] {
@@ -768,7 +821,7 @@ void do_grad(tcif_ctx *c) {
     if (!c->G) { c->G = c->dalloc<double>((size_t)c->P * 3 * c->stride); c->Gb = c->dalloc<double>((size_t)c->P * 3 * std::max(c->nBF, 1)); }
     ForceArgs a = force_args(c, false, true);
     sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, false, true), [&] { launch_grad_tensor<false, true>(c, a); }); },
-             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, a); }); });
+             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, a); }); }, side_needed(c));
     join(c);
     if (!c->nBF) return;
     for (int p = 0; p < c->P; ++p) {
@@ -791,7 +844,7 @@ void do_grad(tcif_ctx *c) {
 
 // psi.correctBoundaryConditions() for a set of phases: zeroGradient patches + processor halo
 void correct_alpha_bcs(tcif_ctx *c, const int *phases, int nPh) {
-    touch(c);
+    for (int k = 0; k < nPh; ++k) alpha_changed(c, phases[k]);
     if (!c->nBF) return;
     for (int k = 0; k < nPh; ++k) {
         int p = phases[k];
@@ -813,7 +866,7 @@ MulesBatch mules_batch(tcif_ctx *c, const int *phases, int nPh, bool fromHO) {
     for (int k = 0; k < nPh; ++k) {
         int p = phases[k];
         MulesPh &ph = b.ph[k];
-        ph.psi = c->alpha[p]; ph.psi0 = c->alpha0[p]; ph.psib = c->alphab[p];
+        ph.psi = c->alpha[p]; ph.psi0 = c->alpha0[p]; ph.psi0w = c->alpha0[p]; ph.psib = c->alphab[p];
         ph.Su = c->haveSu[p] ? c->Su[p] : nullptr; ph.Sp = c->haveSp[p] ? c->Sp[p] : nullptr;
         ph.bc = c->bc[p];
         ph.phiIn = fromHO ? c->phiHO[p] : c->phiPsi[p]; ph.phiInb = fromHO ? c->phiHOb[p] : c->phiPsib[p];
@@ -828,22 +881,6 @@ MulesBatch mules_batch(tcif_ctx *c, const int *phases, int nPh, bool fromHO) {
     return b;
 }
 
-// Phase-looped volume kernels (kvp_*, tcif_volume.cuh): batches of 2 or 3 phases on fixed-K meshes.
-// TCIF_KVP=0 falls back to the (cell, phase)-per-thread kernels (A/B and debugging aid).
-bool use_kvp(tcif_ctx *c, const MulesBatch &b) {
-    static const int on = [] { const char *e = getenv("TCIF_KVP"); return e ? atoi(e) : 1; }();
-    return on && kshape(c) != 0 && (b.nPh == 2 || b.nPh == 3);
-}
-#define DISPATCH_KVP(CALL)                                                         \
-    switch (kshape(c) * 10 + b.nPh) {                                              \
-        case 22: { constexpr int K = 2, NPH = 2; CALL; } break;                    \
-        case 23: { constexpr int K = 2, NPH = 3; CALL; } break;                    \
-        case 32: { constexpr int K = 3, NPH = 2; CALL; } break;                    \
-        case 33: { constexpr int K = 3, NPH = 3; CALL; } break;                    \
-        case 42: { constexpr int K = 4, NPH = 2; CALL; } break;                    \
-        case 43: { constexpr int K = 4, NPH = 3; CALL; } break;                    \
-        default: failf("kvp dispatch: unsupported shape");                         \
-    }
 // ping-pong buffers of the limiter resolved for one sweep
 MulesBatch resolve_flip(const MulesBatch &b0, int flip) {
     MulesBatch b = b0;
@@ -856,68 +893,41 @@ MulesBatch resolve_flip(const MulesBatch &b0, int flip) {
 }
 
 template <bool BND> void launch_setup(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm) {
+    if (const SweepFns *f = fns(c)) {
+        if (BND && !c->nDef) return;
+        f->setup(b.nPh, BND, BND ? c->side : c->stream, c->dm, b, prm);
+        c->launches++;
+        return;
+    }
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    int grid = cdiv(n, TCIF_TPB) * b.nPh;
-    if constexpr (!BND) {
-        if (use_kvp(c, b)) {
-            DISPATCH_KVP((kvp_mules_setup<K, NPH><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)));
-            c->launches++; return;
-        }
-        DISPATCH_KV((kv_mules_setup<K><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)),
-                    (k_mules_setup<0, 0, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm)));
-    } else {
-        DISPATCH_K(k_mules_setup<KO, KN, true><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, b, prm));
-    }
+    k_mules_setup<0, 0, BND><<<cdiv(n, TCIF_TPB) * b.nPh, TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, b, prm);
     c->launches++;
 }
 template <bool BND> void launch_iter(tcif_ctx *c, const MulesBatch &b, int first, int flip) {
+    if (const SweepFns *f = fns(c)) {
+        if (BND && !c->nDef) return;
+        f->iter(b.nPh, first != 0, BND, BND ? c->side : c->stream, c->dm, resolve_flip(b, flip));
+        c->launches++;
+        return;
+    }
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    int grid = cdiv(n, TCIF_TPB) * b.nPh;
-    if constexpr (!BND) {
-        if (use_kvp(c, b)) {
-            const MulesBatch br = resolve_flip(b, flip);
-            if (first) { DISPATCH_KVP((kvp_mules_iter<K, true, NPH><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, br))); }
-            else       { DISPATCH_KVP((kvp_mules_iter<K, false, NPH><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, br))); }
-            c->launches++; return;
-        }
-        if (first) {
-            DISPATCH_KV((kv_mules_iter<K, true><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, flip)),
-                        (k_mules_iter<0, 0, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, first, flip)));
-        } else {
-            DISPATCH_KV((kv_mules_iter<K, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, flip)),
-                        (k_mules_iter<0, 0, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, first, flip)));
-        }
-    } else {
-        DISPATCH_K(k_mules_iter<KO, KN, true><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, b, first, flip));
-    }
+    k_mules_iter<0, 0, BND><<<cdiv(n, TCIF_TPB) * b.nPh, TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, b, first, flip);
     c->launches++;
 }
-template <bool BND, int MODE, bool LSUM = false>
-void launch_final(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm, int first, int flip, int nIter) {
+template <bool BND, int MODE>
+void launch_final(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm, int first, int flip, int nIter, bool lsum = false) {
+    if (const SweepFns *f = fns(c)) {
+        if (BND && !c->nDef) return;
+        f->fin(b.nPh, MODE, first != 0, lsum, BND, BND ? c->side : c->stream, c->dm, resolve_flip(b, flip), prm, nIter);
+        c->launches++;
+        return;
+    }
+    if (lsum) failf("launch_final: fused limitSum needs the fixed-K kernels");
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    int grid = cdiv(n, TCIF_TPB) * b.nPh;
-    if constexpr (!BND) {
-        if (use_kvp(c, b)) {
-            const MulesBatch br = resolve_flip(b, flip);
-            constexpr bool LS = LSUM && MODE == 0;
-            if (first) { DISPATCH_KVP((kvp_mules_final<K, MODE, true, NPH, LS><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, br, prm, nIter))); }
-            else       { DISPATCH_KVP((kvp_mules_final<K, MODE, false, NPH, LS><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, br, prm, nIter))); }
-            c->launches++; return;
-        }
-        if (LSUM) failf("launch_final: fused limitSum needs the phase-looped kernels");
-        if (first) {
-            DISPATCH_KV((kv_mules_final<K, MODE, true><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter)),
-                        (k_mules_final<0, 0, false, MODE><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, first, flip, nIter)));
-        } else {
-            DISPATCH_KV((kv_mules_final<K, MODE, false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, flip, nIter)),
-                        (k_mules_final<0, 0, false, MODE><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, first, flip, nIter)));
-        }
-    } else {
-        DISPATCH_K(k_mules_final<KO, KN, true, MODE><<<grid, TCIF_TPB, 0, c->side>>>(c->dm, b, prm, first, flip, nIter));
-    }
+    k_mules_final<0, 0, BND, MODE><<<cdiv(n, TCIF_TPB) * b.nPh, TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, b, prm, first, flip, nIter);
     c->launches++;
 }
 
@@ -933,9 +943,11 @@ void halo_lambda(tcif_ctx *c, const MulesBatch &b, int flip) {
 
 // MULES::limit for a batch of phases.  mode 0: returnCorr=true; 1: returnCorr=false;
 // 2: explicitSolve's limit fused with surfaceIntegrate + Euler update (psi -> alphaNew).
-// fuseLimitSum (mode 0, batch = all phases): limitSum of the interior cells' owner faces rides on the apply sweep;
+// fuseLimitSum (mode 0, batch = all phases): limitSum of the owner faces rides on the apply sweep;
 // the caller finishes with do_limit_sum_rest().
-void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode, bool addUpwind, bool fromHO, bool fuseLimitSum = false) {
+// storeOld: psi.oldTime() := psi for the phases of the batch before anything else (rides on the set-up sweep).
+void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode, bool addUpwind, bool fromHO,
+              bool fuseLimitSum = false, bool storeOld = false) {
     require_comm(c);
     MulesBatch b = mules_batch(c, phases, nPh, fromHO);
     MulesParams prm{};
@@ -943,37 +955,48 @@ void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode,
     prm.extremaCoeff = c->cfg.extremaCoeff; prm.smoothLimiter = c->cfg.smoothLimiter;
     prm.boundaryExtrema = c->cfg.boundaryExtrema; prm.addUpwind = addUpwind ? 1 : 0;
     prm.phi = c->phi; prm.phib = c->phib;
+    if (storeOld) {
+        if (fns(c)) prm.storeOld = 1;
+        else for (int k = 0; k < nPh; ++k)
+            CUDA_OK(cudaMemcpyAsync(c->alpha0[phases[k]], c->alpha[phases[k]], sizeof(double) * c->nC, cudaMemcpyDeviceToDevice, c->stream));
+    }
     const int L = c->cfg.nLimiterIter;
-    sweep(c, [&] { timed(c, T_MULES_SETUP, bytes_mules_setup(c, nPh), [&] { launch_setup<false>(c, b, prm); }); },
-             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_setup<true>(c, b, prm); }); });
+    const bool side = side_needed(c);
+    sweep(c, [&] { timed(c, T_MULES_SETUP, bytes_mules_setup(c, nPh, prm.storeOld != 0), [&] { launch_setup<false>(c, b, prm); }); },
+             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_setup<true>(c, b, prm); }); }, side);
     int first = 1, flip = 0;
     for (int j = 1; j < L; ++j) {
         sweep(c, [&] { timed(c, T_MULES_ITER, bytes_mules_iter(c, nPh, first), [&] { launch_iter<false>(c, b, first, flip); }); },
                  [&] { halo_lambda(c, b, flip);      // syncTools::syncFaceList(min) of the previous iteration
-                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b, first, flip); }); });
+                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b, first, flip); }); }, side);
         flip ^= 1; first = 0;
     }
     double fb = bytes_mules_final(c, nPh, mode, first);
+    if (fuseLimitSum && (mode != 0 || !fns(c))) failf("do_limit: fused limitSum needs the fixed-K kernels and returnCorr=true");
     auto fin = [&](auto modeTag) {
         constexpr int MODE = decltype(modeTag)::value;
-        sweep(c, [&] { timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, MODE>(c, b, prm, first, flip, L); }); },
+        sweep(c, [&] { timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, MODE>(c, b, prm, first, flip, L, fuseLimitSum); }); },
                  [&] { if (L > 0) halo_lambda(c, b, flip);
-                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_final<true, MODE>(c, b, prm, first, flip, L); }); });
+                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_final<true, MODE>(c, b, prm, first, flip, L, fuseLimitSum); }); }, side);
     };
-    if (mode == 0 && fuseLimitSum) {
-        if (!use_kvp(c, b)) failf("do_limit: fused limitSum requested without the phase-looped kernels");
-        sweep(c, [&] { timed(c, T_MULES_FINAL, fb + 0.0, [&] { launch_final<false, 0, true>(c, b, prm, first, flip, L); }); },
-                 [&] { if (L > 0) halo_lambda(c, b, flip);
-                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_final<true, 0>(c, b, prm, first, flip, L); }); });
-    }
-    else if (mode == 0) fin(std::integral_constant<int, 0>{});
+    if (mode == 0) fin(std::integral_constant<int, 0>{});
     else if (mode == 1) fin(std::integral_constant<int, 1>{});
     else {
         fin(std::integral_constant<int, 2>{});
-        for (int k = 0; k < nPh; ++k) std::swap(c->alpha[phases[k]], c->alphaNew[phases[k]]);
-        touch(c);
+        for (int k = 0; k < nPh; ++k) { std::swap(c->alpha[phases[k]], c->alphaNew[phases[k]]); alpha_changed(c, phases[k]); }
     }
     join(c);
+}
+
+void do_limit_sum_coupled(tcif_ctx *c) {
+    if (!c->nCoupled) return;
+    LimitSumArgs ab{};
+    ab.nPh = c->P;
+    for (int p = 0; p < c->P; ++p) ab.f[p] = c->phiPsib[p];
+    timed(c, T_BOUNDARY, 0, [&] {
+        k_limit_sum_coupled<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nCoupled, c->dm.coupledFaces, ab);
+        c->launches++;
+    });
 }
 
 void do_limit_sum(tcif_ctx *c) {
@@ -984,44 +1007,14 @@ void do_limit_sum(tcif_ctx *c) {
         k_limit_sum<<<cdiv((long long)c->nFd, TCIF_TPB), TCIF_TPB, 0, c->stream>>>((int)c->nFd, a);
         c->launches++;
     });
-    if (c->nCoupled) {
-        LimitSumArgs ab{};
-        ab.nPh = c->P;
-        for (int p = 0; p < c->P; ++p) ab.f[p] = c->phiPsib[p];
-        timed(c, T_BOUNDARY, 0, [&] {
-            k_limit_sum_coupled<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nCoupled, c->dm.coupledFaces, ab);
-            c->launches++;
-        });
-    }
+    do_limit_sum_coupled(c);
 }
 
 // whether limit(all phases, returnCorr=true) + limitSum can run fused (do_limit(..., fuseLimitSum=true) + do_limit_sum_rest)
-bool can_fuse_limit_sum(tcif_ctx *c) {
-    MulesBatch b{};
-    b.nPh = c->P;
-    return use_kvp(c, b);
-}
-// the part of limitSum the fused volume sweep did not cover: owner faces of boundary-adjacent cells, coupled faces
-void do_limit_sum_rest(tcif_ctx *c) {
-    LimitSumArgs a{};
-    a.nPh = c->P;
-    for (int p = 0; p < c->P; ++p) a.f[p] = c->phiPsi[p];
-    if (c->nBndCells) {
-        timed(c, T_BOUNDARY, 0, [&] {
-            k_limit_sum_bndcells<<<cdiv(c->nBndCells * c->Ko, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a);
-            c->launches++;
-        });
-    }
-    if (c->nCoupled) {
-        LimitSumArgs ab{};
-        ab.nPh = c->P;
-        for (int p = 0; p < c->P; ++p) ab.f[p] = c->phiPsib[p];
-        timed(c, T_BOUNDARY, 0, [&] {
-            k_limit_sum_coupled<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->nCoupled, c->dm.coupledFaces, ab);
-            c->launches++;
-        });
-    }
-}
+bool can_fuse_limit_sum(tcif_ctx *c) { return fns(c) != nullptr; }
+// the part of limitSum the fused sweep did not cover: the coupled patch faces (every internal face is owned by a cell
+// of the volume or the deferred launch)
+void do_limit_sum_rest(tcif_ctx *c) { do_limit_sum_coupled(c); }
 
 // MULES::explicitSolve for a batch of phases (optionally preceded by phiAlpha += upwind flux)
 void do_explicit(tcif_ctx *c, const int *phases, int nPh, double deltaT, bool addUpwind) {
@@ -1035,7 +1028,7 @@ void do_explicit(tcif_ctx *c, const int *phases, int nPh, double deltaT, bool ad
 void do_add_upwind(tcif_ctx *c, int phase) {
     timed(c, T_MULES_SETUP, 0, [&] {
         int grid = cdiv(c->nC, TCIF_TPB);
-        DISPATCH_K(k_add_upwind<KO><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, c->phi, c->alpha[phase], c->phiPsi[phase]));
+        k_add_upwind<0><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, c->phi, c->alpha[phase], c->phiPsi[phase]);
         c->launches++;
         if (c->nBF) {
             k_add_upwind_bnd<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->phib, c->alpha[phase], c->alphab[phase], c->phiPsib[phase]);
@@ -1079,7 +1072,7 @@ void do_flux_assembly(tcif_ctx *c, int schemePhi, int schemePhir, PhicState &st)
     ensure_G(c);
     ForceArgs ga = force_args(c, false, true);
     sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, false, true), [&] { launch_grad_tensor<false, true>(c, ga); }); },
-             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, ga); }); });
+             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, ga); }); }, side_needed(c));
     join(c);
     if (c->nCoupled) {                            // neighbour-rank gradients on processor faces
         const double *src[36]; double *dst[36];
@@ -1150,8 +1143,7 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
                            k_pred_setup<true><<<gridB, TCIF_TPB, 0, c->side>>>(c->dm, b); c->launches++; }); });
     }
     bool active[4] = {true, true, true, true};
-    bool kvpPred;
-    { MulesBatch mb{}; mb.nPh = nPh; kvpPred = use_kvp(c, mb); }
+    const SweepFns *kvpPred = fns(c);
     for (int it = 0; it < maxIter; ++it) {
         bool any = false;
         for (int k = 0; k < nPh; ++k) any = any || active[k];
@@ -1159,7 +1151,7 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
         CUDA_OK(cudaMemsetAsync(c->dmaxDev, 0, sizeof(double) * 8, c->stream));
         PredBatch b = batch(active);
         sweep(c, [&] { timed(c, T_PREDICTOR, (double)nPh * c->nC * (32.0 + 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko), [&] {
-                           if (kvpPred) { DISPATCH_KVP((kvp_pred_jacobi<K, NPH><<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, b))); }
+                           if (kvpPred) kvpPred->pred_jacobi(nPh, c->stream, c->dm, b);
                            else k_pred_jacobi<false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b);
                            c->launches++; }); },
                  [&] {
@@ -1180,7 +1172,7 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
         for (int k = 0; k < nPh; ++k) {
             if (!active[k]) continue;
             std::swap(c->alpha[phases[k]], c->alphaNew[phases[k]]);
-            touch(c);
+            alpha_changed(c, phases[k]);
             c->predictorSweeps[phases[k]]++;
             if (v[k] <= tol) active[k] = false;
         }
@@ -1202,9 +1194,8 @@ void do_stage(tcif_ctx *c, double deltaT) {
 }
 void do_mules_stage(tcif_ctx *c, double deltaT) {
     int all[4] = {0, 1, 2, 3};
-    store_old(c);
     const bool fuse = can_fuse_limit_sum(c);
-    do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true, fuse); // multiphaseSystem.C:296-319
+    do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true, fuse, true); // alpha.oldTime() := alpha, then multiphaseSystem.C:296-319
     if (fuse) do_limit_sum_rest(c); else do_limit_sum(c);       // :321
     do_explicit(c, all, c->P, deltaT, true);                    // :346 (bounded flux) + :365-375
 }
@@ -1228,7 +1219,7 @@ void do_rho_phi(tcif_ctx *c, double wgt, bool accumulate) {
 
 // alpha += alpha*(1 - sumAlpha), cells and patch values   (multiphaseSystem.C:414-426)
 void do_renormalise(tcif_ctx *c) {
-    touch(c);
+    for (int p = 0; p < c->P; ++p) alpha_changed(c, p);
     RenormArgs r{};
     r.P = c->P;
     for (int p = 0; p < c->P; ++p) r.a[p] = c->alpha[p];
@@ -1743,17 +1734,37 @@ void laser_sync_points(tcif_ctx *c) {
 // neighbour rank between generations), Q /= V
 int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const double *p1, const double *I, const double *dA,
                        const int32_t *cell, double sigmaSB, int maxParticles) {
-    if (!c->laserGeoSet) failf("tcif_laser_calculate: call tcif_laser_set_polymesh first");
-    if (!c->haveT) failf("tcif_laser_calculate: temperature not set");
-    if (!c->lzAbsFields && c->lzNAbs == 0) failf("tcif_laser_calculate: no absorption model set");
-    if (nParticles < 0 || (nParticles && (!p0 || !p1 || !I || !dA || !cell))) failf("tcif_laser_calculate: bad arguments");
+    // On a decomposed mesh every check below is made by all ranks and agreed on BEFORE anybody throws: a rank-local
+    // throw would leave the others waiting in the next collective.
     const int nCp = (int)c->cpPatch.size();
     const bool par = c->nCoupled > 0;
+    std::string argErr;
+    if (!c->laserGeoSet) argErr = "call tcif_laser_set_polymesh first";
+    else if (!c->haveT) argErr = "temperature not set";
+    else if (!c->lzAbsFields && c->lzNAbs == 0) argErr = "no absorption model set";
+    else if (nParticles < 0 || (nParticles && (!p0 || !p1 || !I || !dA || !cell))) argErr = "bad arguments";
+    else if (par && !c->lzSharedSet) argErr = "mesh has processor patches, call tcif_laser_set_shared_points first";
+    else if (par && nCp > 64) argErr = "more than 64 processor patches";
+    int nSeeds = 0;
+    if (argErr.empty())
+        for (int k = 0; k < nParticles; ++k) {
+            if (cell[k] < 0) continue;
+            if (cell[k] >= c->nC) { argErr = "cell[" + std::to_string(k) + "] out of range"; break; }
+            ++nSeeds;
+        }
+    // seeds of the whole cloud (each seed is owned by the one rank that found its cell, laserDTRM.C:287-296) and the
+    // largest maxParticles: cloud and mailbox capacities must be the same on every rank, because a rank with few or no
+    // seeds of its own can receive the whole cloud from its neighbours
+    long long globalSeeds = nSeeds;
+    int maxPartAll = maxParticles;
     if (par) {
         require_comm(c);
-        if (!c->lzSharedSet) failf("tcif_laser_calculate: mesh has processor patches, call tcif_laser_set_shared_points first");
-        if (nCp > 64) failf("tcif_laser_calculate: more than 64 processor patches");
-    }
+        double v[3] = {argErr.empty() ? 0.0 : 1.0, (double)nSeeds, (double)maxParticles};
+        const int ops[3] = {RED_MAX, RED_SUM, RED_MAX};
+        allreduce_host(c, v, ops, 3);
+        if (v[0] != 0.0) failf("tcif_laser_calculate: %s", argErr.empty() ? "another rank rejected its arguments" : argErr.c_str());
+        globalSeeds = (long long)v[1]; maxPartAll = (int)v[2];
+    } else if (!argErr.empty()) failf("tcif_laser_calculate: %s", argErr.c_str());
     if (c->lzDeltaN == 0.0) {
         double v[2] = {c->sumV, (double)c->nC};
         int ops[2] = {RED_SUM, RED_SUM};
@@ -1774,23 +1785,23 @@ int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const doub
     seeds.reserve(nParticles);
     for (int k = 0; k < nParticles; ++k) {
         if (cell[k] < 0) continue;
-        if (cell[k] >= c->nC) failf("tcif_laser_calculate: cell[%d] out of range", k);
         LaserPart q{};
         for (int d = 0; d < 3; ++d) { q.pos[d] = q.p0[d] = p0[3 * (size_t)k + d]; q.p1[d] = p1[3 * (size_t)k + d]; }
         q.I0 = q.I = I[k]; q.dA = dA[k]; q.frac = 0; q.cell = cell[k]; q.tid = -1; q.face = -1; q.keep = 1;
         seeds.push_back(q);
     }
-    const int nSeeds = (int)seeds.size();
-    // on a decomposed mesh any rank may end up walking every ray: capacity from the full seed list
-    const int base = par ? std::max(nParticles, 1) : std::max(nSeeds, 1);
-    const int cap = std::max(maxParticles > 0 ? maxParticles : 64 * base, nSeeds);
+    // on a decomposed mesh any rank may end up walking every ray: capacity from the global seed count
+    const long long base = std::max<long long>(globalSeeds, 1);
+    const long long cap64 = std::max<long long>(maxPartAll > 0 ? maxPartAll : 64 * base, nSeeds);
+    if (cap64 > 0x7fffffffLL / 2) failf("tcif_laser_calculate: cloud capacity %lld too large", cap64);
+    const int cap = (int)cap64;
     if (cap > c->lzCap) {
         if (c->lzCloud) CUDA_OK(cudaFree(c->lzCloud));
         c->lzCloud = nullptr; c->lzCap = 0;
         CUDA_OK(cudaMalloc((void **)&c->lzCloud, sizeof(LaserPart) * (size_t)cap));
         c->lzCap = cap;
     }
-    const int mailCap = par ? std::max(4 * nParticles, 1024) : 0;
+    const int mailCap = par ? (int)std::min<long long>(std::max<long long>(4 * base, 1024), cap64) : 0;
     if (par && mailCap > c->lzMailCap) {
         if (c->lzOutbox) CUDA_OK(cudaFree(c->lzOutbox));
         if (c->lzInbox) CUDA_OK(cudaFree(c->lzInbox));
@@ -1836,12 +1847,13 @@ int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const doub
             continue;
         }
         // hand-over: every rank learns how many particles each rank sends to each rank, who failed, who still has work
-        std::vector<double> mine(c->nRanks + 2, 0.0), all;
+        std::vector<double> mine(c->nRanks + 3, 0.0), all;
         for (int i = 0; i < nCp; ++i) mine[c->patchNbr[c->cpPatch[i]]] += cnt[4 + i];
         mine[c->nRanks] = error.empty() ? 0.0 : 1.0;
         mine[c->nRanks + 1] = total - done;
-        allgather_host(c, mine.data(), c->nRanks + 2, all);
-        const int W = c->nRanks + 2;
+        mine[c->nRanks + 2] = cap - total;                 // free slots of this rank's cloud
+        allgather_host(c, mine.data(), c->nRanks + 3, all);
+        const int W = c->nRanks + 3;
         bool anyErr = false;
         double pending = 0.0;
         for (int r = 0; r < c->nRanks; ++r) {
@@ -1850,23 +1862,40 @@ int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const doub
             for (int e = 0; e < c->nRanks; ++e) pending += all[(size_t)r * W + e];
         }
         if (anyErr) failf("tcif_laser_calculate: %s", error.empty() ? "another rank failed" : error.c_str());
+        // receiver-side capacity, evaluated by every rank for every rank (the counts and the free slots are global
+        // knowledge now), so that all ranks fail together
+        for (int r = 0; r < c->nRanks; ++r) {
+            double got = 0.0;
+            for (int e = 0; e < c->nRanks; ++e) {
+                const double n = all[(size_t)e * W + r];
+                if (n > c->lzMailCap) failf("tcif_laser_calculate: %d particles handed from rank %d to rank %d exceed the mailbox (%d), raise maxParticles", (int)n, e, r, c->lzMailCap);
+                got += n;
+            }
+            if (got > all[(size_t)r * W + c->nRanks + 2])
+                failf("tcif_laser_calculate: cloud overflow on hand-over to rank %d, raise maxParticles (capacity %d)", r, cap);
+        }
         if (pending == 0.0) break;
         std::vector<int> inCount(nCp, 0);
         for (int i = 0; i < nCp; ++i) inCount[i] = (int)all[(size_t)c->patchNbr[c->cpPatch[i]] * W + c->rank];
         if (c->group) {
             tcif_group *g = c->group;
             g->barrier();
-            for (int i = 0; i < nCp; ++i) {
+            std::string bad;
+            for (int i = 0; i < nCp && bad.empty(); ++i) {
                 if (!inCount[i]) continue;
                 tcif_ctx *o = g->members[c->patchNbr[c->cpPatch[i]]];
                 int peer = -1;
-                for (size_t j = 0; j < o->cpPatch.size(); ++j) if (o->patchNbr[o->cpPatch[j]] == c->rank) { peer = (int)j; break; }
-                if (peer < 0) failf("tcif_laser_calculate: neighbour rank has no patch facing this rank");
-                CUDA_OK(cudaMemcpyAsync(c->lzInbox + (size_t)i * c->lzMailCap, o->lzOutbox + (size_t)peer * o->lzMailCap,
-                                        sizeof(LaserPart) * inCount[i], cudaMemcpyDeviceToDevice, c->stream));
+                for (size_t j = 0; o && j < o->cpPatch.size(); ++j) if (o->patchNbr[o->cpPatch[j]] == c->rank) { peer = (int)j; break; }
+                if (peer < 0) { bad = "neighbour rank has no patch facing this rank"; break; }
+                if (cudaMemcpyAsync(c->lzInbox + (size_t)i * c->lzMailCap, o->lzOutbox + (size_t)peer * o->lzMailCap,
+                                    sizeof(LaserPart) * inCount[i], cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess)
+                    bad = std::string("hand-over copy failed: ") + cudaGetErrorString(cudaGetLastError());
             }
-            CUDA_OK(cudaStreamSynchronize(c->stream));
+            if (cudaStreamSynchronize(c->stream) != cudaSuccess && bad.empty()) bad = std::string("hand-over copy failed: ") + cudaGetErrorString(cudaGetLastError());
+            if (!bad.empty()) g->failed.store(1);
             g->barrier();
+            if (!bad.empty()) failf("tcif_laser_calculate: %s", bad.c_str());
+            if (g->failed.load()) failf("tcif_laser_calculate: hand-over failed on another rank of the group");
         } else {
             static_assert(sizeof(LaserPart) % sizeof(double) == 0, "LaserPart is sent as doubles");
             const size_t dpp = sizeof(LaserPart) / sizeof(double);
@@ -1880,7 +1909,7 @@ int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const doub
         }
         int got = 0;
         for (int i = 0; i < nCp; ++i) got += inCount[i];
-        if (total + got > cap) failf("tcif_laser_calculate: cloud overflow on hand-over, raise maxParticles (capacity %d)", cap);
+        if (total + got > cap) failf("tcif_laser_calculate: internal error: hand-over exceeds the agreed capacity %d", cap);
         for (int i = 0; i < nCp; ++i) {
             if (!inCount[i]) continue;
             k_laser_receive<<<cdiv(inCount[i], TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->lg, inCount[i], c->lzInbox + (size_t)i * c->lzMailCap,
@@ -2108,10 +2137,14 @@ int tcif_comm_init_local(tcif_ctx *c, int rank, tcif_group *g) {
 // ---- fields ---------------------------------------------------------------------------------
 int tcif_set_alpha_bc(tcif_ctx *c, int phase, const int32_t *bcKind) {
     API_BEGIN(c)
-    touch(c);
     check_phase(c, phase);
     if (c->nPatches) {
+        if (!bcKind) failf("tcif_set_alpha_bc: null kinds");
         for (int p = 0; p < c->nPatches; ++p) if (bcKind[p] != TCIF_BC_ZERO_GRADIENT && bcKind[p] != TCIF_BC_FIXED_VALUE) failf("unsupported alpha boundary condition %d on patch %d", bcKind[p], p);
+        std::vector<int> &h = c->bcHost[phase];
+        if (h.size() == (size_t)c->nPatches && std::equal(h.begin(), h.end(), bcKind)) return 0;    // unchanged: F stays valid
+        h.assign(bcKind, bcKind + c->nPatches);
+        touch(c);
         CUDA_OK(cudaMemcpyAsync(c->bc[phase], bcKind, sizeof(int) * c->nPatches, cudaMemcpyDefault, c->stream));
         CUDA_OK(cudaStreamSynchronize(c->stream));
     }
@@ -2120,13 +2153,43 @@ int tcif_set_alpha_bc(tcif_ctx *c, int phase, const int32_t *bcKind) {
 
 int tcif_set_alpha(tcif_ctx *c, int phase, const double *internal, const double *boundary) {
     API_BEGIN(c)
-    touch(c);
     check_phase(c, phase);
     if (!internal || (c->nBF && !boundary)) failf("tcif_set_alpha: null field");
+    alpha_changed(c, phase);
+    c->xfer[0]++;
     up_cells(c, c->alpha[phase], internal);
     up_bnd(c, c->alphab[phase], boundary);
     CUDA_OK(cudaStreamSynchronize(c->stream));
     API_END(c)
+}
+
+int tcif_set_alpha_stamped(tcif_ctx *c, int phase, uint64_t stamp, const double *internal, const double *boundary, int32_t *uploaded) {
+    if (uploaded) *uploaded = 0;
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (!internal || (c->nBF && !boundary)) failf("tcif_set_alpha_stamped: null field");
+    if (stamp != 0 && stamp == c->alphaStamp[phase]) { c->xfer[1]++; return 0; }      // the device copy IS this field
+    alpha_changed(c, phase);
+    c->xfer[0]++;
+    up_cells(c, c->alpha[phase], internal);
+    up_bnd(c, c->alphab[phase], boundary);
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    c->alphaStamp[phase] = stamp;
+    if (uploaded) *uploaded = 1;
+    API_END(c)
+}
+
+int tcif_mark_alpha(tcif_ctx *c, int phase, uint64_t stamp) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    c->alphaStamp[phase] = stamp;
+    API_END(c)
+}
+
+int tcif_transfer_counters(const tcif_ctx *c, int64_t uploads[4]) {
+    if (!c || !uploads) return 1;
+    for (int i = 0; i < 4; ++i) uploads[i] = c->xfer[i];
+    return 0;
 }
 
 int tcif_get_alpha(tcif_ctx *c, int phase, double *internal, double *boundary) {
@@ -2157,10 +2220,28 @@ int tcif_set_temperature(tcif_ctx *c, const double *internal, const double *boun
     API_BEGIN(c)
     touch(c);
     if (!internal || (c->nBF && !boundary)) failf("tcif_set_temperature: null field");
+    c->tStamp = 0;
+    c->xfer[2]++;
     up_cells(c, c->Tc, internal);
     up_bnd(c, c->Tb, boundary);
     c->haveT = true;
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    API_END(c)
+}
+
+int tcif_set_temperature_stamped(tcif_ctx *c, uint64_t stamp, const double *internal, const double *boundary, int32_t *uploaded) {
+    if (uploaded) *uploaded = 0;
+    API_BEGIN(c)
+    if (!internal || (c->nBF && !boundary)) failf("tcif_set_temperature_stamped: null field");
+    if (stamp != 0 && stamp == c->tStamp && c->haveT) { c->xfer[3]++; return 0; }
+    if (sigma_needs_T(c)) touch(c);          // F depends on T only through a temperatureDependent sigma
+    c->xfer[2]++;
+    up_cells(c, c->Tc, internal);
+    up_bnd(c, c->Tb, boundary);
+    c->haveT = true;
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    c->tStamp = stamp;
+    if (uploaded) *uploaded = 1;
     API_END(c)
 }
 
@@ -2410,6 +2491,7 @@ int tcif_laser_get(tcif_ctx *c, double *Q, int32_t *reflectingCells, double *nHa
 }
 
 int tcif_laser_get_sparse(tcif_ctx *c, int32_t capacity, int32_t *cells, double *values, int32_t *n) {
+    if (n) *n = 0;               // callers tell "capacity too small" (rc != 0, *n > capacity) from any other failure (*n == 0)
     API_BEGIN(c)
     if (!c->laserGeoSet) failf("tcif_laser_get_sparse: call tcif_laser_set_polymesh first");
     if (capacity < 0 || (capacity && (!cells || !values)) || !n) failf("tcif_laser_get_sparse: bad arguments");
@@ -2463,7 +2545,8 @@ int tcif_div_capillary_stress_host(tcif_ctx *c, const double *const *ai, const d
                                    const double *Tb, double *Fi, double *Fb) {
     API_BEGIN(c)
     if (!ai || (c->nBF && !ab)) failf("tcif_div_capillary_stress_host: null alpha lists");
-    touch(c);
+    for (int p = 0; p < c->P; ++p) alpha_changed(c, p);
+    c->tStamp = 0;
     for (int p = 0; p < c->P; ++p) { up_cells(c, c->alpha[p], ai[p]); if (c->nBF) up_bnd(c, c->alphab[p], ab[p]); }
     if (Ti) { up_cells(c, c->Tc, Ti); up_bnd(c, c->Tb, Tb); c->haveT = true; }
     do_force(c);
@@ -2550,7 +2633,8 @@ int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const
     API_BEGIN(c)
     if (!ai || !pai || !apo || (c->nBF && (!ab || !pab || !apob))) failf("tcif_stage_host: null field lists");
     if (!(deltaT > 0)) failf("tcif_stage_host: deltaT must be positive");
-    touch(c);
+    for (int p = 0; p < c->P; ++p) alpha_changed(c, p);
+    c->tStamp = 0;
     if (!c->sIn) {
         CUDA_OK(cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking));
         CUDA_OK(cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking));
@@ -2632,7 +2716,8 @@ int tcif_time_step_host(tcif_ctx *c, const tcif_alpha_controls *ctl, double delt
                         double *const *apo, double *const *apob, double *rpi, double *rpb, double *Fi, double *Fb) {
     API_BEGIN(c)
     if (!ai || (c->nBF && !ab) || !phii) failf("tcif_time_step_host: null field lists");
-    touch(c);
+    for (int p = 0; p < c->P; ++p) alpha_changed(c, p);
+    c->tStamp = 0;
     if (!c->sIn) {
         CUDA_OK(cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking));
         CUDA_OK(cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking));
@@ -2841,5 +2926,11 @@ int tcif_timers_read(tcif_ctx *c, double *ms, int64_t *launches, double *bytes) 
 }
 int64_t tcif_launch_count(const tcif_ctx *c) { return c ? c->launches : 0; }
 int64_t tcif_device_bytes(const tcif_ctx *c) { return c ? c->devBytes : 0; }
+int tcif_mesh_info(const tcif_ctx *c, int32_t out[8]) {
+    if (!c || !out) return 1;
+    out[0] = c->Ko; out[1] = c->Kn; out[2] = kshape(c); out[3] = c->tileStrips; out[4] = c->dm.pfTiles;
+    out[5] = c->nBndCells; out[6] = fns(c) ? c->nDef : c->nBndCells; out[7] = c->nCoupled;
+    return 0;
+}
 
 }  // extern "C"

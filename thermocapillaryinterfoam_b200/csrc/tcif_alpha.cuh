@@ -293,7 +293,7 @@ struct RhoPhiArgs {
     double *out, *outb;
     double wgt; int accumulate;      // sub-cycling: out += wgt * rhoPhi   (multiphaseSystem.C:158)
 };
-__global__ void __launch_bounds__(TCIF_TPB)
+static __global__ void __launch_bounds__(TCIF_TPB)
 k_rho_phi(const __grid_constant__ DMesh m, const __grid_constant__ RhoPhiArgs a) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= m.nC) return;
@@ -309,7 +309,7 @@ k_rho_phi(const __grid_constant__ DMesh m, const __grid_constant__ RhoPhiArgs a)
         a.out[fo] = a.accumulate ? a.out[fo] + a.wgt * s : a.wgt * s;      // wgt == 1 without sub-cycles
     }
 }
-__global__ void __launch_bounds__(TCIF_TPB)
+static __global__ void __launch_bounds__(TCIF_TPB)
 k_rho_phi_bnd(const __grid_constant__ DMesh m, const __grid_constant__ RhoPhiArgs a) {
     const int bf = blockIdx.x * blockDim.x + threadIdx.x;
     if (bf >= m.nBF) return;
@@ -327,7 +327,7 @@ k_rho_phi_bnd(const __grid_constant__ DMesh m, const __grid_constant__ RhoPhiArg
 
 // ---- alpha += alpha*(1 - sum alpha) on cells and patch values (:414-426; no BC re-evaluation) --
 struct RenormArgs { int P; double *a[4]; };
-__global__ void __launch_bounds__(TCIF_TPB)
+static __global__ void __launch_bounds__(TCIF_TPB)
 k_renormalise(int n, const __grid_constant__ RenormArgs r) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -338,7 +338,7 @@ k_renormalise(int n, const __grid_constant__ RenormArgs r) {
 }
 
 // max over all face slots / boundary faces of phic0 = |phi|/|Sf| (multiphaseSystem.C:181, 237)
-__global__ void __launch_bounds__(TCIF_TPB)
+static __global__ void __launch_bounds__(TCIF_TPB)
 k_phic_max(const __grid_constant__ DMesh m, const double *phi, const double *phib, double *out, int allPatches = 0) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     double v = 0.0;
@@ -355,7 +355,7 @@ k_phic_max(const __grid_constant__ DMesh m, const double *phi, const double *phi
 }
 
 // ---- fvc::flux(F) = linear(F) & Sf  (pEqn.H:31-38) ------------------------------------------------------------
-__global__ void __launch_bounds__(TCIF_TPB)
+static __global__ void __launch_bounds__(TCIF_TPB)
 k_flux_of_force(const __grid_constant__ DMesh m, const double *F, double *out) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= m.nC) return;
@@ -369,7 +369,7 @@ k_flux_of_force(const __grid_constant__ DMesh m, const double *F, double *out) {
         out[fo] = ix * m.Sfx[fo] + iy * m.Sfy[fo] + iz * m.Sfz[fo];
     }
 }
-__global__ void __launch_bounds__(TCIF_TPB)
+static __global__ void __launch_bounds__(TCIF_TPB)
 k_flux_of_force_bnd(const __grid_constant__ DMesh m, const double *F, const double *Fb, double *outb) {
     const int bf = blockIdx.x * blockDim.x + threadIdx.x;
     if (bf >= m.nBF) return;

@@ -62,7 +62,11 @@ struct DMesh {
     const int *neiFace;     // [Kn*stride] device face index of the k-th neighbour-side face (-1: none)
     const double *Sfx, *Sfy, *Sfz, *w;   // [Ko*stride]
     const double *V;        // [nC]
-    const unsigned *bndMask;// [stride/32] bit c: cell c owns >=1 boundary face (volume sweeps skip it)
+    const unsigned *bndMask;// [stride/32] bit c: cell c owns >=1 boundary face
+    const int *bndWordRank; // [stride/32] number of boundary-adjacent cells below cell 32*w (rank of a mask bit -> index in bndCells)
+    const unsigned *defMask;// [stride/32] bit c: cell c is deferred to the O(surface) launch (null: none), see tcif_volume.cuh
+    const int *defCells;    // [nDef] the deferred cells as indices into bndCells, ascending
+    int nDef;
     const int *bndCells;    // [nBndCells] ascending cell ids owning >=1 boundary face
     const int *bndCellStart;// [nBndCells+1]
     const int *bndFaces;    // boundary face ids grouped by cell, ascending
@@ -384,6 +388,7 @@ k_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs 
 // ------------------------------------------------------------------------------------
 struct MulesPh {
     const double *psi, *psi0, *psib;    // alpha, alpha.oldTime(), patch values (halo on processor)
+    double *psi0w;                      // = psi0, written by the set-up sweep when MulesParams::storeOld
     const double *Su, *Sp;              // may be null (= 0)
     const int *bc;                      // [nPatches]
     const double *phiIn, *phiInb;       // HO flux read by the set-up sweep (may alias phiPsi)
@@ -401,6 +406,7 @@ struct MulesBatch { int nPh; MulesPh ph[4]; };
 struct MulesParams {
     double rDeltaT, psiMax, psiMin, extremaCoeff, smoothLimiter;
     int boundaryExtrema, addUpwind;
+    int storeOld;                       // set-up sweep: psi.oldTime() := psi (fixed-K kernels; the generic path copies on the host side)
     const double *phi, *phib;
 };
 
@@ -645,7 +651,7 @@ k_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatc
 
 // MULES::limitSum on the internal faces (device face slots; padded slots hold 0) .
 struct LimitSumArgs { int nPh; double *f[4]; };
-__global__ void __launch_bounds__(TCIF_TPB)
+static __global__ void __launch_bounds__(TCIF_TPB)
 k_limit_sum(int n, const __grid_constant__ LimitSumArgs a) {
     int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= n) return;
@@ -664,7 +670,7 @@ k_limit_sum(int n, const __grid_constant__ LimitSumArgs a) {
     }
 }
 // same on the owner-side faces of the boundary-adjacent cells only (the volume sweep fused the rest)
-__global__ void __launch_bounds__(TCIF_TPB)
+static __global__ void __launch_bounds__(TCIF_TPB)
 k_limit_sum_bndcells(const __grid_constant__ DMesh m, const __grid_constant__ LimitSumArgs a) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= m.nBndCells * m.Ko) return;
@@ -686,7 +692,7 @@ k_limit_sum_bndcells(const __grid_constant__ DMesh m, const __grid_constant__ Li
     }
 }
 // same on the coupled boundary faces
-__global__ void k_limit_sum_coupled(int n, const int *coupledFaces, const __grid_constant__ LimitSumArgs a) {
+static __global__ void k_limit_sum_coupled(int n, const int *coupledFaces, const __grid_constant__ LimitSumArgs a) {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     int f = coupledFaces[k];
@@ -722,7 +728,7 @@ k_add_upwind(const __grid_constant__ DMesh m, const double *phi, const double *p
         }
     }
 }
-__global__ void k_add_upwind_bnd(const __grid_constant__ DMesh m, const double *phib, const double *psi,
+static __global__ void k_add_upwind_bnd(const __grid_constant__ DMesh m, const double *phib, const double *psi,
                                  const double *psib, double *phiPsib) {
     int bf = blockIdx.x * blockDim.x + threadIdx.x;
     if (bf >= m.nBF) return;
@@ -738,14 +744,14 @@ __global__ void k_add_upwind_bnd(const __grid_constant__ DMesh m, const double *
 // boundary evaluation, halo pack/unpack, layout conversion, reductions
 // ------------------------------------------------------------------------------------
 // vol-field correctBoundaryConditions on non-coupled patches: zeroGradient -> adjacent cell.
-__global__ void k_correct_bc_scalar(const __grid_constant__ DMesh m, const double *vi, double *vb, const int *bc) {
+static __global__ void k_correct_bc_scalar(const __grid_constant__ DMesh m, const double *vi, double *vb, const int *bc) {
     int bf = blockIdx.x * blockDim.x + threadIdx.x;
     if (bf >= m.nBF) return;
     if (m.bfType[bf] == PATCH_PROCESSOR) return;
     if (bc[m.bfPatch[bf]] == BC_ZERO_GRADIENT) vb[bf] = vi[m.faceCells[bf]];
 }
 // extrapolatedCalculated patches of a result field (ncomp SoA comps, cell stride `cs`, bnd stride nBF)
-__global__ void k_extrapolate_bnd(const __grid_constant__ DMesh m, int ncomp, size_t cs, const double *vi, double *vb) {
+static __global__ void k_extrapolate_bnd(const __grid_constant__ DMesh m, int ncomp, size_t cs, const double *vi, double *vb) {
     int bf = blockIdx.x * blockDim.x + threadIdx.x;
     if (bf >= m.nBF) return;
     if (m.bfType[bf] == PATCH_PROCESSOR) return;
@@ -753,7 +759,7 @@ __global__ void k_extrapolate_bnd(const __grid_constant__ DMesh m, int ncomp, si
     for (int d = 0; d < ncomp; ++d) vb[(size_t)d * m.nBF + bf] = vi[d * cs + fc];
 }
 // gaussGrad::correctBoundaryConditions on non-coupled patches of one phase gradient
-__global__ void k_grad_bnd_correct(const __grid_constant__ DMesh m, const double *alpha, const double *alphab,
+static __global__ void k_grad_bnd_correct(const __grid_constant__ DMesh m, const double *alpha, const double *alphab,
                                    const int *bc, double *gb) {
     int bf = blockIdx.x * blockDim.x + threadIdx.x;
     if (bf >= m.nBF) return;
@@ -776,13 +782,13 @@ __device__ __forceinline__ size_t halo_slot(const DMesh &m, int k, int d, int nc
     return (size_t)off * ncomp + (size_t)d * sz + (k - off);
 }
 // patchInternalField of cell arrays
-__global__ void k_halo_pack(const __grid_constant__ DMesh m, const __grid_constant__ HaloArgs h, double *send) {
+static __global__ void k_halo_pack(const __grid_constant__ DMesh m, const __grid_constant__ HaloArgs h, double *send) {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= m.nCoupled) return;
     int fc = m.faceCells[m.coupledFaces[k]];
     for (int d = 0; d < h.ncomp; ++d) send[halo_slot(m, k, d, h.ncomp)] = h.src[d][fc];
 }
-__global__ void k_halo_unpack(const __grid_constant__ DMesh m, const __grid_constant__ HaloArgs h, const double *recv) {
+static __global__ void k_halo_unpack(const __grid_constant__ DMesh m, const __grid_constant__ HaloArgs h, const double *recv) {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= m.nCoupled) return;
     int bf = m.coupledFaces[k];
@@ -790,29 +796,29 @@ __global__ void k_halo_unpack(const __grid_constant__ DMesh m, const __grid_cons
 }
 
 // host order <-> device slots
-__global__ void k_face_scatter(int nIF, const int *faceMap, const double *src, double *dst) {
+static __global__ void k_face_scatter(int nIF, const int *faceMap, const double *src, double *dst) {
     int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f < nIF) dst[faceMap[f]] = src[f];
 }
-__global__ void k_face_gather(int nIF, const int *faceMap, const double *src, double *dst) {
+static __global__ void k_face_gather(int nIF, const int *faceMap, const double *src, double *dst) {
     int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f < nIF) dst[f] = src[faceMap[f]];
 }
-__global__ void k_face_scatter_vec(int nIF, const int *faceMap, const double *src, double *x, double *y, double *z) {
+static __global__ void k_face_scatter_vec(int nIF, const int *faceMap, const double *src, double *x, double *y, double *z) {
     int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f < nIF) { int fd = faceMap[f]; x[fd] = src[3 * (size_t)f]; y[fd] = src[3 * (size_t)f + 1]; z[fd] = src[3 * (size_t)f + 2]; }
 }
-__global__ void k_soa_to_aos3(int n, size_t stride, const double *src, double *dst) {
+static __global__ void k_soa_to_aos3(int n, size_t stride, const double *src, double *dst) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) { dst[3 * (size_t)i] = src[i]; dst[3 * (size_t)i + 1] = src[stride + i]; dst[3 * (size_t)i + 2] = src[2 * stride + i]; }
 }
-__global__ void k_aos3_to_soa(int n, size_t stride, const double *src, double *dst) {
+static __global__ void k_aos3_to_soa(int n, size_t stride, const double *src, double *dst) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) { dst[i] = src[3 * (size_t)i]; dst[stride + i] = src[3 * (size_t)i + 1]; dst[2 * stride + i] = src[3 * (size_t)i + 2]; }
 }
 
 // sum(V*a), min(a), max(a): deterministic two-level tree
-__global__ void __launch_bounds__(TCIF_TPB)
+static __global__ void __launch_bounds__(TCIF_TPB)
 k_stats_partial(int n, const double *V, const double *a, double *part) {
     __shared__ double s0[TCIF_TPB], s1[TCIF_TPB], s2[TCIF_TPB];
     double sum = 0.0, mn = 1e300, mx = -1e300;
@@ -832,7 +838,7 @@ k_stats_partial(int n, const double *V, const double *a, double *part) {
     }
     if (threadIdx.x == 0) { part[blockIdx.x * 3] = s0[0]; part[blockIdx.x * 3 + 1] = s1[0]; part[blockIdx.x * 3 + 2] = s2[0]; }
 }
-__global__ void k_stats_final(int nPart, const double *part, double *out3) {
+static __global__ void k_stats_final(int nPart, const double *part, double *out3) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         double sum = 0.0, mn = 1e300, mx = -1e300;
         for (int i = 0; i < nPart; ++i) { sum += part[i * 3]; mn = dmin(mn, part[i * 3 + 1]); mx = dmax(mx, part[i * 3 + 2]); }

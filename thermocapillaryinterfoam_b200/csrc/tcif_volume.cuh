@@ -1,5 +1,5 @@
-// tcif_volume.cuh -- the O(volume) sweeps for meshes with a compile-time slot count K (2: one-cell-
-// thick hex, 3: hex, 4: tet/prism), restructured for memory-level parallelism.
+// tcif_volume.cuh -- the cell-centric sweeps of the hot path for meshes with a compile-time slot count
+// K (2: one-cell-thick hex, 3: hex, 4: tet/prism), restructured for memory-level parallelism.
 //
 // round-1 ncu (profiles/r01_ncu_full_n400_*.csv) showed the first versions of these kernels latency-
 // bound: ~80 % of warp stalls on long-scoreboard with 0.8 eligible warps per scheduler, because
@@ -9,6 +9,17 @@
 // reference's arithmetic under the original `valid` predicates -- same operations, same order, so
 // results stay bit-identical to the serial oracle.  Never-reused streams (Sf, w, Q+-, sums, outputs)
 // use evict-first loads/stores (__ldcs/__stcs) so that L2 keeps the arrays neighbours gather from.
+//
+// round 2: ONE kernel body per sweep.  Every kernel here takes a template flag DEF:
+//   DEF = false  the O(volume) launch: all cells in tile order.  A cell that owns boundary faces of
+//                non-coupled patches (walls, wedges) handles them inline, after its internal faces, in
+//                patch order (the reference's accumulation order) -- a rare, warp-divergent tail instead
+//                of a second launch.  Cells flagged in DMesh::defMask are skipped.
+//   DEF = true   the O(surface) launch over DMesh::defCells: the cells next to a processor patch, which
+//                must wait for the halo exchange; runs on the side stream behind the exchange.
+// The round-1 design ran a generic-K, one-thread-per-(cell, phase) "twin" kernel over ALL boundary-adjacent
+// cells next to every volume launch (5.6 ms per stage at 64 M cells for 1.5 % of the cells, co-running
+// with and slowing the volume sweep); on one GPU there is now no second launch at all.
 #pragma once
 #include "tcif_device.cuh"
 #include "tcif_alpha.cuh"      // PredBatch (kvp_pred_jacobi)
@@ -80,6 +91,29 @@ template <int TPB_> __device__ __forceinline__ CellIdx cell_of(const DMesh &m, i
     return r;
 }
 
+// The cell of this thread.  bi = index of the cell in bndCells / bndCellStart (-1: the cell has no boundary
+// face).  Volume launch: bi comes from the boundary bit mask (rank of the bit = prefix count of its word +
+// popcount below it), so interior cells read one mask word per warp and nothing else.
+struct CellCtx { int c, cp, bi; };
+template <int TPB_, bool DEF>
+__device__ __forceinline__ bool pick_cell(const DMesh &m, CellCtx &x) {
+    if (DEF) {
+        const int i = blockIdx.x * TPB_ + threadIdx.x;
+        if (i >= m.nDef) return false;
+        x.bi = m.defCells[i]; x.c = m.bndCells[x.bi]; x.cp = -1;
+        return true;
+    }
+    const CellIdx ci = cell_of<TPB_>(m, blockIdx.x);
+    x.c = ci.c; x.cp = ci.cp; x.bi = -1;
+    if (x.c >= m.nC) return false;
+    const int w = x.c >> 5;
+    const unsigned bit = 1u << (x.c & 31);
+    if (m.defMask && (m.defMask[w] & bit)) return false;
+    const unsigned bw = m.bndMask[w];
+    if (bw & bit) x.bi = m.bndWordRank[w] + __popc(bw & (bit - 1u));
+    return true;
+}
+
 // L2 prefetch of the contiguous (own-slot) streams a later CTA will read (cp of cell_of()).  The volume
 // sweeps are bound by memory latency (ncu: long-scoreboard stalls, ~45 % occupancy), and everything a cell
 // reads from HBM for the first time is one of these streams, so a prefetch issued one or two waves ahead
@@ -98,16 +132,16 @@ template <int K> __device__ __forceinline__ void pf_geom(const DMesh &m, int cp)
 }
 
 // ---- K1: grad(alpha_p) for all phases + capillary stress tensors of all pairs ---------------------
-template <int P, int K>
+template <int P, int K, bool DEF>
 __global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
 kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
-    const CellIdx ci = cell_of<TCIF_TPB_FORCE>(m, blockIdx.x);
-    const int c = ci.c;
-    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    CellCtx x;
+    if (!pick_cell<TCIF_TPB_FORCE, DEF>(m, x)) return;
+    const int c = x.c;
     Slots<K> s;
     s.load(m, c);
-    {
-        const int cp = ci.cp;
+    if (!DEF) {
+        const int cp = x.cp;
         if (cp >= 0) {
             pf_slots<K>(m, cp); pf_geom<K>(m, cp);
 #pragma unroll
@@ -154,8 +188,27 @@ kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArg
             }
         }
     }
+    if (x.bi >= 0) {                         // patch faces, in patch order (gaussGrad: boundary loop after the internal faces)
+        for (int j = m.bndCellStart[x.bi], e = m.bndCellStart[x.bi + 1]; j < e; ++j) {
+            const int bf = m.bndFaces[j];
+            const bool coupled = m.bfType[bf] == PATCH_PROCESSOR;
+            const double wb = m.wb[bf], sx = m.Sfbx[bf], sy = m.Sfby[bf], sz = m.Sfbz[bf];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                const double ab = a.alphab[p][bf];
+                const double af = coupled ? wb * aS[p] + (1.0 - wb) * ab : ab;
+                g[p][0] += sx * af; g[p][1] += sy * af; g[p][2] += sz * af;
+            }
+        }
+    }
 #pragma unroll
     for (int p = 0; p < P; ++p) { g[p][0] = f_div(g[p][0], rV); g[p][1] = f_div(g[p][1], rV); g[p][2] = f_div(g[p][2], rV); }
+    if (x.bi >= 0) {                         // kept for the patch values of the tensor (kv_div_tensor)
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+#pragma unroll
+            for (int d = 0; d < 3; ++d) a.gBnd[(size_t)(p * 3 + d) * m.nBndCells + x.bi] = g[p][d];
+    }
     if (a.G) {
 #pragma unroll
         for (int p = 0; p < P; ++p)
@@ -187,18 +240,76 @@ kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArg
     }
 }
 
+// S_b . T_b over the patch faces of boundary cell bi (A.4): processor faces interpolate with the neighbour-rank
+// tensor, elsewhere T_b is the tensor expression evaluated on the patch values alpha_b, (grad alpha)_b after the
+// gaussGrad correction, sigma(T_b); pair q only, or (tsum) all pairs summed in pair order.  Kept out of line: it is
+// the rare path and must not cost the volume sweep registers.
+template <int P>
+__device__ __noinline__ void div_bnd_faces(const DMesh &m, const ForceArgs &a, int bi, int c, int q, const double *Ts, double *acc) {
+    for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
+        const int bf = m.bndFaces[j];
+        const double sx = m.Sfbx[bf], sy = m.Sfby[bf], sz = m.Sfbz[bf];
+        double t[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        if (m.bfType[bf] == PATCH_PROCESSOR) {
+            const double wb = m.wb[bf];
+#pragma unroll
+            for (int kk = 0; kk < 6; ++kk)
+                t[kk] = wb * Ts[kk] + (1.0 - wb) * a.TqHalo[(size_t)(q * 6 + kk) * m.nBF + bf];
+        } else {
+            const double mag = m.magSfb[bf];
+            const double nx = sx / mag, ny = sy / mag, nz = sz / mag;
+            int qq = 0;
+            for (int p1 = 0; p1 < P; ++p1)
+                for (int p2 = p1 + 1; p2 < P; ++p2, ++qq) {
+                    if (!a.tsum && qq != q) continue;
+                    double gb[2][3], ab[2];
+                    const int pp[2] = {p1, p2};
+#pragma unroll
+                    for (int s = 0; s < 2; ++s) {
+                        const int p = pp[s];
+                        const double gc0 = a.gBnd[(size_t)(p * 3 + 0) * m.nBndCells + bi];
+                        const double gc1 = a.gBnd[(size_t)(p * 3 + 1) * m.nBndCells + bi];
+                        const double gc2 = a.gBnd[(size_t)(p * 3 + 2) * m.nBndCells + bi];
+                        ab[s] = a.alphab[p][bf];
+                        double sn = 0.0;
+                        if (a.bc[p][m.bfPatch[bf]] == BC_FIXED_VALUE) sn = m.dcb[bf] * (ab[s] - a.alpha[p][c]);
+                        const double ng = nx * gc0 + ny * gc1 + nz * gc2;
+                        const double sc = sn - ng;
+                        gb[s][0] = gc0 + nx * sc; gb[s][1] = gc1 + ny * sc; gb[s][2] = gc2 + nz * sc;
+                    }
+                    const double sg = sigma_eval(a.sig[qq], a.Tb ? a.Tb[bf] : 0.0);
+                    double tq[6];
+                    pair_tensor(ab[0], ab[1], gb[0], gb[1], sg, a.deltaN, tq);
+                    if (a.tsum) {
+#pragma unroll
+                        for (int kk = 0; kk < 6; ++kk) t[kk] += tq[kk];
+                    } else {
+#pragma unroll
+                        for (int kk = 0; kk < 6; ++kk) t[kk] = tq[kk];
+                    }
+                }
+        }
+        acc[0] += sx * t[0] + sy * t[1] + sz * t[2];
+        acc[1] += sx * t[1] + sy * t[3] + sz * t[4];
+        acc[2] += sx * t[2] + sy * t[4] + sz * t[5];
+    }
+}
+
 // ---- K2: F = sum_q div(T_q) ---------------------------------------------------------------------------
-template <int P, int K>
+// The one sweep that keeps ALL boundary-adjacent cells in the deferred launch (tcif.cu passes a DMesh whose deferred
+// list is bndCells): the patch-face tensor (div_bnd_faces) is a function call with ~50 live doubles around it, and
+// inlining it in the volume launch cost 2 ms per stage at 64 M cells in spills (3.7 -> 5.8 ms, profiles/r03_variants.md).
+template <int P, int K, bool DEF>
 __global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
 kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
     constexpr int Q = P * (P - 1) / 2;
-    const CellIdx ci = cell_of<TCIF_TPB_FORCE>(m, blockIdx.x);
-    const int c = ci.c;
-    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    CellCtx x;
+    if (!pick_cell<TCIF_TPB_FORCE, DEF>(m, x)) return;
+    const int c = x.c;
     Slots<K> s;
     s.load(m, c);
-    {
-        const int cp = ci.cp;
+    if (!DEF) {
+        const int cp = x.cp;
         if (cp >= 0) {
             pf_slots<K>(m, cp); pf_geom<K>(m, cp);
 #pragma unroll
@@ -235,211 +346,71 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
 #pragma unroll
         for (int k = 0; k < K; ++k)
             if (s.vO[k]) face_div_acc(wO[k], sxO[k], syO[k], szO[k], Ts, Tn[k], 1.0, acc);
+        if (DEF && x.bi >= 0) div_bnd_faces<P>(m, a, x.bi, c, q, Ts, acc);
         F[0] += f_div(acc[0], rV); F[1] += f_div(acc[1], rV); F[2] += f_div(acc[2], rV);
     }
     __stcs(a.F + c, F[0]); __stcs(a.F + (size_t)m.stride + c, F[1]); __stcs(a.F + (size_t)2 * m.stride + c, F[2]);
 }
 
-// ---- MULES set-up sweep (see k_mules_setup) ------------------------------------------------------------
-template <int K>
-__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_SETUP)
-kv_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
-               const __grid_constant__ MulesParams prm) {
-    const int p = blockIdx.x % b.nPh;
-    const int c = cell_of<TCIF_TPB>(m, blockIdx.x / b.nPh).c;
-    if (c >= m.nC || is_bnd_cell(m, c)) return;
-    const MulesPh &ph = b.ph[p];
-    Slots<K> s;
-    s.load(m, c);
-    const double psiC = ph.psi[c];
-    double psiO[K], phiN[K], ppN[K], psiN[K], phiO[K], ppO[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        const int fo = k * m.stride + c;
-        psiO[k] = ph.psi[s.oN[k]]; phiN[k] = prm.phi[s.fdN[k]]; ppN[k] = ph.phiIn[s.fdN[k]];
-        psiN[k] = ph.psi[s.nO[k]]; phiO[k] = prm.phi[fo]; ppO[k] = ph.phiIn[fo];
-    }
-    const double V = m.V[c], psi0 = __ldcs(ph.psi0 + c);
-    const double Su = ph.Su ? __ldcs(ph.Su + c) : 0.0, Sp = ph.Sp ? __ldcs(ph.Sp + c) : 0.0;
-    double psiMaxn = prm.psiMin, psiMinn = prm.psiMax, sBD = 0.0, sP = 0.0, sM = 0.0;
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        if (s.vN[k]) {
-            double bd = upwind_flux(phiN[k], psiO[k], psiC);
-            double pp = ppN[k];
-            if (prm.addUpwind) pp = pp + bd;
-            double pc = pp - bd;
-            psiMaxn = dmax(psiMaxn, psiO[k]); psiMinn = dmin(psiMinn, psiO[k]);
-            sBD -= bd;
-            if (pc > 0) sM += pc; else sP -= pc;
-        }
-    }
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        if (s.vO[k]) {
-            double bd = upwind_flux(phiO[k], psiC, psiN[k]);
-            double pp = ppO[k];
-            if (prm.addUpwind) pp = pp + bd;
-            double pc = pp - bd;
-            ph.phiCorr[k * m.stride + c] = pc;
-            psiMaxn = dmax(psiMaxn, psiN[k]); psiMinn = dmin(psiMinn, psiN[k]);
-            sBD += bd;
-            if (pc > 0) sP += pc; else sM -= pc;
-        }
-    }
-    psiMaxn = dmin(psiMaxn + prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMax);
-    psiMinn = dmax(psiMinn - prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMin);
-    if (prm.smoothLimiter > TCIF_SMALL) {
-        double sl = prm.smoothLimiter;
-        psiMaxn = dmin(sl * psiC + (1.0 - sl) * psiMaxn, prm.psiMax);
-        psiMinn = dmax(sl * psiC + (1.0 - sl) * psiMinn, prm.psiMin);
-    }
-    double Qp = V * ((prm.rDeltaT - Sp) * psiMaxn - Su) - (V * prm.rDeltaT) * psi0 + sBD;
-    double Qm = V * (Su - (prm.rDeltaT - Sp) * psiMinn) + (V * prm.rDeltaT) * psi0 - sBD;
-    __stcs(ph.Qp + c, Qp); __stcs(ph.Qm + c, Qm); __stcs(ph.sP + c, sP); __stcs(ph.sM + c, sM);
-    ph.lmA[c] = dmax(dmin((sP + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
-    ph.lpA[c] = dmax(dmin((sM + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
-}
-
-// ---- face pass of limiter iteration j + cell pass of iteration j+1 (see k_mules_iter) -------------------
-template <int K, bool FIRST>
-__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_ITER)
-kv_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, int flip) {
-    const int p = blockIdx.x % b.nPh;
-    const int c = cell_of<TCIF_TPB>(m, blockIdx.x / b.nPh).c;
-    if (c >= m.nC || is_bnd_cell(m, c)) return;
-    const MulesPh &ph = b.ph[p];
-    const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
-    double *lpOut = flip ? ph.lpA : ph.lpB, *lmOut = flip ? ph.lmA : ph.lmB;
-    const double *lamIn = flip ? ph.lamB : ph.lamA;
-    double *lamOut = flip ? ph.lamA : ph.lamB;
-    Slots<K> s;
-    s.load(m, c);
-    const double lpC = lpIn[c], lmC = lmIn[c];
-    double pcN[K], laN[K], lpO[K], lmO[K], pcO[K], laO[K], lpN[K], lmN[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        const int fo = k * m.stride + c;
-        pcN[k] = ph.phiCorr[s.fdN[k]]; laN[k] = FIRST ? 1.0 : lamIn[s.fdN[k]];
-        lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
-        pcO[k] = ph.phiCorr[fo]; laO[k] = FIRST ? 1.0 : lamIn[fo];
-        lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
-    }
-    const double Qp = __ldcs(ph.Qp + c), Qm = __ldcs(ph.Qm + c), sP = __ldcs(ph.sP + c), sM = __ldcs(ph.sM + c);
-    double slp = 0.0, slm = 0.0;
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        if (s.vN[k]) {
-            double lam = lambda_face(laN[k], pcN[k], lpO[k], lmO[k], lpC, lmC);
-            double l = lam * pcN[k];
-            if (l > 0) slm += l; else slp -= l;
-        }
-    }
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        if (s.vO[k]) {
-            double lam = lambda_face(laO[k], pcO[k], lpC, lmC, lpN[k], lmN[k]);
-            lamOut[k * m.stride + c] = lam;
-            double l = lam * pcO[k];
-            if (l > 0) slp += l; else slm -= l;
-        }
-    }
-    lmOut[c] = dmax(dmin((slp + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
-    lpOut[c] = dmax(dmin((slm + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
-}
-
-// ---- last face pass + apply / explicit update (see k_mules_final) ----------------------------------------
-template <int K, int MODE, bool FIRST>
-__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
-kv_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
-               const __grid_constant__ MulesParams prm, int flip, int nIter) {
-    const int p = blockIdx.x % b.nPh;
-    const int c = cell_of<TCIF_TPB>(m, blockIdx.x / b.nPh).c;
-    if (c >= m.nC || is_bnd_cell(m, c)) return;
-    const MulesPh &ph = b.ph[p];
-    const double *lpIn = flip ? ph.lpB : ph.lpA, *lmIn = flip ? ph.lmB : ph.lmA;
-    const double *lamIn = flip ? ph.lamB : ph.lamA;
-    Slots<K> s;
-    s.load(m, c);
-    const double lpC = lpIn[c], lmC = lmIn[c];
-    const double psiC = (MODE >= 1) ? ph.psi[c] : 0.0;
-    double pcN[K], laN[K], lpO[K], lmO[K], phN[K], psO[K];
-    double pcO[K], laO[K], lpN[K], lmN[K], phO[K], psN[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        const int fo = k * m.stride + c;
-        if (MODE == 2) {
-            pcN[k] = ph.phiCorr[s.fdN[k]]; laN[k] = FIRST ? 1.0 : lamIn[s.fdN[k]];
-            lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
-            phN[k] = prm.phi[s.fdN[k]]; psO[k] = ph.psi[s.oN[k]];
-        }
-        pcO[k] = ph.phiCorr[fo]; laO[k] = FIRST ? 1.0 : lamIn[fo];
-        lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
-        if (MODE >= 1) { phO[k] = prm.phi[fo]; psN[k] = ph.psi[s.nO[k]]; }
-    }
-    double V = 1.0, psi0 = 0.0, Su = 0.0, Sp = 0.0;
-    if (MODE == 2) {
-        V = m.V[c]; psi0 = __ldcs(ph.psi0 + c);
-        Su = ph.Su ? __ldcs(ph.Su + c) : 0.0; Sp = ph.Sp ? __ldcs(ph.Sp + c) : 0.0;
-    }
-    double sum = 0.0;
-    if (MODE == 2) {
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            if (s.vN[k]) {
-                double lam = laN[k];
-                if (nIter > 0) lam = lambda_face(lam, pcN[k], lpO[k], lmO[k], lpC, lmC);
-                double bd = upwind_flux(phN[k], psO[k], psiC);
-                sum -= bd + lam * pcN[k];
-            }
-        }
-    }
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        if (s.vO[k]) {
-            double lam = laO[k];
-            if (nIter > 0) lam = lambda_face(lam, pcO[k], lpC, lmC, lpN[k], lmN[k]);
-            double fl;
-            if (MODE == 0) fl = pcO[k] * lam;
-            else           fl = upwind_flux(phO[k], psiC, psN[k]) + lam * pcO[k];
-            ph.phiPsi[k * m.stride + c] = fl;
-            sum += fl;
-        }
-    }
-    if (MODE == 2) {
-        double d = sum / V;
-        ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
-    }
-}
-
 // =====================================================================================================
-// Phase-looped variants (kvp_*): one thread per cell, ALL phases of the batch handled by that thread.
+// MULES sweeps, phase-looped (kvp_*): one thread per cell, ALL phases of the batch handled by that thread.
 // The 2K slot indices are loaded once per cell instead of once per (cell, phase), which removes one of
 // the two dependent memory round trips (indices -> gathers) for every phase after the first, and the
 // per-phase pointers are compile-time offsets into the kernel parameters (NPH is a template argument).
-// Same arithmetic, same order as the kv_* kernels.
+// Arithmetic and order: SURVEY.md A.6 (see also the generic-K kernels k_mules_* in tcif_device.cuh).
 // =====================================================================================================
-template <int K, int NPH>
+
+// patch faces of the set-up sweep: phiBD_b, phiCorr_b, lambda_b = 1, local extrema, sums
+__device__ __forceinline__ void bnd_setup(const DMesh &m, const MulesPh &ph, const MulesParams &prm, int bi, double psiC,
+                                          double &psiMaxn, double &psiMinn, double &sBD, double &sP, double &sM) {
+    for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
+        const int bf = m.bndFaces[j];
+        const bool coupled = m.bfType[bf] == PATCH_PROCESSOR;
+        const double psb = ph.psib[bf], phb = prm.phib[bf];
+        double pp = ph.phiInb[bf], bd;
+        if (coupled) {
+            const double w = phb >= 0 ? 1.0 : 0.0;
+            const double up = phb * (w * psiC + (1.0 - w) * psb);
+            if (prm.addUpwind) pp = pp + up;
+            bd = up;
+        } else {
+            if (prm.addUpwind) pp = pp + phb * psb;
+            bd = pp;                       // phiBD_b := phiPsi_b on non-coupled patches
+        }
+        const double pc = pp - bd;
+        ph.phiBDb[bf] = bd; ph.phiCorrb[bf] = pc; ph.lamb[bf] = 1.0;
+        if (coupled || ph.bc[m.bfPatch[bf]] == BC_FIXED_VALUE || prm.boundaryExtrema == 1) {
+            psiMaxn = dmax(psiMaxn, psb); psiMinn = dmin(psiMinn, psb);
+        } else {
+            psiMaxn = dmax(psiMaxn, prm.psiMax); psiMinn = dmin(psiMinn, prm.psiMin);
+        }
+        sBD += bd;
+        if (pc > 0) sP += pc; else sM -= pc;
+    }
+}
+
+template <int K, int NPH, bool DEF>
 __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_SETUP)
 kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                 const __grid_constant__ MulesParams prm) {
-    const CellIdx ci = cell_of<TCIF_TPB>(m, blockIdx.x);
-    const int c = ci.c;
-    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    CellCtx x;
+    if (!pick_cell<TCIF_TPB, DEF>(m, x)) return;
+    const int c = x.c;
     Slots<K> s;
     s.load(m, c);
     double phiN[K], phiO[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) { phiN[k] = prm.phi[s.fdN[k]]; phiO[k] = __ldcs(prm.phi + k * m.stride + c); }
     const double V = m.V[c];
-    const int cp = ci.cp;
-    const bool pf = cp >= 0;
+    const int cp = x.cp;
+    const bool pf = !DEF && cp >= 0;
     if (pf) { pf_slots<K>(m, cp); pf_face<K>(prm.phi, m.stride, cp); pf_l2(m.V + cp); }
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
         const MulesPh &ph = b.ph[p];
         if (pf) {
-            pf_l2(ph.psi + cp); pf_l2(ph.psi0 + cp); pf_face<K>(ph.phiIn, m.stride, cp);
+            pf_l2(ph.psi + cp); pf_face<K>(ph.phiIn, m.stride, cp);
+            if (!prm.storeOld) pf_l2(ph.psi0 + cp);
             if (ph.Su) pf_l2(ph.Su + cp);
             if (ph.Sp) pf_l2(ph.Sp + cp);
         }
@@ -451,7 +422,11 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
             psiO[k] = ph.psi[s.oN[k]]; ppN[k] = ph.phiIn[s.fdN[k]];
             psiN[k] = ph.psi[s.nO[k]]; ppO[k] = ph.phiIn[fo];
         }
-        const double psi0 = __ldcs(ph.psi0 + c);
+        // storeOld: this sweep opens a (sub-)time step, psi.oldTime() := psi rides on it (8 B stored instead of a
+        // separate 16 B copy sweep, and psi0 need not be read)
+        double psi0;
+        if (prm.storeOld) { psi0 = psiC; __stcs(ph.psi0w + c, psiC); }
+        else psi0 = __ldcs(ph.psi0 + c);
         const double Su = ph.Su ? __ldcs(ph.Su + c) : 0.0, Sp = ph.Sp ? __ldcs(ph.Sp + c) : 0.0;
         double psiMaxn = prm.psiMin, psiMinn = prm.psiMax, sBD = 0.0, sP = 0.0, sM = 0.0;
 #pragma unroll
@@ -479,6 +454,7 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 if (pc > 0) sP += pc; else sM -= pc;
             }
         }
+        if (x.bi >= 0) bnd_setup(m, ph, prm, x.bi, psiC, psiMaxn, psiMinn, sBD, sP, sM);
         psiMaxn = dmin(psiMaxn + prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMax);
         psiMinn = dmax(psiMinn - prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMin);
         if (prm.smoothLimiter > TCIF_SMALL) {
@@ -489,21 +465,34 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
         double Qp = V * ((prm.rDeltaT - Sp) * psiMaxn - Su) - (V * prm.rDeltaT) * psi0 + sBD;
         double Qm = V * (Su - (prm.rDeltaT - Sp) * psiMinn) + (V * prm.rDeltaT) * psi0 - sBD;
         __stcs(ph.Qp + c, Qp); __stcs(ph.Qm + c, Qm); __stcs(ph.sP + c, sP); __stcs(ph.sM + c, sM);
+        // limiter iteration 1, cell pass: lambda == 1 so sumlPhip == sumPhip, mSumlPhim == mSumPhim
         ph.lmA[c] = dmax(dmin((sP + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
         ph.lpA[c] = dmax(dmin((sM + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
     }
 }
 
-template <int K, bool FIRST, int NPH>
+// patch faces of a limiter iteration: face rule + contribution to the next cell pass
+__device__ __forceinline__ void bnd_iter(const DMesh &m, const MulesPh &ph, int bi, double lpC, double lmC, double &slp, double &slm) {
+    for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
+        const int bf = m.bndFaces[j];
+        const double pc = ph.phiCorrb[bf];
+        const double lam = lambda_bface(m.bfType[bf], ph.lamb[bf], pc, ph.phiBDb[bf], lpC, lmC, ph.lpHalo[bf], ph.lmHalo[bf]);
+        ph.lamb[bf] = lam;
+        const double l = lam * pc;
+        if (l > 0) slp += l; else slm -= l;
+    }
+}
+
+template <int K, bool FIRST, int NPH, bool DEF>
 __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_ITER)
 kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b) {
-    const CellIdx ci = cell_of<TCIF_TPB>(m, blockIdx.x);
-    const int c = ci.c;
-    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    CellCtx x;
+    if (!pick_cell<TCIF_TPB, DEF>(m, x)) return;
+    const int c = x.c;
     Slots<K> s;
     s.load(m, c);
-    const int cp = ci.cp;
-    const bool pf = cp >= 0;
+    const int cp = x.cp;
+    const bool pf = !DEF && cp >= 0;
     if (pf) pf_slots<K>(m, cp);
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
@@ -544,6 +533,7 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
                 if (l > 0) slp += l; else slm -= l;
             }
         }
+        if (x.bi >= 0) bnd_iter(m, ph, x.bi, lpC, lmC, slp, slm);
         lmOut[c] = dmax(dmin((slp + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
         lpOut[c] = dmax(dmin((slm + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
     }
@@ -566,16 +556,34 @@ template <int NPH> __device__ __forceinline__ void limit_sum_face(double *v) {
     }
 }
 
+// patch faces of the last face pass: lambda_b, limited patch flux, contribution to surfaceIntegrate
+template <int MODE>
+__device__ __forceinline__ void bnd_final(const DMesh &m, const MulesPh &ph, int bi, int nIter, double lpC, double lmC, double &sum) {
+    for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
+        const int bf = m.bndFaces[j];
+        const double pc = ph.phiCorrb[bf], bd = ph.phiBDb[bf];
+        double lam = ph.lamb[bf];
+        if (nIter > 0) lam = lambda_bface(m.bfType[bf], lam, pc, bd, lpC, lmC, ph.lpHalo[bf], ph.lmHalo[bf]);
+        ph.lamb[bf] = lam;
+        const double fl = (MODE == 0) ? pc * lam : bd + lam * pc;
+        ph.phiPsib[bf] = fl;
+        sum += fl;
+    }
+}
+
+// MODE 0: returnCorr  -> phiPsi = lambda*phiCorr           (owner-side faces)
+// MODE 1: !returnCorr -> phiPsi = phiBD + lambda*phiCorr   (owner-side faces)
+// MODE 2: explicitSolve: MODE 1 + surfaceIntegrate + Euler update into psiNew
 // LSUM (MODE 0 only, batch = all phases): MULES::limitSum of the owner-side faces applied in registers
 // before the store, which saves the separate read-modify-write sweep over the P flux arrays.
-template <int K, int MODE, bool FIRST, int NPH, bool LSUM>
+template <int K, int MODE, bool FIRST, int NPH, bool LSUM, bool DEF>
 __global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
 kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                 const __grid_constant__ MulesParams prm, int nIter) {
     static_assert(!LSUM || MODE == 0, "limitSum is fused into the returnCorr=true apply only");
-    const CellIdx ci = cell_of<TCIF_TPB>(m, blockIdx.x);
-    const int c = ci.c;
-    if (c >= m.nC || is_bnd_cell(m, c)) return;
+    CellCtx x;
+    if (!pick_cell<TCIF_TPB, DEF>(m, x)) return;
+    const int c = x.c;
     Slots<K> s;
     s.load(m, c);
     double phN[K], phO[K];
@@ -585,8 +593,8 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
         if (MODE >= 1) phO[k] = __ldcs(prm.phi + k * m.stride + c);
     }
     const double V = (MODE == 2) ? m.V[c] : 1.0;
-    const int cp = ci.cp;
-    const bool pf = cp >= 0;
+    const int cp = x.cp;
+    const bool pf = !DEF && cp >= 0;
     if (pf) {
         pf_slots<K>(m, cp);
         if (MODE >= 1) pf_face<K>(prm.phi, m.stride, cp);
@@ -654,6 +662,7 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 sum += fl;
             }
         }
+        if (x.bi >= 0) bnd_final<MODE>(m, ph, x.bi, nIter, lpC, lmC, sum);
         if (MODE == 2) {
             double d = sum / V;
             ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
