@@ -144,19 +144,57 @@ def cpu_layout(cores):
     return nd, tuple(procs)
 
 
-def cpu_stage_rate(config, n_edge, nStages, cores):
-    """Mcell-updates/s of the CPU oracle on an n_edge^3 sample of the workload, one thread per sub-domain."""
+def _mem_available_gb():
+    try:
+        with open("/proc/meminfo") as fh:
+            for ln in fh:
+                if ln.startswith("MemAvailable:"):
+                    return int(ln.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
+
+
+def cpu_stage_rate(config, n_edge, nStages, cores, warmup=0):
+    """Mcell-updates/s of the CPU oracle on an n_edge^3 box of the workload, one thread per sub-domain (each worker
+    first-touches its own sub-mesh and fields, oracle/tcif_oracle.c thr_main).  `warmup` untimed stages first."""
+    from concurrent.futures import ThreadPoolExecutor
     from oracle import oracle as orc
     from thermocapillaryinterfoam_b200 import cases, mesh as hm
     spec = cases.case(config, n_edge)
     nd, procs = cpu_layout(cores)
-    meshes = [hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, r) for r in range(nd)]
-    fs = [cases.synthetic_fields(spec, m) for m in meshes]
-    secs, _ = orc.stage_threads(meshes, orc.mules_cfg(3), [f["alpha_i"] for f in fs], [f["alpha_b"] for f in fs],
-                                [f["alphaBc"] for f in fs], spec.sigma, [f["T_i"] for f in fs], [f["T_b"] for f in fs],
-                                [f["phi_i"] for f in fs], [f["phi_b"] for f in fs], [f["phiAlpha_i"] for f in fs],
-                                [f["phiAlpha_b"] for f in fs], spec.deltaT, nStages=nStages)
+
+    def block(r):
+        m = hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, r)
+        return m, cases.synthetic_fields(spec, m)
+    with ThreadPoolExecutor(max_workers=min(nd, 8)) as ex:
+        built = list(ex.map(block, range(nd)))
+    meshes, fs = [b[0] for b in built], [b[1] for b in built]
+
+    def run(n):
+        return orc.stage_threads(meshes, orc.mules_cfg(3), [f["alpha_i"] for f in fs], [f["alpha_b"] for f in fs],
+                                 [f["alphaBc"] for f in fs], spec.sigma, [f["T_i"] for f in fs], [f["T_b"] for f in fs],
+                                 [f["phi_i"] for f in fs], [f["phi_b"] for f in fs], [f["phiAlpha_i"] for f in fs],
+                                 [f["phiAlpha_b"] for f in fs], spec.deltaT, nStages=n)[0]
+    if warmup > 0:
+        run(warmup)
+    secs = run(nStages)
     return spec.nCells * nStages / secs / 1e6, secs, nd, procs, spec
+
+
+def cpu_one_core_rate(config, n_edge=96, nStages=2):
+    """The serial oracle (one core, no decomposition) on a small box of the same workload."""
+    from oracle import oracle as orc
+    from thermocapillaryinterfoam_b200 import cases, mesh as hm
+    spec = cases.case(config, n_edge)
+    m = hm.box_block(spec.n, spec.lengths, spec.patch_types, (1, 1, 1), 0)
+    f = cases.synthetic_fields(spec, m)
+    t0 = time.perf_counter()
+    for _ in range(nStages):
+        orc.stage(m, orc.mules_cfg(3), f["alpha_i"], f["alpha_b"], f["alphaBc"], f["sigma"], f["T_i"], f["T_b"],
+                  f["phi_i"], f["phi_b"], f["phiAlpha_i"], f["phiAlpha_b"], f["deltaT"])
+    secs = time.perf_counter() - t0
+    return spec.nCells * nStages / secs / 1e6, f"{spec.name} {n_edge}^3 = {spec.nCells} cells, {nStages} stages, serial, {secs:.1f} s"
 
 
 def cpu_sample_edge(args, cores):
@@ -166,23 +204,39 @@ def cpu_sample_edge(args, cores):
     return min(full, 160 if cores >= 8 else 96)      # ~10-20 s of CPU work at 16 stages on 16 cores
 
 
+def reference_edge(args, cores):
+    """--impl reference runs the workload it names: the full box when the host can hold it (configs[4] at 400^3 needs
+    ~70 GB for 16 sub-meshes, their fields, the workers' first-touch copies and the oracle's temporaries), else the
+    bounded sample -- and then the line's config.workload names the SAMPLE, not the full box."""
+    full = args.n or {1: 64, 2: 512, 3: 128, 4: 200, 5: 400}[args.config]
+    if args.cpu_n:
+        return args.cpu_n, full
+    need_gb = 1.1e-6 * full ** 3 + 4
+    if _mem_available_gb() >= need_gb and cores >= 8:
+        return full, full
+    return cpu_sample_edge(args, cores), full
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
+    from thermocapillaryinterfoam_b200 import cases
     cores = os.cpu_count() or 1
-    edge = cpu_sample_edge(args, cores)
-    nd, procs = cpu_layout(cores)
-    for _ in range(min(args.warmup, 1)):
-        cpu_stage_rate(args.config, edge, 1, cores)
-    rate, secs, nd, procs, spec = cpu_stage_rate(args.config, edge, args.steps, cores)
-    sample = (f"{spec.name} {edge}^3 = {spec.nCells} cells, {spec.nPhases} phases, {args.steps} stages, "
-              f"{nd} sub-domains {procs[0]}x{procs[1]}x{procs[2]} (one thread each)")
+    edge, full = reference_edge(args, cores)
+    rate, secs, nd, procs, spec = cpu_stage_rate(args.config, edge, args.steps, cores, warmup=args.warmup)
+    one_core, one_core_sample = cpu_one_core_rate(args.config)
+    sample = (f"{spec.name} {edge}^3 = {spec.nCells} cells, {spec.nPhases} phases, {args.steps} stages after {args.warmup} warm-up "
+              f"stages, {nd} sub-domains {procs[0]}x{procs[1]}x{procs[2]} (one thread each, first-touch local copies)")
+    wl = (f"configs[{args.config - 1}] {spec.name} {spec.n[0]}x{spec.n[1]}x{spec.n[2]} = {spec.nCells} cells, "
+          f"{spec.nPhases} phases")
+    if edge != full:
+        wl += f" (SAMPLE of the {full}^3 box: host memory or cores too small for the full one)"
     line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args), "sample": sample},
+            "config": {"workload": wl, "sample": sample},
             "cpu_baseline": {"value": rate, "unit": UNIT, "cores": nd, "kind": "port", "sample": sample,
-                             "host_cores": cores},
+                             "host_cores": cores, "one_core": {"value": one_core, "unit": UNIT, "sample": one_core_sample}},
             "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "CPU oracle (restatement of the reference path; the OpenFOAM v2106 binary is unbuildable here)"}
@@ -265,14 +319,12 @@ def run_ours(args, rank, world, local_rank):
         sampler.mark("load")
         for _ in range(args.warmup):
             ctx.stage(dt)
-        ctx.timers_enable(True)
-        ctx.timers_reset()
         launches0 = ctx.launch_count
         barrier()
         sampler.mark("t0")
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        for _ in range(args.steps):
+        for _ in range(args.steps):                 # the timed region: per-kernel timers OFF (no event records inside)
             ctx.stage(dt)
         e1.record(stream)
         barrier()
@@ -280,8 +332,15 @@ def run_ours(args, rank, world, local_rank):
         clocks = sampler.stop() if rank == 0 else None
         ms = max_over_ranks(e0.elapsed_time(e1))
         launches = ctx.launch_count - launches0
+        # per-kernel breakdown (roofline of the dominant kernel): a SECOND loop with the CUDA-event timers on
+        ksteps = max(1, min(args.steps, 5))
+        ctx.timers_enable(True)
+        ctx.timers_reset()
+        for _ in range(ksteps):
+            ctx.stage(dt)
         timers = ctx.timers_read()
         ctx.timers_enable(False)
+        barrier()
     total_cells = spec.nCells
     value = total_cells * args.steps / (ms * 1e-3) / 1e6
 
@@ -292,7 +351,7 @@ def run_ours(args, rank, world, local_rank):
     tk = vol[top]
     achieved = tk["bytes"] / (tk["ms"] * 1e-3) / 1e9
     step_ms_sum = sum(v["ms"] for v in timers.values())
-    stage_bytes_compulsory = sum(v["bytes"] for k, v in timers.items() if k not in ("convert", "stats")) / args.steps
+    stage_bytes_compulsory = sum(v["bytes"] for k, v in timers.items() if k not in ("convert", "stats")) / ksteps
     contract = contract_bytes(nC, nIF, nBF, P, QT, 3)
     traffic, traffic_src = None, None
     tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")      # written by profiles/summarise_ncu.py from the committed capture
@@ -310,7 +369,8 @@ def run_ours(args, rank, world, local_rank):
                           "contract_bytes_per_cell": contract / nC,
                           "achieved_GBs_contract": contract * args.steps / (ms * 1e-3) / 1e9,
                           "frac_contract": contract * args.steps / (ms * 1e-3) / 1e9 / hbm},
-                "per_kernel_ms_per_step": {k: v["ms"] / args.steps for k, v in timers.items() if v["launches"]}}
+                "per_kernel_ms_per_step": {k: v["ms"] / ksteps for k, v in timers.items() if v["launches"]},
+                "per_kernel_note": f"second loop of {ksteps} stages with the per-kernel CUDA-event timers on; `value` is timed with them off"}
 
     # ---- e2e: host buffers through tcif_stage_host ------------------------------------------
     e2e = None
@@ -339,14 +399,31 @@ def run_ours(args, rank, world, local_rank):
                 barrier()
                 return max_over_ranks(time.perf_counter() - tw)
 
-        # (1) exactly the stage the device-resident number times: every field it consumes comes from host
-        #     memory and every field it produces goes back, pipelined over separate copy streams
-        e2e_s = timed_host(lambda: ctx.stage_host(dt, ai, ab, Ti, Tb, phii, phib, pi0, pb0, pi, pb, Fi, Fb), args.e2e_steps)
+        # What a time-stepping caller really sends: alpha is only ever changed by the device (solve / the stage), so after
+        # the first step its stamp matches and it is not uploaded again (tcif_host_alpha_stamps); F and alpha come back
+        # as deltas against what the host arrays already hold (tcif_host_sparse_returns).  phi, T and the flux arrays
+        # cross the link every step.  Bytes are the ones actually copied (tcif_host_bytes_moved), not a formula.
+        ctx.host_sparse_returns(True)
+        counter = [0]
+
+        def stamped(call):
+            def fn():
+                k = counter[0]
+                ctx.host_alpha_stamps([k] * P if k else None, [k + 1] * P)
+                counter[0] = k + 1
+                call()
+            return fn
+
+        # (1) exactly the stage the device-resident number times: every field it consumes comes from host memory and
+        #     every field it produces goes back, pipelined over separate copy streams
+        e2e_s = timed_host(stamped(lambda: ctx.stage_host(dt, ai, ab, Ti, Tb, phii, phib, pi0, pb0, pi, pb, Fi, Fb)), args.e2e_steps)
+        moved = ctx.host_bytes_moved
         e2e = {"value": total_cells * args.e2e_steps / e2e_s / 1e6, "unit": UNIT,
-               "h2d_bytes_per_step": int(sum_over_ranks(h2d)), "d2h_bytes_per_step": int(sum_over_ranks(d2h)),
+               "h2d_bytes_per_step": int(sum_over_ranks(moved[0])), "d2h_bytes_per_step": int(sum_over_ranks(moved[1])),
+               "dense_h2d_bytes_per_step": int(sum_over_ranks(h2d)), "dense_d2h_bytes_per_step": int(sum_over_ranks(d2h)),
                "steps": args.e2e_steps, "ms_per_step": 1e3 * e2e_s / args.e2e_steps,
-               "api": "tcif_stage_host: H2D alpha[P],T,phi,phiAlphaCorr[P]; D2H F,alpha[P],alphaPhi[P]; pinned host "
-                      "buffers, uploads/compute/downloads pipelined"}
+               "api": "tcif_stage_host: H2D T,phi,phiAlphaCorr[P] (+alpha[P] in the first step only: stamps); D2H alphaPhi[P] dense, "
+                      "F and alpha[P] as deltas; pinned host buffers, uploads/compute/downloads pipelined; bytes = last step, as copied"}
         # (2) the reference's own call surface: fluid.solve() (flux assembly + implicit predictor + MULES + rhoPhi,
         #     all on the device) then fluid.divCapillaryStress(): more work per step, fewer bytes over PCIe
         ctx.set_cell_centres(np.asarray(f["C"]), np.asarray(f["deltab"]))
@@ -357,15 +434,20 @@ def run_ours(args, rank, world, local_rank):
 
         for p in range(P):
             ai[p][...] = ai0[p]; ab[p][...] = ab0[p]
-        cs_s = timed_host(lambda: ctx.time_step_host(ctl, dt, ai, ab, Ti, Tb, phii, phib, rpi, rpb, Fi, Fb), args.e2e_steps)
+        counter[0] = 0                                   # the host rewrote alpha: unknown stamp, uploaded once more
+        cs_s = timed_host(stamped(lambda: ctx.time_step_host(ctl, dt, ai, ab, Ti, Tb, phii, phib, rpi, rpb, Fi, Fb)), args.e2e_steps)
+        moved = ctx.host_bytes_moved
         sweeps = [int(abi.lib().tcif_predictor_sweeps(ctx.h, p)) for p in range(P)]
         extra["e2e_call_surface"] = {
             "value": total_cells * args.e2e_steps / cs_s / 1e6, "unit": UNIT, "ms_per_step": 1e3 * cs_s / args.e2e_steps,
-            "h2d_bytes_per_step": int(sum_over_ranks(8 * ((P + 1) * (nC + nBF) + nIF + nBF))),
-            "d2h_bytes_per_step": int(sum_over_ranks(8 * ((P + 3) * (nC + nBF) + nIF + nBF))),
+            "h2d_bytes_per_step": int(sum_over_ranks(moved[0])), "d2h_bytes_per_step": int(sum_over_ranks(moved[1])),
+            "dense_h2d_bytes_per_step": int(sum_over_ranks(8 * ((P + 1) * (nC + nBF) + nIF + nBF))),
+            "dense_d2h_bytes_per_step": int(sum_over_ranks(8 * ((P + 3) * (nC + nBF) + nIF + nBF))),
             "api": "tcif_time_step_host = multiphaseSystem::solve() (vanLeer + linear compression, implicit upwind "
-                   "predictor, nAlphaCorr 1) + divCapillaryStress(); H2D alpha[P],T,phi; D2H alpha[P],rhoPhi,F",
+                   "predictor, nAlphaCorr 1) + divCapillaryStress(); H2D T,phi (+alpha[P] first step only); D2H rhoPhi dense, "
+                   "alpha[P] and F as deltas",
             "predictor_sweeps": sweeps}
+        ctx.host_sparse_returns(False)
         # device-resident cost of that call surface
         with torch.cuda.stream(stream):
             ctx.solve_alphas(ctl, dt)
@@ -399,7 +481,9 @@ def run_ours(args, rank, world, local_rank):
         edge = cpu_sample_edge(args, cores)
         nst = 16
         rate, secs, nd, cprocs, cspec = cpu_stage_rate(args.config, edge, nst, cores)
+        one_core, one_core_sample = cpu_one_core_rate(args.config)
         cpu = {"value": rate, "unit": UNIT, "cores": nd, "kind": "port", "host_cores": cores,
+               "one_core": {"value": one_core, "unit": UNIT, "sample": one_core_sample},
                "sample": f"{cspec.name} {edge}^3 = {cspec.nCells} cells, {cspec.nPhases} phases, {nst} stages, "
                          f"{nd} sub-domains {cprocs[0]}x{cprocs[1]}x{cprocs[2]}, {secs:.1f} s"}
 

@@ -194,6 +194,23 @@ TCIF_API int tcif_stage_host(tcif_ctx *ctx, double deltaT,
                              double *const *alphaPhiInternal, double *const *alphaPhiBoundary,
                              double *Finternal, double *Fboundary);
 
+/* ---- what the host-buffer entry points (tcif_stage_host, tcif_time_step_host) move over PCIe ----------------
+ * One-shot stamps for the NEXT *_host call: in[p] = stamp of the state the caller's alpha array p holds (skips the
+ * upload when the device copy carries the same non-zero stamp), out[p] = stamp the device assigns to its alpha when
+ * the call returns (the caller's arrays then hold the same values).  A time-stepping caller whose alpha is only
+ * ever changed by solve() passes out of step k as in of step k+1 and never uploads alpha again.  NULL = zeros. */
+TCIF_API int tcif_host_alpha_stamps(tcif_ctx *ctx, const uint64_t *in, const uint64_t *out);
+/* on: alpha, F and alphaPhi come back as DELTAS -- the entries whose value differs from what the caller's array
+ * already holds (alpha: the values passed in; F, alphaPhi: what the previous call wrote to the same array) are
+ * compacted on the device, copied as (index, value) and scattered into the array by the calling thread (a few host
+ * threads for long lists); a field with more than a quarter of its entries changed is copied densely.  F and the
+ * fractions and fluxes of dispersed phases are exactly zero away from the interfaces, so most of their bytes never
+ * cross the link.  The caller must leave the F and alphaPhi arrays as the previous call returned them.  The arrays
+ * equal those of the dense path entry by entry (compared by value: the sign of a zero may differ). */
+TCIF_API int tcif_host_sparse_returns(tcif_ctx *ctx, int on);
+/* bytes the last *_host call really copied host->device and device->host */
+TCIF_API int tcif_host_bytes_moved(const tcif_ctx *ctx, int64_t *h2d, int64_t *d2h);
+
 /* ---- rest of multiphaseSystem::solveAlphas() on the device --------- */
 /* convection schemes of fvSchemes' div(phi,alpha) / div(phir,alpha,alpha) the device path supports */
 enum { TCIF_SCHEME_UPWIND = 0, TCIF_SCHEME_LINEAR = 1, TCIF_SCHEME_VANLEER = 2 };

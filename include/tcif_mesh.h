@@ -36,6 +36,13 @@ TCIF_API int tcif_mesh_decompose(const tcif_mesh *global, const int32_t *cellPro
 /* `simple (px py pz)` cell->rank map of a uniform box. */
 TCIF_API int tcif_mesh_simple_map(int32_t nx, int32_t ny, int32_t nz, int32_t px, int32_t py, int32_t pz,
                                   int32_t *cellProc);
+/* An OpenFOAM ASCII polyMesh directory (<case>/constant/polyMesh or <case>/processorN/constant/polyMesh: points,
+ * faces, owner, neighbour, boundary) of ANY cell shape; geometry by OpenFOAM's primitiveMesh formulas, linear weights.
+ * Patch types: patch | wall | symmetry(Plane) (generic), empty, wedge, processor (neighbProcNo is read). */
+TCIF_API int tcif_mesh_read_polymesh(const char *polyMeshDir, tcif_mesh **out);
+/* A labelList file, e.g. the `cellDecomposition` that decomposePar -cellDist writes for scotch: *count labels into
+ * labels[capacity] (call with capacity 0 to learn the count; returns 1 when capacity is too small). */
+TCIF_API int tcif_mesh_read_label_list(const char *path, int32_t capacity, int32_t *labels, int32_t *count);
 TCIF_API void tcif_mesh_free(tcif_mesh *m);
 /* Borrowed view for tcif_create (valid while the mesh lives). */
 TCIF_API int tcif_mesh_get_desc(const tcif_mesh *m, tcif_mesh_desc *out);

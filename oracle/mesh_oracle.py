@@ -66,9 +66,14 @@ class Mesh:
         return int(self.patchType.shape[0])
 
 
+def dot3(a, b):
+    """row-wise a.b summed left to right (x, y, z): the order of the C++ side; einsum may contract differently"""
+    return a[:, 0] * b[:, 0] + a[:, 1] * b[:, 1] + a[:, 2] * b[:, 2]
+
+
 def linear_weights(Sf, Cf, CP, CN):
-    a = np.abs(np.einsum("ij,ij->i", Sf, CN - Cf))
-    b = np.abs(np.einsum("ij,ij->i", Sf, Cf - CP))
+    a = np.abs(dot3(Sf, CN - Cf))
+    b = np.abs(dot3(Sf, Cf - CP))
     return a / (b + a)
 
 
@@ -193,10 +198,10 @@ def decompose(g: Mesh, cellProc: np.ndarray, nProcs: int) -> list[Mesh]:
             S = np.where(flip[:, None], -g.Sf[f], g.Sf[f])
             mag = np.sqrt(S[:, 0] * S[:, 0] + S[:, 1] * S[:, 1] + S[:, 2] * S[:, 2])
             nf = S / mag[:, None]
-            dP = np.einsum("ij,ij->i", nf, g.Cf[f] - g.C[lc_g])
+            dP = dot3(nf, g.Cf[f] - g.C[lc_g])
             SN = -S
             nN = SN / (mag[:, None] + VSMALL)
-            dN = np.einsum("ij,ij->i", nN, g.Cf[f] - g.C[nc_g])
+            dN = dot3(nN, g.Cf[f] - g.C[nc_g])
             wgt = dN / (dP + dN)
             dl = g.C[nc_g] - g.C[lc_g]
             ptype.append(PATCH_PROCESSOR); pstart.append(pos); psize.append(len(f)); pnbr.append(e); bpa.append(-1)

@@ -645,32 +645,59 @@ typedef struct thr_args {
 
 static double now_s(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec + 1e-9 * ts.tv_nsec; }
 
+/* first touch: a worker copies what it is going to stream (its sub-mesh and its fields) into pages it allocates and
+ * writes itself, so that on a multi-socket host they live on the worker's own NUMA node -- what an MPI rank of the
+ * reference gets for free by reading its processor directory itself.  The callers' arrays were written by ONE thread. */
+static double *dclone(const double *src, size_t n) { double *d = dnew(n ? n : 1); if (n) memcpy(d, src, sizeof(double) * n); return d; }
+static int32_t *iclone(const int32_t *src, size_t n) { int32_t *d = (int32_t *)xmalloc(sizeof(int32_t) * (n ? n : 1)); if (n) memcpy(d, src, sizeof(int32_t) * n); return d; }
+
 static void *thr_main(void *p) {
     thr_args *a = (thr_args *)p;
-    const orc_mesh *m = &a->tc.sh->meshes[a->tc.dom];
+    const orc_mesh *m0 = &a->tc.sh->meshes[a->tc.dom];
     orc_comm comm = { &a->tc, thr_halo, thr_reduce };
     int nP = a->nPhases;
+    const size_t nC = m0->nCells, nIF = m0->nIF, nBF = m0->nBF;
+    /* local sub-mesh (patch tables stay shared: the halo hook reads the neighbours' through sh->meshes) */
+    orc_mesh lm = *m0;
+    int32_t *own = iclone(m0->owner, nIF), *nei = iclone(m0->neighbour, nIF), *fc = iclone(m0->faceCells, nBF);
+    double *Sf = dclone(m0->Sf, 3 * nIF), *w = dclone(m0->w, nIF), *V = dclone(m0->V, nC), *Sfb = dclone(m0->Sfb, 3 * nBF);
+    double *magSfb = dclone(m0->magSfb, nBF), *dcb = dclone(m0->deltaCoeffsb, nBF), *wb = dclone(m0->wb, nBF);
+    lm.owner = own; lm.neighbour = nei; lm.faceCells = fc; lm.Sf = Sf; lm.w = w; lm.V = V; lm.Sfb = Sfb;
+    lm.magSfb = magSfb; lm.deltaCoeffsb = dcb; lm.wb = wb;
+    const orc_mesh *m = &lm;
+    double **ai = (double **)xmalloc(sizeof(double *) * nP), **ab = (double **)xmalloc(sizeof(double *) * nP);
+    double **pai = (double **)xmalloc(sizeof(double *) * nP), **pab = (double **)xmalloc(sizeof(double *) * nP);
     /* keep the HO flux so every stage starts from the same phiAlpha input */
     double **pa0i = (double **)xmalloc(sizeof(double *) * nP), **pa0b = (double **)xmalloc(sizeof(double *) * nP);
     for (int k = 0; k < nP; ++k) {
-        pa0i[k] = dnew(m->nIF); memcpy(pa0i[k], a->phiAlphai[k], sizeof(double) * m->nIF);
-        pa0b[k] = dnew(m->nBF); memcpy(pa0b[k], a->phiAlphab[k], sizeof(double) * m->nBF);
+        ai[k] = dclone(a->alphai[k], nC); ab[k] = dclone(a->alphab[k], nBF);
+        pai[k] = dclone(a->phiAlphai[k], nIF); pab[k] = dclone(a->phiAlphab[k], nBF);
+        pa0i[k] = dclone(a->phiAlphai[k], nIF); pa0b[k] = dclone(a->phiAlphab[k], nBF);
     }
+    double *Ti = a->Ti ? dclone(a->Ti, nC) : NULL, *Tb = a->Tb ? dclone(a->Tb, nBF) : NULL;
+    double *phii = dclone(a->phii, nIF), *phib = dclone(a->phib, nBF);
+    double *Fi = dnew(3 * nC + 1), *Fb = dnew(3 * nBF + 1);
     pthread_barrier_wait(&a->tc.sh->bar);
     double t0 = now_s();
     for (int s = 0; s < a->nStages; ++s) {
         if (s > 0)
             for (int k = 0; k < nP; ++k) {
-                memcpy(a->phiAlphai[k], pa0i[k], sizeof(double) * m->nIF);
-                memcpy(a->phiAlphab[k], pa0b[k], sizeof(double) * m->nBF);
+                memcpy(pai[k], pa0i[k], sizeof(double) * nIF);
+                memcpy(pab[k], pa0b[k], sizeof(double) * nBF);
             }
-        orc_stage(m, &comm, a->cfg, nP, a->alphai, a->alphab, a->alphaBc, a->sigma, a->Ti, a->Tb,
-                  a->phii, a->phib, a->phiAlphai, a->phiAlphab, NULL, NULL, a->deltaT, a->Fi, a->Fb);
+        orc_stage(m, &comm, a->cfg, nP, ai, ab, a->alphaBc, a->sigma, Ti, Tb, phii, phib, pai, pab, NULL, NULL, a->deltaT, Fi, Fb);
     }
     pthread_barrier_wait(&a->tc.sh->bar);
     a->seconds = now_s() - t0;
-    for (int k = 0; k < nP; ++k) { free(pa0i[k]); free(pa0b[k]); }
-    free(pa0i); free(pa0b);
+    for (int k = 0; k < nP; ++k) {      /* results back into the caller's arrays */
+        memcpy(a->alphai[k], ai[k], sizeof(double) * nC); memcpy(a->alphab[k], ab[k], sizeof(double) * nBF);
+        memcpy(a->phiAlphai[k], pai[k], sizeof(double) * nIF); memcpy(a->phiAlphab[k], pab[k], sizeof(double) * nBF);
+        free(ai[k]); free(ab[k]); free(pai[k]); free(pab[k]); free(pa0i[k]); free(pa0b[k]);
+    }
+    memcpy(a->Fi, Fi, sizeof(double) * 3 * nC); memcpy(a->Fb, Fb, sizeof(double) * 3 * nBF);
+    free(ai); free(ab); free(pai); free(pab); free(pa0i); free(pa0b);
+    free(Ti); free(Tb); free(phii); free(phib); free(Fi); free(Fb);
+    free(own); free(nei); free(fc); free(Sf); free(w); free(V); free(Sfb); free(magSfb); free(dcb); free(wb);
     return NULL;
 }
 

@@ -1,0 +1,227 @@
+"""Residency through the boundary: one reference time step replayed with exactly the calls foam_shim/ makes.
+
+Call order of the reference (thermocapillaryInterFoam.C:104-150):
+    fluid.solve()                              :105   foam_shim/multiphaseSystemDeviceSolve.C
+    UEqn.H:29        fluid.divCapillaryStress()       foam_shim/phaseSystemDevice.C
+    TEqn.H           T changes on the host
+    pEqn.H:35        fvc::flux(fluid.divCapillaryStress())   x nCorr (PIMPLE correctors)
+    :150             divCapillaryStress = fluid.divCapillaryStress()
+The host fields carry a modification stamp (OpenFOAM: regIOobject::eventNo(); here a counter the stand-in
+`HostField` advances on every write access, as GeometricField::ref() does).
+
+Asserted: after the first step NO alpha crosses PCIe host->device any more (solve() left the newest alpha on the
+device and getAlpha() marked it), T is uploaded once per step (TEqn changed it), F is evaluated once per distinct
+(alpha, T) state -- 2 per step with a temperatureDependent sigma, 1 with a constant sigma -- and every other call
+is a cache hit; and the results equal a context that is fed everything afresh for every call (bitwise).
+"""
+import numpy as np
+import pytest
+
+from thermocapillaryinterfoam_b200 import abi, cases
+from helpers import global_mesh
+
+pytestmark = pytest.mark.gpu
+
+
+class HostField:
+    """volScalarField stand-in: values + eventNo() that every non-const access advances."""
+
+    def __init__(self, internal, boundary):
+        self.i, self.b, self.event = np.array(internal), np.array(boundary), 1
+
+    def ref(self):                       # GeometricField::ref() / primitiveFieldRef(): setUpToDate() -> eventNo++
+        self.event += 1
+        return self
+
+
+class Bridge:
+    """The calls of foam_shim/tcifFoamBridge.H, one to one."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+
+    def setAlpha(self, p, fld):
+        return self.ctx.set_alpha_stamped(p, fld.event, fld.i, fld.b)
+
+    def getAlpha(self, p, fld):
+        fld.ref()                        # primitiveFieldRef()
+        fld.i, b = self.ctx.get_alpha(p)
+        fld.ref()                        # boundaryFieldRef() in unflatBoundary
+        fld.b = b
+        self.ctx.mark_alpha(p, fld.event)
+
+    def setTemperature(self, fld):
+        return self.ctx.set_temperature_stamped(fld.event, fld.i, fld.b)
+
+
+def _div_capillary_stress(br, ctx, alphas, T, bc):
+    """body of phaseSystem::divCapillaryStress() in foam_shim/phaseSystemDevice.C"""
+    for p, a in enumerate(alphas):
+        ctx.set_alpha_bc(p, bc[p])
+        br.setAlpha(p, a)
+    br.setTemperature(T)
+    ctx.div_capillary_stress()
+    return ctx.get_force()
+
+
+def _solve(br, ctx, alphas, phi, bc, ctl, dt, rho):
+    """body of multiphaseSystem::solve() in foam_shim/multiphaseSystemDeviceSolve.C"""
+    ctx.set_phi(*phi)
+    for p, a in enumerate(alphas):
+        ctx.set_alpha_bc(p, bc[p])
+        br.setAlpha(p, a)
+        ctx.set_rho(p, rho[p])
+    ctx.solve_alphas(ctl, dt)
+    out = []
+    for p, a in enumerate(alphas):
+        br.getAlpha(p, a)
+        out.append(ctx.get_phi_alpha(p))
+    return out, ctx.get_rho_phi()
+
+
+@pytest.mark.parametrize("config,n,evalsPerStep", [(5, 20, 2), (1, 32, 1)])
+def test_time_step_replay_keeps_fields_resident(config, n, evalsPerStep):
+    spec = cases.case(config, n)
+    m = global_mesh(spec)
+    f = cases.synthetic_fields(spec, m)
+    P, nCorr, nSteps = spec.nPhases, 3, 3
+    rho = (1000.0, 800.0, 1.2, 50.0)
+    ctl = abi.alpha_controls(1, 1, "vanLeer", "linear", True, 1e-10, 200)
+    ctx = abi.Context(m, P, device=0)
+    cases.load_case(ctx, spec, f)                      # sigma models etc.; fields are re-sent below through the bridge
+    ctx.set_cell_centres(np.asarray(f["C"]), np.asarray(f["deltab"]))
+    br = Bridge(ctx)
+    alphas = [HostField(f["alpha_i"][p], f["alpha_b"][p]) for p in range(P)]
+    T = HostField(f["T_i"], f["T_b"])
+    phi = (f["phi_i"], f["phi_b"])
+    bc = f["alphaBc"]
+    # reference run: a second context that is given every field afresh (unstamped) before every call
+    ref = abi.Context(m, P, device=0)
+    cases.load_case(ref, spec, f)
+    ref.set_cell_centres(np.asarray(f["C"]), np.asarray(f["deltab"]))
+    ref.set_force_cache(False)
+
+    def ref_force():
+        for p in range(P):
+            ref.set_alpha(p, alphas[p].i, alphas[p].b)
+        ref.set_temperature(T.i, T.b)
+        ref.div_capillary_stress()
+        return ref.get_force()
+
+    # createFields.H:168-179 evaluates the force once before the time loop
+    F0 = _div_capillary_stress(br, ctx, alphas, T, bc)
+    assert np.array_equal(F0[0], ref_force()[0])
+    for step in range(nSteps):
+        x0 = ctx.transfer_counters
+        e0, h0 = ctx.force_counters()
+        # fluid.solve()
+        for p in range(P):                              # the reference context starts from the same host state
+            ref.set_alpha(p, alphas[p].i, alphas[p].b)
+            ref.set_rho(p, rho[p])
+        ref.set_phi(*phi)
+        ref.solve_alphas(ctl, f["deltaT"])
+        _solve(br, ctx, alphas, phi, bc, ctl, f["deltaT"], rho)
+        for p in range(P):
+            assert np.array_equal(alphas[p].i, ref.get_alpha(p)[0]), f"alpha{p} after solve(), step {step}"
+        # UEqn.H:29
+        Fu = _div_capillary_stress(br, ctx, alphas, T, bc)
+        assert np.array_equal(Fu[0], ref_force()[0])
+        # TEqn.H: the energy equation changes T on the host
+        T.ref()
+        T.i = T.i + 0.01 * (step + 1) * np.sin(np.arange(T.i.size))
+        # pEqn.H:35 per PIMPLE corrector, then thermocapillaryInterFoam.C:150
+        for _ in range(nCorr + 1):
+            Fp = _div_capillary_stress(br, ctx, alphas, T, bc)
+        Fr = ref_force()
+        assert np.array_equal(Fp[0], Fr[0]) and np.array_equal(Fp[1], Fr[1])
+        x1 = ctx.transfer_counters
+        e1, h1 = ctx.force_counters()
+        nCalls = nCorr + 2
+        assert e1 - e0 == evalsPerStep, (step, e1 - e0)
+        assert h1 - h0 == nCalls - evalsPerStep, (step, h1 - h0)
+        assert x1["TUploads"] - x0["TUploads"] == 1, "T crosses PCIe once per time step (after TEqn)"
+        if step == 0:
+            assert x1["alphaUploads"] - x0["alphaUploads"] == 0, "alpha was uploaded by the createFields evaluation already"
+        else:
+            assert x1["alphaUploads"] - x0["alphaUploads"] == 0, f"alpha re-uploaded in step {step}"
+        assert x1["alphaSkipped"] - x0["alphaSkipped"] == P * (nCalls + 1)
+    # a host-side change of alpha (e.g. a function object clipping it) is seen: the stamp moved
+    alphas[0].ref()
+    alphas[0].i = np.clip(alphas[0].i, 0.0, 1.0)
+    x0 = ctx.transfer_counters
+    _div_capillary_stress(br, ctx, alphas, T, bc)
+    assert ctx.transfer_counters["alphaUploads"] - x0["alphaUploads"] == 1
+    ctx.close()
+    ref.close()
+
+
+def test_device_side_change_invalidates_the_stamp():
+    """tcif_stage advances alpha on the device: a stamped set with the OLD host stamp must upload again."""
+    spec = cases.case(5, 12)
+    m = global_mesh(spec)
+    f = cases.synthetic_fields(spec, m)
+    ctx = abi.Context(m, 3, device=0)
+    cases.load_case(ctx, spec, f)
+    assert ctx.set_alpha_stamped(0, 7, f["alpha_i"][0], f["alpha_b"][0]) is True
+    assert ctx.set_alpha_stamped(0, 7, f["alpha_i"][0], f["alpha_b"][0]) is False
+    ctx.stage(f["deltaT"])
+    assert ctx.set_alpha_stamped(0, 7, f["alpha_i"][0], f["alpha_b"][0]) is True
+    assert ctx.set_alpha_stamped(0, 0, f["alpha_i"][0], f["alpha_b"][0]) is True, "stamp 0 = unknown: always uploads"
+    assert ctx.set_alpha_stamped(0, 0, f["alpha_i"][0], f["alpha_b"][0]) is True
+    ctx.close()
+
+
+@pytest.mark.parametrize("api", ["stage_host", "time_step_host"])
+def test_sparse_returns_and_host_stamps_are_bit_identical_to_the_dense_path(api):
+    """tcif_host_sparse_returns + tcif_host_alpha_stamps: three consecutive steps through host buffers; the host arrays
+    must equal, bit for bit, those of a context that uploads everything and downloads densely, while fewer bytes move."""
+    spec = cases.case(5, 32)
+    m = global_mesh(spec)
+    f = cases.synthetic_fields(spec, m)
+    P = spec.nPhases
+    # sharpen the tanh tails to exact zeros (at BASELINE sizes the dispersed phases are exactly 0 beyond ~28 cells from
+    # the interface; at this size the tails would fill the box and every delta would fall back to the dense copy)
+    for arr in (f["alpha_i"], f["alpha_b"]):
+        for p in (0, 1):
+            arr[p][arr[p] < 1e-2] = 0.0
+        arr[2][...] = 1.0 - arr[0] - arr[1]
+    ctl = abi.alpha_controls(1, 1, "vanLeer", "linear", True, 1e-10, 200)
+
+    def make():
+        ctx = abi.Context(m, P, device=0)
+        cases.load_case(ctx, spec, f)
+        ctx.set_cell_centres(np.asarray(f["C"]), np.asarray(f["deltab"]))
+        for p in range(P):
+            ctx.set_rho(p, (1000.0, 800.0, 1.2)[p])
+        st = dict(ai=[x.copy() for x in f["alpha_i"]], ab=[x.copy() for x in f["alpha_b"]],
+                  pi=[np.zeros(m.nIF) for _ in range(P)], pb=[np.zeros(m.nBF) for _ in range(P)],
+                  ri=np.zeros(m.nIF), rb=np.zeros(m.nBF), Fi=np.zeros((m.nCells, 3)), Fb=np.zeros((m.nBF, 3)))
+        return ctx, st
+
+    def step(ctx, st):
+        if api == "stage_host":
+            ctx.stage_host(f["deltaT"], st["ai"], st["ab"], f["T_i"], f["T_b"], f["phi_i"], f["phi_b"], f["phiAlpha_i"],
+                           f["phiAlpha_b"], st["pi"], st["pb"], st["Fi"], st["Fb"])
+        else:
+            ctx.time_step_host(ctl, f["deltaT"], st["ai"], st["ab"], f["T_i"], f["T_b"], f["phi_i"], f["phi_b"], st["ri"],
+                               st["rb"], st["Fi"], st["Fb"], st["pi"], st["pb"])
+        return ctx.host_bytes_moved
+
+    dense, sd = make()
+    sparse, ss = make()
+    sparse.host_sparse_returns(True)
+    for k in range(3):
+        bd = step(dense, sd)
+        sparse.host_alpha_stamps([k] * P if k else None, [k + 1] * P)       # out of step k is in of step k+1
+        bs = step(sparse, ss)
+        for key in ("Fi", "Fb", "ri", "rb") if api == "time_step_host" else ("Fi", "Fb"):
+            assert np.array_equal(sd[key], ss[key]), (key, k)
+        for p in range(P):
+            assert np.array_equal(sd["ai"][p], ss["ai"][p]) and np.array_equal(sd["ab"][p], ss["ab"][p]), (p, k)
+            assert np.array_equal(sd["pi"][p], ss["pi"][p]) and np.array_equal(sd["pb"][p], ss["pb"][p]), (p, k)
+        if k > 0:
+            assert bs[0] <= bd[0] - P * 8 * m.nCells, "alpha was uploaded although the stamps matched"
+            # alpha and alphaPhi of the two dispersed phases come back as deltas (F's band exceeds the cap at this size)
+            assert bs[1] < bd[1] - 2 * 8 * m.nCells, ("the delta read-back did not save device->host bytes", bs, bd)
+    dense.close()
+    sparse.close()

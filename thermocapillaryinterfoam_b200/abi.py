@@ -108,6 +108,9 @@ def lib():
     L.tcif_set_temperature_stamped.argtypes = [C.c_void_p, C.c_uint64, c_dp, c_dp, C.POINTER(C.c_int32)]
     L.tcif_mark_alpha.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
     L.tcif_transfer_counters.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+    L.tcif_host_alpha_stamps.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.tcif_host_sparse_returns.argtypes = [C.c_void_p, C.c_int]
+    L.tcif_host_bytes_moved.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.tcif_predictor_sweeps.argtypes = [C.c_void_p, C.c_int]
     L.tcif_destroy.argtypes = [C.c_void_p]
     L.tcif_destroy.restype = None
@@ -567,6 +570,22 @@ class Context:
                                            _d(Tb), _d(phii), _d(phib), _pp(alphaPhi_i) if alphaPhi_i else None,
                                            _pp(alphaPhi_b) if alphaPhi_b else None, _d(rhoPhi_i), _d(rhoPhi_b), _d(Fi),
                                            _d(Fb)))
+
+    def host_alpha_stamps(self, stamps_in=None, stamps_out=None):
+        """one-shot stamps of the alpha arrays of the NEXT stage_host / time_step_host call (tcif_host_alpha_stamps)"""
+        P = self.P
+        a = (C.c_uint64 * P)(*[int(x) for x in (stamps_in or [0] * P)])
+        b = (C.c_uint64 * P)(*[int(x) for x in (stamps_out or [0] * P)])
+        self._ck(lib().tcif_host_alpha_stamps(self.h, a, b))
+
+    def host_sparse_returns(self, on=True):
+        self._ck(lib().tcif_host_sparse_returns(self.h, int(bool(on))))
+
+    @property
+    def host_bytes_moved(self):
+        a, b = C.c_int64(), C.c_int64()
+        self._ck(lib().tcif_host_bytes_moved(self.h, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
 
     def get_rho_phi(self):
         a, b = np.empty(self.nIF), np.empty(self.nBF)

@@ -2,7 +2,7 @@
 // Builds what the OpenFOAM shim would read off an fvMesh: single-block hex meshes in blockMesh
 // ordering, and processor sub-meshes in decomposePar conventions.
 // Checked bit-exactly against the independent numpy restatement oracle/mesh_oracle.py.
-#include "../../include/tcif_mesh.h"
+#include "mesh_host.h"
 
 #include <algorithm>
 #include <cmath>
@@ -13,67 +13,9 @@
 #include <string>
 #include <vector>
 
-namespace {
-
-thread_local std::string g_err;
-const double VSMALL = 1e-300;
-
-[[noreturn]] void failf(const char *fmt, ...) {
-    char buf[512];
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(buf, sizeof buf, fmt, ap);
-    va_end(ap);
-    throw std::runtime_error(buf);
-}
-
-struct V3 { double x, y, z; };
-inline V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
-inline V3 neg(V3 a) { return {-a.x, -a.y, -a.z}; }
-inline double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-inline double mag(V3 a) { return std::sqrt(a.x * a.x + a.y * a.y + a.z * a.z); }
-
-// surfaceInterpolation::makeWeights (linear)
-inline double linear_weight(V3 S, V3 Cf, V3 CP, V3 CN) {
-    double a = std::fabs(dot(S, CN - Cf)), b = std::fabs(dot(S, Cf - CP));
-    return a / (b + a);
-}
-// processorFvPatch::makeWeights: unit-normal projections of both sides
-inline double processor_weight(V3 S, V3 Cf, V3 Clocal, V3 Cnbr) {
-    double m = mag(S);
-    V3 nf{S.x / m, S.y / m, S.z / m};
-    double dP = dot(nf, Cf - Clocal);
-    V3 SN = neg(S);
-    double mn = m + VSMALL;
-    V3 nN{SN.x / mn, SN.y / mn, SN.z / mn};
-    double dN = dot(nN, Cf - Cnbr);
-    return dN / (dP + dN);
-}
-
-}  // namespace
-
-struct tcif_mesh {
-    int32_t nCells = 0;
-    std::vector<int32_t> owner, neighbour;
-    std::vector<double> Sf, w, V, C, Cf;
-    std::vector<int32_t> patchType, patchStart, patchSize, patchNbr;
-    std::vector<int32_t> faceCells;
-    std::vector<double> Sfb, magSfb, dcb, wb, Cfb, nbrC;
-    std::vector<int64_t> cellGlobal, nbrGlobal, faceAddr, bfaceAddr, bndAddr;
-
-    void push_face(int32_t o, int32_t n, V3 S, V3 cf, double wt, int64_t gface) {
-        owner.push_back(o); neighbour.push_back(n);
-        Sf.insert(Sf.end(), {S.x, S.y, S.z}); Cf.insert(Cf.end(), {cf.x, cf.y, cf.z});
-        w.push_back(wt); faceAddr.push_back(gface + 1);
-    }
-    void push_bface(int32_t fc, V3 S, V3 cf, double dc, double wt, V3 nc, int64_t ng, int64_t addr) {
-        faceCells.push_back(fc);
-        Sfb.insert(Sfb.end(), {S.x, S.y, S.z}); Cfb.insert(Cfb.end(), {cf.x, cf.y, cf.z});
-        magSfb.push_back(mag(S)); dcb.push_back(dc); wb.push_back(wt);
-        nbrC.insert(nbrC.end(), {nc.x, nc.y, nc.z}); nbrGlobal.push_back(ng); bfaceAddr.push_back(addr);
-    }
-    V3 centre(int32_t c) const { return {C[3 * (size_t)c], C[3 * (size_t)c + 1], C[3 * (size_t)c + 2]}; }
-};
+using namespace tcif_host;
+namespace tcif_host { std::string &last_error() { thread_local std::string e; return e; } }
+#define g_err (tcif_host::last_error())
 
 namespace {
 

@@ -24,6 +24,7 @@
 #include <mutex>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <type_traits>
 #include <unordered_map>
 #include <vector>
@@ -235,6 +236,21 @@ struct tcif_ctx {
     uint64_t alphaStamp[4]{}, tStamp = 0;
     int64_t xfer[4]{};                  // alpha uploaded / skipped, T uploaded / skipped
     std::vector<int> bcHost[4];         // last alpha BC kinds uploaded (tcif_set_alpha_bc re-uploads only on change)
+    // host-buffer entry points (tcif_stage_host / tcif_time_step_host): one-shot stamps of the caller's alpha arrays and
+    // delta read-back of alpha and F (tcif_host_alpha_stamps, tcif_host_sparse_returns)
+    bool hsArmed = false;
+    uint64_t hsIn[4]{}, hsOut[4]{};
+    bool sparseReturns = false;
+    double *shAlpha[4]{}, *shF = nullptr;      // device record of what the caller's arrays hold
+    double *shFace[5]{};                       // same for alphaPhi[p] (host face order)
+    const void *shFaceHost[5]{};
+    const void *shFHost = nullptr;             // the host F array shF mirrors
+    int *dIdx = nullptr, *dCount = nullptr;
+    double *dVal = nullptr;
+    int dCap = 0;
+    int *hIdx = nullptr, *hCount = nullptr;    // pinned
+    double *hVal = nullptr;
+    int64_t d2hBytes = 0, h2dBytes = 0;        // bytes actually moved by the last *_host call
     int64_t forceEvaluations = 0, forceCacheHits = 0;
     double deltaN = 0.0;
     bool deltaNValid = false;
@@ -1932,6 +1948,140 @@ int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const doub
     return (int)created;
 }
 
+// ---- host-buffer entry points: what crosses PCIe ---------------------------------------------------------------
+void host_pipeline_init(tcif_ctx *c) {
+    if (c->sIn) return;
+    CUDA_OK(cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking));
+    CUDA_OK(cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        CUDA_OK(cudaEventCreateWithFlags(&c->evIn[i], cudaEventDisableTiming));
+        CUDA_OK(cudaEventCreateWithFlags(&c->evC[i], cudaEventDisableTiming));
+    }
+    c->stagingOut = c->dalloc<double>(c->stagingDoubles);
+}
+void delta_init(tcif_ctx *c) {
+    if (c->dIdx) return;
+    // (index, value) pairs cost 1.5x (scalar) / 1.17x (vector) the dense bytes per entry: beyond 1/4 of the entries the
+    // dense copy is preferred
+    c->dCap = std::max(std::max(c->nC, c->nIF) / 4, 1024);
+    const size_t nVal = std::max<size_t>((size_t)c->dCap, 3 * (size_t)std::max(c->nC / 4, 1024));
+    c->dIdx = c->dalloc<int>(c->dCap); c->dVal = c->dalloc<double>(nVal); c->dCount = c->dalloc<int>(8);
+    CUDA_OK(cudaHostAlloc((void **)&c->hIdx, sizeof(int) * (size_t)c->dCap, cudaHostAllocDefault));
+    CUDA_OK(cudaHostAlloc((void **)&c->hVal, sizeof(double) * nVal, cudaHostAllocDefault));
+    CUDA_OK(cudaHostAlloc((void **)&c->hCount, sizeof(int) * 8, cudaHostAllocDefault));
+}
+// dst[idx[k]] = val[k] (ncomp values per entry) on a few host threads: the indices of one list are distinct
+void host_scatter(double *dst, const int *ix, const double *v, int n, int ncomp) {
+    auto work = [=](int k0, int k1) {
+        if (ncomp == 1) for (int k = k0; k < k1; ++k) dst[ix[k]] = v[k];
+        else for (int k = k0; k < k1; ++k) { double *d = dst + 3 * (size_t)ix[k]; d[0] = v[3 * (size_t)k]; d[1] = v[3 * (size_t)k + 1]; d[2] = v[3 * (size_t)k + 2]; }
+    };
+    const int nT = n < (1 << 18) ? 1 : (int)std::min<unsigned>(8, std::max(1u, std::thread::hardware_concurrency()));
+    if (nT == 1) { work(0, n); return; }
+    std::vector<std::thread> th;
+    for (int t = 0; t < nT; ++t) th.emplace_back(work, (int)((long long)n * t / nT), (int)((long long)n * (t + 1) / nT));
+    for (auto &t : th) t.join();
+}
+// Bring the entries of a device array `cur` (n entries of ncomp SoA components `stride` apart) whose value differs from
+// `shadow` to the host array `dst` (AoS when ncomp == 3) on stream st, and update the shadow.  Returns false when too
+// many differ (nothing was written: copy densely).  Synchronises st twice; every kernel the result depends on must
+// have been enqueued before.
+bool down_delta(tcif_ctx *c, cudaStream_t st, double *dst, const double *cur, double *shadow, int n, int ncomp, size_t stride) {
+    delta_init(c);
+    const int cap = ncomp == 1 ? c->dCap : std::min(c->dCap, std::max(c->nC / 4, 1024));
+    CUDA_OK(cudaMemsetAsync(c->dCount, 0, sizeof(int), st));
+    if (ncomp == 1) k_delta_compact<<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, st>>>(n, cur, shadow, cap, c->dIdx, c->dVal, c->dCount);
+    else k_delta_compact3<<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, st>>>(n, stride, cur, shadow, cap, c->dIdx, c->dVal, c->dCount);
+    c->launches++;
+    CUDA_OK(cudaMemcpyAsync(c->hCount, c->dCount, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    const int m = c->hCount[0];
+    c->d2hBytes += sizeof(int);
+    if (m > cap) return false;
+    if (m == 0) return true;
+    CUDA_OK(cudaMemcpyAsync(c->hIdx, c->dIdx, sizeof(int) * (size_t)m, cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaMemcpyAsync(c->hVal, c->dVal, sizeof(double) * (size_t)m * ncomp, cudaMemcpyDeviceToHost, st));
+    k_delta_apply<<<cdiv(m, TCIF_TPB), TCIF_TPB, 0, st>>>(m, ncomp, stride, c->dIdx, c->dVal, shadow);
+    c->launches++;
+    CUDA_OK(cudaStreamSynchronize(st));
+    c->d2hBytes += (int64_t)m * (sizeof(int) + sizeof(double) * ncomp);
+    host_scatter(dst, c->hIdx, c->hVal, m, ncomp);
+    return true;
+}
+// a face field (device slots) -> caller's array in OpenFOAM face order: delta against what the SAME host array received
+// from the same slot last time, or the dense copy.  slot: 0..P-1 alphaPhi, P rhoPhi
+void down_faces_host(tcif_ctx *c, cudaStream_t st, int slot, double *dst, const double *src) {
+    if (!c->nIF || !dst) return;
+    const size_t fb = sizeof(double) * c->nIF;
+    k_face_gather<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, st>>>(c->nIF, c->d_faceMap, src, c->stagingOut);
+    c->launches++;
+    bool done = false;
+    if (c->sparseReturns && slot < c->P) {          // rhoPhi (slot P) changes wherever phi does: always dense
+        if (!c->shFace[slot]) c->shFace[slot] = c->dalloc<double>(c->nIF);
+        if (c->shFaceHost[slot] == (const void *)dst) done = down_delta(c, st, dst, c->stagingOut, c->shFace[slot], c->nIF, 1, 0);
+        if (!done) CUDA_OK(cudaMemcpyAsync(c->shFace[slot], c->stagingOut, fb, cudaMemcpyDeviceToDevice, st));
+        c->shFaceHost[slot] = dst;
+    }
+    if (!done) { CUDA_OK(cudaMemcpyAsync(dst, c->stagingOut, fb, cudaMemcpyDefault, st)); c->d2hBytes += fb; }
+}
+// alpha[p] -> caller's array (in/out): delta against the snapshot taken at entry, or the dense copy
+void down_alpha(tcif_ctx *c, cudaStream_t st, int p, double *ai, double *ab) {
+    const size_t cb = sizeof(double) * c->nC, bb = sizeof(double) * c->nBF;
+    if (!(c->sparseReturns && c->shAlpha[p] && down_delta(c, st, ai, c->alpha[p], c->shAlpha[p], c->nC, 1, 0))) {
+        CUDA_OK(cudaMemcpyAsync(ai, c->alpha[p], cb, cudaMemcpyDefault, st));
+        c->d2hBytes += cb;
+    }
+    if (c->nBF && ab) { CUDA_OK(cudaMemcpyAsync(ab, c->alphab[p], bb, cudaMemcpyDefault, st)); c->d2hBytes += bb; }
+}
+// F -> caller's AoS arrays: delta against what the SAME host array received last time, or the dense copy
+void down_force(tcif_ctx *c, cudaStream_t st, double *Fi, double *Fb) {
+    const size_t cb = sizeof(double) * c->nC, bb = sizeof(double) * c->nBF;
+    if (Fi) {
+        bool done = false;
+        if (c->sparseReturns) {
+            if (!c->shF) c->shF = c->dalloc<double>(3 * (size_t)c->stride);
+            if (c->shFHost == (const void *)Fi) done = down_delta(c, st, Fi, c->F, c->shF, c->nC, 3, (size_t)c->stride);
+        }
+        if (!done) {
+            k_soa_to_aos3<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, st>>>(c->nC, (size_t)c->stride, c->F, c->stagingOut);
+            c->launches++;
+            CUDA_OK(cudaMemcpyAsync(Fi, c->stagingOut, 3 * cb, cudaMemcpyDefault, st));
+            c->d2hBytes += 3 * cb;
+            if (c->sparseReturns) CUDA_OK(cudaMemcpyAsync(c->shF, c->F, sizeof(double) * 3 * (size_t)c->stride, cudaMemcpyDeviceToDevice, st));
+        }
+        if (c->sparseReturns) c->shFHost = Fi;       // the host array now equals F
+    }
+    if (Fb && c->nBF) {
+        k_soa_to_aos3<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, st>>>(c->nBF, (size_t)c->nBF, c->Fb, c->stagingOut);
+        c->launches++;
+        CUDA_OK(cudaMemcpyAsync(Fb, c->stagingOut, 3 * bb, cudaMemcpyDefault, st));
+        c->d2hBytes += 3 * bb;
+    }
+}
+// uploads of the caller's alpha arrays on stream `in`, skipped where the one-shot stamps say the device copy is that
+// array; then (sparse returns) the snapshot of alpha the deltas are taken against, on the same stream
+void up_alphas_host(tcif_ctx *c, cudaStream_t in, double *const *ai, double *const *ab) {
+    const size_t cb = sizeof(double) * c->nC, bb = sizeof(double) * c->nBF;
+    for (int p = 0; p < c->P; ++p) {
+        const bool resident = c->hsArmed && c->hsIn[p] != 0 && c->hsIn[p] == c->alphaStamp[p];
+        if (!resident) {
+            alpha_changed(c, p);
+            CUDA_OK(cudaMemcpyAsync(c->alpha[p], ai[p], cb, cudaMemcpyDefault, in));
+            c->h2dBytes += cb;
+            if (c->nBF) { CUDA_OK(cudaMemcpyAsync(c->alphab[p], ab[p], bb, cudaMemcpyDefault, in)); c->h2dBytes += bb; }
+            c->xfer[0]++;
+        } else c->xfer[1]++;
+        if (c->sparseReturns) {
+            if (!c->shAlpha[p]) c->shAlpha[p] = c->dalloc<double>(c->stride);
+            CUDA_OK(cudaMemcpyAsync(c->shAlpha[p], c->alpha[p], cb, cudaMemcpyDeviceToDevice, in));
+        }
+    }
+}
+void finish_host_stamps(tcif_ctx *c) {
+    if (c->hsArmed) for (int p = 0; p < c->P; ++p) c->alphaStamp[p] = c->hsOut[p];
+    c->hsArmed = false;
+}
+
 }  // namespace
 
 // ========================================================================================
@@ -2032,6 +2182,9 @@ void tcif_destroy(tcif_ctx *c) {
     if (c->lzSpVals) cudaFree(c->lzSpVals);
     if (c->lzInbox) cudaFree(c->lzInbox);
     if (c->h_small) cudaFreeHost(c->h_small);
+    if (c->hIdx) cudaFreeHost(c->hIdx);
+    if (c->hVal) cudaFreeHost(c->hVal);
+    if (c->hCount) cudaFreeHost(c->hCount);
     if (c->sIn) cudaStreamDestroy(c->sIn);
     if (c->sOut) cudaStreamDestroy(c->sOut);
     for (int i = 0; i < 2; ++i) { if (c->evIn[i]) cudaEventDestroy(c->evIn[i]); if (c->evC[i]) cudaEventDestroy(c->evC[i]); }
@@ -2627,25 +2780,17 @@ int tcif_stage(tcif_ctx *c, double deltaT) {
 }
 
 // Pipelined host-buffer stage: [H2D alpha,T] -> force -> [D2H F || H2D phi, phiAlpha] -> MULES -> [D2H alpha, alphaPhi]
+// All compute is enqueued before the first download, because the delta read-back synchronises the download stream.
 int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const *ab, const double *Ti, const double *Tb,
                     const double *phii, const double *phib, const double *const *pai, const double *const *pab,
                     double *const *apo, double *const *apob, double *Fi, double *Fb) {
     API_BEGIN(c)
     if (!ai || !pai || !apo || (c->nBF && (!ab || !pab || !apob))) failf("tcif_stage_host: null field lists");
     if (!(deltaT > 0)) failf("tcif_stage_host: deltaT must be positive");
-    for (int p = 0; p < c->P; ++p) alpha_changed(c, p);
-    c->tStamp = 0;
-    if (!c->sIn) {
-        CUDA_OK(cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking));
-        CUDA_OK(cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking));
-        for (int i = 0; i < 2; ++i) {
-            CUDA_OK(cudaEventCreateWithFlags(&c->evIn[i], cudaEventDisableTiming));
-            CUDA_OK(cudaEventCreateWithFlags(&c->evC[i], cudaEventDisableTiming));
-        }
-        c->stagingOut = c->dalloc<double>(c->stagingDoubles);
-    }
+    host_pipeline_init(c);
     join(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    c->h2dBytes = c->d2hBytes = 0;
     const size_t cb = sizeof(double) * c->nC, bb = sizeof(double) * c->nBF, fb = sizeof(double) * c->nIF;
     cudaStream_t in = c->sIn, out = c->sOut;
     auto upFaces = [&](double *dst, const double *src) {
@@ -2653,59 +2798,46 @@ int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const
         CUDA_OK(cudaMemcpyAsync(c->staging, src, fb, cudaMemcpyDefault, in));
         k_face_scatter<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, in>>>(c->nIF, c->d_faceMap, c->staging, dst);
         c->launches++;
+        c->h2dBytes += fb;
     };
     // group A: what the force needs
-    for (int p = 0; p < c->P; ++p) {
-        CUDA_OK(cudaMemcpyAsync(c->alpha[p], ai[p], cb, cudaMemcpyDefault, in));
-        if (c->nBF) CUDA_OK(cudaMemcpyAsync(c->alphab[p], ab[p], bb, cudaMemcpyDefault, in));
-    }
+    up_alphas_host(c, in, ai, ab);
     if (Ti) {
+        touch(c); c->tStamp = 0; c->xfer[2]++;
         CUDA_OK(cudaMemcpyAsync(c->Tc, Ti, cb, cudaMemcpyDefault, in));
         if (c->nBF && Tb) CUDA_OK(cudaMemcpyAsync(c->Tb, Tb, bb, cudaMemcpyDefault, in));
+        c->h2dBytes += cb + (Tb ? bb : 0);
         c->haveT = true;
     }
     CUDA_OK(cudaEventRecord(c->evIn[0], in));
     // group B: what MULES needs, streaming in while the force runs
-    if (phii || !c->nIF) { upFaces(c->phi, phii); if (c->nBF && phib) CUDA_OK(cudaMemcpyAsync(c->phib, phib, bb, cudaMemcpyDefault, in)); }
+    if (phii || !c->nIF) { upFaces(c->phi, phii); if (c->nBF && phib) { CUDA_OK(cudaMemcpyAsync(c->phib, phib, bb, cudaMemcpyDefault, in)); c->h2dBytes += bb; } }
     for (int p = 0; p < c->P; ++p) {
         upFaces(c->phiHO[p], pai[p]);
-        if (c->nBF) CUDA_OK(cudaMemcpyAsync(c->phiHOb[p], pab[p], bb, cudaMemcpyDefault, in));
+        if (c->nBF) { CUDA_OK(cudaMemcpyAsync(c->phiHOb[p], pab[p], bb, cudaMemcpyDefault, in)); c->h2dBytes += bb; }
     }
     CUDA_OK(cudaEventRecord(c->evIn[1], in));
-    // force
+    // compute: force, then the MULES corrector
     CUDA_OK(cudaStreamWaitEvent(c->stream, c->evIn[0], 0));
     do_force(c);
     CUDA_OK(cudaEventRecord(c->evC[0], c->stream));
-    CUDA_OK(cudaStreamWaitEvent(out, c->evC[0], 0));
-    k_soa_to_aos3<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nC, (size_t)c->stride, c->F, c->stagingOut);
-    c->launches++;
-    CUDA_OK(cudaMemcpyAsync(Fi, c->stagingOut, 3 * cb, cudaMemcpyDefault, out));
-    if (Fb && c->nBF) {
-        k_soa_to_aos3<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nBF, (size_t)c->nBF, c->Fb, c->stagingOut);
-        c->launches++;
-        CUDA_OK(cudaMemcpyAsync(Fb, c->stagingOut, 3 * bb, cudaMemcpyDefault, out));
-    }
-    // MULES corrector
     CUDA_OK(cudaStreamWaitEvent(c->stream, c->evIn[1], 0));
     do_mules_stage(c, deltaT);
     CUDA_OK(cudaEventRecord(c->evC[1], c->stream));
+    // downloads
+    CUDA_OK(cudaStreamWaitEvent(out, c->evC[0], 0));
+    down_force(c, out, Fi, Fb);
     CUDA_OK(cudaStreamWaitEvent(out, c->evC[1], 0));
     for (int p = 0; p < c->P; ++p) {
-        CUDA_OK(cudaMemcpyAsync(ai[p], c->alpha[p], cb, cudaMemcpyDefault, out));
-        if (c->nBF) CUDA_OK(cudaMemcpyAsync(ab[p], c->alphab[p], bb, cudaMemcpyDefault, out));
+        down_faces_host(c, out, p, apo[p], c->phiPsi[p]);
+        if (c->nBF) { CUDA_OK(cudaMemcpyAsync(apob[p], c->phiPsib[p], bb, cudaMemcpyDefault, out)); c->d2hBytes += bb; }
     }
-    for (int p = 0; p < c->P; ++p) {
-        if (c->nIF) {
-            k_face_gather<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nIF, c->d_faceMap, c->phiPsi[p], c->stagingOut);
-            c->launches++;
-            CUDA_OK(cudaMemcpyAsync(apo[p], c->stagingOut, fb, cudaMemcpyDefault, out));
-        }
-        if (c->nBF) CUDA_OK(cudaMemcpyAsync(apob[p], c->phiPsib[p], bb, cudaMemcpyDefault, out));
-    }
+    for (int p = 0; p < c->P; ++p) down_alpha(c, out, p, ai[p], c->nBF ? ab[p] : nullptr);
     CUDA_OK(cudaStreamSynchronize(out));
     CUDA_OK(cudaStreamSynchronize(in));
     CUDA_OK(cudaStreamSynchronize(c->stream));
     CUDA_OK(cudaGetLastError());
+    finish_host_stamps(c);
     API_END(c)
 }
 
@@ -2716,77 +2848,75 @@ int tcif_time_step_host(tcif_ctx *c, const tcif_alpha_controls *ctl, double delt
                         double *const *apo, double *const *apob, double *rpi, double *rpb, double *Fi, double *Fb) {
     API_BEGIN(c)
     if (!ai || (c->nBF && !ab) || !phii) failf("tcif_time_step_host: null field lists");
-    for (int p = 0; p < c->P; ++p) alpha_changed(c, p);
-    c->tStamp = 0;
-    if (!c->sIn) {
-        CUDA_OK(cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking));
-        CUDA_OK(cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking));
-        for (int i = 0; i < 2; ++i) {
-            CUDA_OK(cudaEventCreateWithFlags(&c->evIn[i], cudaEventDisableTiming));
-            CUDA_OK(cudaEventCreateWithFlags(&c->evC[i], cudaEventDisableTiming));
-        }
-        c->stagingOut = c->dalloc<double>(c->stagingDoubles);
-    }
+    host_pipeline_init(c);
     join(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    c->h2dBytes = c->d2hBytes = 0;
     const size_t cb = sizeof(double) * c->nC, bb = sizeof(double) * c->nBF, fb = sizeof(double) * c->nIF;
     cudaStream_t in = c->sIn, out = c->sOut;
-    for (int p = 0; p < c->P; ++p) {
-        CUDA_OK(cudaMemcpyAsync(c->alpha[p], ai[p], cb, cudaMemcpyDefault, in));
-        if (c->nBF) CUDA_OK(cudaMemcpyAsync(c->alphab[p], ab[p], bb, cudaMemcpyDefault, in));
-    }
+    up_alphas_host(c, in, ai, ab);
     if (c->nIF) {
         CUDA_OK(cudaMemcpyAsync(c->staging, phii, fb, cudaMemcpyDefault, in));
         k_face_scatter<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, in>>>(c->nIF, c->d_faceMap, c->staging, c->phi);
         c->launches++;
+        c->h2dBytes += fb;
     }
-    if (c->nBF && phib) CUDA_OK(cudaMemcpyAsync(c->phib, phib, bb, cudaMemcpyDefault, in));
+    if (c->nBF && phib) { CUDA_OK(cudaMemcpyAsync(c->phib, phib, bb, cudaMemcpyDefault, in)); c->h2dBytes += bb; }
     CUDA_OK(cudaEventRecord(c->evIn[0], in));
     if (Ti) {
+        touch(c); c->tStamp = 0; c->xfer[2]++;
         CUDA_OK(cudaMemcpyAsync(c->Tc, Ti, cb, cudaMemcpyDefault, in));
         if (c->nBF && Tb) CUDA_OK(cudaMemcpyAsync(c->Tb, Tb, bb, cudaMemcpyDefault, in));
+        c->h2dBytes += cb + (Tb ? bb : 0);
         c->haveT = true;
     }
     CUDA_OK(cudaEventRecord(c->evIn[1], in));
+    // compute: solve(), then the force on the new alpha
     CUDA_OK(cudaStreamWaitEvent(c->stream, c->evIn[0], 0));
     do_solve_alphas(c, ctl, deltaT);
     CUDA_OK(cudaEventRecord(c->evC[0], c->stream));
-    CUDA_OK(cudaStreamWaitEvent(out, c->evC[0], 0));
-    for (int p = 0; p < c->P; ++p) {
-        CUDA_OK(cudaMemcpyAsync(ai[p], c->alpha[p], cb, cudaMemcpyDefault, out));
-        if (c->nBF) CUDA_OK(cudaMemcpyAsync(ab[p], c->alphab[p], bb, cudaMemcpyDefault, out));
-    }
-    auto downFaces = [&](double *dst, const double *src) {
-        if (!c->nIF || !dst) return;
-        k_face_gather<<<cdiv(c->nIF, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nIF, c->d_faceMap, src, c->stagingOut);
-        c->launches++;
-        CUDA_OK(cudaMemcpyAsync(dst, c->stagingOut, fb, cudaMemcpyDefault, out));
-    };
-    downFaces(rpi, c->rhoPhi);
-    if (rpb && c->nBF) CUDA_OK(cudaMemcpyAsync(rpb, c->rhoPhib, bb, cudaMemcpyDefault, out));
-    if (apo) for (int p = 0; p < c->P; ++p) {
-        downFaces(apo[p], c->phiPsi[p]);
-        if (apob && c->nBF) CUDA_OK(cudaMemcpyAsync(apob[p], c->phiPsib[p], bb, cudaMemcpyDefault, out));
-    }
     CUDA_OK(cudaStreamWaitEvent(c->stream, c->evIn[1], 0));
     do_force(c);
     CUDA_OK(cudaEventRecord(c->evC[1], c->stream));
+    // downloads: the dense flux arrays first, then the deltas
+    CUDA_OK(cudaStreamWaitEvent(out, c->evC[0], 0));
+    down_faces_host(c, out, c->P, rpi, c->rhoPhi);
+    if (rpb && c->nBF) { CUDA_OK(cudaMemcpyAsync(rpb, c->rhoPhib, bb, cudaMemcpyDefault, out)); c->d2hBytes += bb; }
+    if (apo) for (int p = 0; p < c->P; ++p) {
+        down_faces_host(c, out, p, apo[p], c->phiPsi[p]);
+        if (apob && c->nBF) { CUDA_OK(cudaMemcpyAsync(apob[p], c->phiPsib[p], bb, cudaMemcpyDefault, out)); c->d2hBytes += bb; }
+    }
+    for (int p = 0; p < c->P; ++p) down_alpha(c, out, p, ai[p], c->nBF ? ab[p] : nullptr);
     CUDA_OK(cudaStreamWaitEvent(out, c->evC[1], 0));
-    if (Fi) {
-        k_soa_to_aos3<<<cdiv(c->nC, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nC, (size_t)c->stride, c->F, c->stagingOut);
-        c->launches++;
-        CUDA_OK(cudaMemcpyAsync(Fi, c->stagingOut, 3 * cb, cudaMemcpyDefault, out));
-    }
-    if (Fb && c->nBF) {
-        k_soa_to_aos3<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, out>>>(c->nBF, (size_t)c->nBF, c->Fb, c->stagingOut);
-        c->launches++;
-        CUDA_OK(cudaMemcpyAsync(Fb, c->stagingOut, 3 * bb, cudaMemcpyDefault, out));
-    }
+    down_force(c, out, Fi, Fb);
     CUDA_OK(cudaStreamSynchronize(out));
     CUDA_OK(cudaStreamSynchronize(in));
     CUDA_OK(cudaStreamSynchronize(c->stream));
     CUDA_OK(cudaGetLastError());
+    finish_host_stamps(c);
     API_END(c)
+}
+
+// one-shot stamps of the alpha arrays the NEXT tcif_stage_host / tcif_time_step_host call receives (in) and of the
+// state those arrays hold when it returns (out); see include/tcif.h
+int tcif_host_alpha_stamps(tcif_ctx *c, const uint64_t *in, const uint64_t *out) {
+    API_BEGIN(c)
+    for (int p = 0; p < c->P; ++p) { c->hsIn[p] = in ? in[p] : 0; c->hsOut[p] = out ? out[p] : 0; }
+    c->hsArmed = true;
+    API_END(c)
+}
+int tcif_host_sparse_returns(tcif_ctx *c, int on) {
+    API_BEGIN(c)
+    c->sparseReturns = on != 0;
+    c->shFHost = nullptr;
+    for (auto &h : c->shFaceHost) h = nullptr;
+    API_END(c)
+}
+int tcif_host_bytes_moved(const tcif_ctx *c, int64_t *h2d, int64_t *d2h) {
+    if (!c) return 1;
+    if (h2d) *h2d = c->h2dBytes;
+    if (d2h) *d2h = c->d2hBytes;
+    return 0;
 }
 
 int tcif_set_cell_centres(tcif_ctx *c, const double *C, const double *deltaB) {

@@ -817,6 +817,53 @@ static __global__ void k_aos3_to_soa(int n, size_t stride, const double *src, do
     if (i < n) { dst[i] = src[3 * (size_t)i]; dst[stride + i] = src[3 * (size_t)i + 1]; dst[2 * stride + i] = src[3 * (size_t)i + 2]; }
 }
 
+// ---- delta read-back (tcif_host_sparse_returns): only the entries that differ from what the host already holds ---
+// `shadow` is the device's record of the host array.  Entries whose VALUE differs are appended as (index, value) with
+// one atomic per warp; the order of the pairs is arbitrary, the host array after the scatter is not.  count may
+// exceed cap (the caller then falls back to the dense copy).
+static __global__ void __launch_bounds__(TCIF_TPB)
+k_delta_compact(int n, const double *cur, const double *shadow, int cap, int *idx, double *val, int *counter) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double v = 0.0;
+    bool ch = false;
+    if (i < n) { v = cur[i]; ch = v != shadow[i]; }          // by VALUE: -0.0 == +0.0 is not a change (NaN always is)
+    const unsigned mask = __ballot_sync(0xffffffffu, ch);
+    if (!mask) return;
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == __ffs(mask) - 1) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
+    const int pos = base + __popc(mask & ((1u << lane) - 1u));
+    if (ch && pos < cap) { idx[pos] = i; val[pos] = v; }
+}
+// 3-component SoA field (stride between components) -> (index, x, y, z)
+static __global__ void __launch_bounds__(TCIF_TPB)
+k_delta_compact3(int n, size_t stride, const double *cur, const double *shadow, int cap, int *idx, double *val, int *counter) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double x = 0.0, y = 0.0, z = 0.0;
+    bool ch = false;
+    if (i < n) {
+        x = cur[i]; y = cur[stride + i]; z = cur[2 * stride + i];
+        ch = x != shadow[i] || y != shadow[stride + i] || z != shadow[2 * stride + i];
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, ch);
+    if (!mask) return;
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == __ffs(mask) - 1) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
+    const int pos = base + __popc(mask & ((1u << lane) - 1u));
+    if (ch && pos < cap) { idx[pos] = i; val[3 * (size_t)pos] = x; val[3 * (size_t)pos + 1] = y; val[3 * (size_t)pos + 2] = z; }
+}
+// shadow[idx[k]] := the values just sent (ncomp components, SoA with `stride`)
+static __global__ void __launch_bounds__(TCIF_TPB)
+k_delta_apply(int n, int ncomp, size_t stride, const int *idx, const double *val, double *shadow) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const int i = idx[k];
+    for (int d = 0; d < ncomp; ++d) shadow[d * stride + i] = val[(size_t)ncomp * k + d];
+}
+
 // sum(V*a), min(a), max(a): deterministic two-level tree
 static __global__ void __launch_bounds__(TCIF_TPB)
 k_stats_partial(int n, const double *V, const double *a, double *part) {

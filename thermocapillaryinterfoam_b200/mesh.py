@@ -135,6 +135,26 @@ def decompose(g: HostMesh, cellProc, nProcs, rank) -> HostMesh:
     return HostMesh(h)
 
 
+def read_polymesh(polyMeshDir) -> HostMesh:
+    """An OpenFOAM ASCII polyMesh directory (any cell shape) -> host mesh (tcif_mesh_read_polymesh)."""
+    h = C.c_void_p()
+    if lib().tcif_mesh_read_polymesh(str(polyMeshDir).encode(), C.byref(h)):
+        raise TcifError(lib().tcif_mesh_last_error().decode())
+    return HostMesh(h)
+
+
+def read_label_list(path) -> np.ndarray:
+    """A labelList file such as decomposePar's cellDecomposition (tcif_mesh_read_label_list)."""
+    n = C.c_int32(0)
+    lib().tcif_mesh_read_label_list(str(path).encode(), 0, None, C.byref(n))
+    if n.value == 0:
+        raise TcifError(lib().tcif_mesh_last_error().decode())
+    out = np.zeros(n.value, np.int32)
+    if lib().tcif_mesh_read_label_list(str(path).encode(), n.value, out.ctypes.data_as(c_ip), C.byref(n)):
+        raise TcifError(lib().tcif_mesh_last_error().decode())
+    return out
+
+
 def procs_for(nRanks: int):
     """Block layout used for 1/2/4/8 GPUs."""
     return {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[nRanks]
