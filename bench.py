@@ -223,6 +223,15 @@ def run_reference(args, rank):
     from thermocapillaryinterfoam_b200 import cases
     cores = os.cpu_count() or 1
     edge, full = reference_edge(args, cores)
+    # the run must end within a few minutes: one untimed stage on the chosen box first; if W + K stages of it would not
+    # fit the budget (TCIF_REF_BUDGET_S, default 420 s) the bounded sample is run instead -- and named as such
+    budget = float(os.environ.get("TCIF_REF_BUDGET_S", "420"))
+    if edge == full and not args.cpu_n:
+        t0 = time.time()
+        _, s1, *_ = cpu_stage_rate(args.config, edge, 1, cores)
+        setup = time.time() - t0 - s1
+        if 2 * setup + s1 * (args.steps + args.warmup + 1) > budget:
+            edge = cpu_sample_edge(args, cores)
     rate, secs, nd, procs, spec = cpu_stage_rate(args.config, edge, args.steps, cores, warmup=args.warmup)
     one_core, one_core_sample = cpu_one_core_rate(args.config)
     sample = (f"{spec.name} {edge}^3 = {spec.nCells} cells, {spec.nPhases} phases, {args.steps} stages after {args.warmup} warm-up "
@@ -472,6 +481,7 @@ def run_ours(args, rank, world, local_rank):
 
     stats = [ctx.alpha_stats(p) for p in range(P)]
     dev_bytes = ctx.device_bytes
+    transport = ctx.comm_transport
     ctx.close()
 
     # ---- CPU baseline beside it (rank 0, N=1 only) --------------------------------------------
@@ -495,6 +505,7 @@ def run_ours(args, rank, world, local_rank):
                            f"configs[{args.config - 1}] {spec.name} weak scaling {spec.n[0]}x{spec.n[1]}x{spec.n[2]} = {spec.nCells} cells, {spec.nPhases} phases",
                            "phases": P, "pairs": len(spec.sigma), "nLimiterIter": 3,
                            "decomposition": f"simple {procs[0]}x{procs[1]}x{procs[2]}", "cells_per_gpu": nC,
+                           "halo_transport": transport,
                            "l2": "inputs larger than L2 (no flush needed)" if dev_bytes > 4 * 126e6 else
                                  "L2-resident case: latency-bound, no roofline claim",
                            "device_bytes_per_gpu": dev_bytes, "setup_s": round(setup_s, 1)},

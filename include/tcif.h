@@ -367,6 +367,11 @@ TCIF_API int64_t tcif_device_bytes(const tcif_ctx *ctx);
  * [3] 1 when the volume sweeps walk the 256-cell tiles strip-wise, [4] L2 prefetch distance in tiles,
  * [5] cells with patch faces, [6] of those deferred to the O(surface) launches, [7] processor faces. */
 TCIF_API int tcif_mesh_info(const tcif_ctx *ctx, int32_t out[8]);
+/* How processor-patch values travel: 0 no communicator, 1 in-process group (device-to-device copies), 2 NCCL
+ * send/recv (pack, ncclSend/ncclRecv, unpack), 3 peer memory (the producer stores straight into the neighbour rank's
+ * mapped receive buffer over NVLink and releases a flag; default for NCCL ranks on one node, TCIF_PEER_HALO=0
+ * selects 2). */
+TCIF_API int tcif_comm_transport(const tcif_ctx *ctx);
 
 #ifdef __cplusplus
 }

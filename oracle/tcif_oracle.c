@@ -657,26 +657,38 @@ static void *thr_main(void *p) {
     orc_comm comm = { &a->tc, thr_halo, thr_reduce };
     int nP = a->nPhases;
     const size_t nC = m0->nCells, nIF = m0->nIF, nBF = m0->nBF;
+    /* ORC_FIRST_TOUCH=0: stream the caller's arrays as they are (A/B switch for the NUMA effect) */
+    const char *e = getenv("ORC_FIRST_TOUCH");
+    const int ft = !(e && e[0] == '0');
     /* local sub-mesh (patch tables stay shared: the halo hook reads the neighbours' through sh->meshes) */
     orc_mesh lm = *m0;
-    int32_t *own = iclone(m0->owner, nIF), *nei = iclone(m0->neighbour, nIF), *fc = iclone(m0->faceCells, nBF);
-    double *Sf = dclone(m0->Sf, 3 * nIF), *w = dclone(m0->w, nIF), *V = dclone(m0->V, nC), *Sfb = dclone(m0->Sfb, 3 * nBF);
-    double *magSfb = dclone(m0->magSfb, nBF), *dcb = dclone(m0->deltaCoeffsb, nBF), *wb = dclone(m0->wb, nBF);
-    lm.owner = own; lm.neighbour = nei; lm.faceCells = fc; lm.Sf = Sf; lm.w = w; lm.V = V; lm.Sfb = Sfb;
-    lm.magSfb = magSfb; lm.deltaCoeffsb = dcb; lm.wb = wb;
+    int32_t *own = NULL, *nei = NULL, *fc = NULL;
+    double *Sf = NULL, *w = NULL, *V = NULL, *Sfb = NULL, *magSfb = NULL, *dcb = NULL, *wb = NULL;
+    if (ft) {
+        own = iclone(m0->owner, nIF); nei = iclone(m0->neighbour, nIF); fc = iclone(m0->faceCells, nBF);
+        Sf = dclone(m0->Sf, 3 * nIF); w = dclone(m0->w, nIF); V = dclone(m0->V, nC); Sfb = dclone(m0->Sfb, 3 * nBF);
+        magSfb = dclone(m0->magSfb, nBF); dcb = dclone(m0->deltaCoeffsb, nBF); wb = dclone(m0->wb, nBF);
+        lm.owner = own; lm.neighbour = nei; lm.faceCells = fc; lm.Sf = Sf; lm.w = w; lm.V = V; lm.Sfb = Sfb;
+        lm.magSfb = magSfb; lm.deltaCoeffsb = dcb; lm.wb = wb;
+    }
     const orc_mesh *m = &lm;
     double **ai = (double **)xmalloc(sizeof(double *) * nP), **ab = (double **)xmalloc(sizeof(double *) * nP);
     double **pai = (double **)xmalloc(sizeof(double *) * nP), **pab = (double **)xmalloc(sizeof(double *) * nP);
     /* keep the HO flux so every stage starts from the same phiAlpha input */
     double **pa0i = (double **)xmalloc(sizeof(double *) * nP), **pa0b = (double **)xmalloc(sizeof(double *) * nP);
     for (int k = 0; k < nP; ++k) {
-        ai[k] = dclone(a->alphai[k], nC); ab[k] = dclone(a->alphab[k], nBF);
-        pai[k] = dclone(a->phiAlphai[k], nIF); pab[k] = dclone(a->phiAlphab[k], nBF);
+        ai[k] = ft ? dclone(a->alphai[k], nC) : a->alphai[k]; ab[k] = ft ? dclone(a->alphab[k], nBF) : a->alphab[k];
+        pai[k] = ft ? dclone(a->phiAlphai[k], nIF) : a->phiAlphai[k]; pab[k] = ft ? dclone(a->phiAlphab[k], nBF) : a->phiAlphab[k];
         pa0i[k] = dclone(a->phiAlphai[k], nIF); pa0b[k] = dclone(a->phiAlphab[k], nBF);
     }
-    double *Ti = a->Ti ? dclone(a->Ti, nC) : NULL, *Tb = a->Tb ? dclone(a->Tb, nBF) : NULL;
-    double *phii = dclone(a->phii, nIF), *phib = dclone(a->phib, nBF);
-    double *Fi = dnew(3 * nC + 1), *Fb = dnew(3 * nBF + 1);
+    const double *Ti = a->Ti, *Tb = a->Tb, *phii = a->phii, *phib = a->phib;
+    double *TiL = NULL, *TbL = NULL, *phiiL = NULL, *phibL = NULL, *Fi = a->Fi, *Fb = a->Fb;
+    if (ft) {
+        if (a->Ti) Ti = TiL = dclone(a->Ti, nC);
+        if (a->Tb) Tb = TbL = dclone(a->Tb, nBF);
+        phii = phiiL = dclone(a->phii, nIF); phib = phibL = dclone(a->phib, nBF);
+        Fi = dnew(3 * nC + 1); Fb = dnew(3 * nBF + 1);
+    }
     pthread_barrier_wait(&a->tc.sh->bar);
     double t0 = now_s();
     for (int s = 0; s < a->nStages; ++s) {
@@ -689,15 +701,20 @@ static void *thr_main(void *p) {
     }
     pthread_barrier_wait(&a->tc.sh->bar);
     a->seconds = now_s() - t0;
-    for (int k = 0; k < nP; ++k) {      /* results back into the caller's arrays */
-        memcpy(a->alphai[k], ai[k], sizeof(double) * nC); memcpy(a->alphab[k], ab[k], sizeof(double) * nBF);
-        memcpy(a->phiAlphai[k], pai[k], sizeof(double) * nIF); memcpy(a->phiAlphab[k], pab[k], sizeof(double) * nBF);
-        free(ai[k]); free(ab[k]); free(pai[k]); free(pab[k]); free(pa0i[k]); free(pa0b[k]);
+    for (int k = 0; k < nP; ++k) {
+        if (ft) {      /* results back into the caller's arrays */
+            memcpy(a->alphai[k], ai[k], sizeof(double) * nC); memcpy(a->alphab[k], ab[k], sizeof(double) * nBF);
+            memcpy(a->phiAlphai[k], pai[k], sizeof(double) * nIF); memcpy(a->phiAlphab[k], pab[k], sizeof(double) * nBF);
+            free(ai[k]); free(ab[k]); free(pai[k]); free(pab[k]);
+        }
+        free(pa0i[k]); free(pa0b[k]);
     }
-    memcpy(a->Fi, Fi, sizeof(double) * 3 * nC); memcpy(a->Fb, Fb, sizeof(double) * 3 * nBF);
+    if (ft) {
+        memcpy(a->Fi, Fi, sizeof(double) * 3 * nC); memcpy(a->Fb, Fb, sizeof(double) * 3 * nBF);
+        free(Fi); free(Fb); free(TiL); free(TbL); free(phiiL); free(phibL);
+        free(own); free(nei); free(fc); free(Sf); free(w); free(V); free(Sfb); free(magSfb); free(dcb); free(wb);
+    }
     free(ai); free(ab); free(pai); free(pab); free(pa0i); free(pa0b);
-    free(Ti); free(Tb); free(phii); free(phib); free(Fi); free(Fb);
-    free(own); free(nei); free(fc); free(Sf); free(w); free(V); free(Sfb); free(magSfb); free(dcb); free(wb);
     return NULL;
 }
 

@@ -136,7 +136,8 @@ def test_processor_patches_without_communicator_is_an_error():
 
 
 # ---- NCCL, one process per GPU ----------------------------------------------------------------------
-def _nccl_worker(rank, world, config, n, out):
+def _nccl_worker(rank, world, config, n, out, transport="peer"):
+    os.environ["TCIF_PEER_HALO"] = "1" if transport == "peer" else "0"
     spec = cases.case(config, n)
     m = hm.box_block(spec.n, spec.lengths, spec.patch_types, hm.procs_for(world), rank)
     f = cases.synthetic_fields(spec, m)
@@ -154,6 +155,7 @@ def _nccl_worker(rank, world, config, n, out):
     uid = open(idfile, "rb").read()
     ctx = abi.Context(m, spec.nPhases, device=rank)
     ctx.comm_init_nccl(rank, world, uid)
+    assert ctx.comm_transport == transport, (ctx.comm_transport, transport)
     res = _run_rank(ctx, spec, f)
     np.savez(os.path.join(out, f"rank{rank}.npz"), F_i=res["F_i"], F_b=res["F_b"], stats=np.array(res["stats"]),
              **{f"{k}{p}": res[k][p] for k in ("alpha_i", "alpha_b", "alphaPhi_i", "alphaPhi_b")
@@ -161,9 +163,11 @@ def _nccl_worker(rank, world, config, n, out):
     ctx.close()
 
 
-@pytest.mark.timeout(600)
+@pytest.mark.timeout(900)
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_nccl_ranks_match_serial(world):
+    """One process per GPU: processor-patch values over peer memory (default) and over ncclSend/ncclRecv; both
+    against the serial oracle, and bit-identical to each other."""
     if abi.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     import multiprocessing as mp
@@ -171,17 +175,26 @@ def test_nccl_ranks_match_serial(world):
     spec = cases.case(config, n)
     g, ref = _serial(spec)
     ctxm = mp.get_context("spawn")
-    with tempfile.TemporaryDirectory() as out:
-        ps = [ctxm.Process(target=_nccl_worker, args=(r, world, config, n, out)) for r in range(world)]
-        [p.start() for p in ps]
-        [p.join(timeout=500) for p in ps]
-        assert all(p.exitcode == 0 for p in ps), [p.exitcode for p in ps]
-        stats0 = None
-        for r in range(world):
-            m = hm.box_block(spec.n, spec.lengths, spec.patch_types, hm.procs_for(world), r)
-            z = np.load(os.path.join(out, f"rank{r}.npz"))
-            res = dict(F_i=z["F_i"], F_b=z["F_b"],
-                       **{k: [z[f"{k}{p}"] for p in range(3)] for k in ("alpha_i", "alpha_b", "alphaPhi_i", "alphaPhi_b")})
-            _compare(spec, ref, m, res)
-            stats0 = z["stats"] if stats0 is None else stats0
-            assert np.array_equal(z["stats"], stats0)
+    results = {}
+    for transport in ("peer", "nccl"):
+        with tempfile.TemporaryDirectory() as out:
+            ps = [ctxm.Process(target=_nccl_worker, args=(r, world, config, n, out, transport)) for r in range(world)]
+            [p.start() for p in ps]
+            [p.join(timeout=400) for p in ps]
+            assert all(p.exitcode == 0 for p in ps), (transport, [p.exitcode for p in ps])
+            stats0 = None
+            for r in range(world):
+                m = hm.box_block(spec.n, spec.lengths, spec.patch_types, hm.procs_for(world), r)
+                z = np.load(os.path.join(out, f"rank{r}.npz"))
+                res = dict(F_i=z["F_i"], F_b=z["F_b"],
+                           **{k: [z[f"{k}{p}"] for p in range(3)] for k in ("alpha_i", "alpha_b", "alphaPhi_i", "alphaPhi_b")})
+                _compare(spec, ref, m, res)
+                stats0 = z["stats"] if stats0 is None else stats0
+                assert np.array_equal(z["stats"], stats0)
+                results[(transport, r)] = res
+    for r in range(world):
+        a, b = results[("peer", r)], results[("nccl", r)]
+        assert np.array_equal(a["F_i"], b["F_i"]) and np.array_equal(a["F_b"], b["F_b"]), f"force differs between transports, rank {r}"
+        for k in ("alpha_i", "alpha_b", "alphaPhi_i", "alphaPhi_b"):
+            for p in range(3):
+                assert np.array_equal(a[k][p], b[k][p]), (k, p, r)

@@ -104,6 +104,7 @@ def lib():
     L.tcif_device_bytes.restype = C.c_int64
     L.tcif_device_bytes.argtypes = [C.c_void_p]
     L.tcif_mesh_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+    L.tcif_comm_transport.argtypes = [C.c_void_p]
     L.tcif_set_alpha_stamped.argtypes = [C.c_void_p, C.c_int, C.c_uint64, c_dp, c_dp, C.POINTER(C.c_int32)]
     L.tcif_set_temperature_stamped.argtypes = [C.c_void_p, C.c_uint64, c_dp, c_dp, C.POINTER(C.c_int32)]
     L.tcif_mark_alpha.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
@@ -624,6 +625,10 @@ class Context:
         self._ck(lib().tcif_mesh_info(self.h, out))
         return dict(Ko=out[0], Kn=out[1], fixedK=out[2], tileStrips=out[3], prefetchTiles=out[4], boundaryCells=out[5],
                     deferredCells=out[6], processorFaces=out[7])
+
+    @property
+    def comm_transport(self):
+        return {0: "none", 1: "local", 2: "nccl", 3: "peer"}[int(lib().tcif_comm_transport(self.h))]
 
     @property
     def tile_strips(self):

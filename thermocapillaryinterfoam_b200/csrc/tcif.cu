@@ -14,6 +14,7 @@
 #include "../../include/tcif.h"
 
 #include <dlfcn.h>
+#include <unistd.h>
 #include <algorithm>
 #include <atomic>
 #include <condition_variable>
@@ -265,6 +266,15 @@ struct tcif_ctx {
     tcif_group *group = nullptr;
     ncclComm_t nccl = nullptr;
     double *d_gather = nullptr;         // nRanks*16 doubles (nccl scalar reductions)
+    // processor-patch exchange over peer memory (k_halo_push / k_halo_wait / k_halo_pull), NCCL ranks on one node
+    bool peerOn = false;
+    double *peerBuf = nullptr;          // own receive buffer: 2 parities x haloDoubles, then nRanks flag words
+    unsigned *peerFlags = nullptr;      // = (unsigned *)(peerBuf + 2*haloDoubles): one word per source rank
+    std::vector<void *> peerMapped;     // per rank: that rank's peerBuf mapped here (null: not a neighbour)
+    HaloPeer hp{};
+    unsigned exSeq = 0;
+    int *peerCounter = nullptr, *peerStatus = nullptr;
+    cudaEvent_t evX = nullptr;          // end of the previous exchange (exchanges are totally ordered on a rank)
     double *agBuf = nullptr;            // allgather_host staging
     int agCap = 0;
     // timers
@@ -444,7 +454,7 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
     c->patchSize.assign(m->patchSize, m->patchSize + nP);
     c->patchNbr.assign(nP, -1);
     if (m->patchNeighbProcNo) c->patchNbr.assign(m->patchNeighbProcNo, m->patchNeighbProcNo + nP);
-    std::vector<int> bfPatch(nBF, 0), bfType(nBF, 0), coupled, cOff, cSize;
+    std::vector<int> bfPatch(nBF, 0), bfType(nBF, 0), coupled, cOff, cSize, cPatchIdx;
     int covered = 0;
     for (int p = 0; p < nP; ++p) {
         int s = c->patchStart[p], n = c->patchSize[p], t = c->patchType[p];
@@ -456,7 +466,7 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
             if (c->patchNbr[p] < 0) failf("tcif_create: processor patch %d without neighbour rank", p);
             c->cpPatch.push_back(p); c->cpOff.push_back((int)coupled.size());
             int off = (int)coupled.size();
-            for (int i = 0; i < n; ++i) { coupled.push_back(s + i); cOff.push_back(off); cSize.push_back(n); }
+            for (int i = 0; i < n; ++i) { coupled.push_back(s + i); cOff.push_back(off); cSize.push_back(n); cPatchIdx.push_back((int)c->cpPatch.size() - 1); }
         }
         for (int i = 0; i < n; ++i) { bfPatch[s + i] = p; bfType[s + i] = t; }
     }
@@ -515,6 +525,7 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
     d.Sfbx = c->upload(bx); d.Sfby = c->upload(by); d.Sfbz = c->upload(bz);
     d.magSfb = c->upload(mag); d.dcb = c->upload(dc); d.wb = c->upload(wb);
     d.coupledFaces = c->upload(coupled); d.coupledOff = c->upload(cOff); d.coupledSize = c->upload(cSize);
+    d.coupledPatchIdx = c->upload(cPatchIdx);
 }
 
 void alloc_fields(tcif_ctx *c) {
@@ -666,6 +677,88 @@ void exchange(tcif_ctx *c, int ncomp, cudaStream_t st) {
     } else failf("exchange without communicator");
 }
 
+// Map every neighbour's receive buffer (collective over the NCCL ranks).  Falls back to ncclSend/ncclRecv -- on ALL
+// ranks together -- when the ranks are not on one node, a rank has too many processor patches, or the mapping fails.
+// TCIF_PEER_HALO=0 keeps the NCCL path (the checked alternative).
+void peer_setup(tcif_ctx *c) {
+    const char *e = getenv("TCIF_PEER_HALO");
+    const bool want = !(e && atoi(e) == 0);
+    const int nR = c->nRanks;
+    const size_t bufDoubles = 2 * c->haloDoubles + (size_t)(nR + 1) / 2 + 8;
+    bool ok = want && (int)c->cpPatch.size() <= TCIF_MAX_PEER_PATCHES;
+    cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof mine);
+    if (ok) {
+        ok = cudaMalloc((void **)&c->peerBuf, sizeof(double) * bufDoubles) == cudaSuccess;
+        if (ok) {
+            c->devBytes += (int64_t)(sizeof(double) * bufDoubles);
+            c->peerFlags = (unsigned *)(c->peerBuf + 2 * c->haloDoubles);
+            ok = cudaMemset(c->peerBuf, 0, sizeof(double) * bufDoubles) == cudaSuccess && cudaIpcGetMemHandle(&mine, c->peerBuf) == cudaSuccess;
+        }
+        if (!ok) cudaGetLastError();
+    }
+    // one all-gather: [ok, host id, handle (8 doubles), haloDoubles, cpOff of the patch facing each rank (nR)]
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t travels as 8 doubles");
+    char host[256] = {0};
+    gethostname(host, sizeof host - 1);
+    unsigned long long hh = 1469598103934665603ULL;
+    for (const char *q = host; *q; ++q) hh = (hh ^ (unsigned char)*q) * 1099511628211ULL;
+    const int W = 11 + nR;
+    std::vector<double> me(W, -1.0), all;
+    me[0] = ok ? 1.0 : 0.0; me[1] = (double)(hh & 0xffffffffffffULL);
+    memcpy(&me[2], &mine, 64);
+    me[10] = (double)c->haloDoubles;
+    for (size_t i = 0; i < c->cpPatch.size(); ++i) me[11 + c->patchNbr[c->cpPatch[i]]] = (double)c->cpOff[i];
+    allgather_host(c, me.data(), W, all);
+    for (int r = 0; r < nR; ++r) ok = ok && all[(size_t)r * W] == 1.0 && all[(size_t)r * W + 1] == me[1];
+    c->peerMapped.assign(nR, nullptr);
+    if (ok) {
+        c->hp = HaloPeer{};
+        c->hp.nPatches = (int)c->cpPatch.size();
+        for (size_t i = 0; i < c->cpPatch.size() && ok; ++i) {
+            const int nb = c->patchNbr[c->cpPatch[i]];
+            const double peerOff = all[(size_t)nb * W + 11 + c->rank];
+            if (peerOff < 0) { ok = false; break; }              // the neighbour has no patch facing this rank
+            if (!c->peerMapped[nb]) {
+                cudaIpcMemHandle_t h;
+                memcpy(&h, &all[(size_t)nb * W + 2], 64);
+                void *ptr = nullptr;
+                if (cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+                c->peerMapped[nb] = ptr;
+            }
+            const size_t nbHalo = (size_t)all[(size_t)nb * W + 10];
+            c->hp.base[i] = (double *)c->peerMapped[nb];
+            c->hp.peerOff[i] = (int)peerOff;
+            c->hp.remoteFlag[i] = (unsigned *)((double *)c->peerMapped[nb] + 2 * nbHalo) + c->rank;
+            c->hp.localFlag[i] = c->peerFlags + nb;
+            c->hp.stride[i] = nbHalo;
+        }
+    }
+    double v[1] = {ok ? 0.0 : 1.0};
+    const int ops[1] = {RED_MAX};
+    allreduce_host(c, v, ops, 1);                                    // everybody uses the same transport
+    if (v[0] != 0.0) {
+        for (void *ptr : c->peerMapped) if (ptr) cudaIpcCloseMemHandle(ptr);
+        c->peerMapped.assign(nR, nullptr);
+        if (c->peerBuf) { cudaFree(c->peerBuf); c->peerBuf = nullptr; }
+        cudaGetLastError();
+        c->peerOn = false;
+        return;
+    }
+    c->peerCounter = c->dalloc<int>(2);
+    c->peerStatus = c->peerCounter + 1;
+    CUDA_OK(cudaEventCreateWithFlags(&c->evX, cudaEventDisableTiming));
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    c->peerOn = true;
+}
+
+void peer_check(tcif_ctx *c) {           // called where the host synchronises anyway
+    if (!c->peerOn) return;
+    int st = 0;
+    CUDA_OK(cudaMemcpy(&st, c->peerStatus, sizeof(int), cudaMemcpyDeviceToHost));
+    if (st) failf("processor-patch exchange over peer memory timed out waiting for a neighbour rank");
+}
+
 // processorFvPatchField::evaluate for ncomp cell arrays at once: dst[d][bf] := neighbour-rank src[d][faceCell]
 void halo_cells(tcif_ctx *c, int ncomp, const double *const *src, double *const *dst, cudaStream_t st = nullptr) {
     if (!st) st = c->stream;
@@ -676,11 +769,25 @@ void halo_cells(tcif_ctx *c, int ncomp, const double *const *src, double *const 
     h.ncomp = ncomp;
     for (int d = 0; d < ncomp; ++d) { h.src[d] = src[d]; h.dst[d] = dst[d]; }
     double bytes = 16.0 * ncomp * c->nCoupled;
+    const int grid = cdiv(c->nCoupled, TCIF_TPB);
+    if (c->peerOn) {
+        timed_on(c, st, T_HALO, bytes, [&] {
+            if (c->exSeq) CUDA_OK(cudaStreamWaitEvent(st, c->evX, 0));
+            const unsigned seq = ++c->exSeq;
+            const unsigned parity = seq & 1u;
+            k_halo_push<<<grid, TCIF_TPB, 0, st>>>(c->dm, h, c->hp, parity, seq, c->peerCounter);
+            k_halo_wait<<<1, 32, 0, st>>>(c->hp, seq, c->peerStatus);
+            k_halo_pull<<<grid, TCIF_TPB, 0, st>>>(c->dm, h, c->peerBuf + (size_t)parity * c->haloDoubles);
+            c->launches += 3;
+            CUDA_OK(cudaEventRecord(c->evX, st));
+        });
+        return;
+    }
     timed_on(c, st, T_HALO, bytes, [&] {
-        k_halo_pack<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, st>>>(c->dm, h, c->sendBuf);
+        k_halo_pack<<<grid, TCIF_TPB, 0, st>>>(c->dm, h, c->sendBuf);
         c->launches++;
         exchange(c, ncomp, st);
-        k_halo_unpack<<<cdiv(c->nCoupled, TCIF_TPB), TCIF_TPB, 0, st>>>(c->dm, h, c->recvBuf);
+        k_halo_unpack<<<grid, TCIF_TPB, 0, st>>>(c->dm, h, c->recvBuf);
         c->launches++;
     });
 }
@@ -2170,6 +2277,9 @@ void tcif_destroy(tcif_ctx *c) {
     DeviceGuard guard(c->device);
     if (c->side) cudaStreamSynchronize(c->side);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    for (void *ptr : c->peerMapped) if (ptr) cudaIpcCloseMemHandle(ptr);
+    if (c->peerBuf) cudaFree(c->peerBuf);
+    if (c->evX) cudaEventDestroy(c->evX);
     if (c->nccl && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl);
     if (c->group) { std::lock_guard<std::mutex> lk(c->group->mu); if (c->rank < (int)c->group->members.size()) c->group->members[c->rank] = nullptr; }
     for (auto &e : c->evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
@@ -2208,6 +2318,7 @@ int tcif_synchronize(tcif_ctx *c) {
     API_BEGIN(c)
     join(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    peer_check(c);
     API_END(c)
 }
 
@@ -2260,6 +2371,7 @@ int tcif_comm_init_nccl(tcif_ctx *c, int rank, int nRanks, const void *id128) {
     for (int p : c->cpPatch) if (c->patchNbr[p] >= nRanks || c->patchNbr[p] == rank) failf("processor patch %d: neighbour rank %d invalid", p, c->patchNbr[p]);
     c->d_gather = c->dalloc<double>((size_t)nRanks * 16);
     c->deltaNValid = false;
+    peer_setup(c);
     API_END(c)
 }
 
@@ -2351,6 +2463,7 @@ int tcif_get_alpha(tcif_ctx *c, int phase, double *internal, double *boundary) {
     if (internal) CUDA_OK(cudaMemcpyAsync(internal, c->alpha[phase], sizeof(double) * c->nC, cudaMemcpyDefault, c->stream));
     if (boundary && c->nBF) CUDA_OK(cudaMemcpyAsync(boundary, c->alphab[phase], sizeof(double) * c->nBF, cudaMemcpyDefault, c->stream));
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    peer_check(c);
     API_END(c)
 }
 
@@ -2691,6 +2804,7 @@ int tcif_get_force(tcif_ctx *c, double *internal, double *boundary) {
     down_vec(c, internal, c->F, c->nC, c->stride);
     if (boundary && c->nBF) down_vec(c, boundary, c->Fb, c->nBF, c->nBF);
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    peer_check(c);
     API_END(c)
 }
 
@@ -3026,6 +3140,7 @@ int tcif_alpha_stats(tcif_ctx *c, int phase, double out3[3]) {
     int ops[3] = {RED_SUM, RED_MIN, RED_MAX};
     allreduce_host(c, v, ops, 3);
     out3[0] = v[0]; out3[1] = v[1]; out3[2] = v[2];
+    peer_check(c);
     API_END(c)
 }
 
@@ -3056,6 +3171,7 @@ int tcif_timers_read(tcif_ctx *c, double *ms, int64_t *launches, double *bytes) 
 }
 int64_t tcif_launch_count(const tcif_ctx *c) { return c ? c->launches : 0; }
 int64_t tcif_device_bytes(const tcif_ctx *c) { return c ? c->devBytes : 0; }
+int tcif_comm_transport(const tcif_ctx *c) { return !c ? 0 : c->group ? 1 : c->nccl ? (c->peerOn ? 3 : 2) : 0; }
 int tcif_mesh_info(const tcif_ctx *c, int32_t out[8]) {
     if (!c || !out) return 1;
     out[0] = c->Ko; out[1] = c->Kn; out[2] = kshape(c); out[3] = c->tileStrips; out[4] = c->dm.pfTiles;

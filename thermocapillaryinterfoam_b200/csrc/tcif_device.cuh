@@ -77,6 +77,7 @@ struct DMesh {
     const int *coupledFaces;// [nCoupled] boundary face ids of processor faces, ascending
     const int *coupledOff;  // [nCoupled] offset (in coupled-face units) of the face's processor patch
     const int *coupledSize; // [nCoupled] size of the face's processor patch
+    const int *coupledPatchIdx; // [nCoupled] index of the face's processor patch among this rank's processor patches
 };
 
 // hint: pull the sector holding *p from HBM into L2 (no register destination, never faults on a valid mapping)
@@ -793,6 +794,67 @@ static __global__ void k_halo_unpack(const __grid_constant__ DMesh m, const __gr
     if (k >= m.nCoupled) return;
     int bf = m.coupledFaces[k];
     for (int d = 0; d < h.ncomp; ++d) h.dst[d][bf] = recv[halo_slot(m, k, d, h.ncomp)];
+}
+
+// ---- processor-patch exchange over peer memory (NVLink): no pack buffer, no NCCL kernel ----------------------------
+// Every rank owns a receive buffer (two parities) and one flag word per source rank; neighbours map it with
+// cudaIpcOpenMemHandle.  k_halo_push stores patchInternalField straight into the neighbour's buffer, in the layout
+// k_halo_unpack reads (patch-major, component-major inside a patch); the last CTA to finish releases the flags
+// (value = exchange number) at system scope.  k_halo_wait (one warp) acquires this rank's flags, k_halo_pull then
+// reads the buffer with cache-volatile loads.  Parity double-buffering is safe because a rank pushes exchange n+1 only
+// after it has pulled exchange n, i.e. after every neighbour has pushed n -- which each did after pulling n-1.
+#define TCIF_MAX_PEER_PATCHES 64
+struct HaloPeer {
+    int nPatches;
+    double *base[TCIF_MAX_PEER_PATCHES];              // neighbour's receive buffer (mapped), start of the parity-0 half
+    int peerOff[TCIF_MAX_PEER_PATCHES];               // offset (coupled-face units) of the matching patch in the NEIGHBOUR's layout
+    unsigned *remoteFlag[TCIF_MAX_PEER_PATCHES];      // neighbour's flag word for this rank
+    const unsigned *localFlag[TCIF_MAX_PEER_PATCHES]; // this rank's flag word for that neighbour
+    size_t stride[TCIF_MAX_PEER_PATCHES];             // doubles per parity half of the NEIGHBOUR's buffer
+};
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+static __global__ void __launch_bounds__(TCIF_TPB)
+k_halo_push(const __grid_constant__ DMesh m, const __grid_constant__ HaloArgs h, const __grid_constant__ HaloPeer hp,
+            unsigned parity, unsigned seq, int *counter) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < m.nCoupled) {
+        const int pi = m.coupledPatchIdx[k], off = m.coupledOff[k], sz = m.coupledSize[k];
+        const int fc = m.faceCells[m.coupledFaces[k]];
+        double *dst = hp.base[pi] + parity * hp.stride[pi] + (size_t)hp.peerOff[pi] * h.ncomp + (k - off);
+        for (int d = 0; d < h.ncomp; ++d) dst[(size_t)d * sz] = h.src[d][fc];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int done = atomicAdd(counter, 1);
+        if (done == (int)gridDim.x - 1) {            // every CTA's stores are ordered before this point (fence + atomic)
+            *counter = 0;
+            __threadfence_system();
+            for (int p = 0; p < hp.nPatches; ++p) st_release_sys(hp.remoteFlag[p], seq);
+        }
+    }
+}
+// one warp: wait until every neighbour has released exchange `seq`; gives up after ~2 s and raises *status
+static __global__ void k_halo_wait(const __grid_constant__ HaloPeer hp, unsigned seq, int *status) {
+    const long long t0 = clock64();
+    for (int p = threadIdx.x; p < hp.nPatches; p += blockDim.x) {
+        while ((int)(ld_acquire_sys(hp.localFlag[p]) - seq) < 0) {
+            if (clock64() - t0 > 4000000000LL) { atomicExch(status, 1); break; }
+            __nanosleep(200);
+        }
+    }
+}
+static __global__ void __launch_bounds__(TCIF_TPB)
+k_halo_pull(const __grid_constant__ DMesh m, const __grid_constant__ HaloArgs h, const double *recv) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= m.nCoupled) return;
+    const int bf = m.coupledFaces[k];
+    for (int d = 0; d < h.ncomp; ++d) h.dst[d][bf] = __ldcv(recv + halo_slot(m, k, d, h.ncomp));
 }
 
 // host order <-> device slots
