@@ -345,6 +345,11 @@ TCIF_API int tcif_laser_get_sparse(tcif_ctx *ctx, int32_t capacity, int32_t *cel
 TCIF_API int tcif_laser_set_shared_points(tcif_ctx *ctx, int32_t nShared, const int32_t *localPoint, const int64_t *globalPoint);
 /* launches of the walk kernel in the last calculate() = depth of the reflection cascade + 1 */
 TCIF_API int tcif_laser_generations(const tcif_ctx *ctx);
+/* Decomposed meshes only.  on = 1: a reflected particle whose insertion point (0.1 cbrt(V) behind the hit point) lies
+ * behind a processor patch is DROPPED, exactly as the reference's rank-local mesh().findCell(insertP) does
+ * (DTRMParticle.C:189-206) -- for comparing a decomposed device run with a decomposed run of the reference.
+ * Default 0: the neighbour rank locates the particle, so that the result does not depend on the decomposition. */
+TCIF_API int tcif_laser_set_local_find_cell(tcif_ctx *ctx, int on);
 
 /* Logging scalars of multiphaseSystem.C:408-425: sum(V*alpha), min, max (global over ranks). */
 TCIF_API int tcif_alpha_stats(tcif_ctx *ctx, int phase, double out3[3]);

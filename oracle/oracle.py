@@ -544,7 +544,7 @@ class OrcReflection(C.Structure):
 
 class OrcLaserCfg(C.Structure):
     _fields_ = [("nModels", C.c_int32), ("models", C.POINTER(OrcReflection)), ("alphaCut", C.c_double),
-                ("sigmaSB", C.c_double), ("maxParticles", C.c_int32)]
+                ("sigmaSB", C.c_double), ("maxParticles", C.c_int32), ("localFindCell", C.c_int32)]
 
 
 class LaserGeomHandle:
@@ -607,7 +607,7 @@ def laser_calculate(m, geom, models, alphas_i, alphas_b, alphaBc, a, e, E, T, p0
     bc = i32(alphaBc).reshape(P, -1)
     arr = reflection_array(models)
     n = len(I)
-    cfg = OrcLaserCfg(len(models), arr, float(alphaCut), float(sigmaSB), int(maxParticles or 64 * max(n, 1)))
+    cfg = OrcLaserCfg(len(models), arr, float(alphaCut), float(sigmaSB), int(maxParticles or 64 * max(n, 1)), 0)
     nC = h.s.nCells
     Q = np.zeros(nC); refl = np.zeros(nC, np.int32); nHat = np.zeros((nC, 3)); nPts = np.zeros((g.s.nPoints, 3))
     nFinal = C.c_int32(0)
@@ -622,7 +622,7 @@ def laser_calculate(m, geom, models, alphas_i, alphas_b, alphaBc, a, e, E, T, p0
 
 
 def laser_calculate_ranks(meshes, geoms, models, refl, nHat, pointGlobal, a, e, E, T, p0, p1, I, dA, cells, alphaCut=0.5,
-                          sigmaSB=SIGMA_SB, maxParticles=0):
+                          sigmaSB=SIGMA_SB, maxParticles=0, localFindCell=False):
     """The decomposed laser walk with all ranks on one CPU (orc_laser_calculate_ranks).  Per-rank lists: meshes, geoms,
     refl/nHat (the marking restricted to the rank's cells), pointGlobal, a/e/E/T, cells (local cell of each seed or -1).
     Returns dict(Q=[...], created=[...], nHatPoints=[...])."""
@@ -631,7 +631,7 @@ def laser_calculate_ranks(meshes, geoms, models, refl, nHat, pointGlobal, a, e, 
     gs = [g if isinstance(g, LaserGeomHandle) else LaserGeomHandle(h.m, g) for h, g in zip(hs, geoms)]
     arr = reflection_array(models)
     n = len(I)
-    cfg = OrcLaserCfg(len(models), arr, float(alphaCut), float(sigmaSB), int(maxParticles or 64 * max(n, 1)))
+    cfg = OrcLaserCfg(len(models), arr, float(alphaCut), float(sigmaSB), int(maxParticles or 64 * max(n, 1)), int(bool(localFindCell)))
     mp = (C.POINTER(OrcMesh) * R)(*[C.pointer(h.s) for h in hs])
     gp = (C.POINTER(OrcLaserGeom) * R)(*[C.pointer(g.s) for g in gs])
     refl = [i32(x) for x in refl]; nHat = [f64(x) for x in nHat]

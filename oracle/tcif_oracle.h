@@ -313,6 +313,9 @@ typedef struct orc_laser_cfg {
     double alphaCut;           /* laserDTRM.C:379 (default 0.5)  */
     double sigmaSB;            /* physicoChemical::sigma          */
     int32_t maxParticles;      /* capacity of the cloud incl. reflected particles */
+    int32_t localFindCell;     /* 1: a reflected particle whose insertion point lies behind a processor patch is dropped, as the
+                                  reference's rank-local mesh().findCell does (DTRMParticle.C:189-206); 0: the neighbour rank
+                                  locates it (decomposition-independent result) */
 } orc_laser_cfg;
 enum { ORC_PD_GAUSSIAN = 0, ORC_PD_UNIFORM = 2, ORC_PD_GAUSSIAN_PEAK = 3 };
 /* laserDTRM::initialise() (laserDTRM.C:169-331) without findCell: the polar disk of seeds.  rArea is the unit

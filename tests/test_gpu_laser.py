@@ -222,6 +222,78 @@ def test_decomposed_matches_serial_oracle(procs):
     grp.close()
 
 
+def test_local_find_cell_reproduces_the_decomposed_reference_walk():
+    """tcif_laser_set_local_find_cell(1): a reflected particle whose insertion point lies behind a processor patch is
+    dropped, as the reference's rank-local mesh().findCell does (DTRMParticle.C:189-206).  The decomposed device run then
+    equals the decomposed walk of the oracle with the same rule (counts exact, Q to 1e-10 of max), which is what a
+    decomposed run of the reference computes -- and both lose particles against the serial walk here."""
+    import threading
+    n, procs = 16, (2, 2, 2)
+    spec = cases.case(5, n)
+    g = mo.box_mesh(*spec.n, spec.lengths, spec.patch_types)
+    xs, ys, zs = (hm.vertices(spec.n[d], spec.lengths[d]) for d in range(3))
+    geomG = cases.box_polymesh(g, xs, ys, zs)
+    fg = cases.synthetic_fields(spec, g)
+    aC, eC, EC = (25.0, 10.0, 0.3), (0.1, 0.0, 0.0), (0.0, 0.0, 0.0)
+    d = np.array([0.5, -1.0, 0.2]); d /= np.linalg.norm(d)
+    r = np.cross(d, [0.0, 0.0, 1.0]); r /= np.linalg.norm(r)
+    p0, p1, Ip, dA = cases.laser_seeds((0.3, 0.93, 0.45), d, r, 8, 16, 0.15, geomG["boundsMag"], sigma=0.07, power=200.0)
+    cellG = cases.find_cells_box(spec.n, xs, ys, zs, p0)
+    al = fg["alpha_i"]
+    a, e, E = (orc.local_density(al, c) for c in (aC, eC, EC))
+    serial = orc.laser_calculate(g, geomG, MODELS, al, fg["alpha_b"], fg["alphaBc"], a, e, E, fg["T_i"], p0, p1, Ip, dA, cellG)
+    nd = 8
+    meshes = [hm.box_block(spec.n, spec.lengths, spec.patch_types, procs, rk) for rk in range(nd)]
+    geoms = [cases.box_block_polymesh(spec.n, xs, ys, zs, procs, rk, m) for rk, m in enumerate(meshes)]
+    gids = [np.asarray(m.cellGlobal) for m in meshes]
+    cells = []
+    for gid in gids:
+        g2l = np.full(g.nCells, -1, np.int32); g2l[gid] = np.arange(len(gid), dtype=np.int32)
+        cells.append(g2l[cellG])
+    ref = {}
+    for local in (False, True):
+        ref[local] = orc.laser_calculate_ranks(meshes, geoms, MODELS, [serial["reflectingCells"][i] for i in gids],
+                                               [serial["nHat"][i] for i in gids], [gm["pointGlobal"] for gm in geoms],
+                                               [a[i] for i in gids], [e[i] for i in gids], [E[i] for i in gids],
+                                               [fg["T_i"][i] for i in gids], p0, p1, Ip, dA, cells, localFindCell=local)
+    assert int(ref[False]["created"].sum()) == serial["nParticles"]
+    assert int(ref[True]["created"].sum()) < serial["nParticles"], "no reflected particle is inserted behind a processor patch in this case"
+    fs = [cases.synthetic_fields(spec, m) for m in meshes]
+    grp = abi.Group(nd)
+    ctxs = [abi.Context(m, spec.nPhases) for m in meshes]
+    outs, errs = [None] * nd, []
+
+    def work(rk):
+        try:
+            m, f, ctx = meshes[rk], fs[rk], ctxs[rk]
+            ctx.comm_init_local(rk, grp)
+            cases.load_case(ctx, spec, f)
+            ctx.set_cell_centres(f["C"], f["deltab"])
+            ctx.laser_set_polymesh(m.Cf, m.Cfb, geoms[rk])
+            ctx.laser_set_shared_points(geoms[rk]["sharedLocal"], geoms[rk]["sharedGlobal"])
+            ctx.laser_set_shared_points(geoms[rk]["sharedLocal"], geoms[rk]["sharedGlobal"])     # idempotent (collective)
+            ctx.laser_set_reflection(MODELS)
+            ctx.laser_set_local_density_absorption([0, 1, 2], aC, eC, EC)
+            ctx.laser_set_local_find_cell(True)
+            own = cells[rk] >= 0                        # each rank hands over ONLY its own seeds, as the solver does
+            Q, created = ctx.laser_calculate(p0[own], p1[own], Ip[own], dA[own], cells[rk][own])
+            outs[rk] = (Q, created)
+        except Exception as ex:          # noqa: BLE001
+            errs.append((rk, ex))
+    ts = [threading.Thread(target=work, args=(rk,), daemon=True) for rk in range(nd)]
+    [t.start() for t in ts]
+    [t.join(180) for t in ts]
+    assert not errs, errs
+    assert all(o is not None for o in outs), "a rank did not finish"
+    assert sum(o[1] for o in outs) == int(ref[True]["created"].sum())
+    scale = max(np.abs(q).max() for q in ref[True]["Q"])
+    for rk in range(nd):
+        assert np.abs(outs[rk][0] - ref[True]["Q"][rk]).max() <= 1e-10 * scale, rk
+    for c in ctxs:
+        c.close()
+    grp.close()
+
+
 # ---- NCCL, one process per GPU: hand-over by ncclSend/ncclRecv, point sums and counts by ncclAllGather ---------------
 _NCCL_ABS = ((25.0, 10.0, 0.3), (0.1, 0.0, 0.0), (0.0, 0.0, 0.0))
 
@@ -262,7 +334,10 @@ def _nccl_laser_worker(rank, world, n, out):
     ctx.laser_set_local_density_absorption([0, 1, 2], *_NCCL_ABS)
     gid = np.asarray(m.cellGlobal)
     g2l = np.full(spec.nCells, -1, np.int32); g2l[gid] = np.arange(len(gid), dtype=np.int32)
-    Q, created = ctx.laser_calculate(p0, p1, Ip, dA, g2l[cellG])
+    # each rank hands over ONLY the seeds whose cell it found, as laserDTRM::initialise() seeds its local cloud: a rank
+    # with few or no seeds of its own still receives its neighbours' particles (capacities come from the global count)
+    own = g2l[cellG] >= 0
+    Q, created = ctx.laser_calculate(p0[own], p1[own], Ip[own], dA[own], g2l[cellG][own])
     np.savez(os.path.join(out, f"rank{rank}.npz"), Q=Q, created=np.array([created]), gid=gid)
     ctx.close()
 

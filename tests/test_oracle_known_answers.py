@@ -339,3 +339,89 @@ def test_flux_of_vector_uniform_and_linear():
     A = np.array([[1.0, 2.0, 0.0], [0.0, -1.0, 3.0], [0.5, 0.0, 1.0]])
     fi, _ = orc.flux_of_vector(m, m.C @ A.T, m.Cfb @ A.T)
     assert np.allclose(fi, np.einsum("ij,ij->i", m.Cf @ A.T, m.Sf), rtol=1e-13, atol=1e-16)   # linear weights: exact
+
+
+# ---- hand-derived known answers of MULES::limiter on a row of three unit cells ----------------------------------------
+# [UPSTREAM] OpenFOAM-v2106 src/finiteVolume/fvMatrices/solvers/MULES/MULESTemplates.C, MULES::limiter(): the branches
+# SURVEY.md 8(a) M4 / A.6 flags -- (i) the local extrema are taken over the NEIGHBOURS (the cell's own value is not
+# among them), (ii) on non-coupled patches that do not fix the value the extrema take the global bounds psiMax/psiMin
+# (`boundaryExtrema` = global; the patch-value alternative is the run-time switch), (iii) the denominators carry
+# ROOTVSMALL.  The source is not on this machine (parity unpinned); what IS pinned here is that the oracle does
+# exactly what that restatement says, by numbers worked out by hand below -- so a reader with the v2106 source can check
+# the three branches against nine literals.
+def _row3():
+    m = mo.box_mesh(3, 1, 1, (3.0, 1.0, 1.0), (0, 0, 1, 1, 1, 1))      # x walls, y/z empty: V = 1, |Sf| = 1
+    assert m.nIF == 2 and m.nBF == 2 and np.allclose(m.V, 1.0)
+    return m
+
+
+def test_k6_limiter_hand_derived_row_global_and_patch_value_branches():
+    """psi = (0.9, 0.5, 0.1), phi = +0.5 on both faces, HO flux (1.0, 0.6), dt = 1, Su = Sp = 0, walls zeroGradient.
+         phiBD   = phi*psi_upwind          = (0.45, 0.25)       phiCorr = (0.55, 0.35)   (both > 0)
+         sumPhiBD (own +, nei -)           = (0.45, -0.20, -0.25)
+         sumPhip  (outflow corrections)    = (0.55, 0.35, 0)    mSumPhim (inflow) = (0, 0.55, 0.35)
+       global bounds on the walls: psiMaxn = 1, psiMinn = 0 in every cell (cell 1: neighbours 0.9 / 0.1 clipped by nothing)
+         Q+ = psiMaxn - psi0 + sumPhiBD    = (0.55, 0.30, 0.65)  Q- = psi0 - psiMinn - sumPhiBD = (0.45, 0.60, 0.35)   [cell 1: 0.5-0.1+0.2]
+       iteration 1 (lambda = 1):  lambdap_0 = (mSumlPhim_0 + Q-_0)/sumPhip_0 = 0.45/0.55 = 9/11, every other lambda+- >= 1
+         face 0: min(lambdap_0, lambdam_1) = 9/11;  face 1: 1.   Further iterations leave them (lambdap_0 stays 9/11).
+       explicitSolve: phiPsi = phiBD + lambda phiCorr = (0.45 + 0.45, 0.6);  psi_new = psi0 - div = (0, 0.8, 0.7):
+       cell 0 lands EXACTLY on psiMin -- the limiter's definition of "as much anti-diffusion as boundedness allows"."""
+    m = _row3()
+    psi = np.array([0.9, 0.5, 0.1]); psib = psi[m.faceCells]
+    phii, phib = np.array([0.5, 0.5]), np.zeros(2)
+    ho = np.array([1.0, 0.6])
+    bc = np.zeros(m.nPatches, np.int32)
+    z = np.zeros(3)
+    bdi, bdb = orc.upwind_flux(m, phii, phib, psi, psib)
+    assert np.allclose(bdi, [0.45, 0.25], rtol=0, atol=1e-16)
+    lam, _ = orc.mules_limiter(m, orc.mules_cfg(3), 1.0, psi, psib, psi, bc, bdi, bdb, ho - bdi, np.zeros(2), z, z)
+    assert np.allclose(lam, [9.0 / 11.0, 1.0], rtol=0, atol=2e-16), lam
+    qi, _, pi, _ = orc.mules_explicit_solve(m, orc.mules_cfg(3), 1.0, psi, psib, psi, bc, phii, phib, ho - bdi + bdi, np.zeros(2), z, z)
+    assert np.allclose(pi, [0.9, 0.6], rtol=0, atol=2e-16) and np.allclose(qi, [0.0, 0.8, 0.7], rtol=0, atol=3e-16), (pi, qi)
+    # patch-value branch: the wall of cell 0 contributes psi_b = 0.9 instead of the global bounds -> psiMinn_0 = min(0.5, 0.9)
+    #   Q-_0 = 0.9 - 0.5 - 0.45 = -0.05 < 0  ->  lambdap_0 = clamp(-0.05/0.55) = 0: face 0 gets NO anti-diffusion
+    #   psi_new_0 = 0.9 - 0.45 = 0.45;  cell 1: 0.5 + 0.45 - 0.6 = 0.35   [face 1: psiMaxn_2 = max(0.5, psi_b = 0.1) = 0.5,
+    #   Q+_2 = 0.5 - 0.1 - 0.25 = 0.15, lambdam_2 = 0.15/0.35 = 3/7 -> phiPsi_1 = 0.25 + 0.15 = 0.4 -> psi_new = (0.45, 0.55, 0.5)]
+    cfgp = orc.mules_cfg(3, boundaryExtrema=orc.BEXT_PATCHVALUE)
+    lam2, _ = orc.mules_limiter(m, cfgp, 1.0, psi, psib, psi, bc, bdi, bdb, ho - bdi, np.zeros(2), z, z)
+    assert np.allclose(lam2, [0.0, 3.0 / 7.0], rtol=0, atol=2e-16), lam2
+    q2, _, p2, _ = orc.mules_explicit_solve(m, cfgp, 1.0, psi, psib, psi, bc, phii, phib, ho, np.zeros(2), z, z)
+    assert np.allclose(p2, [0.45, 0.4], rtol=0, atol=2e-16) and np.allclose(q2, [0.45, 0.55, 0.5], rtol=0, atol=3e-16), (p2, q2)
+
+
+def test_k6_limiter_hand_derived_own_value_is_not_a_local_extremum():
+    """psi = (0.2, 0.9, 0.3): cell 1 is a local MAXIMUM.  phi = +0.5, HO flux (0.3, 0.75), dt = 1.
+         phiBD = (0.10, 0.45), phiCorr = (0.20, 0.30);  cell 1: sumPhiBD = -0.10 + 0.45 = 0.35,
+         inflow correction mSumPhim_1 = 0.20 (face 0), outflow sumPhip_1 = 0.30 (face 1).
+       Neighbours only: psiMaxn_1 = max(0.2, 0.3) = 0.3  ->  Q+_1 = 0.3 - 0.9 + 0.35 = -0.25
+         iteration 1: lambdam_1 = clamp((sumlPhip_1 + Q+_1)/mSumPhim_1) = (0.30 - 0.25)/0.20 = 0.25  -> face 0: 0.25
+       (had the own value 0.9 been included: Q+_1 = +0.35, lambdam_1 = 1, face 0 unlimited).
+         face 1: lambdap_1 = (mSumlPhim_1 + Q-_1)/sumPhip_1 with psiMinn_1 = 0.2: Q-_1 = 0.9 - 0.2 - 0.35 = 0.35 -> (0.2+0.35)/0.3 > 1;
+                 lambdam_2: psiMaxn_2 = 1 (wall, global), Q+_2 = 1 - 0.3 - 0.45 = 0.25 -> 0.25/0.30 = 5/6  -> face 1: 5/6
+       iteration 2 (lambda = (0.25, 5/6)): sumlPhip_1 = 5/6*0.3 = 0.25 -> lambdam_1 = (0.25 - 0.25)/0.2 = 0 -> face 0: 0;
+                 mSumlPhim_1 = 0.25*0.2 = 0.05 -> lambdap_1 = (0.05 + 0.35)/0.3 > 1; lambdam_2 unchanged -> face 1: 5/6
+       iteration 3 changes nothing: lambda = (0, 5/6)."""
+    m = _row3()
+    psi = np.array([0.2, 0.9, 0.3]); psib = psi[m.faceCells]
+    phii, phib = np.array([0.5, 0.5]), np.zeros(2)
+    ho = np.array([0.3, 0.75])
+    bc = np.zeros(m.nPatches, np.int32)
+    z = np.zeros(3)
+    bdi, bdb = orc.upwind_flux(m, phii, phib, psi, psib)
+    for L, expect in ((1, [0.25, 5.0 / 6.0]), (2, [0.0, 5.0 / 6.0]), (3, [0.0, 5.0 / 6.0])):
+        lam, _ = orc.mules_limiter(m, orc.mules_cfg(L), 1.0, psi, psib, psi, bc, bdi, bdb, ho - bdi, np.zeros(2), z, z)
+        assert np.allclose(lam, expect, rtol=0, atol=2e-15), (L, lam)      # a few roundings in Q and the quotient
+
+
+def test_k6_limiter_rootvsmall_keeps_cells_without_corrections_unlimited():
+    """A cell with no outflow (inflow) correction has sumPhip (mSumPhim) = 0: the quotient is Q/ROOTVSMALL = +-1e150*Q,
+    clamped to 1 (Q > 0) or 0 (Q < 0) -- never NaN.  psi = (0.3, 0.5, 0.7), phiBD = (0.15, 0.25), one small correction
+    (+0.05) on face 0: Q-_0 = 0.3 - 0.15 = 0.15 -> lambdap_0 = 0.15/0.05 -> 1; Q+_1 = 0.7 - 0.5 + 0.1 = 0.3 -> lambdam_1 -> 1;
+    face 1 (phiCorr = 0, not > 0) takes min(lambdam_1, lambdap_2) with lambdap_2 = (0 + 0.95)/(0 + ROOTVSMALL) -> 1."""
+    m = _row3()
+    psi = np.array([0.3, 0.5, 0.7]); psib = psi[m.faceCells]
+    bc = np.zeros(m.nPatches, np.int32)
+    z = np.zeros(3)
+    bdi, bdb = np.array([0.15, 0.25]), np.zeros(2)
+    lam, _ = orc.mules_limiter(m, orc.mules_cfg(3), 1.0, psi, psib, psi, bc, bdi, bdb, np.array([0.05, 0.0]), np.zeros(2), z, z)
+    assert np.isfinite(lam).all() and np.array_equal(lam, [1.0, 1.0]), lam

@@ -401,6 +401,9 @@ class Context:
         gp = np.ascontiguousarray(globalPoint, dtype=np.int64)
         self._ck(lib().tcif_laser_set_shared_points(self.h, len(lp), _i(lp), gp.ctypes.data_as(C.POINTER(C.c_int64))))
 
+    def laser_set_local_find_cell(self, on=True):
+        self._ck(lib().tcif_laser_set_local_find_cell(self.h, int(bool(on))))
+
     def laser_set_reflection(self, models, alphaCut=0.5):
         arr = (ReflectionModel * max(len(models), 1))()
         for i, md in enumerate(models):

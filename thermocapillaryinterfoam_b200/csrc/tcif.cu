@@ -142,8 +142,6 @@ struct tcif_ctx {
     double *stagingOut = nullptr;
     cudaEvent_t evV = nullptr, evB = nullptr;
     bool noOverlap = false;
-    int *bndIdentity = nullptr;   // [nBndCells] 0, 1, 2, ...: the deferred list of the one sweep that defers every boundary cell
-    int nDef = 0;            // cells deferred to the O(surface) launches (fixed-K meshes: the cells next to a processor patch)
     // host copy of the small mesh tables
     int nC = 0, nIF = 0, nBF = 0, nPatches = 0, stride = 0, Ko = 0, Kn = 0, nBndCells = 0, nCoupled = 0;
     size_t nFd = 0;
@@ -209,8 +207,10 @@ struct tcif_ctx {
     double *lzNHat = nullptr, *lzNHatPts = nullptr, *lzQ = nullptr;
     LaserPart *lzCloud = nullptr;
     int lzCap = 0, lzParticles = 0, lzGenerations = 0;
+    bool lzLocalFind = false;             // reflected particles inserted behind a processor patch are dropped (reference behaviour)
     // decomposed runs: point weights kept on the host for the global normalisation, shared points, mailboxes
-    std::vector<double> lzPwRaw;
+    std::vector<double> lzPwRaw;          // per point: LOCAL sum of the raw inverse-distance weights (never rescaled)
+    std::vector<double> lzPwDenom;        // per point: the sum the device weights are currently normalised with
     std::vector<int> lzPcStart;
     std::vector<unsigned char> lzIsPatch;
     double *lzPw = nullptr;
@@ -324,22 +324,29 @@ template <class F> void timed_on(tcif_ctx *c, cudaStream_t st, int id, double by
 }
 template <class F> void timed(tcif_ctx *c, int id, double bytes, F &&launch) { timed_on(c, c->stream, id, bytes, launch); }
 
-// One sweep of the path = an O(volume) kernel over the interior cells on the main stream and, on the
-// side stream, the halo exchange it does NOT need plus the O(surface) kernel over the boundary-adjacent
-// cells (which consumes the halo).  Sweep k's volume kernel reads sweep k-1's boundary results and
-// vice versa, hence the two events; the exchange and the boundary kernel hide behind the volume kernel.
-// side = false: the volume launch covers every cell (fixed-K mesh without processor patches: patch faces are handled
-// inline, nothing is deferred), the side stream stays idle.
-template <class FV, class FB> void sweep(tcif_ctx *c, FV &&volume, FB &&boundary, bool side = true) {
-    if (!side) { volume(); return; }
-    CUDA_OK(cudaEventRecord(c->evV, c->stream));
-    CUDA_OK(cudaStreamWaitEvent(c->side, c->evV, 0));
-    CUDA_OK(cudaStreamWaitEvent(c->stream, c->evB, 0));
+// One sweep of the path = the O(volume) kernel over the interior cells, the processor-patch exchange it does NOT need
+// and the O(surface) kernel over the deferred (boundary-adjacent) cells, which consumes the halo:
+//     main stream :  volume_k ------------------> [wait halo_k] deferred_k   volume_k+1 ...
+//     side stream :  halo_k (push / wait / pull)
+// The exchange hides behind the volume kernel; the deferred kernel runs AFTER it on the same stream.  (Rounds 1 ran
+// the deferred kernel concurrently on the high-priority side stream: the volume sweeps are latency/occupancy-bound and
+// lost 10-12 % to the co-runner -- 42.5 ms of volume kernels in isolation under ncu, 48.4 ms in the bench -- and
+// handling patch faces inline in the volume kernel cost the same through longer-lived divergent warps; see
+// profiles/r03_variants.md.)
+template <class FV, class FH, class FB> void sweep(tcif_ctx *c, FV &&volume, FH &&halo, FB &&boundary) {
+    const bool ex = c->nCoupled > 0;
+    if (ex) {
+        CUDA_OK(cudaEventRecord(c->evV, c->stream));
+        CUDA_OK(cudaStreamWaitEvent(c->side, c->evV, 0));
+        halo();
+        CUDA_OK(cudaEventRecord(c->evB, c->side));
+    }
     volume();
+    if (ex) CUDA_OK(cudaStreamWaitEvent(c->stream, c->evB, 0));
     boundary();
-    CUDA_OK(cudaEventRecord(c->evB, c->side));
 }
-void join(tcif_ctx *c) { CUDA_OK(cudaStreamWaitEvent(c->stream, c->evB, 0)); }
+template <class FV, class FB> void sweep(tcif_ctx *c, FV &&volume, FB &&boundary) { volume(); boundary(); }
+void join(tcif_ctx *c) { CUDA_OK(cudaStreamWaitEvent(c->stream, c->evB, 0)); }     // (kept: harmless, the sweeps already waited)
 
 void timers_collect(tcif_ctx *c) {
     join(c);
@@ -490,29 +497,19 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
     d.bndMask = c->upload(mask);
     d.bndCells = c->upload(bndCells); d.bndCellStart = c->upload(bndStart); d.bndFaces = c->upload(order);
     {
-        // fixed-K sweeps (tcif_volume.cuh): rank of a mask bit -> index in bndCells, and the cells whose patch faces
-        // must wait for the halo exchange (>= 1 processor face).  TCIF_INLINE_BND=0 defers every boundary-adjacent
-        // cell instead (the round-1 split, kept for A/B runs); generic-K meshes always use the k_* twin kernels.
-        std::vector<int> rank((size_t)stride / 32, 0);
-        int acc = 0;
-        for (size_t wd = 0; wd < rank.size(); ++wd) { rank[wd] = acc; acc += __builtin_popcount(mask[wd]); }
-        d.bndWordRank = c->upload(rank);
-        const char *e = getenv("TCIF_INLINE_BND");
-        const bool inl = !(e && atoi(e) == 0);
-        std::vector<int> def;
-        std::vector<unsigned> dmask((size_t)stride / 32, 0u);
-        for (int k = 0; k < (int)bndCells.size(); ++k) {
-            bool defer = !inl;
-            for (int j = bndStart[k]; j < bndStart[k + 1] && !defer; ++j) defer = bfType[order[j]] == TCIF_PATCH_PROCESSOR;
-            if (defer) { def.push_back(k); dmask[bndCells[k] >> 5] |= 1u << (bndCells[k] & 31); }
+        // one 32-byte record per boundary-adjacent cell: its (<= 3) patch faces with their patch type and id, so that a
+        // thread reaches the patch values with ONE dependent load after its cell index instead of three (start, face, type)
+        std::vector<int> rec(8 * std::max<size_t>(bndCells.size(), 1), 0);
+        for (size_t k = 0; k < bndCells.size(); ++k) {
+            const int n = bndStart[k + 1] - bndStart[k];
+            int *r = &rec[8 * k];
+            r[0] = n <= 3 ? n : -n;
+            for (int j = 0; j < 3; ++j) {
+                const int bf = order[bndStart[k] + (j < n ? j : 0)];
+                r[1 + j] = bf; r[4 + j] = bfType[bf] | (bfPatch[bf] << 4);
+            }
         }
-        std::vector<int> ident(bndCells.size());
-        for (size_t k = 0; k < ident.size(); ++k) ident[k] = (int)k;
-        c->bndIdentity = c->upload(ident);
-        c->nDef = (int)def.size();
-        d.nDef = c->nDef;
-        d.defCells = c->upload(def);
-        d.defMask = def.empty() ? nullptr : c->upload(dmask);
+        d.bndRec = (const int4 *)c->upload(rec);
     }
     d.faceCells = c->upload(fc); d.bfPatch = c->upload(bfPatch); d.bfType = c->upload(bfType);
     std::vector<double> bx(nBF), by(nBF), bz(nBF), mag(nBF), dc(nBF), wb(nBF);
@@ -805,8 +802,6 @@ const SweepFns *fns(const tcif_ctx *c) {
         default: return nullptr;
     }
 }
-// does a sweep have O(surface) work for the side stream?
-bool side_needed(const tcif_ctx *c) { return fns(c) ? (c->nDef > 0 || c->nCoupled > 0) : (c->nBndCells > 0 || c->nCoupled > 0); }
 
 #define DISPATCH_P(...)                                      \
     switch (c->P) {                                          \
@@ -829,36 +824,29 @@ ForceArgs force_args(tcif_ctx *c, bool withTensor, bool withG) {
 // the force sweeps gather few arrays (their +-z planes fit in L2): ascending tile order is faster for them
 // (profiles/r02_variants.md), the strip order is for the MULES sweeps
 DMesh dm_ascending(const tcif_ctx *c) { DMesh d = c->dm; d.tileOrder = nullptr; return d; }
-// kv_div_tensor defers every boundary-adjacent cell (see tcif_volume.cuh): deferred list = bndCells
-DMesh dm_div(const tcif_ctx *c) {
-    DMesh d = c->dm;
-    d.tileOrder = nullptr; d.defMask = c->nBndCells ? d.bndMask : nullptr; d.defCells = c->bndIdentity; d.nDef = c->nBndCells;
-    return d;
-}
-
-// BND: the O(surface) launch on the side stream (deferred cells / generic-K twin)
+// BND: the O(surface) launch over the boundary-adjacent cells (fixed-K: same body as the volume launch; generic K: twin)
 template <bool BND, bool WG> void launch_grad_tensor(tcif_ctx *c, const ForceArgs &a) {
     if (const SweepFns *f = fns(c)) {
-        if (BND && !c->nDef) return;
-        f->grad_tensor(c->P, BND, BND ? c->side : c->stream, BND ? c->dm : dm_ascending(c), a);
+        if (BND && !c->nBndCells) return;
+        f->grad_tensor(c->P, BND, c->stream, BND ? c->dm : dm_ascending(c), a);
         c->launches++;
         return;
     }
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    DISPATCH_P(k_grad_tensor<PP, 0, 0, BND, WG><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, a));
+    DISPATCH_P(k_grad_tensor<PP, 0, 0, BND, WG><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a));
     c->launches++;
 }
 template <bool BND> void launch_div_tensor(tcif_ctx *c, const ForceArgs &a) {
     if (const SweepFns *f = fns(c)) {
         if (BND && !c->nBndCells) return;
-        f->div_tensor(c->P, BND, BND ? c->side : c->stream, dm_div(c), a);
+        f->div_tensor(c->P, BND, c->stream, dm_ascending(c), a);
         c->launches++;
         return;
     }
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    DISPATCH_P(k_div_tensor<PP, 0, 0, BND><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, a));
+    DISPATCH_P(k_div_tensor<PP, 0, 0, BND><<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, a));
     c->launches++;
 }
 
@@ -912,17 +900,15 @@ void do_force(tcif_ctx *c) {
     ensure_deltaN(c);
     ForceArgs a = force_args(c, true, false);
     sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, true, false), [&] { launch_grad_tensor<false, false>(c, a); }); },
-             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, false>(c, a); }); }, side_needed(c));
+             [&] { timed(c, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, false>(c, a); }); });
     sweep(c, [&] { timed(c, T_DIV_TENSOR, bytes_div_tensor(c), [&] { launch_div_tensor<false>(c, a); }); },
-             [&] {
-                 if (c->nCoupled) {      // neighbour-rank tensors of the processor faces: hidden behind the volume sweep
-                     const double *src[36]; double *dst[36];
-                     const int nT = (c->tsum ? 1 : c->Q) * 6;
-                     for (int k = 0; k < nT; ++k) { src[k] = c->Tq + (size_t)k * c->stride; dst[k] = c->TqHalo + (size_t)k * std::max(c->nBF, 1); }
-                     halo_cells(c, nT, src, dst, c->side);
-                 }
-                 timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_div_tensor<true>(c, a); });
-             }, c->nBndCells > 0 || c->nCoupled > 0);
+             [&] {                   // neighbour-rank tensors of the processor faces: hidden behind the volume sweep
+                 const double *src[36]; double *dst[36];
+                 const int nT = (c->tsum ? 1 : c->Q) * 6;
+                 for (int k = 0; k < nT; ++k) { src[k] = c->Tq + (size_t)k * c->stride; dst[k] = c->TqHalo + (size_t)k * std::max(c->nBF, 1); }
+                 halo_cells(c, nT, src, dst, c->side);
+             },
+             [&] { timed(c, T_BOUNDARY, 0, [&] { launch_div_tensor<true>(c, a); }); });
     join(c);
     if (c->nBF) {
         timed(c, T_BOUNDARY, 0, [&] {
@@ -944,7 +930,7 @@ void do_grad(tcif_ctx *c) {
     if (!c->G) { c->G = c->dalloc<double>((size_t)c->P * 3 * c->stride); c->Gb = c->dalloc<double>((size_t)c->P * 3 * std::max(c->nBF, 1)); }
     ForceArgs a = force_args(c, false, true);
     sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, false, true), [&] { launch_grad_tensor<false, true>(c, a); }); },
-             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, a); }); }, side_needed(c));
+             [&] { timed(c, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, a); }); });
     join(c);
     if (!c->nBF) return;
     for (int p = 0; p < c->P; ++p) {
@@ -1017,40 +1003,40 @@ MulesBatch resolve_flip(const MulesBatch &b0, int flip) {
 
 template <bool BND> void launch_setup(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm) {
     if (const SweepFns *f = fns(c)) {
-        if (BND && !c->nDef) return;
-        f->setup(b.nPh, BND, BND ? c->side : c->stream, c->dm, b, prm);
+        if (BND && !c->nBndCells) return;
+        f->setup(b.nPh, BND, c->stream, c->dm, b, prm);
         c->launches++;
         return;
     }
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    k_mules_setup<0, 0, BND><<<cdiv(n, TCIF_TPB) * b.nPh, TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, b, prm);
+    k_mules_setup<0, 0, BND><<<cdiv(n, TCIF_TPB) * b.nPh, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm);
     c->launches++;
 }
 template <bool BND> void launch_iter(tcif_ctx *c, const MulesBatch &b, int first, int flip) {
     if (const SweepFns *f = fns(c)) {
-        if (BND && !c->nDef) return;
-        f->iter(b.nPh, first != 0, BND, BND ? c->side : c->stream, c->dm, resolve_flip(b, flip));
+        if (BND && !c->nBndCells) return;
+        f->iter(b.nPh, first != 0, BND, c->stream, c->dm, resolve_flip(b, flip));
         c->launches++;
         return;
     }
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    k_mules_iter<0, 0, BND><<<cdiv(n, TCIF_TPB) * b.nPh, TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, b, first, flip);
+    k_mules_iter<0, 0, BND><<<cdiv(n, TCIF_TPB) * b.nPh, TCIF_TPB, 0, c->stream>>>(c->dm, b, first, flip);
     c->launches++;
 }
 template <bool BND, int MODE>
 void launch_final(tcif_ctx *c, const MulesBatch &b, const MulesParams &prm, int first, int flip, int nIter, bool lsum = false) {
     if (const SweepFns *f = fns(c)) {
-        if (BND && !c->nDef) return;
-        f->fin(b.nPh, MODE, first != 0, lsum, BND, BND ? c->side : c->stream, c->dm, resolve_flip(b, flip), prm, nIter);
+        if (BND && !c->nBndCells) return;
+        f->fin(b.nPh, MODE, first != 0, lsum, BND, c->stream, c->dm, resolve_flip(b, flip), prm, nIter);
         c->launches++;
         return;
     }
     if (lsum) failf("launch_final: fused limitSum needs the fixed-K kernels");
     int n = BND ? c->nBndCells : c->nC;
     if (n == 0) return;
-    k_mules_final<0, 0, BND, MODE><<<cdiv(n, TCIF_TPB) * b.nPh, TCIF_TPB, 0, BND ? c->side : c->stream>>>(c->dm, b, prm, first, flip, nIter);
+    k_mules_final<0, 0, BND, MODE><<<cdiv(n, TCIF_TPB) * b.nPh, TCIF_TPB, 0, c->stream>>>(c->dm, b, prm, first, flip, nIter);
     c->launches++;
 }
 
@@ -1084,14 +1070,13 @@ void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode,
             CUDA_OK(cudaMemcpyAsync(c->alpha0[phases[k]], c->alpha[phases[k]], sizeof(double) * c->nC, cudaMemcpyDeviceToDevice, c->stream));
     }
     const int L = c->cfg.nLimiterIter;
-    const bool side = side_needed(c);
     sweep(c, [&] { timed(c, T_MULES_SETUP, bytes_mules_setup(c, nPh, prm.storeOld != 0), [&] { launch_setup<false>(c, b, prm); }); },
-             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_setup<true>(c, b, prm); }); }, side);
+             [&] { timed(c, T_BOUNDARY, 0, [&] { launch_setup<true>(c, b, prm); }); });
     int first = 1, flip = 0;
     for (int j = 1; j < L; ++j) {
         sweep(c, [&] { timed(c, T_MULES_ITER, bytes_mules_iter(c, nPh, first), [&] { launch_iter<false>(c, b, first, flip); }); },
-                 [&] { halo_lambda(c, b, flip);      // syncTools::syncFaceList(min) of the previous iteration
-                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b, first, flip); }); }, side);
+                 [&] { halo_lambda(c, b, flip); },      // syncTools::syncFaceList(min) of the previous iteration
+                 [&] { timed(c, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b, first, flip); }); });
         flip ^= 1; first = 0;
     }
     double fb = bytes_mules_final(c, nPh, mode, first);
@@ -1099,8 +1084,8 @@ void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode,
     auto fin = [&](auto modeTag) {
         constexpr int MODE = decltype(modeTag)::value;
         sweep(c, [&] { timed(c, T_MULES_FINAL, fb, [&] { launch_final<false, MODE>(c, b, prm, first, flip, L, fuseLimitSum); }); },
-                 [&] { if (L > 0) halo_lambda(c, b, flip);
-                       timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_final<true, MODE>(c, b, prm, first, flip, L, fuseLimitSum); }); }, side);
+                 [&] { if (L > 0) halo_lambda(c, b, flip); },
+                 [&] { timed(c, T_BOUNDARY, 0, [&] { launch_final<true, MODE>(c, b, prm, first, flip, L, fuseLimitSum); }); });
     };
     if (mode == 0) fin(std::integral_constant<int, 0>{});
     else if (mode == 1) fin(std::integral_constant<int, 1>{});
@@ -1195,7 +1180,7 @@ void do_flux_assembly(tcif_ctx *c, int schemePhi, int schemePhir, PhicState &st)
     ensure_G(c);
     ForceArgs ga = force_args(c, false, true);
     sweep(c, [&] { timed(c, T_GRAD_TENSOR, bytes_grad_tensor(c, false, true), [&] { launch_grad_tensor<false, true>(c, ga); }); },
-             [&] { timed_on(c, c->side, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, ga); }); }, side_needed(c));
+             [&] { timed(c, T_BOUNDARY, 0, [&] { launch_grad_tensor<true, true>(c, ga); }); });
     join(c);
     if (c->nCoupled) {                            // neighbour-rank gradients on processor faces
         const double *src[36]; double *dst[36];
@@ -1262,8 +1247,8 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
         PredBatch b = batch(nullptr);
         sweep(c, [&] { timed(c, T_PREDICTOR, (double)nPh * c->nC * (40.0 + 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko), [&] {
                            k_pred_setup<false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b); c->launches++; }); },
-                 [&] { if (c->nBndCells) timed_on(c, c->side, T_BOUNDARY, 0, [&] {
-                           k_pred_setup<true><<<gridB, TCIF_TPB, 0, c->side>>>(c->dm, b); c->launches++; }); });
+                 [&] { if (c->nBndCells) timed(c, T_BOUNDARY, 0, [&] {
+                           k_pred_setup<true><<<gridB, TCIF_TPB, 0, c->stream>>>(c->dm, b); c->launches++; }); });
     }
     bool active[4] = {true, true, true, true};
     const SweepFns *kvpPred = fns(c);
@@ -1277,14 +1262,14 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
                            if (kvpPred) kvpPred->pred_jacobi(nPh, c->stream, c->dm, b);
                            else k_pred_jacobi<false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b);
                            c->launches++; }); },
+                 [&] {                            // patchNeighbourField of the iterate
+                     const double *src[4]; double *dst[4]; int n = 0;
+                     for (int k = 0; k < nPh; ++k) if (active[k]) { src[n] = c->alpha[phases[k]]; dst[n] = c->alphab[phases[k]]; ++n; }
+                     halo_cells(c, n, src, dst, c->side);
+                 },
                  [&] {
-                     if (c->nCoupled) {           // patchNeighbourField of the iterate
-                         const double *src[4]; double *dst[4]; int n = 0;
-                         for (int k = 0; k < nPh; ++k) if (active[k]) { src[n] = c->alpha[phases[k]]; dst[n] = c->alphab[phases[k]]; ++n; }
-                         halo_cells(c, n, src, dst, c->side);
-                     }
-                     if (c->nBndCells) timed_on(c, c->side, T_BOUNDARY, 0, [&] {
-                         k_pred_jacobi<true><<<gridB, TCIF_TPB, 0, c->side>>>(c->dm, b); c->launches++; });
+                     if (c->nBndCells) timed(c, T_BOUNDARY, 0, [&] {
+                         k_pred_jacobi<true><<<gridB, TCIF_TPB, 0, c->stream>>>(c->dm, b); c->launches++; });
                  });
         join(c);
         CUDA_OK(cudaMemcpyAsync(c->h_small, c->dmaxDev, sizeof(double) * 4, cudaMemcpyDeviceToHost, c->stream));
@@ -1636,6 +1621,11 @@ void do_laser_set_polymesh(tcif_ctx *c, const double *Cf, const double *Cfb, int
     if ((nIF && !Cf) || (nBF && !Cfb) || nPoints <= 0 || !points || !fpStart || !fpPts || !tetBasePt || !(boundsMag > 0))
         failf("tcif_laser_set_polymesh: bad arguments");
     if (!c->Cx) failf("tcif_laser_set_polymesh: cell centres needed, call tcif_set_cell_centres first");
+    // 2-D cases: the reference subtracts particle::deviationFromMeshCentre() from every displacement (DTRMParticle.C:110)
+    // and the cells are open in the empty direction here (empty patches carry no faces): not supported, not guessed
+    for (int pa = 0; pa < c->nPatches; ++pa)
+        if (c->patchType[pa] == TCIF_PATCH_EMPTY || c->patchType[pa] == TCIF_PATCH_WEDGE)
+            failf("tcif_laser_set_polymesh: laserDTRM on meshes with empty or wedge patches (fewer than 3 solution directions) is not supported");
     if (fpStart[0] != 0) failf("tcif_laser_set_polymesh: fpStart[0] must be 0");
     for (int f = 0; f < nF; ++f) {
         if (fpStart[f + 1] - fpStart[f] < 3) failf("tcif_laser_set_polymesh: face %d has fewer than 3 vertices", f);
@@ -1745,6 +1735,7 @@ void do_laser_set_polymesh(tcif_ctx *c, const double *Cf, const double *Cfb, int
         for (size_t i = 0; i < c->cpPatch.size(); ++i) info[2 * c->cpPatch[i]] = (int)i;
         c->lzPatchInfo = c->upload(info);
     }
+    c->lzPwDenom = c->lzPwRaw;
     c->lzSharedSet = false;
     // walk table: one contiguous record of all face planes per cell (TCIF_LASER_TABLE=0 keeps the ELL gathers)
     {
@@ -1814,9 +1805,9 @@ void do_laser_set_shared_points(tcif_ctx *c, int nShared, const int32_t *localPo
         CUDA_OK(cudaMemcpy(pw.data(), c->lzPw, sizeof(double) * pw.size(), cudaMemcpyDeviceToHost));
         for (int i = 0; i < nShared; ++i) {
             const int p = localPoint[i];
-            const double f = c->lzPwRaw[p] / sumW[i];
+            const double f = c->lzPwDenom[p] / sumW[i];      // idempotent: a second call finds the weights already global
             for (int k = c->lzPcStart[p]; k < c->lzPcStart[p + 1]; ++k) pw[k] *= f;
-            c->lzPwRaw[p] = sumW[i];
+            c->lzPwDenom[p] = sumW[i];
             if (flag[i]) c->lzIsPatch[p] = 1;
         }
         CUDA_OK(cudaMemcpy(c->lzPw, pw.data(), sizeof(double) * pw.size(), cudaMemcpyHostToDevice));
@@ -1898,6 +1889,8 @@ int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const doub
     a.nModels = (int)c->lzModels.size(); a.P = c->P;
     for (int i = 0; i < a.nModels; ++i) a.models[i] = c->lzModels[i];
     a.alphaCut = c->lzAlphaCut; a.sigmaSB = sigmaSB; a.deltaN = c->lzDeltaN;
+    a.localFindCell = c->lzLocalFind ? 1 : 0;
+    a.maxSteps = 64 * (int)cbrt((double)std::max(c->nC, 1)) + 4096;      // a straight ray crosses O(nCells^(1/3)) cells
     for (int p = 0; p < c->P; ++p) a.alpha[p] = c->alpha[p];
     a.refl = c->lzRefl; a.nHat = c->lzNHat; a.nHatPts = c->lzNHatPts; a.Q = c->lzQ; a.T = c->Tc;
     a.nAbs = c->lzNAbs;
@@ -1961,6 +1954,7 @@ int do_laser_calculate(tcif_ctx *c, int nParticles, const double *p0, const doub
         CUDA_OK(cudaStreamSynchronize(c->stream));
         if (cnt[1] == LASER_ERR_PROCESSOR) error = "a particle reached a processor patch of a context without mailboxes";
         if (cnt[1] == LASER_ERR_OVERFLOW || cnt[0] > cap) error = "cloud overflow, raise maxParticles";
+        if (cnt[1] == LASER_ERR_STUCK) error = "a particle crossed more cells than a straight ray can (warped or non-convex cells?)";
         created += cnt[0] - total;
         done = total; total = std::min(cnt[0], cap);
         if (++generations > 10000) error = "reflection cascade does not end";
@@ -2787,6 +2781,12 @@ int tcif_laser_get_sparse(tcif_ctx *c, int32_t capacity, int32_t *cells, double 
 
 int tcif_laser_generations(const tcif_ctx *c) { return c ? c->lzGenerations : -1; }
 
+int tcif_laser_set_local_find_cell(tcif_ctx *c, int on) {
+    API_BEGIN(c)
+    c->lzLocalFind = on != 0;
+    API_END(c)
+}
+
 int tcif_laser_set_shared_points(tcif_ctx *c, int32_t nShared, const int32_t *localPoint, const int64_t *globalPoint) {
     API_BEGIN(c)
     do_laser_set_shared_points(c, nShared, localPoint, globalPoint);
@@ -3175,7 +3175,7 @@ int tcif_comm_transport(const tcif_ctx *c) { return !c ? 0 : c->group ? 1 : c->n
 int tcif_mesh_info(const tcif_ctx *c, int32_t out[8]) {
     if (!c || !out) return 1;
     out[0] = c->Ko; out[1] = c->Kn; out[2] = kshape(c); out[3] = c->tileStrips; out[4] = c->dm.pfTiles;
-    out[5] = c->nBndCells; out[6] = fns(c) ? c->nDef : c->nBndCells; out[7] = c->nCoupled;
+    out[5] = c->nBndCells; out[6] = c->nBndCells; out[7] = c->nCoupled;
     return 0;
 }
 

@@ -63,13 +63,11 @@ struct DMesh {
     const double *Sfx, *Sfy, *Sfz, *w;   // [Ko*stride]
     const double *V;        // [nC]
     const unsigned *bndMask;// [stride/32] bit c: cell c owns >=1 boundary face
-    const int *bndWordRank; // [stride/32] number of boundary-adjacent cells below cell 32*w (rank of a mask bit -> index in bndCells)
-    const unsigned *defMask;// [stride/32] bit c: cell c is deferred to the O(surface) launch (null: none), see tcif_volume.cuh
-    const int *defCells;    // [nDef] the deferred cells as indices into bndCells, ascending
-    int nDef;
     const int *bndCells;    // [nBndCells] ascending cell ids owning >=1 boundary face
     const int *bndCellStart;// [nBndCells+1]
     const int *bndFaces;    // boundary face ids grouped by cell, ascending
+    const int4 *bndRec;     // [2*nBndCells] packed record of a boundary-adjacent cell: {n, bf0, bf1, bf2}, {tp0, tp1, tp2, 0};
+                            //   tp = patch type | patch id << 4; unused slots repeat face 0; n < 0: more than 3 faces (use the lists)
     const int *faceCells;   // [nBF]
     const int *bfPatch;     // [nBF]
     const int *bfType;      // [nBF] patch type of the face

@@ -20,7 +20,7 @@ namespace tcif {
 #define TCIF_VGREAT 1e300
 
 enum { REFL_NONE = 0, REFL_FRESNEL = 1, REFL_FRESNEL_LASER = 2 };
-enum { LASER_ERR_PROCESSOR = 2, LASER_ERR_OVERFLOW = 3 };
+enum { LASER_ERR_PROCESSOR = 2, LASER_ERR_OVERFLOW = 3, LASER_ERR_STUCK = 4 };
 
 struct LaserRefl { int kind, from, to; double nk1[2], nk2[2], epsilon; };
 
@@ -70,6 +70,8 @@ struct LaserArgs {
     LaserPart *outbox;                  // [nCoupledPatches * mailCap], null on a single domain
     int mailCap;
     const int *patchInfo;               // [nPatches*2]: coupled-patch slot (-1: none), first boundary face of the patch
+    int localFindCell;                  // 1: reference behaviour, a reflected particle inserted behind a processor patch is dropped
+    int maxSteps;                       // bound on the cells one particle may cross in one launch (LASER_ERR_STUCK beyond)
 };
 
 __device__ __forceinline__ double l_dot(const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
@@ -425,7 +427,11 @@ k_laser_move(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g
     LaserPart p = a.cloud[ip];
     if (p.keep != 1) return;            // a received particle whose insertion point was not found on this rank
     int err = 0;
+    int steps = 0;
     do {
+        // l_track clips a negative crossing parameter to 0: on warped cells the plane walk could cycle without advancing
+        // p.frac; a hung kernel needs a device reset, so the walk is bounded and reports instead
+        if (++steps > a.maxSteps) { err = LASER_ERR_STUCK; break; }
         const double pos0[3] = {p.pos[0], p.pos[1], p.pos[2]};
         const int cell1 = p.cell;
         const double f = 1 - p.frac;
@@ -477,7 +483,7 @@ k_laser_move(const __grid_constant__ DMesh m, const __grid_constant__ LaserGeo g
                     int procFace;
                     const int cellI = l_walk_find(m, g, cell1, insertP, &procFace);
                     // noReflection: R() = 0 and rho = 0, the new particle would deposit exactly nothing
-                    if ((cellI > -1 || (procFace >= 0 && a.outbox)) && r.kind != REFL_NONE) {
+                    if ((cellI > -1 || (procFace >= 0 && a.outbox && !a.localFindCell)) && r.kind != REFL_NONE) {
                         const double s2 = 2.0 * (-l_dot(pDir, nh));                   // R(i, n) = i + 2(-i & n) n
                         LaserPart q;
                         for (int d = 0; d < 3; ++d) {

@@ -1,6 +1,6 @@
 // tcif_sweeps.h -- host-side launch table of the fixed-K sweeps (tcif_volume.cuh).  The kernels are instantiated
 // per slot count K in their own translation units (tcif_sweeps_k2.cu, _k3.cu, _k4.cu: compiled in parallel),
-// tcif.cu picks the table of the mesh at hand.  def = the O(surface) launch over DMesh::defCells.
+// tcif.cu picks the table of the mesh at hand.  def = the O(surface) launch over DMesh::bndCells.
 #pragma once
 #include "tcif_device.cuh"
 #include "tcif_alpha.cuh"
@@ -8,7 +8,7 @@
 namespace tcif {
 
 struct SweepFns {
-    // grid sizes are computed inside from DMesh (nTiles for the volume launch, nDef for the deferred one)
+    // grid sizes are computed inside from DMesh (nTiles for the volume launch, nBndCells for the deferred one)
     void (*grad_tensor)(int P, bool def, cudaStream_t st, const DMesh &m, const ForceArgs &a);
     void (*div_tensor)(int P, bool def, cudaStream_t st, const DMesh &m, const ForceArgs &a);
     void (*setup)(int nPh, bool def, cudaStream_t st, const DMesh &m, const MulesBatch &b, const MulesParams &prm);

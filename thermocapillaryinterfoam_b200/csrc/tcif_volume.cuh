@@ -11,15 +11,16 @@
 // use evict-first loads/stores (__ldcs/__stcs) so that L2 keeps the arrays neighbours gather from.
 //
 // round 2: ONE kernel body per sweep.  Every kernel here takes a template flag DEF:
-//   DEF = false  the O(volume) launch: all cells in tile order.  A cell that owns boundary faces of
-//                non-coupled patches (walls, wedges) handles them inline, after its internal faces, in
-//                patch order (the reference's accumulation order) -- a rare, warp-divergent tail instead
-//                of a second launch.  Cells flagged in DMesh::defMask are skipped.
-//   DEF = true   the O(surface) launch over DMesh::defCells: the cells next to a processor patch, which
-//                must wait for the halo exchange; runs on the side stream behind the exchange.
-// The round-1 design ran a generic-K, one-thread-per-(cell, phase) "twin" kernel over ALL boundary-adjacent
-// cells next to every volume launch (5.6 ms per stage at 64 M cells for 1.5 % of the cells, co-running
-// with and slowing the volume sweep); on one GPU there is now no second launch at all.
+//   DEF = false  the O(volume) launch: the cells without patch faces, in tile order (boundary-adjacent cells return at
+//                once: one mask word per warp).
+//   DEF = true   the O(surface) launch over DMesh::bndCells: the same body plus the patch faces (walls, wedges,
+//                processor patches with their halo values), after the cell's internal faces, in patch order -- the
+//                reference's accumulation order.  It runs AFTER the volume launch on the same stream (tcif.cu sweep()).
+// What was measured on the way (profiles/r03_variants.md): a generic-K one-thread-per-(cell, phase) twin running
+// concurrently on a high-priority stream (round 1) cost the latency/occupancy-bound volume sweeps 10-12 %; handling the
+// patch faces inline in the volume launch cost 7 % at 400^3 and 17 % on 200x400x400 sub-domains, because a CTA stays
+// resident until its one boundary lane is done; deferring every boundary-adjacent cell to a second launch that runs
+// alone is the cheapest, provided that launch is short -- hence the packed per-cell records (BndRec) below.
 #pragma once
 #include "tcif_device.cuh"
 #include "tcif_alpha.cuh"      // PredBatch (kvp_pred_jacobi)
@@ -91,28 +92,22 @@ template <int TPB_> __device__ __forceinline__ CellIdx cell_of(const DMesh &m, i
     return r;
 }
 
-// The cell of this thread.  bi = index of the cell in bndCells / bndCellStart (-1: the cell has no boundary
-// face).  Volume launch: bi comes from the boundary bit mask (rank of the bit = prefix count of its word +
-// popcount below it), so interior cells read one mask word per warp and nothing else.
+// The cell of this thread.  bi = index of the cell in bndCells / bndRec (deferred launch), -1 in the volume launch
+// (a compile-time constant there, so that the patch-face code is not even compiled into the volume kernels).
 struct CellCtx { int c, cp, bi; };
 template <int TPB_, bool DEF>
 __device__ __forceinline__ bool pick_cell(const DMesh &m, CellCtx &x) {
     if (DEF) {
         const int i = blockIdx.x * TPB_ + threadIdx.x;
-        if (i >= m.nDef) return false;
-        x.bi = m.defCells[i]; x.c = m.bndCells[x.bi]; x.cp = -1;
+        if (i >= m.nBndCells) return false;
+        x.bi = i; x.c = m.bndCells[i]; x.cp = -1;
         return true;
     }
     const CellIdx ci = cell_of<TPB_>(m, blockIdx.x);
     x.c = ci.c; x.cp = ci.cp; x.bi = -1;
-    if (x.c >= m.nC) return false;
-    const int w = x.c >> 5;
-    const unsigned bit = 1u << (x.c & 31);
-    if (m.defMask && (m.defMask[w] & bit)) return false;
-    const unsigned bw = m.bndMask[w];
-    if (bw & bit) x.bi = m.bndWordRank[w] + __popc(bw & (bit - 1u));
-    return true;
+    return x.c < m.nC && !is_bnd_cell(m, x.c);
 }
+#define TCIF_BI(x) (DEF ? (x).bi : -1)
 
 // L2 prefetch of the contiguous (own-slot) streams a later CTA will read (cp of cell_of()).  The volume
 // sweeps are bound by memory latency (ncu: long-scoreboard stalls, ~45 % occupancy), and everything a cell
@@ -129,6 +124,23 @@ template <int K> __device__ __forceinline__ void pf_face(const double *a, int st
 template <int K> __device__ __forceinline__ void pf_geom(const DMesh &m, int cp) {
     pf_face<K>(m.w, m.stride, cp); pf_face<K>(m.Sfx, m.stride, cp); pf_face<K>(m.Sfy, m.stride, cp); pf_face<K>(m.Sfz, m.stride, cp);
     pf_l2(m.V + cp);
+}
+
+// Packed record of a boundary-adjacent cell (DMesh::bndRec): with it the patch values of a cell are ONE dependent load
+// away from its index (record -> values) instead of three (bndCellStart -> bndFaces -> bfType/bfPatch -> values), and
+// the helpers below issue all loads of the (<= 3) patch faces before the first store, so nothing serialises on a
+// possible alias.  That matters twice: the deferred launch is pure latency (one wave of threads, strided cells), and in
+// the inline mode a boundary lane keeps its whole CTA resident until it is done.
+struct BndRec { int n, bf[3], tp[3]; };
+__device__ __forceinline__ BndRec bnd_load(const DMesh &m, int bi) {
+    BndRec r;
+    r.n = 0;
+    r.bf[0] = r.bf[1] = r.bf[2] = 0; r.tp[0] = r.tp[1] = r.tp[2] = 0;
+    if (bi >= 0) {
+        const int4 a = __ldg(m.bndRec + 2 * (size_t)bi), b = __ldg(m.bndRec + 2 * (size_t)bi + 1);
+        r.n = a.x; r.bf[0] = a.y; r.bf[1] = a.z; r.bf[2] = a.w; r.tp[0] = b.x; r.tp[1] = b.y; r.tp[2] = b.z;
+    }
+    return r;
 }
 
 // ---- K1: grad(alpha_p) for all phases + capillary stress tensors of all pairs ---------------------
@@ -188,22 +200,45 @@ kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArg
             }
         }
     }
-    if (x.bi >= 0) {                         // patch faces, in patch order (gaussGrad: boundary loop after the internal faces)
-        for (int j = m.bndCellStart[x.bi], e = m.bndCellStart[x.bi + 1]; j < e; ++j) {
-            const int bf = m.bndFaces[j];
-            const bool coupled = m.bfType[bf] == PATCH_PROCESSOR;
-            const double wb = m.wb[bf], sx = m.Sfbx[bf], sy = m.Sfby[bf], sz = m.Sfbz[bf];
+    if (TCIF_BI(x) >= 0) {                   // patch faces, in patch order (gaussGrad: boundary loop after the internal faces)
+        const BndRec r = bnd_load(m, x.bi);
+        if (r.n >= 0) {
+            double wb[3], sx[3], sy[3], sz[3], ab[3][P];
 #pragma unroll
-            for (int p = 0; p < P; ++p) {
-                const double ab = a.alphab[p][bf];
-                const double af = coupled ? wb * aS[p] + (1.0 - wb) * ab : ab;
-                g[p][0] += sx * af; g[p][1] += sy * af; g[p][2] += sz * af;
+            for (int k = 0; k < 3; ++k) {
+                const int bf = r.bf[k];
+                wb[k] = m.wb[bf]; sx[k] = m.Sfbx[bf]; sy[k] = m.Sfby[bf]; sz[k] = m.Sfbz[bf];
+#pragma unroll
+                for (int p = 0; p < P; ++p) ab[k][p] = a.alphab[p][bf];
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                if (k < r.n) {
+                    const bool coupled = (r.tp[k] & 15) == PATCH_PROCESSOR;
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        const double af = coupled ? wb[k] * aS[p] + (1.0 - wb[k]) * ab[k][p] : ab[k][p];
+                        g[p][0] += sx[k] * af; g[p][1] += sy[k] * af; g[p][2] += sz[k] * af;
+                    }
+                }
+            }
+        } else {
+            for (int j = m.bndCellStart[x.bi], e = m.bndCellStart[x.bi + 1]; j < e; ++j) {
+                const int bf = m.bndFaces[j];
+                const bool coupled = m.bfType[bf] == PATCH_PROCESSOR;
+                const double wb = m.wb[bf], sx = m.Sfbx[bf], sy = m.Sfby[bf], sz = m.Sfbz[bf];
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    const double ab = a.alphab[p][bf];
+                    const double af = coupled ? wb * aS[p] + (1.0 - wb) * ab : ab;
+                    g[p][0] += sx * af; g[p][1] += sy * af; g[p][2] += sz * af;
+                }
             }
         }
     }
 #pragma unroll
     for (int p = 0; p < P; ++p) { g[p][0] = f_div(g[p][0], rV); g[p][1] = f_div(g[p][1], rV); g[p][2] = f_div(g[p][2], rV); }
-    if (x.bi >= 0) {                         // kept for the patch values of the tensor (kv_div_tensor)
+    if (TCIF_BI(x) >= 0) {                   // kept for the patch values of the tensor (kv_div_tensor)
 #pragma unroll
         for (int p = 0; p < P; ++p)
 #pragma unroll
@@ -296,9 +331,6 @@ __device__ __noinline__ void div_bnd_faces(const DMesh &m, const ForceArgs &a, i
 }
 
 // ---- K2: F = sum_q div(T_q) ---------------------------------------------------------------------------
-// The one sweep that keeps ALL boundary-adjacent cells in the deferred launch (tcif.cu passes a DMesh whose deferred
-// list is bndCells): the patch-face tensor (div_bnd_faces) is a function call with ~50 live doubles around it, and
-// inlining it in the volume launch cost 2 ms per stage at 64 M cells in spills (3.7 -> 5.8 ms, profiles/r03_variants.md).
 template <int P, int K, bool DEF>
 __global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
 kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
@@ -346,7 +378,7 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
 #pragma unroll
         for (int k = 0; k < K; ++k)
             if (s.vO[k]) face_div_acc(wO[k], sxO[k], syO[k], szO[k], Ts, Tn[k], 1.0, acc);
-        if (DEF && x.bi >= 0) div_bnd_faces<P>(m, a, x.bi, c, q, Ts, acc);
+        if (TCIF_BI(x) >= 0) div_bnd_faces<P>(m, a, x.bi, c, q, Ts, acc);
         F[0] += f_div(acc[0], rV); F[1] += f_div(acc[1], rV); F[2] += f_div(acc[2], rV);
     }
     __stcs(a.F + c, F[0]); __stcs(a.F + (size_t)m.stride + c, F[1]); __stcs(a.F + (size_t)2 * m.stride + c, F[2]);
@@ -361,36 +393,54 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
 // =====================================================================================================
 
 // patch faces of the set-up sweep: phiBD_b, phiCorr_b, lambda_b = 1, local extrema, sums
-__device__ __forceinline__ void bnd_setup(const DMesh &m, const MulesPh &ph, const MulesParams &prm, int bi, double psiC,
+__device__ __forceinline__ void bnd_setup_face(const MulesPh &ph, const MulesParams &prm, int bf, bool coupled, int kind, double psb,
+                                               double phb, double pp, double psiC, double &psiMaxn, double &psiMinn, double &sBD,
+                                               double &sP, double &sM) {
+    double bd;
+    if (coupled) {
+        const double w = phb >= 0 ? 1.0 : 0.0;
+        const double up = phb * (w * psiC + (1.0 - w) * psb);
+        if (prm.addUpwind) pp = pp + up;
+        bd = up;
+    } else {
+        if (prm.addUpwind) pp = pp + phb * psb;
+        bd = pp;                       // phiBD_b := phiPsi_b on non-coupled patches
+    }
+    const double pc = pp - bd;
+    ph.phiBDb[bf] = bd; ph.phiCorrb[bf] = pc; ph.lamb[bf] = 1.0;
+    if (coupled || kind == BC_FIXED_VALUE || prm.boundaryExtrema == 1) {
+        psiMaxn = dmax(psiMaxn, psb); psiMinn = dmin(psiMinn, psb);
+    } else {
+        psiMaxn = dmax(psiMaxn, prm.psiMax); psiMinn = dmin(psiMinn, prm.psiMin);
+    }
+    sBD += bd;
+    if (pc > 0) sP += pc; else sM -= pc;
+}
+__device__ __forceinline__ void bnd_setup(const DMesh &m, const BndRec &r, const MulesPh &ph, const MulesParams &prm, int bi, double psiC,
                                           double &psiMaxn, double &psiMinn, double &sBD, double &sP, double &sM) {
+    if (r.n >= 0) {
+        double psb[3], phb[3], pin[3];
+        int kind[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {           // every load first (unused slots repeat face 0: in range)
+            const int bf = r.bf[k];
+            psb[k] = ph.psib[bf]; phb[k] = prm.phib[bf]; pin[k] = ph.phiInb[bf]; kind[k] = ph.bc[r.tp[k] >> 4];
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            if (k < r.n) bnd_setup_face(ph, prm, r.bf[k], (r.tp[k] & 15) == PATCH_PROCESSOR, kind[k], psb[k], phb[k], pin[k], psiC,
+                                        psiMaxn, psiMinn, sBD, sP, sM);
+        return;
+    }
     for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
         const int bf = m.bndFaces[j];
-        const bool coupled = m.bfType[bf] == PATCH_PROCESSOR;
-        const double psb = ph.psib[bf], phb = prm.phib[bf];
-        double pp = ph.phiInb[bf], bd;
-        if (coupled) {
-            const double w = phb >= 0 ? 1.0 : 0.0;
-            const double up = phb * (w * psiC + (1.0 - w) * psb);
-            if (prm.addUpwind) pp = pp + up;
-            bd = up;
-        } else {
-            if (prm.addUpwind) pp = pp + phb * psb;
-            bd = pp;                       // phiBD_b := phiPsi_b on non-coupled patches
-        }
-        const double pc = pp - bd;
-        ph.phiBDb[bf] = bd; ph.phiCorrb[bf] = pc; ph.lamb[bf] = 1.0;
-        if (coupled || ph.bc[m.bfPatch[bf]] == BC_FIXED_VALUE || prm.boundaryExtrema == 1) {
-            psiMaxn = dmax(psiMaxn, psb); psiMinn = dmin(psiMinn, psb);
-        } else {
-            psiMaxn = dmax(psiMaxn, prm.psiMax); psiMinn = dmin(psiMinn, prm.psiMin);
-        }
-        sBD += bd;
-        if (pc > 0) sP += pc; else sM -= pc;
+        bnd_setup_face(ph, prm, bf, m.bfType[bf] == PATCH_PROCESSOR, ph.bc[m.bfPatch[bf]], ph.psib[bf], prm.phib[bf], ph.phiInb[bf], psiC,
+                       psiMaxn, psiMinn, sBD, sP, sM);
     }
 }
 
 template <int K, int NPH, bool DEF>
-__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_SETUP)
+__global__ void __launch_bounds__(TCIF_TPB, DEF ? 2 : TCIF_MINB_SETUP)      // deferred launch: few threads, no spills
 kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                 const __grid_constant__ MulesParams prm) {
     CellCtx x;
@@ -398,6 +448,7 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
     const int c = x.c;
     Slots<K> s;
     s.load(m, c);
+    const BndRec rec = bnd_load(m, TCIF_BI(x));    // in flight together with the slot indices
     double phiN[K], phiO[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) { phiN[k] = prm.phi[s.fdN[k]]; phiO[k] = __ldcs(prm.phi + k * m.stride + c); }
@@ -454,7 +505,7 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 if (pc > 0) sP += pc; else sM -= pc;
             }
         }
-        if (x.bi >= 0) bnd_setup(m, ph, prm, x.bi, psiC, psiMaxn, psiMinn, sBD, sP, sM);
+        if (TCIF_BI(x) >= 0) bnd_setup(m, rec, ph, prm, x.bi, psiC, psiMaxn, psiMinn, sBD, sP, sM);
         psiMaxn = dmin(psiMaxn + prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMax);
         psiMinn = dmax(psiMinn - prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMin);
         if (prm.smoothLimiter > TCIF_SMALL) {
@@ -472,7 +523,25 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
 }
 
 // patch faces of a limiter iteration: face rule + contribution to the next cell pass
-__device__ __forceinline__ void bnd_iter(const DMesh &m, const MulesPh &ph, int bi, double lpC, double lmC, double &slp, double &slm) {
+__device__ __forceinline__ void bnd_iter(const DMesh &m, const BndRec &r, const MulesPh &ph, int bi, double lpC, double lmC, double &slp, double &slm) {
+    if (r.n >= 0) {
+        double pc[3], la[3], bd[3], lpH[3], lmH[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int bf = r.bf[k];
+            pc[k] = ph.phiCorrb[bf]; la[k] = ph.lamb[bf]; bd[k] = ph.phiBDb[bf]; lpH[k] = ph.lpHalo[bf]; lmH[k] = ph.lmHalo[bf];
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (k < r.n) {
+                const double lam = lambda_bface(r.tp[k] & 15, la[k], pc[k], bd[k], lpC, lmC, lpH[k], lmH[k]);
+                ph.lamb[r.bf[k]] = lam;
+                const double l = lam * pc[k];
+                if (l > 0) slp += l; else slm -= l;
+            }
+        }
+        return;
+    }
     for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
         const int bf = m.bndFaces[j];
         const double pc = ph.phiCorrb[bf];
@@ -484,13 +553,14 @@ __device__ __forceinline__ void bnd_iter(const DMesh &m, const MulesPh &ph, int 
 }
 
 template <int K, bool FIRST, int NPH, bool DEF>
-__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_ITER)
+__global__ void __launch_bounds__(TCIF_TPB, DEF ? 2 : TCIF_MINB_ITER)      // deferred launch: few threads, no spills
 kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b) {
     CellCtx x;
     if (!pick_cell<TCIF_TPB, DEF>(m, x)) return;
     const int c = x.c;
     Slots<K> s;
     s.load(m, c);
+    const BndRec rec = bnd_load(m, TCIF_BI(x));    // in flight together with the slot indices
     const int cp = x.cp;
     const bool pf = !DEF && cp >= 0;
     if (pf) pf_slots<K>(m, cp);
@@ -533,7 +603,7 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
                 if (l > 0) slp += l; else slm -= l;
             }
         }
-        if (x.bi >= 0) bnd_iter(m, ph, x.bi, lpC, lmC, slp, slm);
+        if (TCIF_BI(x) >= 0) bnd_iter(m, rec, ph, x.bi, lpC, lmC, slp, slm);
         lmOut[c] = dmax(dmin((slp + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
         lpOut[c] = dmax(dmin((slm + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
     }
@@ -558,7 +628,27 @@ template <int NPH> __device__ __forceinline__ void limit_sum_face(double *v) {
 
 // patch faces of the last face pass: lambda_b, limited patch flux, contribution to surfaceIntegrate
 template <int MODE>
-__device__ __forceinline__ void bnd_final(const DMesh &m, const MulesPh &ph, int bi, int nIter, double lpC, double lmC, double &sum) {
+__device__ __forceinline__ void bnd_final(const DMesh &m, const BndRec &r, const MulesPh &ph, int bi, int nIter, double lpC, double lmC, double &sum) {
+    if (r.n >= 0) {
+        double pc[3], la[3], bd[3], lpH[3], lmH[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int bf = r.bf[k];
+            pc[k] = ph.phiCorrb[bf]; la[k] = ph.lamb[bf]; bd[k] = ph.phiBDb[bf]; lpH[k] = ph.lpHalo[bf]; lmH[k] = ph.lmHalo[bf];
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (k < r.n) {
+                double lam = la[k];
+                if (nIter > 0) lam = lambda_bface(r.tp[k] & 15, lam, pc[k], bd[k], lpC, lmC, lpH[k], lmH[k]);
+                ph.lamb[r.bf[k]] = lam;
+                const double fl = (MODE == 0) ? pc[k] * lam : bd[k] + lam * pc[k];
+                ph.phiPsib[r.bf[k]] = fl;
+                sum += fl;
+            }
+        }
+        return;
+    }
     for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
         const int bf = m.bndFaces[j];
         const double pc = ph.phiCorrb[bf], bd = ph.phiBDb[bf];
@@ -577,7 +667,7 @@ __device__ __forceinline__ void bnd_final(const DMesh &m, const MulesPh &ph, int
 // LSUM (MODE 0 only, batch = all phases): MULES::limitSum of the owner-side faces applied in registers
 // before the store, which saves the separate read-modify-write sweep over the P flux arrays.
 template <int K, int MODE, bool FIRST, int NPH, bool LSUM, bool DEF>
-__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
+__global__ void __launch_bounds__(TCIF_TPB, DEF ? 2 : TCIF_MINB_FINAL)      // deferred launch: few threads, no spills
 kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                 const __grid_constant__ MulesParams prm, int nIter) {
     static_assert(!LSUM || MODE == 0, "limitSum is fused into the returnCorr=true apply only");
@@ -586,6 +676,7 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
     const int c = x.c;
     Slots<K> s;
     s.load(m, c);
+    const BndRec rec = bnd_load(m, TCIF_BI(x));    // in flight together with the slot indices
     double phN[K], phO[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -662,7 +753,7 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 sum += fl;
             }
         }
-        if (x.bi >= 0) bnd_final<MODE>(m, ph, x.bi, nIter, lpC, lmC, sum);
+        if (TCIF_BI(x) >= 0) bnd_final<MODE>(m, rec, ph, x.bi, nIter, lpC, lmC, sum);
         if (MODE == 2) {
             double d = sum / V;
             ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
