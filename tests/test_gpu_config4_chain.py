@@ -24,8 +24,10 @@ pytestmark = pytest.mark.gpu
 # synthetic 3-phase box (cases.synthetic_fields): phases 0 and 1 are the two blobs (metal, melt), phase 2 the gas around
 RHO = [7000.0, 6500.0, 1.2]
 PAIRS = [(0, 1), (0, 2), (1, 2)]
-LEE = [dict(**{"from": 0, "to": 2}, C=0.5, Tactivate=300.05, alphaMin=0.0),
-       dict(**{"from": 2, "to": 0}, C=-0.25, Tactivate=299.98, alphaMin=0.01)]
+# (C small enough that the blobs survive the two steps: with C = 0.5 the first solve() melts phase 0 away and no ray is
+# reflected any more)
+LEE = [dict(**{"from": 0, "to": 2}, C=0.002, Tactivate=300.05, alphaMin=0.0),
+       dict(**{"from": 2, "to": 0}, C=-0.001, Tactivate=299.98, alphaMin=0.01)]
 REFL = [dict(kind="FresnelLaser", **{"from": 2, "to": 0}, epsilon=0.25),          # gas -> metal
         dict(kind="Fresnel", **{"from": 2, "to": 1}, nk1=(1.0, 0.0), nk2=(3.6, 5.0))]     # gas -> melt
 ABS = ((60.0, 25.0, 0.3), (0.2, 0.1, 0.0), (0.0, 0.0, 0.0))

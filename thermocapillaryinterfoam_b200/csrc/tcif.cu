@@ -495,6 +495,12 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
     std::vector<unsigned> mask((size_t)stride / 32, 0u);
     for (int bc : bndCells) mask[bc >> 5] |= 1u << (bc & 31);
     d.bndMask = c->upload(mask);
+    {
+        std::vector<int> rank((size_t)stride / 32, 0);
+        int acc = 0;
+        for (size_t wd = 0; wd < rank.size(); ++wd) { rank[wd] = acc; acc += __builtin_popcount(mask[wd]); }
+        d.bndWordRank = c->upload(rank);
+    }
     d.bndCells = c->upload(bndCells); d.bndCellStart = c->upload(bndStart); d.bndFaces = c->upload(order);
     {
         // one 32-byte record per boundary-adjacent cell: its (<= 3) patch faces with their patch type and id, so that a
@@ -547,6 +553,10 @@ void alloc_fields(tcif_ctx *c) {
     c->gBnd = c->dalloc<double>((size_t)P * 3 * std::max(c->nBndCells, 1));
     c->TqHalo = c->dalloc<double>((size_t)std::max(Q, 1) * 6 * bs);
     c->F = c->dalloc<double>(3 * cs); c->Fb = c->dalloc<double>(3 * bs);
+    {   // partial records of the boundary-adjacent cells: the largest of the sweeps' layouts (tcif_volume.cuh)
+        const int slots = std::max(std::max(4 * P + 2, 1 + 9 * std::max(Q, 1)), 9 * P);
+        c->dm.part = c->dalloc<double>((size_t)slots * std::max(c->nBndCells, 1));
+    }
     c->stagingDoubles = std::max<size_t>(3 * cs, std::max<size_t>((size_t)std::max(c->nIF, 1), 3 * bs));
     c->staging = c->dalloc<double>(c->stagingDoubles);
     int maxComp = std::max(std::max(Q * 6, 3 * P), 3);
@@ -955,13 +965,13 @@ void do_grad(tcif_ctx *c) {
 void correct_alpha_bcs(tcif_ctx *c, const int *phases, int nPh) {
     for (int k = 0; k < nPh; ++k) alpha_changed(c, phases[k]);
     if (!c->nBF) return;
-    for (int k = 0; k < nPh; ++k) {
-        int p = phases[k];
-        timed(c, T_BOUNDARY, 0, [&] {
-            k_correct_bc_scalar<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, c->alpha[p], c->alphab[p], c->bc[p]);
-            c->launches++;
-        });
-    }
+    BcArgs ba{};
+    ba.n = nPh;
+    for (int k = 0; k < nPh; ++k) { const int p = phases[k]; ba.vi[k] = c->alpha[p]; ba.vb[k] = c->alphab[p]; ba.bc[k] = c->bc[p]; }
+    timed(c, T_BOUNDARY, 0, [&] {
+        k_correct_bc_scalar<<<cdiv(c->nBF, TCIF_TPB), TCIF_TPB, 0, c->stream>>>(c->dm, ba);
+        c->launches++;
+    });
     if (c->nCoupled) {
         const double *src[4]; double *dst[4];
         for (int k = 0; k < nPh; ++k) { src[k] = c->alpha[phases[k]]; dst[k] = c->alphab[phases[k]]; }

@@ -63,6 +63,8 @@ struct DMesh {
     const double *Sfx, *Sfy, *Sfz, *w;   // [Ko*stride]
     const double *V;        // [nC]
     const unsigned *bndMask;// [stride/32] bit c: cell c owns >=1 boundary face
+    const int *bndWordRank; // [stride/32] boundary-adjacent cells below cell 32*w: rank of a mask bit = index in bndCells
+    double *part;           // [partSlots*nBndCells] partial records of the boundary-adjacent cells (tcif_volume.cuh), SoA
     const int *bndCells;    // [nBndCells] ascending cell ids owning >=1 boundary face
     const int *bndCellStart;// [nBndCells+1]
     const int *bndFaces;    // boundary face ids grouped by cell, ascending
@@ -742,12 +744,15 @@ static __global__ void k_add_upwind_bnd(const __grid_constant__ DMesh m, const d
 // ------------------------------------------------------------------------------------
 // boundary evaluation, halo pack/unpack, layout conversion, reductions
 // ------------------------------------------------------------------------------------
-// vol-field correctBoundaryConditions on non-coupled patches: zeroGradient -> adjacent cell.
-static __global__ void k_correct_bc_scalar(const __grid_constant__ DMesh m, const double *vi, double *vb, const int *bc) {
+// vol-field correctBoundaryConditions on non-coupled patches: zeroGradient -> adjacent cell; all phases of a batch in one launch.
+struct BcArgs { int n; const double *vi[4]; double *vb[4]; const int *bc[4]; };
+static __global__ void k_correct_bc_scalar(const __grid_constant__ DMesh m, const __grid_constant__ BcArgs a) {
     int bf = blockIdx.x * blockDim.x + threadIdx.x;
     if (bf >= m.nBF) return;
     if (m.bfType[bf] == PATCH_PROCESSOR) return;
-    if (bc[m.bfPatch[bf]] == BC_ZERO_GRADIENT) vb[bf] = vi[m.faceCells[bf]];
+    const int fc = m.faceCells[bf], pa = m.bfPatch[bf];
+    for (int k = 0; k < a.n; ++k)
+        if (a.bc[k][pa] == BC_ZERO_GRADIENT) a.vb[k][bf] = a.vi[k][fc];
 }
 // extrapolatedCalculated patches of a result field (ncomp SoA comps, cell stride `cs`, bnd stride nBF)
 static __global__ void k_extrapolate_bnd(const __grid_constant__ DMesh m, int ncomp, size_t cs, const double *vi, double *vb) {

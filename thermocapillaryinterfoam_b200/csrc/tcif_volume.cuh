@@ -10,17 +10,22 @@
 // results stay bit-identical to the serial oracle.  Never-reused streams (Sf, w, Q+-, sums, outputs)
 // use evict-first loads/stores (__ldcs/__stcs) so that L2 keeps the arrays neighbours gather from.
 //
-// round 2: ONE kernel body per sweep.  Every kernel here takes a template flag DEF:
-//   DEF = false  the O(volume) launch: the cells without patch faces, in tile order (boundary-adjacent cells return at
-//                once: one mask word per warp).
-//   DEF = true   the O(surface) launch over DMesh::bndCells: the same body plus the patch faces (walls, wedges,
-//                processor patches with their halo values), after the cell's internal faces, in patch order -- the
-//                reference's accumulation order.  It runs AFTER the volume launch on the same stream (tcif.cu sweep()).
-// What was measured on the way (profiles/r03_variants.md): a generic-K one-thread-per-(cell, phase) twin running
-// concurrently on a high-priority stream (round 1) cost the latency/occupancy-bound volume sweeps 10-12 %; handling the
-// patch faces inline in the volume launch cost 7 % at 400^3 and 17 % on 200x400x400 sub-domains, because a CTA stays
-// resident until its one boundary lane is done; deferring every boundary-adjacent cell to a second launch that runs
-// alone is the cheapest, provided that launch is short -- hence the packed per-cell records (BndRec) below.
+// round 2: the patch faces CONTINUE the volume sweep instead of repeating it.
+//   volume launch (kv_*/kvp_*)  every cell over its internal faces, in tile order.  A boundary-adjacent cell stops
+//       after its internal faces and writes its partial accumulators (and the few own-cell values the patch faces need)
+//       into DMesh::part, a small SoA buffer indexed by the cell's rank among the boundary-adjacent cells -- a handful
+//       of stores at the end of the thread, no extra loads, no longer-lived warps.
+//   fix launch (kfix_*)  one thread per boundary-adjacent cell: reads the partials (coalesced: consecutive threads,
+//       consecutive ranks), adds the patch faces in patch order, finishes the cell.  Internal faces come before patch
+//       faces in the reference's accumulation order, so continuing from the partial sums reproduces it bit for bit.
+//       Runs after the volume launch on the same stream; the processor-patch exchange it needs hides behind the
+//       volume launch on the side stream (tcif.cu sweep()).
+// What was measured on the way (profiles/r03_variants.md, 400^3 and 200x400x400 per rank): a generic-K twin that
+// RE-COMPUTES the boundary cells concurrently on a high-priority stream (round 1) cost the latency/occupancy-bound volume
+// sweeps 10-12 %; patch faces inline in the volume launch 7-17 % (a CTA stays resident until its one boundary lane is
+// done); a re-computing twin after the volume launch 5.0 ms per stage for 1.5 % of the cells, because the cells next to
+// an x wall are one per mesh row: every one of their ~100 loads fetches its own 32-byte sector.  Continuing from the
+// partials leaves only the outputs strided.
 #pragma once
 #include "tcif_device.cuh"
 #include "tcif_alpha.cuh"      // PredBatch (kvp_pred_jacobi)
@@ -92,22 +97,22 @@ template <int TPB_> __device__ __forceinline__ CellIdx cell_of(const DMesh &m, i
     return r;
 }
 
-// The cell of this thread.  bi = index of the cell in bndCells / bndRec (deferred launch), -1 in the volume launch
-// (a compile-time constant there, so that the patch-face code is not even compiled into the volume kernels).
+// The cell of this thread in the volume launch.  bi = rank of the cell among the boundary-adjacent cells (index into
+// bndCells / bndRec / part), -1 for a cell without patch faces: from the bit mask (prefix count of the mask word +
+// popcount below the bit), so interior cells read one mask word per warp and nothing else.
 struct CellCtx { int c, cp, bi; };
-template <int TPB_, bool DEF>
+template <int TPB_>
 __device__ __forceinline__ bool pick_cell(const DMesh &m, CellCtx &x) {
-    if (DEF) {
-        const int i = blockIdx.x * TPB_ + threadIdx.x;
-        if (i >= m.nBndCells) return false;
-        x.bi = i; x.c = m.bndCells[i]; x.cp = -1;
-        return true;
-    }
     const CellIdx ci = cell_of<TPB_>(m, blockIdx.x);
     x.c = ci.c; x.cp = ci.cp; x.bi = -1;
-    return x.c < m.nC && !is_bnd_cell(m, x.c);
+    if (x.c >= m.nC) return false;
+    const int w = x.c >> 5;
+    const unsigned bit = 1u << (x.c & 31), bw = m.bndMask[w];
+    if (bw & bit) x.bi = m.bndWordRank[w] + __popc(bw & (bit - 1u));
+    return true;
 }
-#define TCIF_BI(x) (DEF ? (x).bi : -1)
+// slot j of the partial record of boundary-adjacent cell bi (SoA: the fix launch reads it coalesced)
+__device__ __forceinline__ double &part_at(const DMesh &m, int j, int bi) { return m.part[(size_t)j * m.nBndCells + bi]; }
 
 // L2 prefetch of the contiguous (own-slot) streams a later CTA will read (cp of cell_of()).  The volume
 // sweeps are bound by memory latency (ncu: long-scoreboard stalls, ~45 % occupancy), and everything a cell
@@ -126,33 +131,43 @@ template <int K> __device__ __forceinline__ void pf_geom(const DMesh &m, int cp)
     pf_l2(m.V + cp);
 }
 
-// Packed record of a boundary-adjacent cell (DMesh::bndRec): with it the patch values of a cell are ONE dependent load
-// away from its index (record -> values) instead of three (bndCellStart -> bndFaces -> bfType/bfPatch -> values), and
-// the helpers below issue all loads of the (<= 3) patch faces before the first store, so nothing serialises on a
-// possible alias.  That matters twice: the deferred launch is pure latency (one wave of threads, strided cells), and in
-// the inline mode a boundary lane keeps its whole CTA resident until it is done.
-struct BndRec { int n, bf[3], tp[3]; };
-__device__ __forceinline__ BndRec bnd_load(const DMesh &m, int bi) {
-    BndRec r;
-    r.n = 0;
-    r.bf[0] = r.bf[1] = r.bf[2] = 0; r.tp[0] = r.tp[1] = r.tp[2] = 0;
-    if (bi >= 0) {
-        const int4 a = __ldg(m.bndRec + 2 * (size_t)bi), b = __ldg(m.bndRec + 2 * (size_t)bi + 1);
-        r.n = a.x; r.bf[0] = a.y; r.bf[1] = a.z; r.bf[2] = a.w; r.tp[0] = b.x; r.tp[1] = b.y; r.tp[2] = b.z;
+// tensor of all pairs from the cell values (phaseSystem.C:1074-1096); stores Tq (pair-summed when a.tsum)
+template <int P>
+__device__ __forceinline__ void store_pair_tensors(const DMesh &m, const ForceArgs &a, int c, const double *aS, const double (*g)[3], double Tc) {
+    double Ts6[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    int q = 0;
+#pragma unroll
+    for (int p1 = 0; p1 < P; ++p1)
+#pragma unroll
+        for (int p2 = p1 + 1; p2 < P; ++p2, ++q) {
+            double T6[6];
+            double sg = sigma_eval(a.sig[q], Tc);
+            pair_tensor(aS[p1], aS[p2], g[p1], g[p2], sg, a.deltaN, T6);
+            if (a.tsum) {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) Ts6[k] += T6[k];
+            } else {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) a.Tq[(size_t)(q * 6 + k) * m.stride + c] = T6[k];
+            }
+        }
+    if (a.tsum) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) a.Tq[(size_t)k * m.stride + c] = Ts6[k];
     }
-    return r;
 }
 
 // ---- K1: grad(alpha_p) for all phases + capillary stress tensors of all pairs ---------------------
-template <int P, int K, bool DEF>
+// partial record of a boundary-adjacent cell: g[p][d] before /V (3P), alpha_p (P), 1/V, T  ->  4P + 2 slots
+template <int P, int K>
 __global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
 kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
     CellCtx x;
-    if (!pick_cell<TCIF_TPB_FORCE, DEF>(m, x)) return;
+    if (!pick_cell<TCIF_TPB_FORCE>(m, x)) return;
     const int c = x.c;
     Slots<K> s;
     s.load(m, c);
-    if (!DEF) {
+    {
         const int cp = x.cp;
         if (cp >= 0) {
             pf_slots<K>(m, cp); pf_geom<K>(m, cp);
@@ -200,87 +215,107 @@ kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArg
             }
         }
     }
-    if (TCIF_BI(x) >= 0) {                   // patch faces, in patch order (gaussGrad: boundary loop after the internal faces)
-        const BndRec r = bnd_load(m, x.bi);
-        if (r.n >= 0) {
-            double wb[3], sx[3], sy[3], sz[3], ab[3][P];
+    if (x.bi >= 0) {                         // the patch faces continue from here (kfix_grad_tensor)
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const int bf = r.bf[k];
-                wb[k] = m.wb[bf]; sx[k] = m.Sfbx[bf]; sy[k] = m.Sfby[bf]; sz[k] = m.Sfbz[bf];
+        for (int p = 0; p < P; ++p) {
 #pragma unroll
-                for (int p = 0; p < P; ++p) ab[k][p] = a.alphab[p][bf];
-            }
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                if (k < r.n) {
-                    const bool coupled = (r.tp[k] & 15) == PATCH_PROCESSOR;
-#pragma unroll
-                    for (int p = 0; p < P; ++p) {
-                        const double af = coupled ? wb[k] * aS[p] + (1.0 - wb[k]) * ab[k][p] : ab[k][p];
-                        g[p][0] += sx[k] * af; g[p][1] += sy[k] * af; g[p][2] += sz[k] * af;
-                    }
-                }
-            }
-        } else {
-            for (int j = m.bndCellStart[x.bi], e = m.bndCellStart[x.bi + 1]; j < e; ++j) {
-                const int bf = m.bndFaces[j];
-                const bool coupled = m.bfType[bf] == PATCH_PROCESSOR;
-                const double wb = m.wb[bf], sx = m.Sfbx[bf], sy = m.Sfby[bf], sz = m.Sfbz[bf];
-#pragma unroll
-                for (int p = 0; p < P; ++p) {
-                    const double ab = a.alphab[p][bf];
-                    const double af = coupled ? wb * aS[p] + (1.0 - wb) * ab : ab;
-                    g[p][0] += sx * af; g[p][1] += sy * af; g[p][2] += sz * af;
-                }
-            }
+            for (int d = 0; d < 3; ++d) part_at(m, p * 3 + d, x.bi) = g[p][d];
+            part_at(m, 3 * P + p, x.bi) = aS[p];
         }
+        part_at(m, 4 * P, x.bi) = rV; part_at(m, 4 * P + 1, x.bi) = Tc;
+        return;
     }
 #pragma unroll
     for (int p = 0; p < P; ++p) { g[p][0] = f_div(g[p][0], rV); g[p][1] = f_div(g[p][1], rV); g[p][2] = f_div(g[p][2], rV); }
-    if (TCIF_BI(x) >= 0) {                   // kept for the patch values of the tensor (kv_div_tensor)
-#pragma unroll
-        for (int p = 0; p < P; ++p)
-#pragma unroll
-            for (int d = 0; d < 3; ++d) a.gBnd[(size_t)(p * 3 + d) * m.nBndCells + x.bi] = g[p][d];
-    }
     if (a.G) {
 #pragma unroll
         for (int p = 0; p < P; ++p)
 #pragma unroll
             for (int d = 0; d < 3; ++d) a.G[(size_t)(p * 3 + d) * m.stride + c] = g[p][d];
     }
-    if (a.Tq) {
-        double Ts6[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-        int q = 0;
+    if (a.Tq) store_pair_tensors<P>(m, a, c, aS, g, Tc);
+}
+
+// Packed record of a boundary-adjacent cell (DMesh::bndRec): the patch values of a cell are ONE dependent load away from
+// its rank (record -> values) instead of three (bndCellStart -> bndFaces -> bfType/bfPatch -> values), and the helpers
+// below issue all loads of the (<= 3) patch faces before the first store, so nothing serialises on a possible alias.
+struct BndRec { int n, bf[3], tp[3]; };
+__device__ __forceinline__ BndRec bnd_load(const DMesh &m, int bi) {
+    const int4 a = __ldg(m.bndRec + 2 * (size_t)bi), b = __ldg(m.bndRec + 2 * (size_t)bi + 1);
+    BndRec r;
+    r.n = a.x; r.bf[0] = a.y; r.bf[1] = a.z; r.bf[2] = a.w; r.tp[0] = b.x; r.tp[1] = b.y; r.tp[2] = b.z;
+    return r;
+}
+
+// fix launch of K1: patch faces (gaussGrad: boundary loop after the internal faces), /V, gBnd, G, tensors
+template <int P>
+__global__ void __launch_bounds__(TCIF_TPB)
+kfix_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
+    const int bi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bi >= m.nBndCells) return;
+    const int c = m.bndCells[bi];
+    const BndRec r = bnd_load(m, bi);
+    double g[P][3], aS[P];
 #pragma unroll
-        for (int p1 = 0; p1 < P; ++p1)
+    for (int p = 0; p < P; ++p) {
 #pragma unroll
-            for (int p2 = p1 + 1; p2 < P; ++p2, ++q) {
-                double T6[6];
-                double sg = sigma_eval(a.sig[q], Tc);
-                pair_tensor(aS[p1], aS[p2], g[p1], g[p2], sg, a.deltaN, T6);
-                if (a.tsum) {
+        for (int d = 0; d < 3; ++d) g[p][d] = part_at(m, p * 3 + d, bi);
+        aS[p] = part_at(m, 3 * P + p, bi);
+    }
+    const double rV = part_at(m, 4 * P, bi), Tc = part_at(m, 4 * P + 1, bi);
+    if (r.n >= 0) {
+        double wb[3], sx[3], sy[3], sz[3], ab[3][P];
 #pragma unroll
-                    for (int k = 0; k < 6; ++k) Ts6[k] += T6[k];
-                } else {
+        for (int k = 0; k < 3; ++k) {
+            const int bf = r.bf[k];
+            wb[k] = m.wb[bf]; sx[k] = m.Sfbx[bf]; sy[k] = m.Sfby[bf]; sz[k] = m.Sfbz[bf];
 #pragma unroll
-                    for (int k = 0; k < 6; ++k) a.Tq[(size_t)(q * 6 + k) * m.stride + c] = T6[k];
+            for (int p = 0; p < P; ++p) ab[k][p] = a.alphab[p][bf];
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (k < r.n) {
+                const bool coupled = (r.tp[k] & 15) == PATCH_PROCESSOR;
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    const double af = coupled ? wb[k] * aS[p] + (1.0 - wb[k]) * ab[k][p] : ab[k][p];
+                    g[p][0] += sx[k] * af; g[p][1] += sy[k] * af; g[p][2] += sz[k] * af;
                 }
             }
-        if (a.tsum) {
+        }
+    } else {
+        for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
+            const int bf = m.bndFaces[j];
+            const bool coupled = m.bfType[bf] == PATCH_PROCESSOR;
+            const double wb = m.wb[bf], sx = m.Sfbx[bf], sy = m.Sfby[bf], sz = m.Sfbz[bf];
 #pragma unroll
-            for (int k = 0; k < 6; ++k) a.Tq[(size_t)k * m.stride + c] = Ts6[k];
+            for (int p = 0; p < P; ++p) {
+                const double ab = a.alphab[p][bf];
+                const double af = coupled ? wb * aS[p] + (1.0 - wb) * ab : ab;
+                g[p][0] += sx * af; g[p][1] += sy * af; g[p][2] += sz * af;
+            }
         }
     }
+#pragma unroll
+    for (int p = 0; p < P; ++p) { g[p][0] = f_div(g[p][0], rV); g[p][1] = f_div(g[p][1], rV); g[p][2] = f_div(g[p][2], rV); }
+#pragma unroll
+    for (int p = 0; p < P; ++p)                  // kept for the patch values of the tensor (kfix_div_tensor)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) a.gBnd[(size_t)(p * 3 + d) * m.nBndCells + bi] = g[p][d];
+    if (a.G) {
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+#pragma unroll
+            for (int d = 0; d < 3; ++d) a.G[(size_t)(p * 3 + d) * m.stride + c] = g[p][d];
+    }
+    if (a.Tq) store_pair_tensors<P>(m, a, c, aS, g, Tc);
 }
 
 // S_b . T_b over the patch faces of boundary cell bi (A.4): processor faces interpolate with the neighbour-rank
 // tensor, elsewhere T_b is the tensor expression evaluated on the patch values alpha_b, (grad alpha)_b after the
-// gaussGrad correction, sigma(T_b); pair q only, or (tsum) all pairs summed in pair order.  Kept out of line: it is
-// the rare path and must not cost the volume sweep registers.
+// gaussGrad correction, sigma(T_b); pair q only, or (tsum) all pairs summed in pair order.
 template <int P>
-__device__ __noinline__ void div_bnd_faces(const DMesh &m, const ForceArgs &a, int bi, int c, int q, const double *Ts, double *acc) {
+__device__ __forceinline__ void div_bnd_faces(const DMesh &m, const ForceArgs &a, int bi, int c, int q, const double *Ts, double *acc) {
     for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
         const int bf = m.bndFaces[j];
         const double sx = m.Sfbx[bf], sy = m.Sfby[bf], sz = m.Sfbz[bf];
@@ -331,16 +366,17 @@ __device__ __noinline__ void div_bnd_faces(const DMesh &m, const ForceArgs &a, i
 }
 
 // ---- K2: F = sum_q div(T_q) ---------------------------------------------------------------------------
-template <int P, int K, bool DEF>
+// partial record: 1/V, then per tensor q: acc[3] over the internal faces, own tensor Ts[6]  ->  1 + 9 nQ slots
+template <int P, int K>
 __global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
 kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
     constexpr int Q = P * (P - 1) / 2;
     CellCtx x;
-    if (!pick_cell<TCIF_TPB_FORCE, DEF>(m, x)) return;
+    if (!pick_cell<TCIF_TPB_FORCE>(m, x)) return;
     const int c = x.c;
     Slots<K> s;
     s.load(m, c);
-    if (!DEF) {
+    {
         const int cp = x.cp;
         if (cp >= 0) {
             pf_slots<K>(m, cp); pf_geom<K>(m, cp);
@@ -358,6 +394,7 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
     const double rV = f_rcp(m.V[c]);
     double F[3] = {0.0, 0.0, 0.0};
     const int nQ = a.tsum ? 1 : Q;
+    if (x.bi >= 0) part_at(m, 0, x.bi) = rV;
 #pragma unroll 1
     for (int q = 0; q < nQ; ++q) {
         const double *Tq = a.Tq + (size_t)q * 6 * m.stride;
@@ -378,10 +415,37 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
 #pragma unroll
         for (int k = 0; k < K; ++k)
             if (s.vO[k]) face_div_acc(wO[k], sxO[k], syO[k], szO[k], Ts, Tn[k], 1.0, acc);
-        if (TCIF_BI(x) >= 0) div_bnd_faces<P>(m, a, x.bi, c, q, Ts, acc);
+        if (x.bi >= 0) {                     // the patch faces continue from here (kfix_div_tensor)
+#pragma unroll
+            for (int d = 0; d < 3; ++d) part_at(m, 1 + 9 * q + d, x.bi) = acc[d];
+#pragma unroll
+            for (int kk = 0; kk < 6; ++kk) part_at(m, 1 + 9 * q + 3 + kk, x.bi) = Ts[kk];
+        }
         F[0] += f_div(acc[0], rV); F[1] += f_div(acc[1], rV); F[2] += f_div(acc[2], rV);
     }
     __stcs(a.F + c, F[0]); __stcs(a.F + (size_t)m.stride + c, F[1]); __stcs(a.F + (size_t)2 * m.stride + c, F[2]);
+}
+
+template <int P>
+__global__ void __launch_bounds__(TCIF_TPB)
+kfix_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
+    constexpr int Q = P * (P - 1) / 2;
+    const int bi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bi >= m.nBndCells) return;
+    const int c = m.bndCells[bi];
+    const double rV = part_at(m, 0, bi);
+    const int nQ = a.tsum ? 1 : Q;
+    double F[3] = {0.0, 0.0, 0.0};
+    for (int q = 0; q < nQ; ++q) {
+        double acc[3], Ts[6];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) acc[d] = part_at(m, 1 + 9 * q + d, bi);
+#pragma unroll
+        for (int kk = 0; kk < 6; ++kk) Ts[kk] = part_at(m, 1 + 9 * q + 3 + kk, bi);
+        div_bnd_faces<P>(m, a, bi, c, q, Ts, acc);
+        F[0] += f_div(acc[0], rV); F[1] += f_div(acc[1], rV); F[2] += f_div(acc[2], rV);
+    }
+    a.F[c] = F[0]; a.F[(size_t)m.stride + c] = F[1]; a.F[(size_t)2 * m.stride + c] = F[2];
 }
 
 // =====================================================================================================
@@ -390,71 +454,46 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
 // the two dependent memory round trips (indices -> gathers) for every phase after the first, and the
 // per-phase pointers are compile-time offsets into the kernel parameters (NPH is a template argument).
 // Arithmetic and order: SURVEY.md A.6 (see also the generic-K kernels k_mules_* in tcif_device.cuh).
+// Partial records of a boundary-adjacent cell, per phase p (slot = p*PART_* + j):
+//   set-up  : psiMaxn, psiMinn, sumPhiBD, sumPhip, mSumPhim, psi, psi0, Su, Sp            (V is read by the fix launch)
+//   iter    : sumlPhip, mSumlPhim, lambda+_C, lambda-_C, Q+, Q-, sumPhip, mSumPhim
+//   final   : sum (faces so far), lambda+_C, lambda-_C, psi0, Su, Sp                      (MODE 2; MODE 0/1: the two lambdas)
 // =====================================================================================================
+enum { PART_SETUP = 9, PART_ITER = 8, PART_FINAL = 6 };
 
-// patch faces of the set-up sweep: phiBD_b, phiCorr_b, lambda_b = 1, local extrema, sums
-__device__ __forceinline__ void bnd_setup_face(const MulesPh &ph, const MulesParams &prm, int bf, bool coupled, int kind, double psb,
-                                               double phb, double pp, double psiC, double &psiMaxn, double &psiMinn, double &sBD,
-                                               double &sP, double &sM) {
-    double bd;
-    if (coupled) {
-        const double w = phb >= 0 ? 1.0 : 0.0;
-        const double up = phb * (w * psiC + (1.0 - w) * psb);
-        if (prm.addUpwind) pp = pp + up;
-        bd = up;
-    } else {
-        if (prm.addUpwind) pp = pp + phb * psb;
-        bd = pp;                       // phiBD_b := phiPsi_b on non-coupled patches
+// finish of the set-up sweep for one cell and phase: extrema coefficients, Q+-, lambda+- of iteration 1
+__device__ __forceinline__ void setup_finish(const MulesPh &ph, const MulesParams &prm, int c, double V, double psiC, double psi0, double Su,
+                                             double Sp, double psiMaxn, double psiMinn, double sBD, double sP, double sM) {
+    psiMaxn = dmin(psiMaxn + prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMax);
+    psiMinn = dmax(psiMinn - prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMin);
+    if (prm.smoothLimiter > TCIF_SMALL) {
+        double sl = prm.smoothLimiter;
+        psiMaxn = dmin(sl * psiC + (1.0 - sl) * psiMaxn, prm.psiMax);
+        psiMinn = dmax(sl * psiC + (1.0 - sl) * psiMinn, prm.psiMin);
     }
-    const double pc = pp - bd;
-    ph.phiBDb[bf] = bd; ph.phiCorrb[bf] = pc; ph.lamb[bf] = 1.0;
-    if (coupled || kind == BC_FIXED_VALUE || prm.boundaryExtrema == 1) {
-        psiMaxn = dmax(psiMaxn, psb); psiMinn = dmin(psiMinn, psb);
-    } else {
-        psiMaxn = dmax(psiMaxn, prm.psiMax); psiMinn = dmin(psiMinn, prm.psiMin);
-    }
-    sBD += bd;
-    if (pc > 0) sP += pc; else sM -= pc;
-}
-__device__ __forceinline__ void bnd_setup(const DMesh &m, const BndRec &r, const MulesPh &ph, const MulesParams &prm, int bi, double psiC,
-                                          double &psiMaxn, double &psiMinn, double &sBD, double &sP, double &sM) {
-    if (r.n >= 0) {
-        double psb[3], phb[3], pin[3];
-        int kind[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {           // every load first (unused slots repeat face 0: in range)
-            const int bf = r.bf[k];
-            psb[k] = ph.psib[bf]; phb[k] = prm.phib[bf]; pin[k] = ph.phiInb[bf]; kind[k] = ph.bc[r.tp[k] >> 4];
-        }
-#pragma unroll
-        for (int k = 0; k < 3; ++k)
-            if (k < r.n) bnd_setup_face(ph, prm, r.bf[k], (r.tp[k] & 15) == PATCH_PROCESSOR, kind[k], psb[k], phb[k], pin[k], psiC,
-                                        psiMaxn, psiMinn, sBD, sP, sM);
-        return;
-    }
-    for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
-        const int bf = m.bndFaces[j];
-        bnd_setup_face(ph, prm, bf, m.bfType[bf] == PATCH_PROCESSOR, ph.bc[m.bfPatch[bf]], ph.psib[bf], prm.phib[bf], ph.phiInb[bf], psiC,
-                       psiMaxn, psiMinn, sBD, sP, sM);
-    }
+    double Qp = V * ((prm.rDeltaT - Sp) * psiMaxn - Su) - (V * prm.rDeltaT) * psi0 + sBD;
+    double Qm = V * (Su - (prm.rDeltaT - Sp) * psiMinn) + (V * prm.rDeltaT) * psi0 - sBD;
+    __stcs(ph.Qp + c, Qp); __stcs(ph.Qm + c, Qm); __stcs(ph.sP + c, sP); __stcs(ph.sM + c, sM);
+    // limiter iteration 1, cell pass: lambda == 1 so sumlPhip == sumPhip, mSumlPhim == mSumPhim
+    ph.lmA[c] = dmax(dmin((sP + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
+    ph.lpA[c] = dmax(dmin((sM + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
 }
 
-template <int K, int NPH, bool DEF>
-__global__ void __launch_bounds__(TCIF_TPB, DEF ? 2 : TCIF_MINB_SETUP)      // deferred launch: few threads, no spills
+template <int K, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_SETUP)
 kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                 const __grid_constant__ MulesParams prm) {
     CellCtx x;
-    if (!pick_cell<TCIF_TPB, DEF>(m, x)) return;
+    if (!pick_cell<TCIF_TPB>(m, x)) return;
     const int c = x.c;
     Slots<K> s;
     s.load(m, c);
-    const BndRec rec = bnd_load(m, TCIF_BI(x));    // in flight together with the slot indices
     double phiN[K], phiO[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) { phiN[k] = prm.phi[s.fdN[k]]; phiO[k] = __ldcs(prm.phi + k * m.stride + c); }
     const double V = m.V[c];
     const int cp = x.cp;
-    const bool pf = !DEF && cp >= 0;
+    const bool pf = cp >= 0;
     if (pf) { pf_slots<K>(m, cp); pf_face<K>(prm.phi, m.stride, cp); pf_l2(m.V + cp); }
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
@@ -505,64 +544,90 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 if (pc > 0) sP += pc; else sM -= pc;
             }
         }
-        if (TCIF_BI(x) >= 0) bnd_setup(m, rec, ph, prm, x.bi, psiC, psiMaxn, psiMinn, sBD, sP, sM);
-        psiMaxn = dmin(psiMaxn + prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMax);
-        psiMinn = dmax(psiMinn - prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMin);
-        if (prm.smoothLimiter > TCIF_SMALL) {
-            double sl = prm.smoothLimiter;
-            psiMaxn = dmin(sl * psiC + (1.0 - sl) * psiMaxn, prm.psiMax);
-            psiMinn = dmax(sl * psiC + (1.0 - sl) * psiMinn, prm.psiMin);
+        if (x.bi >= 0) {                     // the patch faces continue from here (kfix_mules_setup)
+            const int o = p * PART_SETUP;
+            part_at(m, o, x.bi) = psiMaxn; part_at(m, o + 1, x.bi) = psiMinn; part_at(m, o + 2, x.bi) = sBD;
+            part_at(m, o + 3, x.bi) = sP; part_at(m, o + 4, x.bi) = sM; part_at(m, o + 5, x.bi) = psiC;
+            part_at(m, o + 6, x.bi) = psi0; part_at(m, o + 7, x.bi) = Su; part_at(m, o + 8, x.bi) = Sp;
         }
-        double Qp = V * ((prm.rDeltaT - Sp) * psiMaxn - Su) - (V * prm.rDeltaT) * psi0 + sBD;
-        double Qm = V * (Su - (prm.rDeltaT - Sp) * psiMinn) + (V * prm.rDeltaT) * psi0 - sBD;
-        __stcs(ph.Qp + c, Qp); __stcs(ph.Qm + c, Qm); __stcs(ph.sP + c, sP); __stcs(ph.sM + c, sM);
-        // limiter iteration 1, cell pass: lambda == 1 so sumlPhip == sumPhip, mSumlPhim == mSumPhim
-        ph.lmA[c] = dmax(dmin((sP + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
-        ph.lpA[c] = dmax(dmin((sM + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
+        // (a boundary-adjacent cell gets provisional values here, overwritten by the fix launch: no divergent exit)
+        setup_finish(ph, prm, c, V, psiC, psi0, Su, Sp, psiMaxn, psiMinn, sBD, sP, sM);
     }
 }
 
-// patch faces of a limiter iteration: face rule + contribution to the next cell pass
-__device__ __forceinline__ void bnd_iter(const DMesh &m, const BndRec &r, const MulesPh &ph, int bi, double lpC, double lmC, double &slp, double &slm) {
-    if (r.n >= 0) {
-        double pc[3], la[3], bd[3], lpH[3], lmH[3];
+// patch face of the set-up sweep: phiBD_b, phiCorr_b, lambda_b = 1, local extrema, sums
+__device__ __forceinline__ void bnd_setup_face(const MulesPh &ph, const MulesParams &prm, int bf, bool coupled, int kind, double psb,
+                                               double phb, double pp, double psiC, double &psiMaxn, double &psiMinn, double &sBD,
+                                               double &sP, double &sM) {
+    double bd;
+    if (coupled) {
+        const double w = phb >= 0 ? 1.0 : 0.0;
+        const double up = phb * (w * psiC + (1.0 - w) * psb);
+        if (prm.addUpwind) pp = pp + up;
+        bd = up;
+    } else {
+        if (prm.addUpwind) pp = pp + phb * psb;
+        bd = pp;                       // phiBD_b := phiPsi_b on non-coupled patches
+    }
+    const double pc = pp - bd;
+    ph.phiBDb[bf] = bd; ph.phiCorrb[bf] = pc; ph.lamb[bf] = 1.0;
+    if (coupled || kind == BC_FIXED_VALUE || prm.boundaryExtrema == 1) {
+        psiMaxn = dmax(psiMaxn, psb); psiMinn = dmin(psiMinn, psb);
+    } else {
+        psiMaxn = dmax(psiMaxn, prm.psiMax); psiMinn = dmin(psiMinn, prm.psiMin);
+    }
+    sBD += bd;
+    if (pc > 0) sP += pc; else sM -= pc;
+}
+
+template <int NPH>
+__global__ void __launch_bounds__(TCIF_TPB)
+kfix_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, const __grid_constant__ MulesParams prm) {
+    const int bi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bi >= m.nBndCells) return;
+    const int c = m.bndCells[bi];
+    const BndRec r = bnd_load(m, bi);
+    const double V = m.V[c];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const int bf = r.bf[k];
-            pc[k] = ph.phiCorrb[bf]; la[k] = ph.lamb[bf]; bd[k] = ph.phiBDb[bf]; lpH[k] = ph.lpHalo[bf]; lmH[k] = ph.lmHalo[bf];
-        }
+    for (int p = 0; p < NPH; ++p) {
+        const MulesPh &ph = b.ph[p];
+        const int o = p * PART_SETUP;
+        double psiMaxn = part_at(m, o, bi), psiMinn = part_at(m, o + 1, bi), sBD = part_at(m, o + 2, bi), sP = part_at(m, o + 3, bi),
+               sM = part_at(m, o + 4, bi);
+        const double psiC = part_at(m, o + 5, bi), psi0 = part_at(m, o + 6, bi), Su = part_at(m, o + 7, bi), Sp = part_at(m, o + 8, bi);
+        if (r.n >= 0) {
+            double psb[3], phb[3], pin[3];
+            int kind[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            if (k < r.n) {
-                const double lam = lambda_bface(r.tp[k] & 15, la[k], pc[k], bd[k], lpC, lmC, lpH[k], lmH[k]);
-                ph.lamb[r.bf[k]] = lam;
-                const double l = lam * pc[k];
-                if (l > 0) slp += l; else slm -= l;
+            for (int k = 0; k < 3; ++k) {           // every load first (unused slots repeat face 0: in range)
+                const int bf = r.bf[k];
+                psb[k] = ph.psib[bf]; phb[k] = prm.phib[bf]; pin[k] = ph.phiInb[bf]; kind[k] = ph.bc[r.tp[k] >> 4];
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                if (k < r.n) bnd_setup_face(ph, prm, r.bf[k], (r.tp[k] & 15) == PATCH_PROCESSOR, kind[k], psb[k], phb[k], pin[k], psiC,
+                                            psiMaxn, psiMinn, sBD, sP, sM);
+        } else {
+            for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
+                const int bf = m.bndFaces[j];
+                bnd_setup_face(ph, prm, bf, m.bfType[bf] == PATCH_PROCESSOR, ph.bc[m.bfPatch[bf]], ph.psib[bf], prm.phib[bf], ph.phiInb[bf],
+                               psiC, psiMaxn, psiMinn, sBD, sP, sM);
             }
         }
-        return;
-    }
-    for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
-        const int bf = m.bndFaces[j];
-        const double pc = ph.phiCorrb[bf];
-        const double lam = lambda_bface(m.bfType[bf], ph.lamb[bf], pc, ph.phiBDb[bf], lpC, lmC, ph.lpHalo[bf], ph.lmHalo[bf]);
-        ph.lamb[bf] = lam;
-        const double l = lam * pc;
-        if (l > 0) slp += l; else slm -= l;
+        setup_finish(ph, prm, c, V, psiC, psi0, Su, Sp, psiMaxn, psiMinn, sBD, sP, sM);
     }
 }
 
-template <int K, bool FIRST, int NPH, bool DEF>
-__global__ void __launch_bounds__(TCIF_TPB, DEF ? 2 : TCIF_MINB_ITER)      // deferred launch: few threads, no spills
+template <int K, bool FIRST, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_ITER)
 kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b) {
     CellCtx x;
-    if (!pick_cell<TCIF_TPB, DEF>(m, x)) return;
+    if (!pick_cell<TCIF_TPB>(m, x)) return;
     const int c = x.c;
     Slots<K> s;
     s.load(m, c);
-    const BndRec rec = bnd_load(m, TCIF_BI(x));    // in flight together with the slot indices
     const int cp = x.cp;
-    const bool pf = !DEF && cp >= 0;
+    const bool pf = cp >= 0;
     if (pf) pf_slots<K>(m, cp);
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
@@ -603,9 +668,59 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
                 if (l > 0) slp += l; else slm -= l;
             }
         }
-        if (TCIF_BI(x) >= 0) bnd_iter(m, rec, ph, x.bi, lpC, lmC, slp, slm);
+        if (x.bi >= 0) {                     // the patch faces continue from here (kfix_mules_iter)
+            const int o = p * PART_ITER;
+            part_at(m, o, x.bi) = slp; part_at(m, o + 1, x.bi) = slm; part_at(m, o + 2, x.bi) = lpC; part_at(m, o + 3, x.bi) = lmC;
+            part_at(m, o + 4, x.bi) = Qp; part_at(m, o + 5, x.bi) = Qm; part_at(m, o + 6, x.bi) = sP; part_at(m, o + 7, x.bi) = sM;
+        }
         lmOut[c] = dmax(dmin((slp + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
         lpOut[c] = dmax(dmin((slm + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
+    }
+}
+
+// patch faces of a limiter iteration: face rule + contribution to the next cell pass
+template <int NPH>
+__global__ void __launch_bounds__(TCIF_TPB)
+kfix_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b) {
+    const int bi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bi >= m.nBndCells) return;
+    const int c = m.bndCells[bi];
+    const BndRec r = bnd_load(m, bi);
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) {
+        const MulesPh &ph = b.ph[p];
+        const int o = p * PART_ITER;
+        double slp = part_at(m, o, bi), slm = part_at(m, o + 1, bi);
+        const double lpC = part_at(m, o + 2, bi), lmC = part_at(m, o + 3, bi), Qp = part_at(m, o + 4, bi), Qm = part_at(m, o + 5, bi),
+                     sP = part_at(m, o + 6, bi), sM = part_at(m, o + 7, bi);
+        if (r.n >= 0) {
+            double pc[3], la[3], bd[3], lpH[3], lmH[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int bf = r.bf[k];
+                pc[k] = ph.phiCorrb[bf]; la[k] = ph.lamb[bf]; bd[k] = ph.phiBDb[bf]; lpH[k] = ph.lpHalo[bf]; lmH[k] = ph.lmHalo[bf];
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                if (k < r.n) {
+                    const double lam = lambda_bface(r.tp[k] & 15, la[k], pc[k], bd[k], lpC, lmC, lpH[k], lmH[k]);
+                    ph.lamb[r.bf[k]] = lam;
+                    const double l = lam * pc[k];
+                    if (l > 0) slp += l; else slm -= l;
+                }
+            }
+        } else {
+            for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
+                const int bf = m.bndFaces[j];
+                const double pc = ph.phiCorrb[bf];
+                const double lam = lambda_bface(m.bfType[bf], ph.lamb[bf], pc, ph.phiBDb[bf], lpC, lmC, ph.lpHalo[bf], ph.lmHalo[bf]);
+                ph.lamb[bf] = lam;
+                const double l = lam * pc;
+                if (l > 0) slp += l; else slm -= l;
+            }
+        }
+        ph.lmOut[c] = dmax(dmin((slp + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
+        ph.lpOut[c] = dmax(dmin((slm + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
     }
 }
 
@@ -626,57 +741,21 @@ template <int NPH> __device__ __forceinline__ void limit_sum_face(double *v) {
     }
 }
 
-// patch faces of the last face pass: lambda_b, limited patch flux, contribution to surfaceIntegrate
-template <int MODE>
-__device__ __forceinline__ void bnd_final(const DMesh &m, const BndRec &r, const MulesPh &ph, int bi, int nIter, double lpC, double lmC, double &sum) {
-    if (r.n >= 0) {
-        double pc[3], la[3], bd[3], lpH[3], lmH[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const int bf = r.bf[k];
-            pc[k] = ph.phiCorrb[bf]; la[k] = ph.lamb[bf]; bd[k] = ph.phiBDb[bf]; lpH[k] = ph.lpHalo[bf]; lmH[k] = ph.lmHalo[bf];
-        }
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            if (k < r.n) {
-                double lam = la[k];
-                if (nIter > 0) lam = lambda_bface(r.tp[k] & 15, lam, pc[k], bd[k], lpC, lmC, lpH[k], lmH[k]);
-                ph.lamb[r.bf[k]] = lam;
-                const double fl = (MODE == 0) ? pc[k] * lam : bd[k] + lam * pc[k];
-                ph.phiPsib[r.bf[k]] = fl;
-                sum += fl;
-            }
-        }
-        return;
-    }
-    for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
-        const int bf = m.bndFaces[j];
-        const double pc = ph.phiCorrb[bf], bd = ph.phiBDb[bf];
-        double lam = ph.lamb[bf];
-        if (nIter > 0) lam = lambda_bface(m.bfType[bf], lam, pc, bd, lpC, lmC, ph.lpHalo[bf], ph.lmHalo[bf]);
-        ph.lamb[bf] = lam;
-        const double fl = (MODE == 0) ? pc * lam : bd + lam * pc;
-        ph.phiPsib[bf] = fl;
-        sum += fl;
-    }
-}
-
 // MODE 0: returnCorr  -> phiPsi = lambda*phiCorr           (owner-side faces)
 // MODE 1: !returnCorr -> phiPsi = phiBD + lambda*phiCorr   (owner-side faces)
 // MODE 2: explicitSolve: MODE 1 + surfaceIntegrate + Euler update into psiNew
 // LSUM (MODE 0 only, batch = all phases): MULES::limitSum of the owner-side faces applied in registers
 // before the store, which saves the separate read-modify-write sweep over the P flux arrays.
-template <int K, int MODE, bool FIRST, int NPH, bool LSUM, bool DEF>
-__global__ void __launch_bounds__(TCIF_TPB, DEF ? 2 : TCIF_MINB_FINAL)      // deferred launch: few threads, no spills
+template <int K, int MODE, bool FIRST, int NPH, bool LSUM>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
 kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                 const __grid_constant__ MulesParams prm, int nIter) {
     static_assert(!LSUM || MODE == 0, "limitSum is fused into the returnCorr=true apply only");
     CellCtx x;
-    if (!pick_cell<TCIF_TPB, DEF>(m, x)) return;
+    if (!pick_cell<TCIF_TPB>(m, x)) return;
     const int c = x.c;
     Slots<K> s;
     s.load(m, c);
-    const BndRec rec = bnd_load(m, TCIF_BI(x));    // in flight together with the slot indices
     double phN[K], phO[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -685,7 +764,7 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
     }
     const double V = (MODE == 2) ? m.V[c] : 1.0;
     const int cp = x.cp;
-    const bool pf = !DEF && cp >= 0;
+    const bool pf = cp >= 0;
     if (pf) {
         pf_slots<K>(m, cp);
         if (MODE >= 1) pf_face<K>(prm.phi, m.stride, cp);
@@ -753,7 +832,11 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 sum += fl;
             }
         }
-        if (TCIF_BI(x) >= 0) bnd_final<MODE>(m, rec, ph, x.bi, nIter, lpC, lmC, sum);
+        if (x.bi >= 0) {                     // the patch faces continue from here (kfix_mules_final)
+            const int o = p * PART_FINAL;
+            part_at(m, o, x.bi) = sum; part_at(m, o + 1, x.bi) = lpC; part_at(m, o + 2, x.bi) = lmC;
+            if (MODE == 2) { part_at(m, o + 3, x.bi) = psi0; part_at(m, o + 4, x.bi) = Su; part_at(m, o + 5, x.bi) = Sp; }
+        }
         if (MODE == 2) {
             double d = sum / V;
             ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
@@ -767,6 +850,59 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
 #pragma unroll
                 for (int p = 0; p < NPH; ++p) b.ph[p].phiPsi[k * m.stride + c] = flAll[k][p];
             }
+        }
+    }
+}
+
+// patch faces of the last face pass: lambda_b, limited patch flux, contribution to surfaceIntegrate; Euler update (MODE 2)
+template <int MODE, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB)
+kfix_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, const __grid_constant__ MulesParams prm, int nIter) {
+    const int bi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bi >= m.nBndCells) return;
+    const int c = m.bndCells[bi];
+    const BndRec r = bnd_load(m, bi);
+    const double V = (MODE == 2) ? m.V[c] : 1.0;
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) {
+        const MulesPh &ph = b.ph[p];
+        const int o = p * PART_FINAL;
+        double sum = part_at(m, o, bi);
+        const double lpC = part_at(m, o + 1, bi), lmC = part_at(m, o + 2, bi);
+        if (r.n >= 0) {
+            double pc[3], la[3], bd[3], lpH[3], lmH[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int bf = r.bf[k];
+                pc[k] = ph.phiCorrb[bf]; la[k] = ph.lamb[bf]; bd[k] = ph.phiBDb[bf]; lpH[k] = ph.lpHalo[bf]; lmH[k] = ph.lmHalo[bf];
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                if (k < r.n) {
+                    double lam = la[k];
+                    if (nIter > 0) lam = lambda_bface(r.tp[k] & 15, lam, pc[k], bd[k], lpC, lmC, lpH[k], lmH[k]);
+                    ph.lamb[r.bf[k]] = lam;
+                    const double fl = (MODE == 0) ? pc[k] * lam : bd[k] + lam * pc[k];
+                    ph.phiPsib[r.bf[k]] = fl;
+                    sum += fl;
+                }
+            }
+        } else {
+            for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
+                const int bf = m.bndFaces[j];
+                const double pc = ph.phiCorrb[bf], bd = ph.phiBDb[bf];
+                double lam = ph.lamb[bf];
+                if (nIter > 0) lam = lambda_bface(m.bfType[bf], lam, pc, bd, lpC, lmC, ph.lpHalo[bf], ph.lmHalo[bf]);
+                ph.lamb[bf] = lam;
+                const double fl = (MODE == 0) ? pc * lam : bd + lam * pc;
+                ph.phiPsib[bf] = fl;
+                sum += fl;
+            }
+        }
+        if (MODE == 2) {
+            const double psi0 = part_at(m, o + 3, bi), Su = part_at(m, o + 4, bi), Sp = part_at(m, o + 5, bi);
+            double d = sum / V;
+            ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
         }
     }
 }
