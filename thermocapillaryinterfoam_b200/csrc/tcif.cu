@@ -56,11 +56,11 @@ inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 
 // ---- timers ---------------------------------------------------------------------------
 enum TimerId {
-    T_GRAD_TENSOR = 0, T_DIV_TENSOR, T_MULES_SETUP, T_MULES_ITER, T_MULES_FINAL, T_LIMIT_SUM,
+    T_GRAD_TENSOR = 0, T_DIV_TENSOR, T_MULES_SETUP, T_MULES_ITER, T_MULES_FINAL, T_LIMIT_SUM, T_MULES_BRIDGE,
     T_BOUNDARY, T_HALO, T_CONVERT, T_STATS, T_FLUX_ASSEMBLY, T_PREDICTOR, T_RHOPHI, T_MASS, T_LASER, T_COUNT
 };
 const char *kTimerNames[T_COUNT] = {
-    "grad_tensor", "div_tensor", "mules_setup", "mules_iter", "mules_final", "limit_sum",
+    "grad_tensor", "div_tensor", "mules_setup", "mules_iter", "mules_final", "limit_sum", "mules_bridge",
     "boundary", "halo", "convert", "stats", "flux_assembly", "predictor", "rho_phi", "alpha_transfer", "laser_dtrm"};
 
 struct EvPair { cudaEvent_t a, b; int id; double bytes; };
@@ -554,7 +554,7 @@ void alloc_fields(tcif_ctx *c) {
     c->TqHalo = c->dalloc<double>((size_t)std::max(Q, 1) * 6 * bs);
     c->F = c->dalloc<double>(3 * cs); c->Fb = c->dalloc<double>(3 * bs);
     {   // partial records of the boundary-adjacent cells: the largest of the sweeps' layouts (tcif_volume.cuh)
-        const int slots = std::max(std::max(4 * P + 2, 1 + 9 * std::max(Q, 1)), 9 * P);
+        const int slots = std::max(std::max(4 * P + 2, 1 + 9 * std::max(Q, 1)), 11 * P);
         c->dm.part = c->dalloc<double>((size_t)slots * std::max(c->nBndCells, 1));
     }
     c->stagingDoubles = std::max<size_t>(3 * cs, std::max<size_t>((size_t)std::max(c->nIF, 1), 3 * bs));
@@ -1310,12 +1310,77 @@ void do_stage(tcif_ctx *c, double deltaT) {
     do_force(c);
     do_mules_stage(c, deltaT);
 }
+// compulsory bytes of the bridge sweep (see bytes_mules_*)
+double bytes_mules_bridge(const tcif_ctx *c, int nPh, bool first) {
+    double shared = 4.0 * (c->Ko + c->Kn) + 8 /*V*/ + 8.0 * c->Ko /*phi*/;
+    double perPh = 8.0 * c->Ko * (first ? 1 : 2) /*phiCorr, lambda*/ + 16 /*lambda+- in*/ + 8 + 8 /*psi psi0*/ + 8.0 * c->Ko /*phiCorr out*/ + 48;
+    return (double)c->nC * (shared + nPh * perPh);
+}
+
+// One solveAlphas corrector restricted to MULES (the metric stage): limit(returnCorr) for all phases, limitSum,
+// explicitSolve for all phases.  On fixed-K meshes the last face pass of the first limit, limitSum and the set-up
+// sweep of explicitSolve's limit can run as ONE sweep (kvp_mules_bridge, TCIF_BRIDGE=1; measured slower: 128 registers).
 void do_mules_stage(tcif_ctx *c, double deltaT) {
     int all[4] = {0, 1, 2, 3};
-    const bool fuse = can_fuse_limit_sum(c);
-    do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true, fuse, true); // alpha.oldTime() := alpha, then multiphaseSystem.C:296-319
-    if (fuse) do_limit_sum_rest(c); else do_limit_sum(c);       // :321
-    do_explicit(c, all, c->P, deltaT, true);                    // :346 (bounded flux) + :365-375
+    static const int bridgeOn = [] { const char *e = getenv("TCIF_BRIDGE"); return e ? atoi(e) : 0; }();
+    const SweepFns *f = fns(c);
+    if (!(f && bridgeOn && c->P >= 2)) {
+        const bool fuse = can_fuse_limit_sum(c);
+        do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true, fuse, true); // alpha.oldTime() := alpha, then multiphaseSystem.C:296-319
+        if (fuse) do_limit_sum_rest(c); else do_limit_sum(c);           // :321
+        do_explicit(c, all, c->P, deltaT, true);                        // :346 (bounded flux) + :365-375
+        return;
+    }
+    require_comm(c);
+    const int nPh = c->P, L = c->cfg.nLimiterIter;
+    MulesParams prm{};
+    prm.rDeltaT = 1.0 / deltaT; prm.psiMax = 1.0; prm.psiMin = 0.0;
+    prm.extremaCoeff = c->cfg.extremaCoeff; prm.smoothLimiter = c->cfg.smoothLimiter;
+    prm.boundaryExtrema = c->cfg.boundaryExtrema;
+    prm.phi = c->phi; prm.phib = c->phib;
+    // ---- MULES::limit(..., returnCorr = true) up to its last face pass (:296-319)
+    MulesBatch b = mules_batch(c, all, nPh, true);
+    prm.addUpwind = 0; prm.storeOld = 1;
+    sweep(c, [&] { timed(c, T_MULES_SETUP, bytes_mules_setup(c, nPh, true), [&] { launch_setup<false>(c, b, prm); }); },
+             [&] { timed(c, T_BOUNDARY, 0, [&] { launch_setup<true>(c, b, prm); }); });
+    int first = 1, flip = 0;
+    for (int j = 1; j < L; ++j) {
+        sweep(c, [&] { timed(c, T_MULES_ITER, bytes_mules_iter(c, nPh, first), [&] { launch_iter<false>(c, b, first, flip); }); },
+                 [&] { halo_lambda(c, b, flip); },
+                 [&] { timed(c, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b, first, flip); }); });
+        flip ^= 1; first = 0;
+    }
+    // ---- explicitSolve: psi.correctBoundaryConditions() (:365; alpha has not changed since, the values stay)
+    correct_alpha_bcs(c, all, nPh);
+    // ---- bridge: phiAlphaCorr = lambda phiCorr, limitSum (:321), phiAlpha = phiAlphaCorr + upwind flux (:346), set-up of limit #2
+    {
+        MulesBatch br = resolve_flip(b, flip);
+        for (int k = 0; k < nPh; ++k) { br.ph[k].phiCorrOut = c->phiPsi[k]; br.ph[k].phiInb = c->phiPsib[k]; }
+        MulesParams p2 = prm;
+        p2.addUpwind = 1; p2.storeOld = 0;
+        sweep(c, [&] { timed(c, T_MULES_BRIDGE, bytes_mules_bridge(c, nPh, first), [&] { f->bridge(nPh, first != 0, false, c->stream, c->dm, br, p2, L); c->launches++; }); },
+                 [&] { if (L > 0) halo_lambda(c, b, flip); },
+                 [&] { timed(c, T_BOUNDARY, 0, [&] { if (c->nBndCells) { f->bridge(nPh, first != 0, true, c->stream, c->dm, br, p2, L); c->launches++; } }); });
+        for (int k = 0; k < nPh; ++k) std::swap(c->phiCorr[k], c->phiPsi[k]);     // the new phiCorr lives in the old phiPsi array
+    }
+    // ---- rest of limit #2 (returnCorr = false) + surfaceIntegrate + Euler update; lambda+- of iteration 1 are in the
+    //      buffer the bridge wrote (the one limit #1 was not reading)
+    MulesBatch b2 = mules_batch(c, all, nPh, false);
+    MulesParams p2 = prm;
+    p2.addUpwind = 1; p2.storeOld = 0;
+    int first2 = 1, flip2 = flip ^ 1;
+    for (int j = 1; j < L; ++j) {
+        sweep(c, [&] { timed(c, T_MULES_ITER, bytes_mules_iter(c, nPh, first2), [&] { launch_iter<false>(c, b2, first2, flip2); }); },
+                 [&] { halo_lambda(c, b2, flip2); },
+                 [&] { timed(c, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b2, first2, flip2); }); });
+        flip2 ^= 1; first2 = 0;
+    }
+    sweep(c, [&] { timed(c, T_MULES_FINAL, bytes_mules_final(c, nPh, 2, first2), [&] { launch_final<false, 2>(c, b2, p2, first2, flip2, L, false); }); },
+             [&] { if (L > 0) halo_lambda(c, b2, flip2); },
+             [&] { timed(c, T_BOUNDARY, 0, [&] { launch_final<true, 2>(c, b2, p2, first2, flip2, L, false); }); });
+    for (int k = 0; k < nPh; ++k) { std::swap(c->alpha[k], c->alphaNew[k]); alpha_changed(c, k); }
+    join(c);
+    correct_alpha_bcs(c, all, nPh);
 }
 
 // rhoPhi_ (+)= sum_p interpolate(rho_p)*alphaPhi_p   (multiphaseSystem.C:397-406, 158)

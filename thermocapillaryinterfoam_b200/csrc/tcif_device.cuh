@@ -402,6 +402,7 @@ struct MulesPh {
     double *psiNew;                     // explicit update target
     const double *lpIn, *lmIn, *lamIn;  // ping-pong resolved on the host for the current sweep (kvp_* kernels)
     double *lpOut, *lmOut, *lamOut;
+    double *phiCorrOut;                 // bridge sweep: where the NEW phiCorr goes (the phiPsi array; swapped by the host afterwards)
 };
 struct MulesBatch { int nPh; MulesPh ph[4]; };
 struct MulesParams {
@@ -656,28 +657,6 @@ static __global__ void __launch_bounds__(TCIF_TPB)
 k_limit_sum(int n, const __grid_constant__ LimitSumArgs a) {
     int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= n) return;
-    double v[4], sumPos = 0.0, sumNeg = 0.0;
-    for (int p = 0; p < a.nPh; ++p) {
-        v[p] = a.f[p][f];
-        if (v[p] > 0) sumPos += v[p]; else sumNeg += v[p];
-    }
-    double sum = sumPos + sumNeg;
-    if (sum > 0 && sumPos > TCIF_VSMALL) {
-        double lambda = -sumNeg / sumPos;
-        for (int p = 0; p < a.nPh; ++p) if (v[p] > 0) a.f[p][f] = v[p] * lambda;
-    } else if (sum < 0 && sumNeg < -TCIF_VSMALL) {
-        double lambda = -sumPos / sumNeg;
-        for (int p = 0; p < a.nPh; ++p) if (v[p] < 0) a.f[p][f] = v[p] * lambda;
-    }
-}
-// same on the owner-side faces of the boundary-adjacent cells only (the volume sweep fused the rest)
-static __global__ void __launch_bounds__(TCIF_TPB)
-k_limit_sum_bndcells(const __grid_constant__ DMesh m, const __grid_constant__ LimitSumArgs a) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m.nBndCells * m.Ko) return;
-    int cell = m.bndCells[i / m.Ko], k = i % m.Ko;
-    size_t f = (size_t)k * m.stride + cell;
-    if (m.nbrOwn[f] < 0) return;
     double v[4], sumPos = 0.0, sumNeg = 0.0;
     for (int p = 0; p < a.nPh; ++p) {
         v[p] = a.f[p][f];

@@ -97,19 +97,22 @@ template <int TPB_> __device__ __forceinline__ CellIdx cell_of(const DMesh &m, i
     return r;
 }
 
-// The cell of this thread in the volume launch.  bi = rank of the cell among the boundary-adjacent cells (index into
-// bndCells / bndRec / part), -1 for a cell without patch faces: from the bit mask (prefix count of the mask word +
-// popcount below the bit), so interior cells read one mask word per warp and nothing else.
-struct CellCtx { int c, cp, bi; };
+// Rank of cell c among the boundary-adjacent cells (index into bndCells / bndRec / part), -1 for a cell without patch
+// faces: from the bit mask (prefix count of the mask word + popcount below the bit), so interior cells read one mask
+// word per warp and nothing else.  Evaluated where it is needed (the end of a thread) rather than kept in a register
+// across the sweep: the mask word is in L1 by then and the volume kernels are register-starved.
+__device__ __forceinline__ int bnd_rank(const DMesh &m, int c) {
+    const int w = c >> 5;
+    const unsigned bit = 1u << (c & 31), bw = m.bndMask[w];
+    return (bw & bit) ? m.bndWordRank[w] + __popc(bw & (bit - 1u)) : -1;
+}
+// The cell of this thread in the volume launch (every cell: boundary-adjacent ones stop after their internal faces).
+struct CellCtx { int c, cp; };
 template <int TPB_>
 __device__ __forceinline__ bool pick_cell(const DMesh &m, CellCtx &x) {
     const CellIdx ci = cell_of<TPB_>(m, blockIdx.x);
-    x.c = ci.c; x.cp = ci.cp; x.bi = -1;
-    if (x.c >= m.nC) return false;
-    const int w = x.c >> 5;
-    const unsigned bit = 1u << (x.c & 31), bw = m.bndMask[w];
-    if (bw & bit) x.bi = m.bndWordRank[w] + __popc(bw & (bit - 1u));
-    return true;
+    x.c = ci.c; x.cp = ci.cp;
+    return x.c < m.nC;
 }
 // slot j of the partial record of boundary-adjacent cell bi (SoA: the fix launch reads it coalesced)
 __device__ __forceinline__ double &part_at(const DMesh &m, int j, int bi) { return m.part[(size_t)j * m.nBndCells + bi]; }
@@ -215,14 +218,15 @@ kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArg
             }
         }
     }
-    if (x.bi >= 0) {                         // the patch faces continue from here (kfix_grad_tensor)
+    const int bi = bnd_rank(m, c);
+    if (bi >= 0) {                           // the patch faces continue from here (kfix_grad_tensor)
 #pragma unroll
         for (int p = 0; p < P; ++p) {
 #pragma unroll
-            for (int d = 0; d < 3; ++d) part_at(m, p * 3 + d, x.bi) = g[p][d];
-            part_at(m, 3 * P + p, x.bi) = aS[p];
+            for (int d = 0; d < 3; ++d) part_at(m, p * 3 + d, bi) = g[p][d];
+            part_at(m, 3 * P + p, bi) = aS[p];
         }
-        part_at(m, 4 * P, x.bi) = rV; part_at(m, 4 * P + 1, x.bi) = Tc;
+        part_at(m, 4 * P, bi) = rV; part_at(m, 4 * P + 1, bi) = Tc;
         return;
     }
 #pragma unroll
@@ -394,7 +398,6 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
     const double rV = f_rcp(m.V[c]);
     double F[3] = {0.0, 0.0, 0.0};
     const int nQ = a.tsum ? 1 : Q;
-    if (x.bi >= 0) part_at(m, 0, x.bi) = rV;
 #pragma unroll 1
     for (int q = 0; q < nQ; ++q) {
         const double *Tq = a.Tq + (size_t)q * 6 * m.stride;
@@ -415,11 +418,13 @@ kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs
 #pragma unroll
         for (int k = 0; k < K; ++k)
             if (s.vO[k]) face_div_acc(wO[k], sxO[k], syO[k], szO[k], Ts, Tn[k], 1.0, acc);
-        if (x.bi >= 0) {                     // the patch faces continue from here (kfix_div_tensor)
+        const int bi = bnd_rank(m, c);
+        if (bi >= 0) {                       // the patch faces continue from here (kfix_div_tensor)
+            part_at(m, 0, bi) = rV;
 #pragma unroll
-            for (int d = 0; d < 3; ++d) part_at(m, 1 + 9 * q + d, x.bi) = acc[d];
+            for (int d = 0; d < 3; ++d) part_at(m, 1 + 9 * q + d, bi) = acc[d];
 #pragma unroll
-            for (int kk = 0; kk < 6; ++kk) part_at(m, 1 + 9 * q + 3 + kk, x.bi) = Ts[kk];
+            for (int kk = 0; kk < 6; ++kk) part_at(m, 1 + 9 * q + 3 + kk, bi) = Ts[kk];
         }
         F[0] += f_div(acc[0], rV); F[1] += f_div(acc[1], rV); F[2] += f_div(acc[2], rV);
     }
@@ -463,7 +468,8 @@ enum { PART_SETUP = 9, PART_ITER = 8, PART_FINAL = 6 };
 
 // finish of the set-up sweep for one cell and phase: extrema coefficients, Q+-, lambda+- of iteration 1
 __device__ __forceinline__ void setup_finish(const MulesPh &ph, const MulesParams &prm, int c, double V, double psiC, double psi0, double Su,
-                                             double Sp, double psiMaxn, double psiMinn, double sBD, double sP, double sM) {
+                                             double Sp, double psiMaxn, double psiMinn, double sBD, double sP, double sM,
+                                             double *lpDst, double *lmDst) {
     psiMaxn = dmin(psiMaxn + prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMax);
     psiMinn = dmax(psiMinn - prm.extremaCoeff * (prm.psiMax - prm.psiMin), prm.psiMin);
     if (prm.smoothLimiter > TCIF_SMALL) {
@@ -475,8 +481,8 @@ __device__ __forceinline__ void setup_finish(const MulesPh &ph, const MulesParam
     double Qm = V * (Su - (prm.rDeltaT - Sp) * psiMinn) + (V * prm.rDeltaT) * psi0 - sBD;
     __stcs(ph.Qp + c, Qp); __stcs(ph.Qm + c, Qm); __stcs(ph.sP + c, sP); __stcs(ph.sM + c, sM);
     // limiter iteration 1, cell pass: lambda == 1 so sumlPhip == sumPhip, mSumlPhim == mSumPhim
-    ph.lmA[c] = dmax(dmin((sP + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
-    ph.lpA[c] = dmax(dmin((sM + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
+    lmDst[c] = dmax(dmin((sP + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
+    lpDst[c] = dmax(dmin((sM + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
 }
 
 template <int K, int NPH>
@@ -544,14 +550,15 @@ kvp_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 if (pc > 0) sP += pc; else sM -= pc;
             }
         }
-        if (x.bi >= 0) {                     // the patch faces continue from here (kfix_mules_setup)
+        const int bi = bnd_rank(m, c);
+        if (bi >= 0) {                       // the patch faces continue from here (kfix_mules_setup)
             const int o = p * PART_SETUP;
-            part_at(m, o, x.bi) = psiMaxn; part_at(m, o + 1, x.bi) = psiMinn; part_at(m, o + 2, x.bi) = sBD;
-            part_at(m, o + 3, x.bi) = sP; part_at(m, o + 4, x.bi) = sM; part_at(m, o + 5, x.bi) = psiC;
-            part_at(m, o + 6, x.bi) = psi0; part_at(m, o + 7, x.bi) = Su; part_at(m, o + 8, x.bi) = Sp;
+            part_at(m, o, bi) = psiMaxn; part_at(m, o + 1, bi) = psiMinn; part_at(m, o + 2, bi) = sBD;
+            part_at(m, o + 3, bi) = sP; part_at(m, o + 4, bi) = sM; part_at(m, o + 5, bi) = psiC;
+            part_at(m, o + 6, bi) = psi0; part_at(m, o + 7, bi) = Su; part_at(m, o + 8, bi) = Sp;
         }
         // (a boundary-adjacent cell gets provisional values here, overwritten by the fix launch: no divergent exit)
-        setup_finish(ph, prm, c, V, psiC, psi0, Su, Sp, psiMaxn, psiMinn, sBD, sP, sM);
+        setup_finish(ph, prm, c, V, psiC, psi0, Su, Sp, psiMaxn, psiMinn, sBD, sP, sM, ph.lpA, ph.lmA);
     }
 }
 
@@ -614,7 +621,7 @@ kfix_mules_setup(const __grid_constant__ DMesh m, const __grid_constant__ MulesB
                                psiC, psiMaxn, psiMinn, sBD, sP, sM);
             }
         }
-        setup_finish(ph, prm, c, V, psiC, psi0, Su, Sp, psiMaxn, psiMinn, sBD, sP, sM);
+        setup_finish(ph, prm, c, V, psiC, psi0, Su, Sp, psiMaxn, psiMinn, sBD, sP, sM, ph.lpA, ph.lmA);
     }
 }
 
@@ -668,10 +675,11 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
                 if (l > 0) slp += l; else slm -= l;
             }
         }
-        if (x.bi >= 0) {                     // the patch faces continue from here (kfix_mules_iter)
+        const int bi = bnd_rank(m, c);
+        if (bi >= 0) {                       // the patch faces continue from here (kfix_mules_iter)
             const int o = p * PART_ITER;
-            part_at(m, o, x.bi) = slp; part_at(m, o + 1, x.bi) = slm; part_at(m, o + 2, x.bi) = lpC; part_at(m, o + 3, x.bi) = lmC;
-            part_at(m, o + 4, x.bi) = Qp; part_at(m, o + 5, x.bi) = Qm; part_at(m, o + 6, x.bi) = sP; part_at(m, o + 7, x.bi) = sM;
+            part_at(m, o, bi) = slp; part_at(m, o + 1, bi) = slm; part_at(m, o + 2, bi) = lpC; part_at(m, o + 3, bi) = lmC;
+            part_at(m, o + 4, bi) = Qp; part_at(m, o + 5, bi) = Qm; part_at(m, o + 6, bi) = sP; part_at(m, o + 7, bi) = sM;
         }
         lmOut[c] = dmax(dmin((slp + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
         lpOut[c] = dmax(dmin((slm + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
@@ -832,10 +840,11 @@ kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 sum += fl;
             }
         }
-        if (x.bi >= 0) {                     // the patch faces continue from here (kfix_mules_final)
+        const int bi = bnd_rank(m, c);
+        if (bi >= 0) {                       // the patch faces continue from here (kfix_mules_final)
             const int o = p * PART_FINAL;
-            part_at(m, o, x.bi) = sum; part_at(m, o + 1, x.bi) = lpC; part_at(m, o + 2, x.bi) = lmC;
-            if (MODE == 2) { part_at(m, o + 3, x.bi) = psi0; part_at(m, o + 4, x.bi) = Su; part_at(m, o + 5, x.bi) = Sp; }
+            part_at(m, o, bi) = sum; part_at(m, o + 1, bi) = lpC; part_at(m, o + 2, bi) = lmC;
+            if (MODE == 2) { part_at(m, o + 3, bi) = psi0; part_at(m, o + 4, bi) = Su; part_at(m, o + 5, bi) = Sp; }
         }
         if (MODE == 2) {
             double d = sum / V;
@@ -904,6 +913,167 @@ kfix_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesB
             double d = sum / V;
             ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
         }
+    }
+}
+
+
+// ---- bridge: last face pass of limit(returnCorr = true) + limitSum + set-up sweep of explicitSolve's limit ------------
+// multiphaseSystem.C:305-321 ends with phiAlphaCorr_p := lambda_p phiCorr_p followed by MULES::limitSum over the phases;
+// :346-375 starts with phiAlpha_p = phiAlphaCorr_p + upwind flux and MULES::limit's set-up.  Unfused, the limited
+// corrections cross HBM twice (written by the apply sweep, read back on both sides of every face by the set-up sweep);
+// here a cell re-derives them for ALL its faces in registers -- the neighbour-side ones redundantly, from exactly the
+// values the owner thread uses, so the bits agree -- applies limitSum per face and goes straight on to the set-up sums.
+// The new phiCorr goes to phiCorrOut (the phiPsi array, free at this point: the host swaps the two afterwards) because
+// neighbours still read the old one; lambda+- of iteration 1 go to the ping-pong buffer that is not being read.
+// Partial record of a boundary-adjacent cell, per phase: lambda+_C, lambda-_C, then the nine set-up slots.
+#ifndef TCIF_MINB_BRIDGE
+#define TCIF_MINB_BRIDGE 2
+#endif
+enum { PART_BRIDGE = 2 + PART_SETUP };
+template <int K, bool FIRST, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_BRIDGE)
+kvp_mules_bridge(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, const __grid_constant__ MulesParams prm, int nIter) {
+    CellCtx x;
+    if (!pick_cell<TCIF_TPB>(m, x)) return;
+    const int c = x.c;
+    Slots<K> s;
+    s.load(m, c);
+    const int cp = x.cp;
+    const bool pf = cp >= 0;
+    if (pf) { pf_slots<K>(m, cp); pf_face<K>(prm.phi, m.stride, cp); pf_l2(m.V + cp); }
+    double fl[2 * K][NPH];                       // limited corrections: [0, K) neighbour-side faces, [K, 2K) owner-side faces
+    double lpCs[NPH], lmCs[NPH];
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) {
+        const MulesPh &ph = b.ph[p];
+        const double *lpIn = ph.lpIn, *lmIn = ph.lmIn, *lamIn = ph.lamIn;
+        if (pf) {
+            pf_face<K>(ph.phiCorr, m.stride, cp);
+            if (!FIRST) pf_face<K>(lamIn, m.stride, cp);
+            pf_l2_keep(lpIn + cp); pf_l2_keep(lmIn + cp); pf_l2_keep(ph.psi + cp); pf_l2(ph.psi0 + cp);
+            if (ph.Su) pf_l2(ph.Su + cp);
+            if (ph.Sp) pf_l2(ph.Sp + cp);
+        }
+        const double lpC = ld_keep(lpIn + c), lmC = ld_keep(lmIn + c);
+        lpCs[p] = lpC; lmCs[p] = lmC;
+        double pcN[K], laN[K], lpO[K], lmO[K], pcO[K], laO[K], lpN[K], lmN[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int fo = k * m.stride + c;
+            pcN[k] = ph.phiCorr[s.fdN[k]]; laN[k] = FIRST ? 1.0 : lamIn[s.fdN[k]];
+            lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
+            pcO[k] = ld_keep(ph.phiCorr + fo); laO[k] = FIRST ? 1.0 : ld_keep(lamIn + fo);
+            lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            double lam = laN[k];
+            if (nIter > 0) lam = lambda_face(lam, pcN[k], lpO[k], lmO[k], lpC, lmC);
+            fl[k][p] = pcN[k] * lam;
+            lam = laO[k];
+            if (nIter > 0) lam = lambda_face(lam, pcO[k], lpC, lmC, lpN[k], lmN[k]);
+            fl[K + k][p] = pcO[k] * lam;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {                // MULES::limitSum, face by face, all phases in registers
+        if (s.vN[k]) limit_sum_face<NPH>(fl[k]);
+        if (s.vO[k]) limit_sum_face<NPH>(fl[K + k]);
+    }
+    double phiN[K], phiO[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) { phiN[k] = prm.phi[s.fdN[k]]; phiO[k] = __ldcs(prm.phi + k * m.stride + c); }
+    const double V = m.V[c];
+    const int bi = bnd_rank(m, c);
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) {
+        const MulesPh &ph = b.ph[p];
+        const double psiC = ld_keep(ph.psi + c);
+        double psiO[K], psiN[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) { psiO[k] = ph.psi[s.oN[k]]; psiN[k] = ph.psi[s.nO[k]]; }
+        const double psi0 = __ldcs(ph.psi0 + c);
+        const double Su = ph.Su ? __ldcs(ph.Su + c) : 0.0, Sp = ph.Sp ? __ldcs(ph.Sp + c) : 0.0;
+        double psiMaxn = prm.psiMin, psiMinn = prm.psiMax, sBD = 0.0, sP = 0.0, sM = 0.0;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (s.vN[k]) {
+                double bd = upwind_flux(phiN[k], psiO[k], psiC);
+                double pp = fl[k][p];
+                if (prm.addUpwind) pp = pp + bd;
+                double pc = pp - bd;
+                psiMaxn = dmax(psiMaxn, psiO[k]); psiMinn = dmin(psiMinn, psiO[k]);
+                sBD -= bd;
+                if (pc > 0) sM += pc; else sP -= pc;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (s.vO[k]) {
+                double bd = upwind_flux(phiO[k], psiC, psiN[k]);
+                double pp = fl[K + k][p];
+                if (prm.addUpwind) pp = pp + bd;
+                double pc = pp - bd;
+                ph.phiCorrOut[k * m.stride + c] = pc;
+                psiMaxn = dmax(psiMaxn, psiN[k]); psiMinn = dmin(psiMinn, psiN[k]);
+                sBD += bd;
+                if (pc > 0) sP += pc; else sM -= pc;
+            }
+        }
+        if (bi >= 0) {                           // the patch faces continue from here (kfix_mules_bridge)
+            const int o = p * PART_BRIDGE;
+            part_at(m, o, bi) = lpCs[p]; part_at(m, o + 1, bi) = lmCs[p];
+            part_at(m, o + 2, bi) = psiMaxn; part_at(m, o + 3, bi) = psiMinn; part_at(m, o + 4, bi) = sBD;
+            part_at(m, o + 5, bi) = sP; part_at(m, o + 6, bi) = sM; part_at(m, o + 7, bi) = psiC;
+            part_at(m, o + 8, bi) = psi0; part_at(m, o + 9, bi) = Su; part_at(m, o + 10, bi) = Sp;
+        }
+        setup_finish(ph, prm, c, V, psiC, psi0, Su, Sp, psiMaxn, psiMinn, sBD, sP, sM, ph.lpOut, ph.lmOut);
+    }
+}
+
+// patch faces of the bridge: last face rule -> limited patch correction, limitSum on processor faces (MULES::limitSum
+// acts on internal faces and coupled patches only), then the set-up face work with that correction as the input flux
+template <int NPH>
+__global__ void __launch_bounds__(TCIF_TPB)
+kfix_mules_bridge(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, const __grid_constant__ MulesParams prm, int nIter) {
+    const int bi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bi >= m.nBndCells) return;
+    const int c = m.bndCells[bi];
+    const double V = m.V[c];
+    const int j0 = m.bndCellStart[bi], j1 = m.bndCellStart[bi + 1];
+    double acc[NPH][5];                          // psiMaxn, psiMinn, sBD, sP, sM per phase
+#pragma unroll
+    for (int p = 0; p < NPH; ++p)
+#pragma unroll
+        for (int q = 0; q < 5; ++q) acc[p][q] = part_at(m, p * PART_BRIDGE + 2 + q, bi);
+    for (int j = j0; j < j1; ++j) {
+        const int bf = m.bndFaces[j], tp = m.bfType[bf], pa = m.bfPatch[bf];
+        const bool coupled = tp == PATCH_PROCESSOR;
+        const double phb = prm.phib[bf];
+        double flb[NPH];
+#pragma unroll
+        for (int p = 0; p < NPH; ++p) {
+            const MulesPh &ph = b.ph[p];
+            const double pc = ph.phiCorrb[bf], bd = ph.phiBDb[bf];
+            double lam = ph.lamb[bf];
+            if (nIter > 0) lam = lambda_bface(tp, lam, pc, bd, part_at(m, p * PART_BRIDGE, bi), part_at(m, p * PART_BRIDGE + 1, bi),
+                                              ph.lpHalo[bf], ph.lmHalo[bf]);
+            flb[p] = pc * lam;
+        }
+        if (coupled) limit_sum_face<NPH>(flb);
+#pragma unroll
+        for (int p = 0; p < NPH; ++p) {
+            const MulesPh &ph = b.ph[p];
+            bnd_setup_face(ph, prm, bf, coupled, ph.bc[pa], ph.psib[bf], phb, flb[p], part_at(m, p * PART_BRIDGE + 7, bi),
+                           acc[p][0], acc[p][1], acc[p][2], acc[p][3], acc[p][4]);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) {
+        const MulesPh &ph = b.ph[p];
+        const int o = p * PART_BRIDGE;
+        setup_finish(ph, prm, c, V, part_at(m, o + 7, bi), part_at(m, o + 8, bi), part_at(m, o + 9, bi), part_at(m, o + 10, bi),
+                     acc[p][0], acc[p][1], acc[p][2], acc[p][3], acc[p][4], ph.lpOut, ph.lmOut);
     }
 }
 
