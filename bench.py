@@ -431,8 +431,9 @@ def run_ours(args, rank, world, local_rank):
                "h2d_bytes_per_step": int(sum_over_ranks(moved[0])), "d2h_bytes_per_step": int(sum_over_ranks(moved[1])),
                "dense_h2d_bytes_per_step": int(sum_over_ranks(h2d)), "dense_d2h_bytes_per_step": int(sum_over_ranks(d2h)),
                "steps": args.e2e_steps, "ms_per_step": 1e3 * e2e_s / args.e2e_steps,
-               "api": "tcif_stage_host: H2D T,phi,phiAlphaCorr[P] (+alpha[P] in the first step only: stamps); D2H alphaPhi[P] dense, "
-                      "F and alpha[P] as deltas; pinned host buffers, uploads/compute/downloads pipelined; bytes = last step, as copied"}
+               "api": "tcif_stage_host: H2D T,phi,phiAlphaCorr[P] (+alpha[P] in the first step only: stamps); D2H alphaPhi[P], F and alpha[P] as "
+                      "deltas against what the same host arrays received last (dense when more than 1/4 changed); pinned host buffers, "
+                      "uploads/compute/downloads pipelined; bytes = last step, as copied"}
         # (2) the reference's own call surface: fluid.solve() (flux assembly + implicit predictor + MULES + rhoPhi,
         #     all on the device) then fluid.divCapillaryStress(): more work per step, fewer bytes over PCIe
         ctx.set_cell_centres(np.asarray(f["C"]), np.asarray(f["deltab"]))
@@ -477,6 +478,30 @@ def run_ours(args, rank, world, local_rank):
                                             "ms_per_step": sm / args.e2e_steps,
                                             "what": "tcif_solve_alphas + tcif_div_capillary_stress on resident fields",
                                             "per_kernel_ms_per_step": {k: v["ms"] / args.e2e_steps for k, v in st.items() if v["launches"]}}
+        # what the host link of this box gives each rank when ALL ranks copy at once (the e2e numbers above are mostly
+        # this): pinned 256 MB each way, CUDA events, slowest rank and the sum over ranks
+        probe_n = 32 << 20
+        hbuf = abi.pinned_empty((probe_n,)); hbuf[...] = 1.0
+        dbuf = torch.empty(probe_n, dtype=torch.float64, device=dev)
+        hten = torch.from_numpy(hbuf)
+        gbs = []
+        for direction in ("h2d", "d2h"):
+            with torch.cuda.stream(stream):
+                ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                for it in range(3):
+                    if it == 1:
+                        barrier(); ev0.record(stream)
+                    if direction == "h2d":
+                        dbuf.copy_(hten, non_blocking=True)
+                    else:
+                        hten.copy_(dbuf, non_blocking=True)
+                ev1.record(stream)
+                barrier()
+                gbs.append(2 * 8 * probe_n / (ev0.elapsed_time(ev1) * 1e-3) / 1e9)
+        extra["host_link_probe"] = {"what": "256 MB pinned copies, all ranks at once (torch copy_, CUDA events)",
+                                    "h2d_gbs_slowest_rank": -max_over_ranks(-gbs[0]), "h2d_gbs_sum": sum_over_ranks(gbs[0]),
+                                    "d2h_gbs_slowest_rank": -max_over_ranks(-gbs[1]), "d2h_gbs_sum": sum_over_ranks(gbs[1])}
+        del hten, hbuf, dbuf
         del ai, ab, pi, pb, pi0, pb0, Ti, Tb, phii, phib, Fi, Fb, rpi, rpb
 
     stats = [ctx.alpha_stats(p) for p in range(P)]

@@ -56,11 +56,11 @@ inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 
 // ---- timers ---------------------------------------------------------------------------
 enum TimerId {
-    T_GRAD_TENSOR = 0, T_DIV_TENSOR, T_MULES_SETUP, T_MULES_ITER, T_MULES_FINAL, T_LIMIT_SUM, T_MULES_BRIDGE,
+    T_GRAD_TENSOR = 0, T_DIV_TENSOR, T_MULES_SETUP, T_MULES_ITER, T_MULES_FINAL, T_LIMIT_SUM,
     T_BOUNDARY, T_HALO, T_CONVERT, T_STATS, T_FLUX_ASSEMBLY, T_PREDICTOR, T_RHOPHI, T_MASS, T_LASER, T_COUNT
 };
 const char *kTimerNames[T_COUNT] = {
-    "grad_tensor", "div_tensor", "mules_setup", "mules_iter", "mules_final", "limit_sum", "mules_bridge",
+    "grad_tensor", "div_tensor", "mules_setup", "mules_iter", "mules_final", "limit_sum",
     "boundary", "halo", "convert", "stats", "flux_assembly", "predictor", "rho_phi", "alpha_transfer", "laser_dtrm"};
 
 struct EvPair { cudaEvent_t a, b; int id; double bytes; };
@@ -150,6 +150,7 @@ struct tcif_ctx {
     double sumV = 0.0;
     DMesh dm{};
     int tileStrips = 0;      // 1: volume sweeps walk the tiles strip by strip (build_tile_order)
+    const int *forceOrder = nullptr;   // tile order of the two force sweeps (TCIF_FORCE_STRIP_CELLS)
     int tsum = 0;            // force kernels carry the pair-summed stress tensor (6 comps) instead of Q tensors
     int *d_faceMap = nullptr;           // host face f -> device slot
     std::vector<void *> allocs;
@@ -368,8 +369,8 @@ void timers_collect(tcif_ctx *c) {
 // +-z neighbours, which at 400^3 is more than L2 holds across all streams of a sweep; walking the mesh in
 // strips of H rows (all planes of strip 0, then strip 1, ...) shortens it to a*H cells at the price of one
 // extra row fetch per strip edge.  Returns empty (= ascending) when no such structure is found, when one
-// plane is small enough for L2 anyway (< 64 K cells), or with TCIF_TILE_ORDER=0.  TCIF_STRIP_CELLS sets a*H (default 16384).
-std::vector<int> build_tile_order(int nC, int stride, int Ko, const std::vector<int> &nbrOwn) {
+// plane is small enough for L2 anyway (< 64 K cells), or with TCIF_TILE_ORDER=0.  stripCells = a*H (TCIF_STRIP_CELLS, default 16384, for the MULES sweeps; TCIF_FORCE_STRIP_CELLS for the force sweeps).
+std::vector<int> build_tile_order(int nC, int stride, int Ko, const std::vector<int> &nbrOwn, long long stripCells) {
     const char *e = getenv("TCIF_TILE_ORDER");
     const int mode = e ? atoi(e) : 1;                  // 0 off, 1 auto, 2 force (also on small meshes)
     if (mode == 0 || Ko < 3) return {};
@@ -391,8 +392,8 @@ std::vector<int> build_tile_order(int nC, int stride, int Ko, const std::vector<
     if (a < 2 || b <= a || b % a != 0) return {};
     if (mode == 1 && b * 512 < (32 << 20)) return {};  // a plane of all streams of a sweep (~0.5 KB/cell) fits in L2 anyway
     const long long R = b / a;                         // rows per plane
-    const char *sc = getenv("TCIF_STRIP_CELLS");
-    long long H = std::max<long long>(2, (sc ? atoll(sc) : 16384) / a);
+    if (stripCells <= 0) return {};
+    long long H = std::max<long long>(2, stripCells / a);
     if (H >= R) return {};
     const long long nStrips = (R + H - 1) / H;
     H = (R + nStrips - 1) / nStrips;                   // even strips
@@ -442,9 +443,13 @@ void build_mesh(tcif_ctx *c, const tcif_mesh_desc *m) {
     { const char *e = getenv("TCIF_PF_AHEAD"); d.pfTiles = (e ? atoi(e) : 148 * 256) / 256; }   // one CTA per SM ahead (profiles/r02_variants.md)
     d.nTiles = cdiv(nC, 256);
     {
-        std::vector<int> order = build_tile_order(nC, stride, Ko, nbrOwn);
+        const char *sc = getenv("TCIF_STRIP_CELLS"), *fc = getenv("TCIF_FORCE_STRIP_CELLS");
+        std::vector<int> order = build_tile_order(nC, stride, Ko, nbrOwn, sc ? atoll(sc) : 16384);
         d.tileOrder = order.empty() ? nullptr : c->upload(order);
         c->tileStrips = order.empty() ? 0 : 1;
+        // the two force sweeps gather fewer arrays per cell: their own strip size (0 = ascending order)
+        std::vector<int> forder = build_tile_order(nC, stride, Ko, nbrOwn, fc ? atoll(fc) : 0);
+        c->forceOrder = forder.empty() ? nullptr : c->upload(forder);
     }
     d.nC = nC; d.stride = stride; d.Ko = Ko; d.Kn = Kn; d.nFd = (int)c->nFd; d.nBF = nBF; d.nPatches = nP;
     d.nbrOwn = c->upload(nbrOwn); d.neiFace = c->upload(neiFace);
@@ -541,7 +546,8 @@ void alloc_fields(tcif_ctx *c) {
         c->phiHO[p] = c->dalloc<double>(fs); c->phiHOb[p] = c->dalloc<double>(bs);
         c->phiPsi[p] = c->dalloc<double>(fs); c->phiPsib[p] = c->dalloc<double>(bs);
         c->phiCorr[p] = c->dalloc<double>(fs); c->phiCorrb[p] = c->dalloc<double>(bs); c->phiBDb[p] = c->dalloc<double>(bs);
-        c->Qp[p] = c->dalloc<double>(cs); c->Qm[p] = c->dalloc<double>(cs); c->sP[p] = c->dalloc<double>(cs); c->sM[p] = c->dalloc<double>(cs);
+        c->Qp[p] = c->dalloc<double>(cs); c->Qm[p] = c->dalloc<double>(cs);
+        if (c->Ko != c->Kn || c->Ko < 2 || c->Ko > 4) { c->sP[p] = c->dalloc<double>(cs); c->sM[p] = c->dalloc<double>(cs); }   // generic-K kernels only
         c->lpA[p] = c->dalloc<double>(cs); c->lmA[p] = c->dalloc<double>(cs); c->lpB[p] = c->dalloc<double>(cs); c->lmB[p] = c->dalloc<double>(cs);
         c->lamA[p] = c->dalloc<double>(fs); c->lamB[p] = c->dalloc<double>(fs); c->lamb[p] = c->dalloc<double>(bs);
         c->lpHalo[p] = c->dalloc<double>(bs); c->lmHalo[p] = c->dalloc<double>(bs);
@@ -554,7 +560,7 @@ void alloc_fields(tcif_ctx *c) {
     c->TqHalo = c->dalloc<double>((size_t)std::max(Q, 1) * 6 * bs);
     c->F = c->dalloc<double>(3 * cs); c->Fb = c->dalloc<double>(3 * bs);
     {   // partial records of the boundary-adjacent cells: the largest of the sweeps' layouts (tcif_volume.cuh)
-        const int slots = std::max(std::max(4 * P + 2, 1 + 9 * std::max(Q, 1)), 11 * P);
+        const int slots = std::max(std::max(4 * P + 2, 1 + 9 * std::max(Q, 1)), 9 * P);
         c->dm.part = c->dalloc<double>((size_t)slots * std::max(c->nBndCells, 1));
     }
     c->stagingDoubles = std::max<size_t>(3 * cs, std::max<size_t>((size_t)std::max(c->nIF, 1), 3 * bs));
@@ -833,12 +839,12 @@ ForceArgs force_args(tcif_ctx *c, bool withTensor, bool withG) {
 
 // the force sweeps gather few arrays (their +-z planes fit in L2): ascending tile order is faster for them
 // (profiles/r02_variants.md), the strip order is for the MULES sweeps
-DMesh dm_ascending(const tcif_ctx *c) { DMesh d = c->dm; d.tileOrder = nullptr; return d; }
+DMesh dm_force(const tcif_ctx *c) { DMesh d = c->dm; d.tileOrder = c->forceOrder; return d; }
 // BND: the O(surface) launch over the boundary-adjacent cells (fixed-K: same body as the volume launch; generic K: twin)
 template <bool BND, bool WG> void launch_grad_tensor(tcif_ctx *c, const ForceArgs &a) {
     if (const SweepFns *f = fns(c)) {
         if (BND && !c->nBndCells) return;
-        f->grad_tensor(c->P, BND, c->stream, BND ? c->dm : dm_ascending(c), a);
+        f->grad_tensor(c->P, BND, c->stream, BND ? c->dm : dm_force(c), a);
         c->launches++;
         return;
     }
@@ -850,7 +856,7 @@ template <bool BND, bool WG> void launch_grad_tensor(tcif_ctx *c, const ForceArg
 template <bool BND> void launch_div_tensor(tcif_ctx *c, const ForceArgs &a) {
     if (const SweepFns *f = fns(c)) {
         if (BND && !c->nBndCells) return;
-        f->div_tensor(c->P, BND, c->stream, dm_ascending(c), a);
+        f->div_tensor(c->P, BND, c->stream, dm_force(c), a);
         c->launches++;
         return;
     }
@@ -874,12 +880,13 @@ double bytes_div_tensor(const tcif_ctx *c) {
 double bytes_mules_setup(const tcif_ctx *c, int nPh, bool storeOld = false) {
     double shared = 4.0 * (c->Ko + c->Kn) + 8 /*V*/ + 8.0 * c->Ko /*phi*/;
     (void)storeOld;      // psi0 is one 8 B stream either way: read, or (storeOld) written
-    double perPh = 8 + 8 /*psi psi0*/ + 8.0 * c->Ko * 2 /*phiIn phiCorr*/ + 48 /*Q+-,s+-,l+-*/;
+    const bool sums = kshape(c) == 0;        // only the generic-K kernels store sumPhip / mSumPhim
+    double perPh = 8 + 8 /*psi psi0*/ + 8.0 * c->Ko * 2 /*phiIn phiCorr*/ + 32 /*Q+-,l+-*/ + (sums ? 16 : 0);
     return (double)c->nC * (shared + nPh * perPh);
 }
 double bytes_mules_iter(const tcif_ctx *c, int nPh, bool first) {
     double shared = 4.0 * (c->Ko + c->Kn);
-    double perPh = 8.0 * c->Ko * (first ? 2 : 3) + 16 + 16 + 32;
+    double perPh = 8.0 * c->Ko * (first ? 2 : 3) + 16 + 16 /*l+- in, out*/ + 16 /*Q+-*/ + (kshape(c) == 0 ? 16 : 0) /*s+-*/;
     return (double)c->nC * (shared + nPh * perPh);
 }
 double bytes_mules_final(const tcif_ctx *c, int nPh, int mode, bool first) {
@@ -1100,7 +1107,17 @@ void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode,
     if (mode == 0) fin(std::integral_constant<int, 0>{});
     else if (mode == 1) fin(std::integral_constant<int, 1>{});
     else {
-        fin(std::integral_constant<int, 2>{});
+        // explicitSolve: one sweep (MODE 2), or the limited fluxes first and surfaceIntegrate + Euler update from the
+        // stored fluxes in a second, lighter sweep (TCIF_SPLIT_FINAL, fixed-K meshes)
+        static const int split = [] { const char *e = getenv("TCIF_SPLIT_FINAL"); return e ? atoi(e) : 0; }();
+        const SweepFns *f = fns(c);
+        if (split && f) {
+            fb = bytes_mules_final(c, nPh, 1, first);
+            fin(std::integral_constant<int, 1>{});
+            const double ub = (double)c->nC * (4.0 * (c->Ko + c->Kn) + 8 + nPh * (8.0 * c->Ko + 16));
+            sweep(c, [&] { timed(c, T_MULES_FINAL, ub, [&] { f->update(nPh, false, c->stream, c->dm, b, prm); c->launches++; }); },
+                     [&] { timed(c, T_BOUNDARY, 0, [&] { if (c->nBndCells) { f->update(nPh, true, c->stream, c->dm, b, prm); c->launches++; } }); });
+        } else fin(std::integral_constant<int, 2>{});
         for (int k = 0; k < nPh; ++k) { std::swap(c->alpha[phases[k]], c->alphaNew[phases[k]]); alpha_changed(c, phases[k]); }
     }
     join(c);
@@ -1310,77 +1327,14 @@ void do_stage(tcif_ctx *c, double deltaT) {
     do_force(c);
     do_mules_stage(c, deltaT);
 }
-// compulsory bytes of the bridge sweep (see bytes_mules_*)
-double bytes_mules_bridge(const tcif_ctx *c, int nPh, bool first) {
-    double shared = 4.0 * (c->Ko + c->Kn) + 8 /*V*/ + 8.0 * c->Ko /*phi*/;
-    double perPh = 8.0 * c->Ko * (first ? 1 : 2) /*phiCorr, lambda*/ + 16 /*lambda+- in*/ + 8 + 8 /*psi psi0*/ + 8.0 * c->Ko /*phiCorr out*/ + 48;
-    return (double)c->nC * (shared + nPh * perPh);
-}
-
 // One solveAlphas corrector restricted to MULES (the metric stage): limit(returnCorr) for all phases, limitSum,
-// explicitSolve for all phases.  On fixed-K meshes the last face pass of the first limit, limitSum and the set-up
-// sweep of explicitSolve's limit can run as ONE sweep (kvp_mules_bridge, TCIF_BRIDGE=1; measured slower: 128 registers).
+// explicitSolve for all phases.
 void do_mules_stage(tcif_ctx *c, double deltaT) {
     int all[4] = {0, 1, 2, 3};
-    static const int bridgeOn = [] { const char *e = getenv("TCIF_BRIDGE"); return e ? atoi(e) : 0; }();
-    const SweepFns *f = fns(c);
-    if (!(f && bridgeOn && c->P >= 2)) {
-        const bool fuse = can_fuse_limit_sum(c);
-        do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true, fuse, true); // alpha.oldTime() := alpha, then multiphaseSystem.C:296-319
-        if (fuse) do_limit_sum_rest(c); else do_limit_sum(c);           // :321
-        do_explicit(c, all, c->P, deltaT, true);                        // :346 (bounded flux) + :365-375
-        return;
-    }
-    require_comm(c);
-    const int nPh = c->P, L = c->cfg.nLimiterIter;
-    MulesParams prm{};
-    prm.rDeltaT = 1.0 / deltaT; prm.psiMax = 1.0; prm.psiMin = 0.0;
-    prm.extremaCoeff = c->cfg.extremaCoeff; prm.smoothLimiter = c->cfg.smoothLimiter;
-    prm.boundaryExtrema = c->cfg.boundaryExtrema;
-    prm.phi = c->phi; prm.phib = c->phib;
-    // ---- MULES::limit(..., returnCorr = true) up to its last face pass (:296-319)
-    MulesBatch b = mules_batch(c, all, nPh, true);
-    prm.addUpwind = 0; prm.storeOld = 1;
-    sweep(c, [&] { timed(c, T_MULES_SETUP, bytes_mules_setup(c, nPh, true), [&] { launch_setup<false>(c, b, prm); }); },
-             [&] { timed(c, T_BOUNDARY, 0, [&] { launch_setup<true>(c, b, prm); }); });
-    int first = 1, flip = 0;
-    for (int j = 1; j < L; ++j) {
-        sweep(c, [&] { timed(c, T_MULES_ITER, bytes_mules_iter(c, nPh, first), [&] { launch_iter<false>(c, b, first, flip); }); },
-                 [&] { halo_lambda(c, b, flip); },
-                 [&] { timed(c, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b, first, flip); }); });
-        flip ^= 1; first = 0;
-    }
-    // ---- explicitSolve: psi.correctBoundaryConditions() (:365; alpha has not changed since, the values stay)
-    correct_alpha_bcs(c, all, nPh);
-    // ---- bridge: phiAlphaCorr = lambda phiCorr, limitSum (:321), phiAlpha = phiAlphaCorr + upwind flux (:346), set-up of limit #2
-    {
-        MulesBatch br = resolve_flip(b, flip);
-        for (int k = 0; k < nPh; ++k) { br.ph[k].phiCorrOut = c->phiPsi[k]; br.ph[k].phiInb = c->phiPsib[k]; }
-        MulesParams p2 = prm;
-        p2.addUpwind = 1; p2.storeOld = 0;
-        sweep(c, [&] { timed(c, T_MULES_BRIDGE, bytes_mules_bridge(c, nPh, first), [&] { f->bridge(nPh, first != 0, false, c->stream, c->dm, br, p2, L); c->launches++; }); },
-                 [&] { if (L > 0) halo_lambda(c, b, flip); },
-                 [&] { timed(c, T_BOUNDARY, 0, [&] { if (c->nBndCells) { f->bridge(nPh, first != 0, true, c->stream, c->dm, br, p2, L); c->launches++; } }); });
-        for (int k = 0; k < nPh; ++k) std::swap(c->phiCorr[k], c->phiPsi[k]);     // the new phiCorr lives in the old phiPsi array
-    }
-    // ---- rest of limit #2 (returnCorr = false) + surfaceIntegrate + Euler update; lambda+- of iteration 1 are in the
-    //      buffer the bridge wrote (the one limit #1 was not reading)
-    MulesBatch b2 = mules_batch(c, all, nPh, false);
-    MulesParams p2 = prm;
-    p2.addUpwind = 1; p2.storeOld = 0;
-    int first2 = 1, flip2 = flip ^ 1;
-    for (int j = 1; j < L; ++j) {
-        sweep(c, [&] { timed(c, T_MULES_ITER, bytes_mules_iter(c, nPh, first2), [&] { launch_iter<false>(c, b2, first2, flip2); }); },
-                 [&] { halo_lambda(c, b2, flip2); },
-                 [&] { timed(c, T_BOUNDARY, 0, [&] { launch_iter<true>(c, b2, first2, flip2); }); });
-        flip2 ^= 1; first2 = 0;
-    }
-    sweep(c, [&] { timed(c, T_MULES_FINAL, bytes_mules_final(c, nPh, 2, first2), [&] { launch_final<false, 2>(c, b2, p2, first2, flip2, L, false); }); },
-             [&] { if (L > 0) halo_lambda(c, b2, flip2); },
-             [&] { timed(c, T_BOUNDARY, 0, [&] { launch_final<true, 2>(c, b2, p2, first2, flip2, L, false); }); });
-    for (int k = 0; k < nPh; ++k) { std::swap(c->alpha[k], c->alphaNew[k]); alpha_changed(c, k); }
-    join(c);
-    correct_alpha_bcs(c, all, nPh);
+    const bool fuse = can_fuse_limit_sum(c);
+    do_limit(c, all, c->P, 1.0 / deltaT, 0, false, true, fuse, true); // alpha.oldTime() := alpha, then multiphaseSystem.C:296-319
+    if (fuse) do_limit_sum_rest(c); else do_limit_sum(c);           // :321
+    do_explicit(c, all, c->P, deltaT, true);                        // :346 (bounded flux) + :365-375
 }
 
 // rhoPhi_ (+)= sum_p interpolate(rho_p)*alphaPhi_p   (multiphaseSystem.C:397-406, 158)
@@ -2147,12 +2101,14 @@ void delta_init(tcif_ctx *c) {
     CUDA_OK(cudaHostAlloc((void **)&c->hCount, sizeof(int) * 8, cudaHostAllocDefault));
 }
 // dst[idx[k]] = val[k] (ncomp values per entry) on a few host threads: the indices of one list are distinct
-void host_scatter(double *dst, const int *ix, const double *v, int n, int ncomp) {
+void host_scatter(double *dst, const int *ix, const double *v, int n, int ncomp, int nRanks) {
     auto work = [=](int k0, int k1) {
         if (ncomp == 1) for (int k = k0; k < k1; ++k) dst[ix[k]] = v[k];
         else for (int k = k0; k < k1; ++k) { double *d = dst + 3 * (size_t)ix[k]; d[0] = v[3 * (size_t)k]; d[1] = v[3 * (size_t)k + 1]; d[2] = v[3 * (size_t)k + 2]; }
     };
-    const int nT = n < (1 << 18) ? 1 : (int)std::min<unsigned>(8, std::max(1u, std::thread::hardware_concurrency()));
+    // (the ranks of one node share its cores: 8 threads per rank on a 32-core host with 8 ranks only fight each other)
+    const unsigned share = std::max(1u, std::thread::hardware_concurrency() / (unsigned)std::max(nRanks, 1));
+    const int nT = n < (1 << 18) ? 1 : (int)std::min<unsigned>(8, share);
     if (nT == 1) { work(0, n); return; }
     std::vector<std::thread> th;
     for (int t = 0; t < nT; ++t) th.emplace_back(work, (int)((long long)n * t / nT), (int)((long long)n * (t + 1) / nT));
@@ -2181,7 +2137,7 @@ bool down_delta(tcif_ctx *c, cudaStream_t st, double *dst, const double *cur, do
     c->launches++;
     CUDA_OK(cudaStreamSynchronize(st));
     c->d2hBytes += (int64_t)m * (sizeof(int) + sizeof(double) * ncomp);
-    host_scatter(dst, c->hIdx, c->hVal, m, ncomp);
+    host_scatter(dst, c->hIdx, c->hVal, m, ncomp, c->nRanks);
     return true;
 }
 // a face field (device slots) -> caller's array in OpenFOAM face order: delta against what the SAME host array received

@@ -402,7 +402,6 @@ struct MulesPh {
     double *psiNew;                     // explicit update target
     const double *lpIn, *lmIn, *lamIn;  // ping-pong resolved on the host for the current sweep (kvp_* kernels)
     double *lpOut, *lmOut, *lamOut;
-    double *phiCorrOut;                 // bridge sweep: where the NEW phiCorr goes (the phiPsi array; swapped by the host afterwards)
 };
 struct MulesBatch { int nPh; MulesPh ph[4]; };
 struct MulesParams {

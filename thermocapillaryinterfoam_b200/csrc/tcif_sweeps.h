@@ -15,8 +15,8 @@ struct SweepFns {
     void (*iter)(int nPh, bool first, bool def, cudaStream_t st, const DMesh &m, const MulesBatch &b);
     void (*fin)(int nPh, int mode, bool first, bool lsum, bool def, cudaStream_t st, const DMesh &m, const MulesBatch &b,
                 const MulesParams &prm, int nIter);
-    // last face pass of limit(returnCorr) + limitSum + set-up sweep of the next limit in one sweep (tcif_volume.cuh)
-    void (*bridge)(int nPh, bool first, bool def, cudaStream_t st, const DMesh &m, const MulesBatch &b, const MulesParams &prm, int nIter);
+    // surfaceIntegrate + Euler update from the stored fluxes (second half of the split explicitSolve)
+    void (*update)(int nPh, bool def, cudaStream_t st, const DMesh &m, const MulesBatch &b, const MulesParams &prm);
     void (*pred_jacobi)(int nPh, cudaStream_t st, const DMesh &m, const PredBatch &b);
 };
 

@@ -43,10 +43,15 @@ __device__ __forceinline__ int owner_of_k(int stride, int fd) {   // fd mod stri
 #ifndef TCIF_TPB_FORCE
 #define TCIF_TPB_FORCE 128
 #endif
-#ifndef TCIF_MINB_FORCE
-#define TCIF_MINB_FORCE 3
+// resident 128-thread CTAs per SM the force sweeps are compiled for (profiles/r03_variants.md: div at 4 = 128 registers
+// instead of 168 is 12 % faster, 5 spills and loses; grad needs 120 either way)
+#ifndef TCIF_MINB_GRAD
+#define TCIF_MINB_GRAD 3
 #endif
-// register caps chosen from the A/B runs in profiles/r01_variants.md
+#ifndef TCIF_MINB_DIV
+#define TCIF_MINB_DIV 4
+#endif
+// register caps chosen from the A/B runs in profiles/r01_variants.md, r03_variants.md
 #ifndef TCIF_MINB_SETUP
 #define TCIF_MINB_SETUP 4
 #endif
@@ -163,7 +168,7 @@ __device__ __forceinline__ void store_pair_tensors(const DMesh &m, const ForceAr
 // ---- K1: grad(alpha_p) for all phases + capillary stress tensors of all pairs ---------------------
 // partial record of a boundary-adjacent cell: g[p][d] before /V (3P), alpha_p (P), 1/V, T  ->  4P + 2 slots
 template <int P, int K>
-__global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
+__global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_GRAD)
 kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
     CellCtx x;
     if (!pick_cell<TCIF_TPB_FORCE>(m, x)) return;
@@ -372,7 +377,7 @@ __device__ __forceinline__ void div_bnd_faces(const DMesh &m, const ForceArgs &a
 // ---- K2: F = sum_q div(T_q) ---------------------------------------------------------------------------
 // partial record: 1/V, then per tensor q: acc[3] over the internal faces, own tensor Ts[6]  ->  1 + 9 nQ slots
 template <int P, int K>
-__global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_FORCE)
+__global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_DIV)
 kv_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
     constexpr int Q = P * (P - 1) / 2;
     CellCtx x;
@@ -461,7 +466,10 @@ kfix_div_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceAr
 // Arithmetic and order: SURVEY.md A.6 (see also the generic-K kernels k_mules_* in tcif_device.cuh).
 // Partial records of a boundary-adjacent cell, per phase p (slot = p*PART_* + j):
 //   set-up  : psiMaxn, psiMinn, sumPhiBD, sumPhip, mSumPhim, psi, psi0, Su, Sp            (V is read by the fix launch)
-//   iter    : sumlPhip, mSumlPhim, lambda+_C, lambda-_C, Q+, Q-, sumPhip, mSumPhim
+//   iter    : sumlPhip, mSumlPhim, lambda+_C, lambda-_C, Q+, Q-, sumPhip, mSumPhim (both over the internal faces)
+// sumPhip / mSumPhim (the totals of the anti-diffusive out- and inflow of a cell) are NOT stored between the sweeps: every
+// limiter sweep has phiCorr of all 2K faces in registers and re-derives them with the set-up sweep's operations in the
+// set-up sweep's order, i.e. to the same bits (16 B per cell, phase and sweep less to write and to read).
 //   final   : sum (faces so far), lambda+_C, lambda-_C, psi0, Su, Sp                      (MODE 2; MODE 0/1: the two lambdas)
 // =====================================================================================================
 enum { PART_SETUP = 9, PART_ITER = 8, PART_FINAL = 6 };
@@ -479,7 +487,7 @@ __device__ __forceinline__ void setup_finish(const MulesPh &ph, const MulesParam
     }
     double Qp = V * ((prm.rDeltaT - Sp) * psiMaxn - Su) - (V * prm.rDeltaT) * psi0 + sBD;
     double Qm = V * (Su - (prm.rDeltaT - Sp) * psiMinn) + (V * prm.rDeltaT) * psi0 - sBD;
-    __stcs(ph.Qp + c, Qp); __stcs(ph.Qm + c, Qm); __stcs(ph.sP + c, sP); __stcs(ph.sM + c, sM);
+    __stcs(ph.Qp + c, Qp); __stcs(ph.Qm + c, Qm);
     // limiter iteration 1, cell pass: lambda == 1 so sumlPhip == sumPhip, mSumlPhim == mSumPhim
     lmDst[c] = dmax(dmin((sP + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
     lpDst[c] = dmax(dmin((sM + Qm) / (sP + TCIF_ROOTVSMALL), 1.0), 0.0);
@@ -644,7 +652,7 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
         if (pf) {
             pf_face<K>(ph.phiCorr, m.stride, cp);
             if (!FIRST) pf_face<K>(lamIn, m.stride, cp);
-            pf_l2_keep(lpIn + cp); pf_l2_keep(lmIn + cp); pf_l2(ph.Qp + cp); pf_l2(ph.Qm + cp); pf_l2(ph.sP + cp); pf_l2(ph.sM + cp);
+            pf_l2_keep(lpIn + cp); pf_l2_keep(lmIn + cp); pf_l2(ph.Qp + cp); pf_l2(ph.Qm + cp);
         }
         const double lpC = ld_keep(lpIn + c), lmC = ld_keep(lmIn + c);
         double pcN[K], laN[K], lpO[K], lmO[K], pcO[K], laO[K], lpN[K], lmN[K];
@@ -656,14 +664,15 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
             pcO[k] = ld_keep(ph.phiCorr + fo); laO[k] = FIRST ? 1.0 : ld_keep(lamIn + fo);
             lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
         }
-        const double Qp = __ldcs(ph.Qp + c), Qm = __ldcs(ph.Qm + c), sP = __ldcs(ph.sP + c), sM = __ldcs(ph.sM + c);
-        double slp = 0.0, slm = 0.0;
+        const double Qp = __ldcs(ph.Qp + c), Qm = __ldcs(ph.Qm + c);
+        double slp = 0.0, slm = 0.0, sP = 0.0, sM = 0.0;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             if (s.vN[k]) {
                 double lam = lambda_face(laN[k], pcN[k], lpO[k], lmO[k], lpC, lmC);
                 double l = lam * pcN[k];
                 if (l > 0) slm += l; else slp -= l;
+                if (pcN[k] > 0) sM += pcN[k]; else sP -= pcN[k];
             }
         }
 #pragma unroll
@@ -673,6 +682,7 @@ kvp_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBat
                 lamOut[k * m.stride + c] = lam;
                 double l = lam * pcO[k];
                 if (l > 0) slp += l; else slm -= l;
+                if (pcO[k] > 0) sP += pcO[k]; else sM -= pcO[k];
             }
         }
         const int bi = bnd_rank(m, c);
@@ -699,8 +709,8 @@ kfix_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
         const MulesPh &ph = b.ph[p];
         const int o = p * PART_ITER;
         double slp = part_at(m, o, bi), slm = part_at(m, o + 1, bi);
-        const double lpC = part_at(m, o + 2, bi), lmC = part_at(m, o + 3, bi), Qp = part_at(m, o + 4, bi), Qm = part_at(m, o + 5, bi),
-                     sP = part_at(m, o + 6, bi), sM = part_at(m, o + 7, bi);
+        const double lpC = part_at(m, o + 2, bi), lmC = part_at(m, o + 3, bi), Qp = part_at(m, o + 4, bi), Qm = part_at(m, o + 5, bi);
+        double sP = part_at(m, o + 6, bi), sM = part_at(m, o + 7, bi);
         if (r.n >= 0) {
             double pc[3], la[3], bd[3], lpH[3], lmH[3];
 #pragma unroll
@@ -715,6 +725,7 @@ kfix_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                     ph.lamb[r.bf[k]] = lam;
                     const double l = lam * pc[k];
                     if (l > 0) slp += l; else slm -= l;
+                    if (pc[k] > 0) sP += pc[k]; else sM -= pc[k];
                 }
             }
         } else {
@@ -725,6 +736,7 @@ kfix_mules_iter(const __grid_constant__ DMesh m, const __grid_constant__ MulesBa
                 ph.lamb[bf] = lam;
                 const double l = lam * pc;
                 if (l > 0) slp += l; else slm -= l;
+                if (pc > 0) sP += pc; else sM -= pc;
             }
         }
         ph.lmOut[c] = dmax(dmin((slp + Qp) / (sM + TCIF_ROOTVSMALL), 1.0), 0.0);
@@ -917,166 +929,78 @@ kfix_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesB
 }
 
 
-// ---- bridge: last face pass of limit(returnCorr = true) + limitSum + set-up sweep of explicitSolve's limit ------------
-// multiphaseSystem.C:305-321 ends with phiAlphaCorr_p := lambda_p phiCorr_p followed by MULES::limitSum over the phases;
-// :346-375 starts with phiAlpha_p = phiAlphaCorr_p + upwind flux and MULES::limit's set-up.  Unfused, the limited
-// corrections cross HBM twice (written by the apply sweep, read back on both sides of every face by the set-up sweep);
-// here a cell re-derives them for ALL its faces in registers -- the neighbour-side ones redundantly, from exactly the
-// values the owner thread uses, so the bits agree -- applies limitSum per face and goes straight on to the set-up sums.
-// The new phiCorr goes to phiCorrOut (the phiPsi array, free at this point: the host swaps the two afterwards) because
-// neighbours still read the old one; lambda+- of iteration 1 go to the ping-pong buffer that is not being read.
-// Partial record of a boundary-adjacent cell, per phase: lambda+_C, lambda-_C, then the nine set-up slots.
-#ifndef TCIF_MINB_BRIDGE
-#define TCIF_MINB_BRIDGE 2
-#endif
-enum { PART_BRIDGE = 2 + PART_SETUP };
-template <int K, bool FIRST, int NPH>
-__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_BRIDGE)
-kvp_mules_bridge(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, const __grid_constant__ MulesParams prm, int nIter) {
+// ---- explicitSolve split in two sweeps: kvp_mules_final<MODE 1> stores the limited fluxes of the owner-side faces, then
+// this sweep does surfaceIntegrate + the Euler update from the STORED fluxes (one gather per neighbour-side face instead
+// of re-deriving that face's lambda and upwind flux from five).  Same values in the same order as MODE 2, so the bits
+// agree: the stored flux of a neighbour-side face is what MODE 2 recomputes from the same operands.
+// partial record (PART_FINAL layout): slot 0 = sum over the internal faces, 3..5 = psi0, Su, Sp
+template <int K, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB, 4)
+kvp_mules_update(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, const __grid_constant__ MulesParams prm) {
     CellCtx x;
     if (!pick_cell<TCIF_TPB>(m, x)) return;
     const int c = x.c;
     Slots<K> s;
     s.load(m, c);
+    const double V = m.V[c];
     const int cp = x.cp;
     const bool pf = cp >= 0;
-    if (pf) { pf_slots<K>(m, cp); pf_face<K>(prm.phi, m.stride, cp); pf_l2(m.V + cp); }
-    double fl[2 * K][NPH];                       // limited corrections: [0, K) neighbour-side faces, [K, 2K) owner-side faces
-    double lpCs[NPH], lmCs[NPH];
-#pragma unroll
-    for (int p = 0; p < NPH; ++p) {
-        const MulesPh &ph = b.ph[p];
-        const double *lpIn = ph.lpIn, *lmIn = ph.lmIn, *lamIn = ph.lamIn;
-        if (pf) {
-            pf_face<K>(ph.phiCorr, m.stride, cp);
-            if (!FIRST) pf_face<K>(lamIn, m.stride, cp);
-            pf_l2_keep(lpIn + cp); pf_l2_keep(lmIn + cp); pf_l2_keep(ph.psi + cp); pf_l2(ph.psi0 + cp);
-            if (ph.Su) pf_l2(ph.Su + cp);
-            if (ph.Sp) pf_l2(ph.Sp + cp);
-        }
-        const double lpC = ld_keep(lpIn + c), lmC = ld_keep(lmIn + c);
-        lpCs[p] = lpC; lmCs[p] = lmC;
-        double pcN[K], laN[K], lpO[K], lmO[K], pcO[K], laO[K], lpN[K], lmN[K];
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            const int fo = k * m.stride + c;
-            pcN[k] = ph.phiCorr[s.fdN[k]]; laN[k] = FIRST ? 1.0 : lamIn[s.fdN[k]];
-            lpO[k] = lpIn[s.oN[k]]; lmO[k] = lmIn[s.oN[k]];
-            pcO[k] = ld_keep(ph.phiCorr + fo); laO[k] = FIRST ? 1.0 : ld_keep(lamIn + fo);
-            lpN[k] = lpIn[s.nO[k]]; lmN[k] = lmIn[s.nO[k]];
-        }
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            double lam = laN[k];
-            if (nIter > 0) lam = lambda_face(lam, pcN[k], lpO[k], lmO[k], lpC, lmC);
-            fl[k][p] = pcN[k] * lam;
-            lam = laO[k];
-            if (nIter > 0) lam = lambda_face(lam, pcO[k], lpC, lmC, lpN[k], lmN[k]);
-            fl[K + k][p] = pcO[k] * lam;
-        }
-    }
-#pragma unroll
-    for (int k = 0; k < K; ++k) {                // MULES::limitSum, face by face, all phases in registers
-        if (s.vN[k]) limit_sum_face<NPH>(fl[k]);
-        if (s.vO[k]) limit_sum_face<NPH>(fl[K + k]);
-    }
-    double phiN[K], phiO[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) { phiN[k] = prm.phi[s.fdN[k]]; phiO[k] = __ldcs(prm.phi + k * m.stride + c); }
-    const double V = m.V[c];
+    if (pf) { pf_slots<K>(m, cp); pf_l2(m.V + cp); }
     const int bi = bnd_rank(m, c);
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
         const MulesPh &ph = b.ph[p];
-        const double psiC = ld_keep(ph.psi + c);
-        double psiO[K], psiN[K];
+        if (pf) {
+            pf_face<K>(ph.phiPsi, m.stride, cp); pf_l2(ph.psi0 + cp);
+            if (ph.Su) pf_l2(ph.Su + cp);
+            if (ph.Sp) pf_l2(ph.Sp + cp);
+        }
+        double fN[K], fO[K];
 #pragma unroll
-        for (int k = 0; k < K; ++k) { psiO[k] = ph.psi[s.oN[k]]; psiN[k] = ph.psi[s.nO[k]]; }
+        for (int k = 0; k < K; ++k) { fN[k] = ph.phiPsi[s.fdN[k]]; fO[k] = ph.phiPsi[k * m.stride + c]; }
         const double psi0 = __ldcs(ph.psi0 + c);
         const double Su = ph.Su ? __ldcs(ph.Su + c) : 0.0, Sp = ph.Sp ? __ldcs(ph.Sp + c) : 0.0;
-        double psiMaxn = prm.psiMin, psiMinn = prm.psiMax, sBD = 0.0, sP = 0.0, sM = 0.0;
+        double sum = 0.0;
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-            if (s.vN[k]) {
-                double bd = upwind_flux(phiN[k], psiO[k], psiC);
-                double pp = fl[k][p];
-                if (prm.addUpwind) pp = pp + bd;
-                double pc = pp - bd;
-                psiMaxn = dmax(psiMaxn, psiO[k]); psiMinn = dmin(psiMinn, psiO[k]);
-                sBD -= bd;
-                if (pc > 0) sM += pc; else sP -= pc;
-            }
-        }
+        for (int k = 0; k < K; ++k) if (s.vN[k]) sum -= fN[k];
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-            if (s.vO[k]) {
-                double bd = upwind_flux(phiO[k], psiC, psiN[k]);
-                double pp = fl[K + k][p];
-                if (prm.addUpwind) pp = pp + bd;
-                double pc = pp - bd;
-                ph.phiCorrOut[k * m.stride + c] = pc;
-                psiMaxn = dmax(psiMaxn, psiN[k]); psiMinn = dmin(psiMinn, psiN[k]);
-                sBD += bd;
-                if (pc > 0) sP += pc; else sM -= pc;
-            }
+        for (int k = 0; k < K; ++k) if (s.vO[k]) sum += fO[k];
+        if (bi >= 0) {                       // the patch faces continue from here (kfix_mules_update)
+            const int o = p * PART_FINAL;
+            part_at(m, o, bi) = sum; part_at(m, o + 3, bi) = psi0; part_at(m, o + 4, bi) = Su; part_at(m, o + 5, bi) = Sp;
         }
-        if (bi >= 0) {                           // the patch faces continue from here (kfix_mules_bridge)
-            const int o = p * PART_BRIDGE;
-            part_at(m, o, bi) = lpCs[p]; part_at(m, o + 1, bi) = lmCs[p];
-            part_at(m, o + 2, bi) = psiMaxn; part_at(m, o + 3, bi) = psiMinn; part_at(m, o + 4, bi) = sBD;
-            part_at(m, o + 5, bi) = sP; part_at(m, o + 6, bi) = sM; part_at(m, o + 7, bi) = psiC;
-            part_at(m, o + 8, bi) = psi0; part_at(m, o + 9, bi) = Su; part_at(m, o + 10, bi) = Sp;
-        }
-        setup_finish(ph, prm, c, V, psiC, psi0, Su, Sp, psiMaxn, psiMinn, sBD, sP, sM, ph.lpOut, ph.lmOut);
+        const double d = sum / V;
+        ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
     }
 }
 
-// patch faces of the bridge: last face rule -> limited patch correction, limitSum on processor faces (MULES::limitSum
-// acts on internal faces and coupled patches only), then the set-up face work with that correction as the input flux
 template <int NPH>
 __global__ void __launch_bounds__(TCIF_TPB)
-kfix_mules_bridge(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, const __grid_constant__ MulesParams prm, int nIter) {
+kfix_mules_update(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b, const __grid_constant__ MulesParams prm) {
     const int bi = blockIdx.x * blockDim.x + threadIdx.x;
     if (bi >= m.nBndCells) return;
     const int c = m.bndCells[bi];
+    const BndRec r = bnd_load(m, bi);
     const double V = m.V[c];
-    const int j0 = m.bndCellStart[bi], j1 = m.bndCellStart[bi + 1];
-    double acc[NPH][5];                          // psiMaxn, psiMinn, sBD, sP, sM per phase
-#pragma unroll
-    for (int p = 0; p < NPH; ++p)
-#pragma unroll
-        for (int q = 0; q < 5; ++q) acc[p][q] = part_at(m, p * PART_BRIDGE + 2 + q, bi);
-    for (int j = j0; j < j1; ++j) {
-        const int bf = m.bndFaces[j], tp = m.bfType[bf], pa = m.bfPatch[bf];
-        const bool coupled = tp == PATCH_PROCESSOR;
-        const double phb = prm.phib[bf];
-        double flb[NPH];
-#pragma unroll
-        for (int p = 0; p < NPH; ++p) {
-            const MulesPh &ph = b.ph[p];
-            const double pc = ph.phiCorrb[bf], bd = ph.phiBDb[bf];
-            double lam = ph.lamb[bf];
-            if (nIter > 0) lam = lambda_bface(tp, lam, pc, bd, part_at(m, p * PART_BRIDGE, bi), part_at(m, p * PART_BRIDGE + 1, bi),
-                                              ph.lpHalo[bf], ph.lmHalo[bf]);
-            flb[p] = pc * lam;
-        }
-        if (coupled) limit_sum_face<NPH>(flb);
-#pragma unroll
-        for (int p = 0; p < NPH; ++p) {
-            const MulesPh &ph = b.ph[p];
-            bnd_setup_face(ph, prm, bf, coupled, ph.bc[pa], ph.psib[bf], phb, flb[p], part_at(m, p * PART_BRIDGE + 7, bi),
-                           acc[p][0], acc[p][1], acc[p][2], acc[p][3], acc[p][4]);
-        }
-    }
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
         const MulesPh &ph = b.ph[p];
-        const int o = p * PART_BRIDGE;
-        setup_finish(ph, prm, c, V, part_at(m, o + 7, bi), part_at(m, o + 8, bi), part_at(m, o + 9, bi), part_at(m, o + 10, bi),
-                     acc[p][0], acc[p][1], acc[p][2], acc[p][3], acc[p][4], ph.lpOut, ph.lmOut);
+        const int o = p * PART_FINAL;
+        double sum = part_at(m, o, bi);
+        if (r.n >= 0) {
+            double fl[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) fl[k] = ph.phiPsib[r.bf[k]];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) if (k < r.n) sum += fl[k];
+        } else {
+            for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) sum += ph.phiPsib[m.bndFaces[j]];
+        }
+        const double psi0 = part_at(m, o + 3, bi), Su = part_at(m, o + 4, bi), Sp = part_at(m, o + 5, bi);
+        const double d = sum / V;
+        ph.psiNew[c] = (psi0 * prm.rDeltaT + Su - d) / (prm.rDeltaT - Sp);
     }
 }
-
 
 // ---- Jacobi sweep of the implicit upwind predictor, phase-looped (see k_pred_jacobi, tcif_alpha.cuh) -----------
 // The matrix coefficients max(phi,0) / -min(phi,0) and the slot indices are shared by the phases of the batch:
