@@ -367,6 +367,10 @@ TCIF_API int tcif_timers_read(tcif_ctx *ctx, double *ms, int64_t *launches, doub
 TCIF_API int64_t tcif_launch_count(const tcif_ctx *ctx);
 /* Bytes of HBM the context holds. */
 TCIF_API int64_t tcif_device_bytes(const tcif_ctx *ctx);
+/* Debug aid (compute-sanitizer is not available on every pool): a context created with TCIF_GUARD=1 in the environment
+ * places every device array between two 512-byte guard zones; this counts the zones and those whose pattern has been
+ * overwritten (an out-of-bounds write next to an array).  Fails on a context created without the switch. */
+TCIF_API int tcif_debug_guard_check(tcif_ctx *ctx, int64_t *nZones, int64_t *nCorrupt);
 /* How the mesh was laid out on the device (tests assert the benchmarked code path with it):
  * out[0] Ko, [1] Kn (slot counts), [2] compile-time slot count of the fixed-K sweeps (0: generic-K kernels),
  * [3] 1 when the volume sweeps walk the 256-cell tiles strip-wise, [4] L2 prefetch distance in tiles,

@@ -19,7 +19,7 @@ WANT = ["Kernel Name", "dram__bytes_read.sum", "dram__bytes_write.sum",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio", "smsp__inst_executed.sum"]
 TIMER_OF = [("grad_tensor", "grad_tensor"), ("div_tensor", "div_tensor"), ("mules_setup", "mules_setup"),
-            ("mules_iter", "mules_iter"), ("mules_final", "mules_final"), ("limit_sum", "limit_sum"),
+            ("mules_iter", "mules_iter"), ("mules_final", "mules_final"), ("mules_update", "mules_final"), ("limit_sum", "limit_sum"),
             ("flux_assembly", "flux_assembly"), ("pred_jacobi", "predictor"), ("alpha_transfer", "alpha_transfer")]
 
 

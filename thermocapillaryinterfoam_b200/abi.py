@@ -109,6 +109,7 @@ def lib():
     L.tcif_set_temperature_stamped.argtypes = [C.c_void_p, C.c_uint64, c_dp, c_dp, C.POINTER(C.c_int32)]
     L.tcif_mark_alpha.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
     L.tcif_transfer_counters.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+    L.tcif_debug_guard_check.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.tcif_host_alpha_stamps.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.tcif_host_sparse_returns.argtypes = [C.c_void_p, C.c_int]
     L.tcif_host_bytes_moved.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
@@ -621,6 +622,12 @@ class Context:
     @property
     def device_bytes(self):
         return int(lib().tcif_device_bytes(self.h))
+
+    def debug_guard_check(self):
+        """(zones, corrupted zones) of a context created under TCIF_GUARD=1."""
+        nz, nc = C.c_int64(0), C.c_int64(0)
+        self._ck(lib().tcif_debug_guard_check(self.h, C.byref(nz), C.byref(nc)))
+        return int(nz.value), int(nc.value)
 
     @property
     def mesh_info(self):

@@ -286,11 +286,28 @@ struct tcif_ctx {
     int64_t tLaunch[T_COUNT]{};
     int64_t launches = 0;
 
+    // TCIF_GUARD=1 (debug): every device allocation sits between two 512 B guard zones filled with a pattern;
+    // tcif_debug_guard_check() counts the zones that no longer hold it (an out-of-bounds WRITE next to an array)
+    static constexpr size_t kGuard = 512;
+    static constexpr int kGuardByte = 0xA5;
+    struct GuardRec { char *base; size_t bytes; };
+    std::vector<GuardRec> guards;
+    bool guardOn = [] { const char *e = getenv("TCIF_GUARD"); return e && atoi(e) != 0; }();
     template <class T> T *dalloc(size_t n, bool zero = true) {
         void *p = nullptr;
         size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
-        CUDA_OK(cudaMalloc(&p, bytes));
-        allocs.push_back(p);
+        if (guardOn) {
+            const size_t padded = (bytes + 255) / 256 * 256;
+            CUDA_OK(cudaMalloc(&p, padded + 2 * kGuard));
+            allocs.push_back(p);
+            CUDA_OK(cudaMemsetAsync(p, kGuardByte, kGuard, stream));
+            CUDA_OK(cudaMemsetAsync((char *)p + kGuard + bytes, kGuardByte, padded - bytes + kGuard, stream));
+            guards.push_back({(char *)p, bytes});
+            p = (char *)p + kGuard;
+        } else {
+            CUDA_OK(cudaMalloc(&p, bytes));
+            allocs.push_back(p);
+        }
         devBytes += (int64_t)bytes;
         if (zero) CUDA_OK(cudaMemsetAsync(p, 0, bytes, stream));
         return (T *)p;
@@ -1107,9 +1124,11 @@ void do_limit(tcif_ctx *c, const int *phases, int nPh, double rDeltaT, int mode,
     if (mode == 0) fin(std::integral_constant<int, 0>{});
     else if (mode == 1) fin(std::integral_constant<int, 1>{});
     else {
-        // explicitSolve: one sweep (MODE 2), or the limited fluxes first and surfaceIntegrate + Euler update from the
-        // stored fluxes in a second, lighter sweep (TCIF_SPLIT_FINAL, fixed-K meshes)
-        static const int split = [] { const char *e = getenv("TCIF_SPLIT_FINAL"); return e ? atoi(e) : 0; }();
+        // explicitSolve on fixed-K meshes: the limited fluxes first (MODE 1), then surfaceIntegrate + Euler update from the
+        // STORED fluxes in a second, lighter sweep; TCIF_SPLIT_FINAL=0 does both in one sweep (MODE 2), which re-derives the
+        // flux of every neighbour-side face from five gathers and is 1 ms per stage slower at 64 M cells although it
+        // moves fewer bytes (profiles/r03_variants.md).  Bit-identical either way.
+        static const int split = [] { const char *e = getenv("TCIF_SPLIT_FINAL"); return e ? atoi(e) : 1; }();
         const SweepFns *f = fns(c);
         if (split && f) {
             fb = bytes_mules_final(c, nPh, 1, first);
@@ -3202,6 +3221,26 @@ int tcif_timers_read(tcif_ctx *c, double *ms, int64_t *launches, double *bytes) 
 }
 int64_t tcif_launch_count(const tcif_ctx *c) { return c ? c->launches : 0; }
 int64_t tcif_device_bytes(const tcif_ctx *c) { return c ? c->devBytes : 0; }
+int tcif_debug_guard_check(tcif_ctx *c, int64_t *nZones, int64_t *nCorrupt) {
+    API_BEGIN(c)
+    if (!nZones || !nCorrupt) failf("tcif_debug_guard_check: null output");
+    *nZones = 0; *nCorrupt = 0;
+    if (!c->guardOn) failf("tcif_debug_guard_check: the context was not created under TCIF_GUARD=1");
+    CUDA_OK(cudaDeviceSynchronize());
+    std::vector<unsigned char> h;
+    for (const auto &g : c->guards) {
+        const size_t padded = (g.bytes + 255) / 256 * 256;
+        const size_t tail = padded - g.bytes + tcif_ctx::kGuard;
+        h.resize(tcif_ctx::kGuard + tail);
+        CUDA_OK(cudaMemcpy(h.data(), g.base, tcif_ctx::kGuard, cudaMemcpyDeviceToHost));
+        CUDA_OK(cudaMemcpy(h.data() + tcif_ctx::kGuard, g.base + tcif_ctx::kGuard + g.bytes, tail, cudaMemcpyDeviceToHost));
+        bool lo = true, hi = true;
+        for (size_t i = 0; i < tcif_ctx::kGuard; ++i) lo = lo && h[i] == tcif_ctx::kGuardByte;
+        for (size_t i = tcif_ctx::kGuard; i < h.size(); ++i) hi = hi && h[i] == tcif_ctx::kGuardByte;
+        *nZones += 2; *nCorrupt += (lo ? 0 : 1) + (hi ? 0 : 1);
+    }
+    API_END(c)
+}
 int tcif_comm_transport(const tcif_ctx *c) { return !c ? 0 : c->group ? 1 : c->nccl ? (c->peerOn ? 3 : 2) : 0; }
 int tcif_mesh_info(const tcif_ctx *c, int32_t out[8]) {
     if (!c || !out) return 1;
