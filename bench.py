@@ -224,8 +224,8 @@ def run_reference(args, rank):
     cores = os.cpu_count() or 1
     edge, full = reference_edge(args, cores)
     # the run must end within a few minutes: one untimed stage on the chosen box first; if W + K stages of it would not
-    # fit the budget (TCIF_REF_BUDGET_S, default 420 s) the bounded sample is run instead -- and named as such
-    budget = float(os.environ.get("TCIF_REF_BUDGET_S", "420"))
+    # fit the budget (TCIF_REF_BUDGET_S, default 720 s: the driver allows the arm 1800 s) the bounded sample is run instead -- and named as such
+    budget = float(os.environ.get("TCIF_REF_BUDGET_S", "720"))
     if edge == full and not args.cpu_n:
         t0 = time.time()
         _, s1, *_ = cpu_stage_rate(args.config, edge, 1, cores)
