@@ -1305,7 +1305,7 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
         CUDA_OK(cudaMemsetAsync(c->dmaxDev, 0, sizeof(double) * 8, c->stream));
         PredBatch b = batch(active);
         sweep(c, [&] { timed(c, T_PREDICTOR, (double)nPh * c->nC * (32.0 + 4.0 * (c->Ko + c->Kn) + 8.0 * c->Ko), [&] {
-                           if (kvpPred) kvpPred->pred_jacobi(nPh, c->stream, c->dm, b);
+                           if (kvpPred) kvpPred->pred_jacobi(nPh, false, c->stream, c->dm, b);
                            else k_pred_jacobi<false><<<grid, TCIF_TPB, 0, c->stream>>>(c->dm, b);
                            c->launches++; }); },
                  [&] {                            // patchNeighbourField of the iterate
@@ -1315,7 +1315,9 @@ void do_predictor(tcif_ctx *c, const int *phases, int nPh, double deltaT, double
                  },
                  [&] {
                      if (c->nBndCells) timed(c, T_BOUNDARY, 0, [&] {
-                         k_pred_jacobi<true><<<gridB, TCIF_TPB, 0, c->stream>>>(c->dm, b); c->launches++; });
+                         if (kvpPred) kvpPred->pred_jacobi(nPh, true, c->stream, c->dm, b);
+                         else k_pred_jacobi<true><<<gridB, TCIF_TPB, 0, c->stream>>>(c->dm, b);
+                         c->launches++; });
                  });
         join(c);
         CUDA_OK(cudaMemcpyAsync(c->h_small, c->dmaxDev, sizeof(double) * 4, cudaMemcpyDeviceToHost, c->stream));

@@ -17,7 +17,7 @@ struct SweepFns {
                 const MulesParams &prm, int nIter);
     // surfaceIntegrate + Euler update from the stored fluxes (second half of the split explicitSolve)
     void (*update)(int nPh, bool def, cudaStream_t st, const DMesh &m, const MulesBatch &b, const MulesParams &prm);
-    void (*pred_jacobi)(int nPh, cudaStream_t st, const DMesh &m, const PredBatch &b);
+    void (*pred_jacobi)(int nPh, bool def, cudaStream_t st, const DMesh &m, const PredBatch &b);
 };
 
 const SweepFns *sweep_fns_k2();

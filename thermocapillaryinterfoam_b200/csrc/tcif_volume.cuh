@@ -1005,48 +1005,15 @@ kfix_mules_update(const __grid_constant__ DMesh m, const __grid_constant__ Mules
 // ---- Jacobi sweep of the implicit upwind predictor, phase-looped (see k_pred_jacobi, tcif_alpha.cuh) -----------
 // The matrix coefficients max(phi,0) / -min(phi,0) and the slot indices are shared by the phases of the batch:
 // loaded once per cell.  Same operations in the same order as k_pred_jacobi (bit-identical iterates).
-template <int K, int NPH>
-__global__ void __launch_bounds__(TCIF_TPB, 4)
-kvp_pred_jacobi(const __grid_constant__ DMesh m, const __grid_constant__ PredBatch b) {
-    const CellIdx ci = cell_of<TCIF_TPB>(m, blockIdx.x);
-    const int c = ci.c;
-    const bool on = c < m.nC && !is_bnd_cell(m, c);
-    double dl[NPH];
-#pragma unroll
-    for (int p = 0; p < NPH; ++p) dl[p] = 0.0;
-    if (on) {
-        Slots<K> s;
-        s.load(m, c);
-        double cN[K], cO[K];
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            cN[k] = dmax(b.phi[s.fdN[k]], 0.0);
-            cO[k] = dmin(__ldcs(b.phi + k * m.stride + c), 0.0);
-        }
-        const int cp = ci.cp;
-        if (cp >= 0) { pf_slots<K>(m, cp); pf_face<K>(b.phi, m.stride, cp); }
-#pragma unroll
-        for (int p = 0; p < NPH; ++p) {
-            const PredPh &ph = b.ph[p];
-            if (!ph.active) continue;
-            if (cp >= 0) { pf_l2(ph.rhs + cp); pf_l2(ph.diag + cp); pf_l2(ph.x + cp); }
-            double xO[K], xN[K];
-#pragma unroll
-            for (int k = 0; k < K; ++k) { xO[k] = ph.x[s.oN[k]]; xN[k] = ph.x[s.nO[k]]; }
-            const double xC = ph.x[c], dg = __ldcs(ph.diag + c);
-            double acc = __ldcs(ph.rhs + c);
-#pragma unroll
-            for (int k = 0; k < K; ++k) if (s.vN[k]) acc += cN[k] * xO[k];
-#pragma unroll
-            for (int k = 0; k < K; ++k) if (s.vO[k]) acc -= cO[k] * xN[k];
-            const double xn = acc / dg;
-            ph.xn[c] = xn;
-            dl[p] = fabs(xn - xC);
-        }
-    }
-    // max |dpsi| per phase: warp shuffle, then one CTA-level value, then at most one atomic per CTA and phase --
-    // and only if it can still raise the running maximum (one atomic per warp on three addresses serialised in
-    // L2 and cost more than the sweep itself)
+// partial record of a boundary-adjacent cell, per phase: acc over the internal faces, x_C, diag (kfix_pred_jacobi adds
+// the processor-patch faces -- the only patch faces with an off-diagonal coefficient -- and finishes the cell)
+enum { PART_PRED = 3 };
+
+// max |dpsi| per phase: warp shuffle, then one CTA-level value, then at most one atomic per CTA and phase -- and only if
+// it can still raise the running maximum (one atomic per warp on three addresses serialised in L2 and cost more than
+// the sweep itself)
+template <int NPH>
+__device__ __forceinline__ void pred_reduce_max(const PredBatch &b, const double *dl) {
     __shared__ double red[NPH][TCIF_TPB / 32];
 #pragma unroll
     for (int p = 0; p < NPH; ++p) {
@@ -1061,6 +1028,93 @@ kvp_pred_jacobi(const __grid_constant__ DMesh m, const __grid_constant__ PredBat
         for (int w = 0; w < TCIF_TPB / 32; ++w) d = dmax(d, red[threadIdx.x][w]);
         if (d > 0.0 && d > *(volatile double *)(b.dmax + threadIdx.x)) atomic_max_nonneg(b.dmax + threadIdx.x, d);
     }
+}
+
+template <int K, int NPH>
+__global__ void __launch_bounds__(TCIF_TPB, 4)
+kvp_pred_jacobi(const __grid_constant__ DMesh m, const __grid_constant__ PredBatch b) {
+    const CellIdx ci = cell_of<TCIF_TPB>(m, blockIdx.x);
+    const int c = ci.c;
+    double dl[NPH];
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) dl[p] = 0.0;
+    if (c < m.nC) {
+        Slots<K> s;
+        s.load(m, c);
+        double cN[K], cO[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            cN[k] = dmax(b.phi[s.fdN[k]], 0.0);
+            cO[k] = dmin(__ldcs(b.phi + k * m.stride + c), 0.0);
+        }
+        const int cp = ci.cp;
+        if (cp >= 0) { pf_slots<K>(m, cp); pf_face<K>(b.phi, m.stride, cp); }
+        const int bi = bnd_rank(m, c);
+#pragma unroll
+        for (int p = 0; p < NPH; ++p) {
+            const PredPh &ph = b.ph[p];
+            if (!ph.active) continue;
+            if (cp >= 0) { pf_l2(ph.rhs + cp); pf_l2(ph.diag + cp); pf_l2(ph.x + cp); }
+            double xO[K], xN[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) { xO[k] = ph.x[s.oN[k]]; xN[k] = ph.x[s.nO[k]]; }
+            const double xC = ph.x[c], dg = __ldcs(ph.diag + c);
+            double acc = __ldcs(ph.rhs + c);
+#pragma unroll
+            for (int k = 0; k < K; ++k) if (s.vN[k]) acc += cN[k] * xO[k];
+#pragma unroll
+            for (int k = 0; k < K; ++k) if (s.vO[k]) acc -= cO[k] * xN[k];
+            if (bi >= 0) {                   // the processor-patch faces continue from here (kfix_pred_jacobi)
+                const int o = p * PART_PRED;
+                part_at(m, o, bi) = acc; part_at(m, o + 1, bi) = xC; part_at(m, o + 2, bi) = dg;
+            } else {
+                const double xn = acc / dg;
+                ph.xn[c] = xn;
+                dl[p] = fabs(xn - xC);
+            }
+        }
+    }
+    pred_reduce_max<NPH>(b, dl);
+}
+
+template <int NPH>
+__global__ void __launch_bounds__(TCIF_TPB)
+kfix_pred_jacobi(const __grid_constant__ DMesh m, const __grid_constant__ PredBatch b) {
+    const int bi = blockIdx.x * blockDim.x + threadIdx.x;
+    double dl[NPH];
+#pragma unroll
+    for (int p = 0; p < NPH; ++p) dl[p] = 0.0;
+    if (bi < m.nBndCells) {
+        const int c = m.bndCells[bi];
+        const BndRec r = bnd_load(m, bi);
+        double cb[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) cb[k] = (r.n >= 0) ? dmin(b.phib[r.bf[k]], 0.0) : 0.0;
+#pragma unroll
+        for (int p = 0; p < NPH; ++p) {
+            const PredPh &ph = b.ph[p];
+            if (!ph.active) continue;
+            const int o = p * PART_PRED;
+            double acc = part_at(m, o, bi);
+            const double xC = part_at(m, o + 1, bi), dg = part_at(m, o + 2, bi);
+            if (r.n >= 0) {
+                double xb[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) xb[k] = ph.psib[r.bf[k]];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) if (k < r.n && (r.tp[k] & 15) == PATCH_PROCESSOR) acc -= cb[k] * xb[k];
+            } else {
+                for (int j = m.bndCellStart[bi], e = m.bndCellStart[bi + 1]; j < e; ++j) {
+                    const int bf = m.bndFaces[j];
+                    if (m.bfType[bf] == PATCH_PROCESSOR) acc -= dmin(b.phib[bf], 0.0) * ph.psib[bf];
+                }
+            }
+            const double xn = acc / dg;
+            ph.xn[c] = xn;
+            dl[p] = fabs(xn - xC);
+        }
+    }
+    pred_reduce_max<NPH>(b, dl);
 }
 
 }  // namespace tcif
