@@ -105,7 +105,14 @@ template <int TPB_> __device__ __forceinline__ CellIdx cell_of(const DMesh &m, i
 // Rank of cell c among the boundary-adjacent cells (index into bndCells / bndRec / part), -1 for a cell without patch
 // faces: from the bit mask (prefix count of the mask word + popcount below the bit), so interior cells read one mask
 // word per warp and nothing else.  Evaluated where it is needed (the end of a thread) rather than kept in a register
-// across the sweep: the mask word is in L1 by then and the volume kernels are register-starved.
+// across the sweep (the volume kernels are register-starved).  That load sits at the end of every thread with nothing
+// left to overlap it -- 11 % of the stall samples of the grad sweep when it went to DRAM -- so the word is prefetched
+// twice: into L2 a wave ahead with the slot indices (pf_slots) and into L1 when the thread starts (pick_cell).  The
+// grad sweep, which is not capped at 64 registers, simply loads the word first and keeps it (bnd_rank_of).
+__device__ __forceinline__ int bnd_rank_of(const DMesh &m, int c, unsigned bw) {
+    const unsigned bit = 1u << (c & 31);
+    return (bw & bit) ? m.bndWordRank[c >> 5] + __popc(bw & (bit - 1u)) : -1;
+}
 __device__ __forceinline__ int bnd_rank(const DMesh &m, int c) {
     const int w = c >> 5;
     const unsigned bit = 1u << (c & 31), bw = m.bndMask[w];
@@ -113,11 +120,13 @@ __device__ __forceinline__ int bnd_rank(const DMesh &m, int c) {
 }
 // The cell of this thread in the volume launch (every cell: boundary-adjacent ones stop after their internal faces).
 struct CellCtx { int c, cp; };
-template <int TPB_>
+template <int TPB_, bool MASK_L1 = true>
 __device__ __forceinline__ bool pick_cell(const DMesh &m, CellCtx &x) {
     const CellIdx ci = cell_of<TPB_>(m, blockIdx.x);
     x.c = ci.c; x.cp = ci.cp;
-    return x.c < m.nC;
+    if (x.c >= m.nC) return false;
+    if (MASK_L1) asm volatile("prefetch.global.L1 [%0];" ::"l"(m.bndMask + (x.c >> 5)));
+    return true;
 }
 // slot j of the partial record of boundary-adjacent cell bi (SoA: the fix launch reads it coalesced)
 __device__ __forceinline__ double &part_at(const DMesh &m, int j, int bi) { return m.part[(size_t)j * m.nBndCells + bi]; }
@@ -129,6 +138,7 @@ __device__ __forceinline__ double &part_at(const DMesh &m, int j, int bi) { retu
 template <int K> __device__ __forceinline__ void pf_slots(const DMesh &m, int cp) {
 #pragma unroll
     for (int k = 0; k < K; ++k) { pf_l2(m.neiFace + k * m.stride + cp); pf_l2(m.nbrOwn + k * m.stride + cp); }
+    pf_l2(m.bndMask + (cp >> 5));            // the word bnd_rank() tests at the end of the thread
 }
 template <int K> __device__ __forceinline__ void pf_face(const double *a, int stride, int cp) {
 #pragma unroll
@@ -171,8 +181,9 @@ template <int P, int K>
 __global__ void __launch_bounds__(TCIF_TPB_FORCE, TCIF_MINB_GRAD)
 kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArgs a) {
     CellCtx x;
-    if (!pick_cell<TCIF_TPB_FORCE>(m, x)) return;
+    if (!pick_cell<TCIF_TPB_FORCE, false>(m, x)) return;
     const int c = x.c;
+    const unsigned bw = m.bndMask[c >> 5];
     Slots<K> s;
     s.load(m, c);
     {
@@ -223,7 +234,7 @@ kv_grad_tensor(const __grid_constant__ DMesh m, const __grid_constant__ ForceArg
             }
         }
     }
-    const int bi = bnd_rank(m, c);
+    const int bi = bnd_rank_of(m, c, bw);
     if (bi >= 0) {                           // the patch faces continue from here (kfix_grad_tensor)
 #pragma unroll
         for (int p = 0; p < P; ++p) {
@@ -767,7 +778,7 @@ template <int NPH> __device__ __forceinline__ void limit_sum_face(double *v) {
 // LSUM (MODE 0 only, batch = all phases): MULES::limitSum of the owner-side faces applied in registers
 // before the store, which saves the separate read-modify-write sweep over the P flux arrays.
 template <int K, int MODE, bool FIRST, int NPH, bool LSUM>
-__global__ void __launch_bounds__(TCIF_TPB, TCIF_MINB_FINAL)
+__global__ void __launch_bounds__(TCIF_TPB, MODE == 2 ? TCIF_MINB_FINAL : 4)      // MODE 0/1 fit 64 registers, MODE 2 spills there
 kvp_mules_final(const __grid_constant__ DMesh m, const __grid_constant__ MulesBatch b,
                 const __grid_constant__ MulesParams prm, int nIter) {
     static_assert(!LSUM || MODE == 0, "limitSum is fused into the returnCorr=true apply only");
