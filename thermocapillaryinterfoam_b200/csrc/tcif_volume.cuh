@@ -94,9 +94,14 @@ template <int TPB_> __device__ __forceinline__ CellIdx cell_of(const DMesh &m, i
     CellIdx r;
     r.c = (m.tileOrder ? m.tileOrder[tile] : tile) * 256 + sub;
     r.cp = -1;
+    // Prefetch duty: one warp in four, each lane one 32-byte sector (4 doubles / 8 indices), so that ONE instruction
+    // covers 128 cells of a stream -- the same sectors as 32 lanes x 4 warps asking for their own 8 bytes each, with a
+    // quarter of the prefetch and address instructions (the sweeps' issue slots are 50-70 % busy; a sweep issues ~40
+    // prefetches per cell).  The other warps skip the prefetch blocks (cp = -1, warp-uniform branch).
     const int tp = tile + m.pfTiles;
-    if (m.pfTiles > 0 && tp < m.nTiles) {
-        const int cp = (m.tileOrder ? m.tileOrder[tp] : tp) * 256 + sub;
+    if (m.pfTiles > 0 && tp < m.nTiles && (threadIdx.x & 96) == 0) {
+        const int q = sub >> 7;                  // which 128-cell half of the tile this warp covers
+        const int cp = (m.tileOrder ? m.tileOrder[tp] : tp) * 256 + q * 128 + (threadIdx.x & 31) * 4;
         if (cp < m.nC) r.cp = cp;
     }
     return r;
