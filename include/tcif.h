@@ -353,6 +353,20 @@ TCIF_API int tcif_laser_set_local_find_cell(tcif_ctx *ctx, int on);
 
 /* Logging scalars of multiphaseSystem.C:408-425: sum(V*alpha), min, max (global over ranks). */
 TCIF_API int tcif_alpha_stats(tcif_ctx *ctx, int phase, double out3[3]);
+/* The same three scalars for the cells of THIS context (rank-local: no collective; on a decomposed mesh combine the
+ * ranks' triples yourself), computed without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Calls no cudaMalloc / cudaFree / allocating library routine: the scratch of the
+ * reduction is a file-scope `static __device__` array of the library (24.6 KB held by every GPU that loads the library
+ * until exit), the result travels through the context's pinned buffer.  Inputs: the context's resident alpha[phase]
+ * and cell volumes; output: out3 (host).  Bit-identical to tcif_alpha_stats on an undecomposed mesh (same reduction
+ * tree).  Fails with a clear error when the context holds more than TCIF_ALPHA_STATS_STATIC_MAX_CELLS cells.
+ * The first call on a device resolves the array's device address (cudaGetSymbolAddress): make it outside a capture.
+ * All calls on one GPU share the array, which keeps the last call's contents (nothing needs to start at zero: every
+ * slot that is read has been overwritten by the same call); calls that OVERLAP on one GPU -- other streams, contexts
+ * or host threads -- race on it and must be serialised by the caller. */
+#define TCIF_ALPHA_STATS_STATIC_MAX_CELLS (1 << 27)   /* 134 M cells: more than one 180 GB GPU holds of this path's fields */
+TCIF_API int tcif_alpha_stats_static(tcif_ctx *ctx, int phase, double out3[3]);
 
 /* ---- measurement -------------------------------------------------------------------- */
 /* Per-kernel CUDA-event timers on the launching stream.  ids are stable (tcif_timer_name). */

@@ -602,6 +602,12 @@ class Context:
         self._ck(lib().tcif_alpha_stats(self.h, int(phase), out))
         return float(out[0]), float(out[1]), float(out[2])
 
+    def alpha_stats_static(self, phase):
+        """tcif_alpha_stats_static: rank-local (sum V alpha, min, max) with the scratch in a static device array."""
+        out = (C.c_double * 3)()
+        self._ck(lib().tcif_alpha_stats_static(self.h, int(phase), out))
+        return float(out[0]), float(out[1]), float(out[2])
+
     # -- measurement
     def timers_enable(self, on=True):
         self._ck(lib().tcif_timers_enable(self.h, int(bool(on))))

@@ -3196,6 +3196,56 @@ int tcif_alpha_stats(tcif_ctx *c, int phase, double out3[3]) {
     API_END(c)
 }
 
+// ---- tcif_alpha_stats without any allocation (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The scratch of the two-level reduction (one (sum, min, max) triple per CTA of k_stats_partial, then the result
+// triple) lives in this file-scope device array instead of the context's cudaMalloc'ed buffers: 24.6 KB that every GPU
+// which loads the library holds until exit.  In host code `g_statsStaticScratch` is a host-side stand-in for the
+// symbol, NOT a device address: the address a kernel can use comes from cudaGetSymbolAddress, resolved once per
+// device with that device current (stats_static_scratch()).
+//   * every call on a device shares the array and finds the previous call's contents in it: nothing has to start at
+//     zero (the first kernel overwrites all nPart triples the second one reads, the second overwrites the result),
+//     so nothing is cleared;
+//   * for the same reason two calls that overlap on one GPU (different streams / contexts / host threads) RACE on it.
+constexpr int kStatsStaticMaxPart = 1024;                       // CTAs of k_stats_partial = triples of scratch
+constexpr int64_t kStatsStaticMaxCells = TCIF_ALPHA_STATS_STATIC_MAX_CELLS;
+static __device__ __align__(256) double g_statsStaticScratch[3 * kStatsStaticMaxPart + 32];
+
+static double *stats_static_scratch(int device) {               // caller has made `device` current
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static double *addr[kMaxDev] = {};
+    if (device < 0 || device >= kMaxDev) failf("tcif_alpha_stats_static: device ordinal %d out of range", device);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[device]) {
+        double *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, g_statsStaticScratch);
+        if (e != cudaSuccess || !p) failf("tcif_alpha_stats_static: cudaGetSymbolAddress failed on device %d: %s", device, cudaGetErrorString(e));
+        addr[device] = p;
+    }
+    return addr[device];
+}
+
+int tcif_alpha_stats_static(tcif_ctx *c, int phase, double out3[3]) {
+    API_BEGIN(c)
+    check_phase(c, phase);
+    if (!out3) failf("tcif_alpha_stats_static: null output");
+    if ((int64_t)c->nC > kStatsStaticMaxCells)
+        failf("tcif_alpha_stats_static: %d cells exceed the maximum of %lld this entry point is built for "
+              "(TCIF_ALPHA_STATS_STATIC_MAX_CELLS); use tcif_alpha_stats", c->nC, (long long)kStatsStaticMaxCells);
+    const int nPart = std::min(kStatsStaticMaxPart, cdiv(c->nC, TCIF_TPB));     // same tree as tcif_alpha_stats: same bits
+    double *scr = stats_static_scratch(c->device);
+    double *res = scr + 3 * kStatsStaticMaxPart;
+    k_stats_partial<<<nPart, TCIF_TPB, 0, c->stream>>>(c->nC, c->dm.V, c->alpha[phase], scr);
+    k_stats_final<<<1, 32, 0, c->stream>>>(nPart, scr, res);
+    c->launches += 2;
+    CUDA_OK(cudaMemcpyAsync(c->h_small, res, sizeof(double) * 3, cudaMemcpyDeviceToHost, c->stream));   // h_small: pinned at tcif_create
+    CUDA_OK(cudaStreamSynchronize(c->stream));
+    CUDA_OK(cudaGetLastError());
+    out3[0] = c->h_small[0]; out3[1] = c->h_small[1]; out3[2] = c->h_small[2];
+    API_END(c)
+}
+
 // ---- measurement ------------------------------------------------------------------------------
 int tcif_timers_enable(tcif_ctx *c, int on) {
     API_BEGIN(c)
