@@ -17,6 +17,7 @@
 #include <unistd.h>
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cmath>
 #include <cstdarg>
@@ -247,11 +248,13 @@ struct tcif_ctx {
     double *shFace[5]{};                       // same for alphaPhi[p] (host face order)
     const void *shFaceHost[5]{};
     const void *shFHost = nullptr;             // the host F array shF mirrors
-    int *dIdx = nullptr, *dCount = nullptr;
-    double *dVal = nullptr;
-    int dCap = 0;
-    int *hIdx = nullptr, *hCount = nullptr;    // pinned
-    double *hVal = nullptr;
+    // (two sets of index/value buffers: the host scatters read-back i while the GPU compacts and copies read-back i+1)
+    int *dIdx2[2] = {nullptr, nullptr}, *dCount = nullptr;
+    double *dVal2[2] = {nullptr, nullptr};
+    int dCap = 0, dPar = 0;
+    int *hIdx2[2] = {nullptr, nullptr}, *hCount = nullptr;    // pinned
+    double *hVal2[2] = {nullptr, nullptr};
+    std::thread scatterTh;                     // the one host scatter in flight (joined before the API call returns)
     int64_t d2hBytes = 0, h2dBytes = 0;        // bytes actually moved by the last *_host call
     int64_t forceEvaluations = 0, forceCacheHits = 0;
     double deltaN = 0.0;
@@ -2111,14 +2114,17 @@ void host_pipeline_init(tcif_ctx *c) {
     c->stagingOut = c->dalloc<double>(c->stagingDoubles);
 }
 void delta_init(tcif_ctx *c) {
-    if (c->dIdx) return;
+    if (c->dIdx2[0]) return;
     // (index, value) pairs cost 1.5x (scalar) / 1.17x (vector) the dense bytes per entry: beyond 1/4 of the entries the
     // dense copy is preferred
     c->dCap = std::max(std::max(c->nC, c->nIF) / 4, 1024);
     const size_t nVal = std::max<size_t>((size_t)c->dCap, 3 * (size_t)std::max(c->nC / 4, 1024));
-    c->dIdx = c->dalloc<int>(c->dCap); c->dVal = c->dalloc<double>(nVal); c->dCount = c->dalloc<int>(8);
-    CUDA_OK(cudaHostAlloc((void **)&c->hIdx, sizeof(int) * (size_t)c->dCap, cudaHostAllocDefault));
-    CUDA_OK(cudaHostAlloc((void **)&c->hVal, sizeof(double) * nVal, cudaHostAllocDefault));
+    c->dCount = c->dalloc<int>(8);
+    for (int b = 0; b < 2; ++b) {
+        c->dIdx2[b] = c->dalloc<int>(c->dCap); c->dVal2[b] = c->dalloc<double>(nVal);
+        CUDA_OK(cudaHostAlloc((void **)&c->hIdx2[b], sizeof(int) * (size_t)c->dCap, cudaHostAllocDefault));
+        CUDA_OK(cudaHostAlloc((void **)&c->hVal2[b], sizeof(double) * nVal, cudaHostAllocDefault));
+    }
     CUDA_OK(cudaHostAlloc((void **)&c->hCount, sizeof(int) * 8, cudaHostAllocDefault));
 }
 // dst[idx[k]] = val[k] (ncomp values per entry) on a few host threads: the indices of one list are distinct
@@ -2139,12 +2145,21 @@ void host_scatter(double *dst, const int *ix, const double *v, int n, int ncomp,
 // `shadow` to the host array `dst` (AoS when ncomp == 3) on stream st, and update the shadow.  Returns false when too
 // many differ (nothing was written: copy densely).  Synchronises st twice; every kernel the result depends on must
 // have been enqueued before.
+inline void scatter_join(tcif_ctx *c) { if (c->scatterTh.joinable()) c->scatterTh.join(); }
+// joins the scatter in flight when an API call that reads back deltas returns, normally or by exception
+struct ScatterJoin { tcif_ctx *c; explicit ScatterJoin(tcif_ctx *c_) : c(c_) {} ~ScatterJoin() { scatter_join(c); } };
+// TCIF_HOST_TRACE=1: one line per delta read-back on stderr (entries, ms waiting for the GPU, ms scattering on the host)
+static const bool g_hostTrace = [] { const char *e = getenv("TCIF_HOST_TRACE"); return e && atoi(e) != 0; }();
+static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 bool down_delta(tcif_ctx *c, cudaStream_t st, double *dst, const double *cur, double *shadow, int n, int ncomp, size_t stride) {
     delta_init(c);
+    const double t0 = g_hostTrace ? now_ms() : 0.0;
+    int *dIdx = c->dIdx2[c->dPar], *hIdx = c->hIdx2[c->dPar];
+    double *dVal = c->dVal2[c->dPar], *hVal = c->hVal2[c->dPar];
     const int cap = ncomp == 1 ? c->dCap : std::min(c->dCap, std::max(c->nC / 4, 1024));
     CUDA_OK(cudaMemsetAsync(c->dCount, 0, sizeof(int), st));
-    if (ncomp == 1) k_delta_compact<<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, st>>>(n, cur, shadow, cap, c->dIdx, c->dVal, c->dCount);
-    else k_delta_compact3<<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, st>>>(n, stride, cur, shadow, cap, c->dIdx, c->dVal, c->dCount);
+    if (ncomp == 1) k_delta_compact<<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, st>>>(n, cur, shadow, cap, dIdx, dVal, c->dCount);
+    else k_delta_compact3<<<cdiv(n, TCIF_TPB), TCIF_TPB, 0, st>>>(n, stride, cur, shadow, cap, dIdx, dVal, c->dCount);
     c->launches++;
     CUDA_OK(cudaMemcpyAsync(c->hCount, c->dCount, sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_OK(cudaStreamSynchronize(st));
@@ -2152,13 +2167,21 @@ bool down_delta(tcif_ctx *c, cudaStream_t st, double *dst, const double *cur, do
     c->d2hBytes += sizeof(int);
     if (m > cap) return false;
     if (m == 0) return true;
-    CUDA_OK(cudaMemcpyAsync(c->hIdx, c->dIdx, sizeof(int) * (size_t)m, cudaMemcpyDeviceToHost, st));
-    CUDA_OK(cudaMemcpyAsync(c->hVal, c->dVal, sizeof(double) * (size_t)m * ncomp, cudaMemcpyDeviceToHost, st));
-    k_delta_apply<<<cdiv(m, TCIF_TPB), TCIF_TPB, 0, st>>>(m, ncomp, stride, c->dIdx, c->dVal, shadow);
+    CUDA_OK(cudaMemcpyAsync(hIdx, dIdx, sizeof(int) * (size_t)m, cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaMemcpyAsync(hVal, dVal, sizeof(double) * (size_t)m * ncomp, cudaMemcpyDeviceToHost, st));
+    k_delta_apply<<<cdiv(m, TCIF_TPB), TCIF_TPB, 0, st>>>(m, ncomp, stride, dIdx, dVal, shadow);
     c->launches++;
     CUDA_OK(cudaStreamSynchronize(st));
     c->d2hBytes += (int64_t)m * (sizeof(int) + sizeof(double) * ncomp);
-    host_scatter(dst, c->hIdx, c->hVal, m, ncomp, c->nRanks);
+    const double t1 = g_hostTrace ? now_ms() : 0.0;
+    // the scatter runs beside the GPU work of the NEXT read-back (other buffer set); at most one is in flight
+    scatter_join(c);
+    const int nRanks = c->nRanks;
+    c->scatterTh = std::thread([=] {
+        host_scatter(dst, hIdx, hVal, m, ncomp, nRanks);
+        if (g_hostTrace) fprintf(stderr, "[tcif trace] delta n=%d ncomp=%d entries=%d gpu+copy %.2f ms, host scatter %.2f ms\n", n, ncomp, m, t1 - t0, now_ms() - t1);
+    });
+    c->dPar ^= 1;
     return true;
 }
 // a face field (device slots) -> caller's array in OpenFOAM face order: delta against what the SAME host array received
@@ -2338,8 +2361,8 @@ void tcif_destroy(tcif_ctx *c) {
     if (c->lzSpVals) cudaFree(c->lzSpVals);
     if (c->lzInbox) cudaFree(c->lzInbox);
     if (c->h_small) cudaFreeHost(c->h_small);
-    if (c->hIdx) cudaFreeHost(c->hIdx);
-    if (c->hVal) cudaFreeHost(c->hVal);
+    scatter_join(c);
+    for (int b = 0; b < 2; ++b) { if (c->hIdx2[b]) cudaFreeHost(c->hIdx2[b]); if (c->hVal2[b]) cudaFreeHost(c->hVal2[b]); }
     if (c->hCount) cudaFreeHost(c->hCount);
     if (c->sIn) cudaStreamDestroy(c->sIn);
     if (c->sOut) cudaStreamDestroy(c->sOut);
@@ -2951,11 +2974,13 @@ int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const
                     const double *phii, const double *phib, const double *const *pai, const double *const *pab,
                     double *const *apo, double *const *apob, double *Fi, double *Fb) {
     API_BEGIN(c)
+    ScatterJoin scatterGuard(c);
     if (!ai || !pai || !apo || (c->nBF && (!ab || !pab || !apob))) failf("tcif_stage_host: null field lists");
     if (!(deltaT > 0)) failf("tcif_stage_host: deltaT must be positive");
     host_pipeline_init(c);
     join(c);
     CUDA_OK(cudaStreamSynchronize(c->stream));
+    const double tr0 = g_hostTrace ? now_ms() : 0.0;
     c->h2dBytes = c->d2hBytes = 0;
     const size_t cb = sizeof(double) * c->nC, bb = sizeof(double) * c->nBF, fb = sizeof(double) * c->nIF;
     cudaStream_t in = c->sIn, out = c->sOut;
@@ -2991,9 +3016,12 @@ int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const
     do_mules_stage(c, deltaT);
     CUDA_OK(cudaEventRecord(c->evC[1], c->stream));
     // downloads
+    const double tr1 = g_hostTrace ? now_ms() : 0.0;
     CUDA_OK(cudaStreamWaitEvent(out, c->evC[0], 0));
     down_force(c, out, Fi, Fb);
+    const double tr2 = g_hostTrace ? now_ms() : 0.0;
     CUDA_OK(cudaStreamWaitEvent(out, c->evC[1], 0));
+    if (g_hostTrace) { CUDA_OK(cudaStreamSynchronize(c->stream)); fprintf(stderr, "[tcif trace] stage_host: enqueue %.2f ms, F back at %.2f ms, compute done at %.2f ms\n", tr1 - tr0, tr2 - tr0, now_ms() - tr0); }
     for (int p = 0; p < c->P; ++p) {
         down_faces_host(c, out, p, apo[p], c->phiPsi[p]);
         if (c->nBF) { CUDA_OK(cudaMemcpyAsync(apob[p], c->phiPsib[p], bb, cudaMemcpyDefault, out)); c->d2hBytes += bb; }
@@ -3004,6 +3032,8 @@ int tcif_stage_host(tcif_ctx *c, double deltaT, double *const *ai, double *const
     CUDA_OK(cudaStreamSynchronize(c->stream));
     CUDA_OK(cudaGetLastError());
     finish_host_stamps(c);
+    scatter_join(c);
+    if (g_hostTrace) fprintf(stderr, "[tcif trace] stage_host: done at %.2f ms\n", now_ms() - tr0);
     API_END(c)
 }
 
@@ -3013,6 +3043,7 @@ int tcif_time_step_host(tcif_ctx *c, const tcif_alpha_controls *ctl, double delt
                         const double *Ti, const double *Tb, const double *phii, const double *phib,
                         double *const *apo, double *const *apob, double *rpi, double *rpb, double *Fi, double *Fb) {
     API_BEGIN(c)
+    ScatterJoin scatterGuard(c);
     if (!ai || (c->nBF && !ab) || !phii) failf("tcif_time_step_host: null field lists");
     host_pipeline_init(c);
     join(c);
